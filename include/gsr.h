@@ -1,0 +1,169 @@
+/*
+ * gsr.h - C ABI of the B200-native Gaussian-splat rasterizer hot path.
+ *
+ * This is the drop-in boundary.  Every entry point replaces one static method /
+ * free function of the reference's C++ core, which the reference's torch binding
+ * (submodules/diff-gaussian-rasterization/rasterize_points.cu, simple-knn/spatial.cu)
+ * calls with raw device pointers.  Signatures are plain C: pointers, sizes, POD
+ * structs; no torch / C++ types cross this boundary.  All pointers are DEVICE
+ * pointers unless a comment says "host".  Every call is asynchronous on `stream`
+ * except where stated; nothing is ever launched on the legacy default stream.
+ *
+ * Return value: 0 on success, a negative GSR_E* code otherwise (never throws).
+ * gsr_strerror() maps a code to text; gsr_last_cuda_error() gives the CUDA
+ * error string behind GSR_ECUDA.
+ *
+ * reference interface replaced (file:line, relative to /root/reference/submodules):
+ *   gsr_forward        <- CudaRasterizer::Rasterizer::forward      diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:31-57,  rasterizer_impl.cu:198-336
+ *   gsr_backward       <- CudaRasterizer::Rasterizer::backward     rasterizer.h:59-84,  rasterizer_impl.cu:340-434
+ *   gsr_mark_visible   <- CudaRasterizer::Rasterizer::markVisible  rasterizer.h:24-29,  rasterizer_impl.cu:141-153
+ *   gsr_dist2          <- SimpleKNN::knn                           simple-knn/simple_knn.h:17-19, simple_knn.cu:185-221
+ *   gsr_export_binning <- (test hook) layout of BinningState/ImageState, rasterizer_impl.cu:172-194
+ */
+#ifndef GSR_B200_H_INCLUDED
+#define GSR_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_ABI_VERSION 1
+
+/* error codes */
+#define GSR_OK          0
+#define GSR_EINVAL     -1   /* bad argument (null required pointer, negative size, ...) */
+#define GSR_ECUDA      -2   /* a CUDA runtime call or kernel failed; see gsr_last_cuda_error() */
+#define GSR_ENOMEM     -3   /* an allocator callback returned NULL */
+#define GSR_ECHANNELS  -4   /* neither shs nor colors_precomp given (reference: "For non-RGB, provide precomputed Gaussian colors!") */
+#define GSR_ECOV       -5   /* neither (scales, rotations) nor cov3D_precomp given */
+#define GSR_EBLOB      -6   /* a state blob handed to backward does not carry our magic / sizes */
+#define GSR_ETOOBIG    -7   /* image has more than 65535 tiles per axis or R >= 2^31 */
+
+/* CUDA stream handle (== cudaStream_t) without dragging in cuda headers. */
+typedef struct CUstream_st* gsr_stream_t;
+
+/*
+ * Scratch allocator callback: must return a device pointer to at least `bytes`
+ * bytes, 256-byte aligned, that stays valid until the caller (the binding) frees
+ * it - the three state blobs of gsr_forward are saved for gsr_backward.
+ * Mirrors std::function<char*(size_t)> of rasterizer.h:32-34 (implemented in the
+ * reference binding by torch::Tensor::resize_, rasterize_points.cu:27-33).
+ * Each callback is invoked exactly once per gsr_forward call.
+ */
+typedef void* (*gsr_alloc_fn)(void* ctx, size_t bytes);
+typedef struct GsrAlloc { gsr_alloc_fn fn; void* ctx; } GsrAlloc;
+
+typedef struct GsrFwdArgs {
+    int P;                       /* number of Gaussians */
+    int D;                       /* active SH degree 0..3 */
+    int M;                       /* SH coefficients per Gaussian in memory ((Dmax+1)^2), 0 if no shs */
+    int W, H;                    /* image size in pixels */
+    const float* background;     /* [3] */
+    const float* means3D;        /* [P,3] */
+    const float* shs;            /* [P,M,3] or NULL */
+    const float* colors_precomp; /* [P,3]   or NULL (exactly one of shs / colors_precomp) */
+    const float* opacities;      /* [P] */
+    const float* scales;         /* [P,3] or NULL */
+    float        scale_modifier;
+    const float* rotations;      /* [P,4] (r,x,y,z), used un-normalised, or NULL */
+    const float* cov3D_precomp;  /* [P,6] (xx,xy,xz,yy,yz,zz) or NULL */
+    const float* viewmatrix;     /* [16] world->view, row-vector convention: m[4*c+r] */
+    const float* projmatrix;     /* [16] full projection, same convention */
+    const float* cam_pos;        /* [3] */
+    float        tan_fovx, tan_fovy;
+    int          prefiltered;    /* reference traps when a prefiltered point is culled; we report GSR_EINVAL in debug */
+    int          debug;          /* 1: synchronise + check after every stage (CHECK_CUDA semantics, auxiliary.h:166-173) */
+    float*       out_color;      /* [3,H,W] written for every pixel */
+    int*         radii;          /* [P] written for every Gaussian (0 = culled) */
+} GsrFwdArgs;
+
+/*
+ * Forward.  Blocks the host once (like rasterizer_impl.cu:280-281) to learn
+ * num_rendered, because the binning blob is sized from it.
+ * *num_rendered (host) receives R = sum of tiles touched.
+ */
+int gsr_forward(const GsrFwdArgs* args, GsrAlloc geom, GsrAlloc binning, GsrAlloc img,
+                gsr_stream_t stream, int* num_rendered);
+
+typedef struct GsrBwdArgs {
+    int P, D, M, R, W, H;
+    const float* background;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* scales;
+    float        scale_modifier;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    float        tan_fovx, tan_fovy;
+    const int*   radii;          /* [P] as returned by forward */
+    const void*  geom_blob;      /* the three blobs obtained through the forward allocators */
+    const void*  binning_blob;
+    const void*  img_blob;
+    const float* dL_dpix;        /* [3,H,W] */
+    /* outputs. Every element of every non-NULL output is WRITTEN (no pre-zeroing needed),
+       except dL_dmean2D / dL_dconic / dL_dopacity / dL_dcolor which are accumulated with
+       atomics and must be zero on entry (the binding allocates them with zeros). */
+    float* dL_dmean2D;           /* [P,3]  (x,y in NDC units, z == 0) */
+    float* dL_dconic;            /* [P,4]  (.x,.y,unused,.w) */
+    float* dL_dopacity;          /* [P] */
+    float* dL_dcolor;            /* [P,3] */
+    float* dL_dmean3D;           /* [P,3] */
+    float* dL_dcov3D;            /* [P,6] */
+    float* dL_dsh;               /* [P,M,3] or NULL */
+    float* dL_dscale;            /* [P,3]  or NULL */
+    float* dL_drot;              /* [P,4]  or NULL */
+    int    debug;
+} GsrBwdArgs;
+
+int gsr_backward(const GsrBwdArgs* args, gsr_stream_t stream);
+
+/* present[i] = (view-space z of means3D[i] > 0.2).  `present` is uint8 (bool). */
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, gsr_stream_t stream);
+
+/*
+ * distCUDA2: out[i] = mean of the 3 smallest squared distances from points[i] to
+ * the other points (by index; coincident points count as distance 0).
+ * Scratch comes from `scratch` (one call).  Synchronises the stream once
+ * internally (bounding box -> host), like simple_knn.cu:197,200.
+ */
+int gsr_dist2(int P, const float* points, float* out, GsrAlloc scratch, gsr_stream_t stream);
+
+/*
+ * Test hook for the bit-exact integer contract: reconstructs, from our private
+ * blobs, the arrays the reference keeps in BinningState / ImageState:
+ *   keys[R]   = (tile << 32) | float_bits(depth)   sorted
+ *   values[R] = Gaussian index                     sorted
+ *   ranges[2*tiles] = (start, end) per tile, (0,0) for empty tiles
+ *   n_contrib[W*H], final_T[W*H]
+ * Any output pointer may be NULL.
+ */
+int gsr_export_binning(const void* geom_blob, const void* binning_blob, const void* img_blob,
+                       int P, int R, int W, int H,
+                       uint64_t* keys, uint32_t* values, uint32_t* ranges,
+                       uint32_t* n_contrib, float* final_T, gsr_stream_t stream);
+
+/* bytes the three blobs need (geom, img are known up-front; binning needs R) */
+size_t gsr_geom_bytes(int P);
+size_t gsr_img_bytes(int W, int H);
+size_t gsr_binning_bytes(int P, int R, int W, int H);
+
+const char* gsr_strerror(int code);
+const char* gsr_last_cuda_error(void);
+int gsr_abi_version(void);
+
+/* kernel-launch counter (all launches made by this library since the last reset) */
+void gsr_reset_launch_count(void);
+unsigned long long gsr_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_B200_H_INCLUDED */
