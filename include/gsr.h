@@ -107,18 +107,20 @@ typedef struct GsrBwdArgs {
     const void*  binning_blob;
     const void*  img_blob;
     const float* dL_dpix;        /* [3,H,W] */
-    /* outputs. Every element of every non-NULL output is WRITTEN (no pre-zeroing needed),
-       except dL_dmean2D / dL_dconic / dL_dopacity / dL_dcolor which are accumulated with
-       atomics and must be zero on entry (the binding allocates them with zeros). */
-    float* dL_dmean2D;           /* [P,3]  (x,y in NDC units, z == 0) */
-    float* dL_dconic;            /* [P,4]  (.x,.y,unused,.w) */
-    float* dL_dopacity;          /* [P] */
-    float* dL_dcolor;            /* [P,3] */
-    float* dL_dmean3D;           /* [P,3] */
-    float* dL_dcov3D;            /* [P,6] */
-    float* dL_dsh;               /* [P,M,3] or NULL */
-    float* dL_dscale;            /* [P,3]  or NULL */
-    float* dL_drot;              /* [P,4]  or NULL */
+    /* scratch: gsr_bwd_accum_bytes(P) bytes, 16-byte aligned.  Zeroed and filled by gsr_backward itself
+       (packed per-Gaussian accumulator rows of the blending backward; replaces the reference's separate
+       dL_dconic [P,2,2] / dL_dcolors [P,3] atomics targets, rasterize_points.cu:151-159). */
+    void*  accum;
+    /* outputs.  EVERY element of every non-NULL output is written (zeros for culled Gaussians): the
+       caller allocates them uninitialised, no pre-zeroing (the reference needs nine torch::zeros). */
+    float* dL_dmean2D;           /* [P,3]  (x,y in NDC units, z == 0); required */
+    float* dL_dopacity;          /* [P];   required */
+    float* dL_dmean3D;           /* [P,3]; required */
+    float* dL_dcolor;            /* [P,3]  or NULL (wanted when colors_precomp is the input) */
+    float* dL_dcov3D;            /* [P,6]  or NULL (wanted when cov3D_precomp is the input) */
+    float* dL_dsh;               /* [P,M,3]; required iff shs != NULL */
+    float* dL_dscale;            /* [P,3];   required iff scales != NULL */
+    float* dL_drot;              /* [P,4];   required iff rotations != NULL */
     int    debug;
 } GsrBwdArgs;
 
@@ -154,6 +156,7 @@ int gsr_export_binning(const void* geom_blob, const void* binning_blob, const vo
 size_t gsr_geom_bytes(int P);
 size_t gsr_img_bytes(int W, int H);
 size_t gsr_binning_bytes(int P, int R, int W, int H);
+size_t gsr_bwd_accum_bytes(int P);
 
 const char* gsr_strerror(int code);
 const char* gsr_last_cuda_error(void);

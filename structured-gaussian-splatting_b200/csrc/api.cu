@@ -1,0 +1,269 @@
+// api.cu - the C-ABI entry points of include/gsr.h: argument validation, blob carving, stage orchestration.
+//
+// Replaces the host orchestration of the reference core:
+//   gsr_forward   <- CudaRasterizer::Rasterizer::forward   rasterizer_impl.cu:198-336
+//   gsr_backward  <- CudaRasterizer::Rasterizer::backward  rasterizer_impl.cu:340-434
+//   blob carving  <- GeometryState/ImageState/BinningState::fromChunk, rasterizer_impl.cu:155-194
+// Every launch is on the caller's stream (the reference uses the legacy default stream).
+#include "gsr_common.cuh"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+namespace gsr {
+
+unsigned long long g_launches = 0;
+char g_last_cuda_error[256] = "";
+
+int record_cuda_error(cudaError_t e, const char* where)
+{
+    snprintf(g_last_cuda_error, sizeof g_last_cuda_error, "%s: %s", where, cudaGetErrorString(e));
+    cudaGetLastError();   // clear the sticky flag of non-fatal errors
+    return GSR_ECUDA;
+}
+
+int env_int(const char* name, int dflt)
+{
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
+// ------------------------------------------------------------------ blob layouts
+static size_t geom_fixed_bytes(int P)
+{
+    const size_t Pp = (size_t)(P > 0 ? P : 1);
+    return sizeof(BlobHeader) + align_up(Pp * sizeof(SplatRec)) + align_up(Pp) + align_up(Pp * 4) + align_up((Pp + 1) * 4);
+}
+GeomView geom_view(void* blob, int P)
+{
+    const size_t Pp = (size_t)(P > 0 ? P : 1);
+    GeomView g;
+    char* p = (char*)blob;
+    g.hdr = (BlobHeader*)p; p += sizeof(BlobHeader);
+    g.rec = (SplatRec*)p; p += align_up(Pp * sizeof(SplatRec));
+    g.clamped = (uint8_t*)p; p += align_up(Pp);
+    g.order = (uint32_t*)p; p += align_up(Pp * 4);
+    g.offs = (uint32_t*)p; p += align_up((Pp + 1) * 4);
+    g.scratch = (uint32_t*)p;
+    g.scratch_bytes = geom_scratch_bytes(P);
+    return g;
+}
+BinView bin_view(void* blob, long long R)
+{
+    const size_t Rp = (size_t)(R > 0 ? R : 1);
+    BinView b;
+    char* p = (char*)blob;
+    b.hdr = (BlobHeader*)p; p += sizeof(BlobHeader);
+    b.vals = (uint32_t*)p; p += align_up(Rp * 4);
+    b.scratch = (uint32_t*)p;
+    b.scratch_bytes = bin_scratch_bytes(R);
+    return b;
+}
+ImgView img_view(void* blob, int W, int H)
+{
+    const size_t tiles = (size_t)((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
+    const size_t N = (size_t)W * H;
+    ImgView v;
+    char* p = (char*)blob;
+    v.hdr = (BlobHeader*)p; p += sizeof(BlobHeader);
+    v.ranges = (uint2*)p; p += align_up((tiles ? tiles : 1) * sizeof(uint2));
+    v.final_T = (float*)p; p += align_up((N ? N : 1) * 4);
+    v.n_contrib = (uint32_t*)p;
+    return v;
+}
+
+__global__ void init_headers_kernel(BlobHeader* g, BlobHeader* b, BlobHeader* im, int P, int R, int W, int H)
+{
+    BlobHeader* h[3] = {g, b, im};
+    const int k = threadIdx.x;
+    if (k < 3) {
+        h[k]->magic = GSR_MAGIC; h[k]->kind = k + 1;
+        h[k]->P = P; h[k]->R = R; h[k]->W = W; h[k]->H = H;
+    }
+}
+
+// test hook: rebuild the reference's 64-bit keys from (tile of the range, depth bits of the value)
+__global__ void export_keys_kernel(int tiles, const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals,
+                                   const SplatRec* __restrict__ rec, unsigned long long* __restrict__ keys)
+{
+    const int t = blockIdx.x;
+    if (t >= tiles) return;
+    const uint2 r = ranges[t];
+    for (uint32_t i = r.x + threadIdx.x; i < r.y; i += blockDim.x)
+        keys[i] = ((unsigned long long)(uint32_t)t << 32) | __float_as_uint(rec[vals[i]].q2.y);
+}
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" {
+
+size_t gsr_geom_bytes(int P) { return geom_fixed_bytes(P) + geom_scratch_bytes(P); }
+size_t gsr_img_bytes(int W, int H)
+{
+    const size_t tiles = (size_t)((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
+    const size_t N = (size_t)W * H;
+    return sizeof(BlobHeader) + align_up((tiles ? tiles : 1) * sizeof(uint2)) + 2 * align_up((N ? N : 1) * 4);
+}
+size_t gsr_binning_bytes(int P, int R, int W, int H)
+{
+    (void)P; (void)W; (void)H;
+    const size_t Rp = (size_t)(R > 0 ? R : 1);
+    size_t scratch = bin_scratch_bytes(R);
+    if (env_int("GSR_SORT", 0) == 1) { size_t c = cub_sort_scratch_bytes(R); if (c > scratch) scratch = c; }
+    return sizeof(BlobHeader) + align_up(Rp * 4) + scratch;
+}
+size_t gsr_bwd_accum_bytes(int P) { return (size_t)(P > 0 ? P : 1) * 12 * sizeof(float); }
+
+int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream_, int* num_rendered)
+{
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (!a || !num_rendered || !geom.fn || !binning.fn || !img.fn) return GSR_EINVAL;
+    *num_rendered = 0;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3) return GSR_EINVAL;
+    if (!a->out_color || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
+    const int gx = (a->W + GSR_TILE - 1) / GSR_TILE, gy = (a->H + GSR_TILE - 1) / GSR_TILE;
+    if (gx > 65535 || gy > 65535) return GSR_ETOOBIG;
+    if (a->P == 0) {
+        // reference binding returns the zero-filled image without calling the core (rasterize_points.cu:81)
+        GSR_CUDA(cudaMemsetAsync(a->out_color, 0, sizeof(float) * 3 * (size_t)a->W * a->H, s));
+        return GSR_OK;
+    }
+    if (!a->means3D || !a->opacities || !a->radii) return GSR_EINVAL;
+    if (!a->shs && !a->colors_precomp) return GSR_ECHANNELS;
+    if (a->shs && !a->colors_precomp && (!a->cam_pos || a->M < (a->D + 1) * (a->D + 1))) return GSR_EINVAL;
+    if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return GSR_ECOV;
+
+    void* gblob = geom.fn(geom.ctx, gsr_geom_bytes(a->P));
+    void* iblob = img.fn(img.ctx, gsr_img_bytes(a->W, a->H));
+    if (!gblob || !iblob) return GSR_ENOMEM;
+    GeomView g = geom_view(gblob, a->P);
+    ImgView im = img_view(iblob, a->W, a->H);
+    GSR_CUDA(cudaMemsetAsync(g.hdr, 0, sizeof(BlobHeader), s));
+
+    int rc;
+    if ((rc = launch_preprocess(*a, g, s))) return rc;
+    GSR_STAGE(a->debug, s, "preprocess");
+    if ((rc = launch_depth_order(a->P, g, s))) return rc;
+    GSR_STAGE(a->debug, s, "depth_order");
+
+    // the binning blob is sized from R: one blocking read-back, like rasterizer_impl.cu:280-281
+    uint32_t R_host = 0;
+    GSR_CUDA(cudaMemcpyAsync(&R_host, g.offs + a->P, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    GSR_CUDA(cudaStreamSynchronize(s));
+    if (R_host >= 0x80000000u) return GSR_ETOOBIG;
+    const int R = (int)R_host;
+    *num_rendered = R;
+
+    void* bblob = binning.fn(binning.ctx, gsr_binning_bytes(a->P, R, a->W, a->H));
+    if (!bblob) return GSR_ENOMEM;
+    BinView b = bin_view(bblob, R);
+    GSR_LAUNCH(init_headers_kernel, 1, 32, 0, s, g.hdr, b.hdr, im.hdr, a->P, R, a->W, a->H);
+
+    if (env_int("GSR_SORT", 0) == 1) rc = launch_tile_split_cub(a->P, R, a->W, a->H, g, b, im, s);
+    else rc = launch_tile_split(a->P, R, a->W, a->H, g, b, im, s);
+    if (rc) return rc;
+    GSR_STAGE(a->debug, s, "tile_split");
+
+    if ((rc = launch_blend_forward(a->W, a->H, a->background, g, b, im, a->out_color, s))) return rc;
+    GSR_STAGE(a->debug, s, "blend_forward");
+    if (a->debug && a->prefiltered) {
+        int err = 0;
+        GSR_CUDA(cudaMemcpy(&err, &g.hdr->pad[0], sizeof(int), cudaMemcpyDeviceToHost));
+        if (err) return GSR_EINVAL;
+    }
+    return GSR_OK;
+}
+
+int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream_)
+{
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (!a) return GSR_EINVAL;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->R < 0 || a->D < 0 || a->D > 3) return GSR_EINVAL;
+    if (a->P == 0) return GSR_OK;
+    if (!a->means3D || !a->radii || !a->dL_dpix || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
+    if (!a->geom_blob || !a->binning_blob || !a->img_blob || !a->accum) return GSR_EBLOB;
+    if (!a->dL_dmean2D || !a->dL_dopacity || !a->dL_dmean3D) return GSR_EINVAL;
+    if (a->shs && (!a->dL_dsh || !a->cam_pos)) return GSR_EINVAL;
+    if (!a->cov3D_precomp && (!a->scales || !a->rotations || !a->dL_dscale || !a->dL_drot)) return GSR_ECOV;
+
+    GeomView g = geom_view(const_cast<void*>(a->geom_blob), a->P);
+    BinView b = bin_view(const_cast<void*>(a->binning_blob), a->R);
+    ImgView im = img_view(const_cast<void*>(a->img_blob), a->W, a->H);
+    if (a->debug) {
+        BlobHeader h[3];
+        GSR_CUDA(cudaMemcpyAsync(&h[0], g.hdr, sizeof(BlobHeader), cudaMemcpyDeviceToHost, s));
+        GSR_CUDA(cudaMemcpyAsync(&h[1], b.hdr, sizeof(BlobHeader), cudaMemcpyDeviceToHost, s));
+        GSR_CUDA(cudaMemcpyAsync(&h[2], im.hdr, sizeof(BlobHeader), cudaMemcpyDeviceToHost, s));
+        GSR_CUDA(cudaStreamSynchronize(s));
+        for (int k = 0; k < 3; k++)
+            if (h[k].magic != GSR_MAGIC || h[k].kind != (uint32_t)(k + 1) || h[k].P != a->P || h[k].R != a->R || h[k].W != a->W ||
+                h[k].H != a->H)
+                return GSR_EBLOB;
+    }
+    float* accum = (float*)a->accum;
+    GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(a->P), s));
+    int rc;
+    if ((rc = launch_blend_backward(a->W, a->H, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
+    GSR_STAGE(a->debug, s, "blend_backward");
+    if ((rc = launch_preprocess_backward(*a, g, accum, s))) return rc;
+    GSR_STAGE(a->debug, s, "preprocess_backward");
+    return GSR_OK;
+}
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
+                     gsr_stream_t stream)
+{
+    (void)projmatrix;
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return GSR_EINVAL;
+    if (P == 0) return GSR_OK;
+    return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+}
+
+int gsr_dist2(int P, const float* points, float* out, GsrAlloc scratch, gsr_stream_t stream)
+{
+    if (P < 0 || (P > 0 && (!points || !out || !scratch.fn))) return GSR_EINVAL;
+    if (P == 0) return GSR_OK;
+    return launch_dist2(P, points, out, scratch, (cudaStream_t)stream);
+}
+
+int gsr_export_binning(const void* geom_blob, const void* binning_blob, const void* img_blob, int P, int R, int W, int H,
+                       uint64_t* keys, uint32_t* values, uint32_t* ranges, uint32_t* n_contrib, float* final_T,
+                       gsr_stream_t stream_)
+{
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (!geom_blob || !binning_blob || !img_blob) return GSR_EBLOB;
+    GeomView g = geom_view(const_cast<void*>(geom_blob), P);
+    BinView b = bin_view(const_cast<void*>(binning_blob), R);
+    ImgView im = img_view(const_cast<void*>(img_blob), W, H);
+    const int tiles = ((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
+    const size_t N = (size_t)W * H;
+    if (keys && R > 0) GSR_LAUNCH(export_keys_kernel, tiles, 128, 0, s, tiles, im.ranges, b.vals, g.rec, (unsigned long long*)keys);
+    if (values && R > 0) GSR_CUDA(cudaMemcpyAsync(values, b.vals, 4 * (size_t)R, cudaMemcpyDeviceToDevice, s));
+    if (ranges) GSR_CUDA(cudaMemcpyAsync(ranges, im.ranges, 8 * (size_t)tiles, cudaMemcpyDeviceToDevice, s));
+    if (n_contrib) GSR_CUDA(cudaMemcpyAsync(n_contrib, im.n_contrib, 4 * N, cudaMemcpyDeviceToDevice, s));
+    if (final_T) GSR_CUDA(cudaMemcpyAsync(final_T, im.final_T, 4 * N, cudaMemcpyDeviceToDevice, s));
+    return GSR_OK;
+}
+
+const char* gsr_strerror(int code)
+{
+    switch (code) {
+    case GSR_OK: return "ok";
+    case GSR_EINVAL: return "invalid argument";
+    case GSR_ECUDA: return "CUDA error";
+    case GSR_ENOMEM: return "scratch allocator returned NULL";
+    case GSR_ECHANNELS: return "For non-RGB, provide precomputed Gaussian colors!";
+    case GSR_ECOV: return "provide either scales+rotations or a precomputed 3D covariance";
+    case GSR_EBLOB: return "state blob does not belong to this forward call";
+    case GSR_ETOOBIG: return "image or instance count too large";
+    default: return "unknown error";
+    }
+}
+const char* gsr_last_cuda_error(void) { return g_last_cuda_error; }
+int gsr_abi_version(void) { return GSR_ABI_VERSION; }
+void gsr_reset_launch_count(void) { g_launches = 0; }
+unsigned long long gsr_launch_count(void) { return g_launches; }
+
+}  // extern "C"

@@ -1,0 +1,281 @@
+// blend.cu - per-tile alpha blending, forward and backward.
+//
+// Replaces (reference: submodules/diff-gaussian-rasterization/cuda_rasterizer):
+//   blend_fwd_kernel  <- renderCUDA<3> (forward)   forward.cu:261-374
+//   blend_bwd_kernel  <- renderCUDA<3> (backward)  backward.cu:399-557
+//
+// One CTA per 16x16 tile, one thread per pixel.  Tile-list entries are staged in shared memory as
+// packed records gathered with 16-byte cp.async copies (position+conic+opacity+colour: everything
+// the inner loop touches, so the loop never goes to global memory), double buffered so the gather
+// of batch b+1 overlaps the blending of batch b with a single barrier per batch.
+// The per-pixel arithmetic keeps the reference's expression order: skip decisions (power > 0,
+// alpha < 1/255, T < 1e-4) must be identical or a pixel can differ by up to 1/255.
+//
+// Backward: every lane computes its pixel's contribution to the 9 per-Gaussian gradient terms, a
+// transposing warp butterfly (9 + 5 shuffles instead of 45) reduces them, and 9 lanes issue one
+// red.global.add each into a packed 48-byte accumulator row (one or two L2 sectors per warp-entry
+// instead of the reference's 9 atomics per pixel-entry into four arrays).
+#include "gsr_common.cuh"
+
+namespace gsr {
+
+constexpr int BL_THREADS = GSR_TILE * GSR_TILE;   // 256
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
+{
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem)
+{
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+struct BlendStage {
+    float4 q0[BL_THREADS];   // pix.x pix.y conic.x conic.y
+    float4 q1[BL_THREADS];   // conic.z opacity r g
+    float  b[BL_THREADS];    // b
+};
+
+// issue the gather of one batch: entry `pos` of the sorted list (if in range) into slot threadIdx
+__device__ __forceinline__ void stage_gather(BlendStage& st, const SplatRec* __restrict__ rec, uint32_t id, bool valid)
+{
+    if (valid) {
+        const SplatRec* r = rec + id;
+        cp_async16(&st.q0[threadIdx.x], &r->q0);
+        cp_async16(&st.q1[threadIdx.x], &r->q1);
+        cp_async4(&st.b[threadIdx.x], &r->q2);
+    }
+    cp_async_commit();
+}
+
+__global__ void __launch_bounds__(BL_THREADS)
+blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                 int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                 float* __restrict__ out)
+{
+    __shared__ BlendStage stage[2];
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const uint32_t px = blockIdx.x * GSR_TILE + tx, py = blockIdx.y * GSR_TILE + ty;
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    bool done = !inside;
+
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
+
+    float T = 1.0f;
+    uint32_t contributor = 0, last_contributor = 0;
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+
+    // prologue: ids of batches 0 and 1, gather of batch 0
+    uint32_t id_next = 0;
+    {
+        const bool v0 = (int)threadIdx.x < total;
+        const uint32_t id0 = v0 ? vals[range.x + threadIdx.x] : 0;
+        stage_gather(stage[0], rec, id0, v0);
+        const int p1 = BL_THREADS + threadIdx.x;
+        if (p1 < total) id_next = vals[range.x + p1];
+    }
+    int todo = total;
+    for (int i = 0; i < rounds; i++, todo -= BL_THREADS) {
+        cp_async_wait<0>();
+        // barrier: batch i is visible to everyone, everyone has left batch i-1 (its buffer is reused below)
+        const int num_done = __syncthreads_count(done);
+        if (num_done == BL_THREADS) break;
+        // gather batch i+1 into the other buffer, fetch the ids of batch i+2
+        {
+            const int p1 = (i + 1) * BL_THREADS + threadIdx.x;
+            stage_gather(stage[(i + 1) & 1], rec, id_next, p1 < total);
+            const int p2 = p1 + BL_THREADS;
+            if (p2 < total) id_next = vals[range.x + p2];
+        }
+        const BlendStage& st = stage[i & 1];
+        const int n = min(BL_THREADS, todo);
+        for (int j = 0; !done && j < n; j++) {
+            contributor++;
+            const float4 a = st.q0[j];
+            const float4 c = st.q1[j];
+            const float dx = a.x - pxf, dy = a.y - pyf;
+            const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, c.y * expf(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) { done = true; continue; }
+            C0 += c.z * alpha * T;
+            C1 += c.w * alpha * T;
+            C2 += st.b[j] * alpha * T;
+            T = test_T;
+            last_contributor = contributor;
+        }
+    }
+    cp_async_wait<0>();
+    if (inside) {
+        const size_t pix = (size_t)W * py + px;
+        final_T[pix] = T;
+        n_contrib[pix] = last_contributor;
+        const size_t HW = (size_t)H * W;
+        out[pix] = C0 + T * bg[0];
+        out[HW + pix] = C1 + T * bg[1];
+        out[2 * HW + pix] = C2 + T * bg[2];
+    }
+}
+
+int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+                         float* out_color, cudaStream_t s)
+{
+    const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
+    GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
+    return GSR_OK;
+}
+
+// ------------------------------------------------------------------------------------------ backward
+
+// reduces 8 per-lane values over the warp with a transposing butterfly: afterwards lane L holds the
+// warp total of value ((L>>4)&1)*4 + ((L>>3)&1)*2 + ((L>>2)&1)  (replicated over the low two lane bits)
+__device__ __forceinline__ float butterfly8(float v0, float v1, float v2, float v3, float v4, float v5, float v6, float v7,
+                                            int lane)
+{
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+    // offset 16: 8 -> 4
+    float a0 = (b4 ? v4 : v0) + __shfl_xor_sync(0xffffffffu, b4 ? v0 : v4, 16);
+    float a1 = (b4 ? v5 : v1) + __shfl_xor_sync(0xffffffffu, b4 ? v1 : v5, 16);
+    float a2 = (b4 ? v6 : v2) + __shfl_xor_sync(0xffffffffu, b4 ? v2 : v6, 16);
+    float a3 = (b4 ? v7 : v3) + __shfl_xor_sync(0xffffffffu, b4 ? v3 : v7, 16);
+    // offset 8: 4 -> 2
+    float c0 = (b3 ? a2 : a0) + __shfl_xor_sync(0xffffffffu, b3 ? a0 : a2, 8);
+    float c1 = (b3 ? a3 : a1) + __shfl_xor_sync(0xffffffffu, b3 ? a1 : a3, 8);
+    // offset 4: 2 -> 1
+    float e = (b2 ? c1 : c0) + __shfl_xor_sync(0xffffffffu, b2 ? c0 : c1, 4);
+    e += __shfl_xor_sync(0xffffffffu, e, 2);
+    e += __shfl_xor_sync(0xffffffffu, e, 1);
+    return e;
+}
+
+struct BlendStageBwd {
+    float4 q0[BL_THREADS];
+    float4 q1[BL_THREADS];
+    float  b[BL_THREADS];
+    uint32_t id[BL_THREADS];
+};
+
+// accumulator row layout (12 floats per Gaussian): 0-2 dL/dcolour, 3-4 dL/dmean2D (NDC), 5-7 dL/dconic (x, y, w), 8 dL/dopacity
+__global__ void __launch_bounds__(BL_THREADS)
+blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                 int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
+                 const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, float* __restrict__ accum)
+{
+    __shared__ BlendStageBwd stage[2];
+    const int lane = threadIdx.x & 31;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const uint32_t px = blockIdx.x * GSR_TILE + tx, py = blockIdx.y * GSR_TILE + ty;
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t pix = (size_t)W * py + px;
+    const size_t HW = (size_t)H * W;
+
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
+
+    const float T_final = inside ? final_T[pix] : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
+    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
+    const float bg_dot = bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2;
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;       // accum_rec
+    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;     // backward.cu:460-461
+
+    // the warp only has work in list positions below the largest n_contrib of its lanes
+    int warp_last = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+
+    // which accumulator column this lane commits after the butterfly
+    const int col8 = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+
+    // entries are walked back to front: batch i covers list positions total-1-i*256 .. (descending)
+    auto gather = [&](BlendStageBwd& st, int batch) {
+        const int p = batch * BL_THREADS + threadIdx.x;
+        if (p < total) {
+            const uint32_t id = vals[range.y - 1 - p];
+            st.id[threadIdx.x] = id;
+            const SplatRec* r = rec + id;
+            cp_async16(&st.q0[threadIdx.x], &r->q0);
+            cp_async16(&st.q1[threadIdx.x], &r->q1);
+            cp_async4(&st.b[threadIdx.x], &r->q2);
+        }
+        cp_async_commit();
+    };
+    gather(stage[0], 0);
+    int contributor = total;
+    for (int i = 0; i < rounds; i++) {
+        cp_async_wait<0>();
+        __syncthreads();
+        if (i + 1 < rounds) gather(stage[(i + 1) & 1], i + 1);
+        const BlendStageBwd& st = stage[i & 1];
+        const int n = min(BL_THREADS, total - i * BL_THREADS);
+        for (int j = 0; j < n; j++) {
+            contributor--;
+            if (contributor >= warp_last) continue;      // warp-uniform
+            const float4 a = st.q0[j];
+            const float4 c = st.q1[j];
+            const float dx = a.x - pxf, dy = a.y - pyf;
+            const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
+            const float G = expf(power);
+            const float alpha = fminf(0.99f, c.y * G);
+            const bool live = contributor < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+            if (!__any_sync(0xffffffffu, live)) continue;
+
+            float g0 = 0.f, g1 = 0.f, g2 = 0.f, gmx = 0.f, gmy = 0.f, gcx = 0.f, gcy = 0.f, gcw = 0.f, gop = 0.f;
+            if (live) {
+                T = T / (1.f - alpha);
+                const float dchannel_dcolor = alpha * T;
+                const float col2 = st.b[j];
+                float dL_dalpha = 0.0f;
+                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = c.z; dL_dalpha += (c.z - acc0) * dp0;
+                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = c.w; dL_dalpha += (c.w - acc1) * dp1;
+                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = col2; dL_dalpha += (col2 - acc2) * dp2;
+                g0 = dchannel_dcolor * dp0; g1 = dchannel_dcolor * dp1; g2 = dchannel_dcolor * dp2;
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
+                const float dL_dG = c.y * dL_dalpha;
+                const float gdx = G * dx, gdy = G * dy;
+                const float dG_ddelx = -gdx * a.z - gdy * a.w;
+                const float dG_ddely = -gdy * c.x - gdx * a.w;
+                gmx = dL_dG * dG_ddelx * ddelx_dx;
+                gmy = dL_dG * dG_ddely * ddely_dy;
+                gcx = -0.5f * gdx * dx * dL_dG;
+                gcy = -0.5f * gdx * dy * dL_dG;
+                gcw = -0.5f * gdy * dy * dL_dG;
+                gop = G * dL_dalpha;
+            }
+            const float r8 = butterfly8(g0, g1, g2, gmx, gmy, gcx, gcy, gcw, lane);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) gop += __shfl_xor_sync(0xffffffffu, gop, o);
+            float* row = accum + (size_t)st.id[j] * 12;
+            if ((lane & 3) == 0) atomicAdd(row + col8, r8);
+            else if (lane == 1) atomicAdd(row + 8, gop);
+        }
+    }
+}
+
+int launch_blend_backward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+                          const float* dL_dpix, float* accum, cudaStream_t s)
+{
+    const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
+    GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
+               accum);
+    return GSR_OK;
+}
+
+}  // namespace gsr

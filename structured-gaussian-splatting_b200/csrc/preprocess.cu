@@ -1,0 +1,247 @@
+// preprocess.cu - per-Gaussian forward preprocess, frustum marking.
+//
+// Replaces (reference paths relative to submodules/diff-gaussian-rasterization/cuda_rasterizer):
+//   preprocess_fwd_kernel  <- preprocessCUDA<3>            forward.cu:155-256 (+ :20-71, :74-113, :118-152)
+//   mark_visible_kernel    <- checkFrustum                 rasterizer_impl.cu:54-66
+//
+// One thread per Gaussian.  Output is ONE packed 48-byte record per Gaussian (SplatRec) instead of
+// the reference's seven separate arrays (79 B/Gaussian): the blending kernels gather exactly this
+// record per tile-list entry, and the binning stages read radius / tile count / depth out of it.
+// cov3D is not stored: the backward recomputes it from scale/rotation (24 B/Gaussian saved twice).
+#include "gsr_common.cuh"
+#include "math3.cuh"
+
+namespace gsr {
+
+// double arithmetic on purpose: the reference's literals are doubles (auxiliary.h:41-44)
+__device__ __forceinline__ float ndc_to_pix_d(float v, int S)
+{
+    return (float)((((double)v + 1.0) * (double)S - 1.0) * 0.5);
+}
+
+__device__ __forceinline__ void tile_rect(float px, float py, int rad, int gx, int gy, int& x0, int& y0, int& x1, int& y1)
+{
+    // auxiliary.h:46-56: float divide by the tile size, C truncation, clamp to [0, grid]
+    x0 = min(gx, max(0, (int)((px - rad) / GSR_TILE)));
+    y0 = min(gy, max(0, (int)((py - rad) / GSR_TILE)));
+    x1 = min(gx, max(0, (int)((px + rad + GSR_TILE - 1) / GSR_TILE)));
+    y1 = min(gy, max(0, (int)((py + rad + GSR_TILE - 1) / GSR_TILE)));
+}
+
+// scale / rotation -> world covariance, upper triangle (forward.cu:118-152; quaternion used un-normalised)
+__device__ __forceinline__ void cov3d_from_scale_rot(const float3 s, float mod, const float4 q, float* cov6)
+{
+    M3 S = m3_cols(mod * s.x, 0.0f, 0.0f, 0.0f, mod * s.y, 0.0f, 0.0f, 0.0f, mod * s.z);
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    M3 R = m3_cols(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                   2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                   2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    M3 M = m3_mul(S, R);
+    M3 Sig = m3_mul(m3_t(M), M);
+    cov6[0] = Sig.c[0][0]; cov6[1] = Sig.c[0][1]; cov6[2] = Sig.c[0][2];
+    cov6[3] = Sig.c[1][1]; cov6[4] = Sig.c[1][2]; cov6[5] = Sig.c[2][2];
+}
+
+// EWA projection of the 3D covariance (forward.cu:74-113); returns (a, b, c) with the 0.3 low-pass added
+__device__ __forceinline__ float3 cov2d_ewa(const float3 mean, const Camera& cam, const float* cov6)
+{
+    float3 t = xform4x3(mean, cam.view);
+    const float limx = 1.3f * cam.tanx;
+    const float limy = 1.3f * cam.tany;
+    const float txtz = t.x / t.z;
+    const float tytz = t.y / t.z;
+    t.x = fminf(limx, fmaxf(-limx, txtz)) * t.z;
+    t.y = fminf(limy, fmaxf(-limy, tytz)) * t.z;
+
+    M3 J = m3_cols(cam.fx / t.z, 0.0f, -(cam.fx * t.x) / (t.z * t.z),
+                   0.0f, cam.fy / t.z, -(cam.fy * t.y) / (t.z * t.z),
+                   0.0f, 0.0f, 0.0f);
+    M3 Wm = m3_cols(cam.view[0], cam.view[4], cam.view[8],
+                    cam.view[1], cam.view[5], cam.view[9],
+                    cam.view[2], cam.view[6], cam.view[10]);
+    M3 T = m3_mul(Wm, J);
+    M3 Vrk = m3_cols(cov6[0], cov6[1], cov6[2], cov6[1], cov6[3], cov6[4], cov6[2], cov6[4], cov6[5]);
+    M3 cov = m3_mul(m3_mul(m3_t(T), m3_t(Vrk)), T);
+    float3 r = {cov.c[0][0] + 0.3f, cov.c[0][1], cov.c[1][1] + 0.3f};
+    return r;
+}
+
+// SH -> RGB for one Gaussian (forward.cu:20-71).  f = the Gaussian's coefficients, [k][channel] flattened.
+template <int D>
+__device__ __forceinline__ void sh_to_rgb(const float* f, float x, float y, float z, float* rgb, uint32_t& clamp_bits)
+{
+    clamp_bits = 0;
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) {
+#define S_(k) f[3 * (k) + ch]
+        float res = GSR_SH_C0 * S_(0);
+        if (D > 0) {
+            res = res - GSR_SH_C1 * y * S_(1) + GSR_SH_C1 * z * S_(2) - GSR_SH_C1 * x * S_(3);
+            if (D > 1) {
+                float xx = x * x, yy = y * y, zz = z * z;
+                float xy = x * y, yz = y * z, xz = x * z;
+                res = res + GSR_SH_C2_0 * xy * S_(4) + GSR_SH_C2_1 * yz * S_(5) +
+                      GSR_SH_C2_2 * (2.0f * zz - xx - yy) * S_(6) + GSR_SH_C2_3 * xz * S_(7) +
+                      GSR_SH_C2_4 * (xx - yy) * S_(8);
+                if (D > 2) {
+                    res = res + GSR_SH_C3_0 * y * (3.0f * xx - yy) * S_(9) + GSR_SH_C3_1 * xy * z * S_(10) +
+                          GSR_SH_C3_2 * y * (4.0f * zz - xx - yy) * S_(11) +
+                          GSR_SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * S_(12) +
+                          GSR_SH_C3_4 * x * (4.0f * zz - xx - yy) * S_(13) + GSR_SH_C3_5 * z * (xx - yy) * S_(14) +
+                          GSR_SH_C3_6 * x * (xx - 3.0f * yy) * S_(15);
+                }
+            }
+        }
+#undef S_
+        res += 0.5f;
+        if (res < 0) clamp_bits |= 1u << ch;
+        rgb[ch] = fmaxf(res, 0.0f);
+    }
+}
+
+// loads the first NF floats of a Gaussian's SH block; 128-bit loads when the block is 16-byte aligned
+template <int NF>
+__device__ __forceinline__ void load_sh(const float* __restrict__ p, bool vec, float* f)
+{
+    if (vec) {
+        const float4* p4 = reinterpret_cast<const float4*>(p);
+#pragma unroll
+        for (int i = 0; i < NF / 4; i++) {
+            float4 v = __ldg(p4 + i);
+            f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w;
+        }
+#pragma unroll
+        for (int i = NF / 4 * 4; i < NF; i++) f[i] = __ldg(p + i);
+    } else {
+#pragma unroll
+        for (int i = 0; i < NF; i++) f[i] = __ldg(p + i);
+    }
+}
+
+struct PreArgs {
+    int P, D, M;
+    const float* means;
+    const float* shs;
+    const float* colors_pre;
+    const float* opac;
+    const float* scales;
+    const float* rots;
+    const float* cov_pre;
+    float mod;
+    int prefiltered;
+    int* radii;
+    SplatRec* rec;
+    uint8_t* clamped;
+    int* err;          // device flag: prefiltered violated
+};
+
+__global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraArgs ca)
+{
+    __shared__ Camera cam;
+    load_camera(cam, ca);
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.P) return;
+
+    SplatRec out;
+    out.q0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    out.q1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    out.q2 = make_float4(0.f, __uint_as_float(0xFFFFFFFFu), __int_as_float(0), __uint_as_float(0u));
+    int radius_out = 0;
+    uint32_t clamp_bits = 0;
+
+    const float3 p = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
+    const float3 p_view = xform4x3(p, cam.view);
+    if (!(p_view.z <= 0.2f)) {   // near cull only (auxiliary.h:154); NaN passes like the reference
+        const float4 p_hom = xform4x4(p, cam.proj);
+        const float p_w = 1.0f / (p_hom.w + 0.0000001f);
+        const float projx = p_hom.x * p_w, projy = p_hom.y * p_w;
+
+        float c6[6];
+        if (a.cov_pre != nullptr) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) c6[k] = a.cov_pre[6 * (size_t)idx + k];
+        } else {
+            const float3 s = {a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]};
+            const float4 q = {a.rots[4 * idx], a.rots[4 * idx + 1], a.rots[4 * idx + 2], a.rots[4 * idx + 3]};
+            cov3d_from_scale_rot(s, a.mod, q, c6);
+        }
+        const float3 cov = cov2d_ewa(p, cam, c6);
+        const float det = (cov.x * cov.z - cov.y * cov.y);
+        if (det != 0.0f) {
+            const float det_inv = 1.f / det;
+            const float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+            const float mid = 0.5f * (cov.x + cov.z);
+            const float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
+            const float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
+            const float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
+            const float px = ndc_to_pix_d(projx, cam.W), py = ndc_to_pix_d(projy, cam.H);
+            int x0, y0, x1, y1;
+            tile_rect(px, py, (int)my_radius, cam.gx, cam.gy, x0, y0, x1, y1);
+            const uint32_t area = (uint32_t)(x1 - x0) * (uint32_t)(y1 - y0);
+            if (area != 0) {
+                float rgb[3];
+                if (a.colors_pre != nullptr) {
+                    rgb[0] = a.colors_pre[3 * (size_t)idx];
+                    rgb[1] = a.colors_pre[3 * (size_t)idx + 1];
+                    rgb[2] = a.colors_pre[3 * (size_t)idx + 2];
+                } else {
+                    // view direction (forward.cu:26-28): dir / length(dir), IEEE divide per component
+                    float dx = p.x - cam.cam[0], dy = p.y - cam.cam[1], dz = p.z - cam.cam[2];
+                    const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+                    dx = dx / len; dy = dy / len; dz = dz / len;
+                    const float* shp = a.shs + (size_t)3 * a.M * idx;
+                    const bool vec = (((size_t)shp) & 15) == 0;
+                    float f[48];
+                    switch (a.D) {
+                    case 0: load_sh<3>(shp, false, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
+                    case 1: load_sh<12>(shp, vec, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
+                    case 2: load_sh<27>(shp, vec, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
+                    default: load_sh<48>(shp, vec, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
+                    }
+                }
+                out.q0 = make_float4(px, py, conic.x, conic.y);
+                out.q1 = make_float4(conic.z, a.opac[idx], rgb[0], rgb[1]);
+                out.q2 = make_float4(rgb[2], p_view.z, __int_as_float((int)my_radius), __uint_as_float(area));
+                radius_out = (int)my_radius;
+            }
+        }
+    } else if (a.prefiltered) {
+        *a.err = 1;   // reference: printf + __trap (auxiliary.h:156-160); we flag it and report GSR_EINVAL in debug mode
+    }
+    a.radii[idx] = radius_out;
+    a.rec[idx] = out;
+    a.clamped[idx] = (uint8_t)clamp_bits;
+}
+
+int launch_preprocess(const GsrFwdArgs& a, const GeomView& g, cudaStream_t s)
+{
+    const CameraArgs cam = make_camera_args(a.viewmatrix, a.projmatrix, a.cam_pos, a.tan_fovx, a.tan_fovy, a.W, a.H);
+    PreArgs k;
+    k.P = a.P; k.D = a.D; k.M = a.M;
+    k.means = a.means3D; k.shs = a.shs; k.colors_pre = a.colors_precomp; k.opac = a.opacities;
+    k.scales = a.scales; k.rots = a.rotations; k.cov_pre = a.cov3D_precomp; k.mod = a.scale_modifier;
+    k.prefiltered = a.prefiltered; k.radii = a.radii; k.rec = g.rec; k.clamped = g.clamped;
+    k.err = reinterpret_cast<int*>(&g.hdr->pad[0]);
+    GSR_LAUNCH(preprocess_fwd_kernel, cdiv(a.P, 256), 256, 0, s, k, cam);
+    return GSR_OK;
+}
+
+__global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means,
+                                                           CameraArgs ca, uint8_t* present)
+{
+    __shared__ Camera cam;
+    load_camera(cam, ca);
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const float3 p = {means[3 * idx], means[3 * idx + 1], means[3 * idx + 2]};
+    present[idx] = !(xform4x3(p, cam.view).z <= 0.2f);
+}
+
+int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s)
+{
+    const CameraArgs cam = make_camera_args(view, nullptr, nullptr, 1.f, 1.f, GSR_TILE, GSR_TILE);
+    GSR_LAUNCH(mark_visible_kernel, cdiv(P, 256), 256, 0, s, P, means, cam, present);
+    return GSR_OK;
+}
+
+}  // namespace gsr

@@ -1,0 +1,206 @@
+// torch_binding.cpp - thin PyTorch extension over the C ABI of include/gsr.h (host-only C++, no device code).
+//
+// Mirrors the reference bindings' module-level functions (same names, argument order, returns):
+//   rasterize_gaussians            <- RasterizeGaussiansCUDA          diff-gaussian-rasterization/rasterize_points.cu:35-115
+//   rasterize_gaussians_backward   <- RasterizeGaussiansBackwardCUDA  rasterize_points.cu:117-196
+//   mark_visible                   <- markVisible                     rasterize_points.cu:198-217
+//   distCUDA2                      <- distCUDA2                       simple-knn/spatial.cu:15-26
+// Differences a caller can observe: work is issued on torch's CURRENT stream (the reference uses the
+// legacy default stream); gradient tensors nobody asked for (dL_dcolors without colors_precomp,
+// dL_dcov3D without cov3D_precomp) come back empty instead of as P-sized temporaries; errors from the
+// core are raised as RuntimeError carrying gsr_strerror().
+#include <torch/extension.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <tuple>
+#include <string>
+#include "../../include/gsr.h"
+
+namespace {
+
+void* resize_cb(void* ctx, size_t bytes)
+{
+    auto* t = static_cast<torch::Tensor*>(ctx);
+    t->resize_({(long long)bytes});
+    return t->data_ptr();
+}
+
+void check(int rc, const char* what)
+{
+    if (rc == GSR_OK) return;
+    std::string msg = std::string(what) + ": " + gsr_strerror(rc);
+    if (rc == GSR_ECUDA) msg += std::string(" (") + gsr_last_cuda_error() + ")";
+    throw std::runtime_error(msg);
+}
+
+// contiguous fp32 view of an optional input; empty tensor => nullptr (the reference's "absent" sentinel)
+struct F32 {
+    torch::Tensor t;
+    explicit F32(const torch::Tensor& x) { if (x.numel() > 0) t = x.contiguous(); }
+    const float* ptr() const { return t.defined() ? t.data_ptr<float>() : nullptr; }
+};
+
+gsr_stream_t current_stream() { return reinterpret_cast<gsr_stream_t>(at::cuda::getCurrentCUDAStream().stream()); }
+
+}  // namespace
+
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                    const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                    const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                    const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+                    const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                    const bool prefiltered, const bool debug)
+{
+    if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = (int)means3D.size(0);
+    const int H = image_height, W = image_width;
+    auto f32 = means3D.options().dtype(torch::kFloat32);
+    auto i32 = means3D.options().dtype(torch::kInt32);
+    auto u8 = means3D.options().dtype(torch::kByte);
+
+    torch::Tensor out_color = P == 0 ? torch::zeros({3, H, W}, f32) : torch::empty({3, H, W}, f32);
+    torch::Tensor radii = P == 0 ? torch::zeros({P}, i32) : torch::empty({P}, i32);
+    torch::Tensor geomBuffer = torch::empty({0}, u8), binningBuffer = torch::empty({0}, u8), imgBuffer = torch::empty({0}, u8);
+    int rendered = 0;
+    if (P != 0) {
+        int M = 0;
+        if (sh.numel() != 0) M = (int)sh.size(1);
+        F32 bg(background), m3(means3D), col(colors), op(opacity), sc(scales), rot(rotations), cov(cov3D_precomp), vm(viewmatrix),
+            pm(projmatrix), shs(sh), cam(campos);
+        GsrFwdArgs a = {};
+        a.P = P; a.D = degree; a.M = M; a.W = W; a.H = H;
+        a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr(); a.colors_precomp = col.ptr(); a.opacities = op.ptr();
+        a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr(); a.cov3D_precomp = cov.ptr();
+        a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.prefiltered = prefiltered; a.debug = debug;
+        a.out_color = out_color.data_ptr<float>(); a.radii = radii.data_ptr<int>();
+        check(gsr_forward(&a, GsrAlloc{resize_cb, &geomBuffer}, GsrAlloc{resize_cb, &binningBuffer}, GsrAlloc{resize_cb, &imgBuffer},
+                          current_stream(), &rendered),
+              "rasterize_gaussians");
+    }
+    return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer);
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                             const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
+                             const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                             const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                             const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                             const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
+                             const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug)
+{
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = (int)means3D.size(0);
+    const int H = (int)dL_dout_color.size(1), W = (int)dL_dout_color.size(2);
+    int M = 0;
+    if (sh.numel() != 0) M = (int)sh.size(1);
+    auto f32 = means3D.options().dtype(torch::kFloat32);
+    const bool want_colors = colors.numel() != 0, want_cov = cov3D_precomp.numel() != 0;
+    const bool has_sr = scales.numel() != 0 && rotations.numel() != 0;
+
+    // the core writes every element of every gradient it is given: no zero-fill (reference: nine torch::zeros)
+    auto alloc = [&](std::initializer_list<int64_t> shape) { return P == 0 ? torch::zeros(shape, f32) : torch::empty(shape, f32); };
+    torch::Tensor dL_dmeans3D = alloc({P, 3});
+    torch::Tensor dL_dmeans2D = alloc({P, 3});
+    torch::Tensor dL_dcolors = want_colors ? alloc({P, 3}) : torch::empty({0}, f32);
+    torch::Tensor dL_dopacity = alloc({P, 1});
+    torch::Tensor dL_dcov3D = want_cov ? alloc({P, 6}) : torch::empty({0}, f32);
+    torch::Tensor dL_dsh = alloc({P, M, 3});
+    torch::Tensor dL_dscales = has_sr ? alloc({P, 3}) : torch::empty({0}, f32);
+    torch::Tensor dL_drotations = has_sr ? alloc({P, 4}) : torch::empty({0}, f32);
+
+    if (P != 0) {
+        torch::Tensor accum = torch::empty({(long long)(gsr_bwd_accum_bytes(P) / sizeof(float))}, f32);
+        F32 bg(background), m3(means3D), col(colors), sc(scales), rot(rotations), cov(cov3D_precomp), vm(viewmatrix), pm(projmatrix),
+            shs(sh), cam(campos), dpix(dL_dout_color);
+        torch::Tensor radii_c = radii.contiguous();
+        GsrBwdArgs a = {};
+        a.P = P; a.D = degree; a.M = M; a.R = R; a.W = W; a.H = H;
+        a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr(); a.colors_precomp = col.ptr();
+        a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr(); a.cov3D_precomp = cov.ptr();
+        a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+        a.radii = radii_c.data_ptr<int>();
+        a.geom_blob = geomBuffer.data_ptr(); a.binning_blob = binningBuffer.data_ptr(); a.img_blob = imageBuffer.data_ptr();
+        a.dL_dpix = dpix.ptr();
+        a.accum = accum.data_ptr();
+        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>();
+        a.dL_dopacity = dL_dopacity.data_ptr<float>();
+        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>();
+        a.dL_dcolor = want_colors ? dL_dcolors.data_ptr<float>() : nullptr;
+        a.dL_dcov3D = want_cov ? dL_dcov3D.data_ptr<float>() : nullptr;
+        a.dL_dsh = M > 0 ? dL_dsh.data_ptr<float>() : nullptr;
+        a.dL_dscale = has_sr ? dL_dscales.data_ptr<float>() : nullptr;
+        a.dL_drot = has_sr ? dL_drotations.data_ptr<float>() : nullptr;
+        a.debug = debug;
+        check(gsr_backward(&a, current_stream()), "rasterize_gaussians_backward");
+    }
+    return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+}
+
+torch::Tensor mark_visible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix)
+{
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = (int)means3D.size(0);
+    torch::Tensor present = torch::full({P}, false, means3D.options().dtype(at::kBool));
+    if (P != 0) {
+        F32 m3(means3D), vm(viewmatrix), pm(projmatrix);
+        check(gsr_mark_visible(P, m3.ptr(), vm.ptr(), pm.ptr(), reinterpret_cast<uint8_t*>(present.data_ptr<bool>()), current_stream()),
+              "mark_visible");
+    }
+    return present;
+}
+
+torch::Tensor distCUDA2(const torch::Tensor& points)
+{
+    TORCH_CHECK(points.is_cuda(), "points must be a CUDA tensor");
+    const c10::cuda::CUDAGuard guard(points.device());
+    const int P = (int)points.size(0);
+    auto f32 = points.options().dtype(torch::kFloat32);
+    torch::Tensor means = torch::full({P}, 0.0, f32);
+    if (P != 0) {
+        F32 pts(points);
+        torch::Tensor scratch = torch::empty({0}, points.options().dtype(torch::kByte));
+        check(gsr_dist2(P, pts.ptr(), means.data_ptr<float>(), GsrAlloc{resize_cb, &scratch}, current_stream()), "distCUDA2");
+    }
+    return means;
+}
+
+// test / bench hook: the reference's BinningState / ImageState arrays rebuilt from our blobs
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+export_binning(const torch::Tensor& geomBuffer, const torch::Tensor& binningBuffer, const torch::Tensor& imgBuffer, int P, int R,
+               int W, int H)
+{
+    const c10::cuda::CUDAGuard guard(geomBuffer.device());
+    auto o = geomBuffer.options();
+    const int tiles = ((W + 15) / 16) * ((H + 15) / 16);
+    torch::Tensor keys = torch::empty({R}, o.dtype(torch::kInt64));
+    torch::Tensor vals = torch::empty({R}, o.dtype(torch::kInt32));
+    torch::Tensor ranges = torch::empty({tiles, 2}, o.dtype(torch::kInt32));
+    torch::Tensor ncontrib = torch::empty({H, W}, o.dtype(torch::kInt32));
+    torch::Tensor finalT = torch::empty({H, W}, o.dtype(torch::kFloat32));
+    check(gsr_export_binning(geomBuffer.data_ptr(), binningBuffer.data_ptr(), imgBuffer.data_ptr(), P, R, W, H,
+                             reinterpret_cast<uint64_t*>(keys.data_ptr<int64_t>()), reinterpret_cast<uint32_t*>(vals.data_ptr<int>()),
+                             reinterpret_cast<uint32_t*>(ranges.data_ptr<int>()), reinterpret_cast<uint32_t*>(ncontrib.data_ptr<int>()),
+                             finalT.data_ptr<float>(), current_stream()),
+          "export_binning");
+    return std::make_tuple(keys, vals, ranges, ncontrib, finalT);
+}
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
+{
+    m.def("rasterize_gaussians", &rasterize_gaussians);
+    m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
+    m.def("mark_visible", &mark_visible);
+    m.def("distCUDA2", &distCUDA2);
+    m.def("export_binning", &export_binning);
+    m.def("launch_count", []() { return (unsigned long long)gsr_launch_count(); });
+    m.def("reset_launch_count", []() { gsr_reset_launch_count(); });
+    m.def("abi_version", []() { return gsr_abi_version(); });
+}

@@ -1,2 +1,20 @@
-"""Host-side helpers of the B200-native rasterizer hot path (loader for the C-ABI
-library, synthetic scenes, view-sharded data-parallel step)."""
+"""Host-side helpers of the B200-native rasterizer hot path: loader for the C-ABI library and its
+torch binding, synthetic scenes (synth), view-sharded data-parallel step (dp).
+
+There is NO CPU or eager fallback: importing the binding fails loudly if the CUDA extension has not
+been built (python structured-gaussian-splatting_b200/build.py, or __graft_entry__.build()).
+"""
+import os as _os
+
+_HERE = _os.path.dirname(_os.path.abspath(__file__))
+LIB_PATH = _os.path.join(_HERE, "libgsr_b200.so")
+
+
+def load_binding():
+    """Returns the torch extension module (gsr_b200._binding); raises ImportError if it is not built."""
+    if not _os.path.exists(LIB_PATH):
+        raise ImportError("gsr_b200: %s is missing - build the CUDA extension first "
+                          "(python structured-gaussian-splatting_b200/build.py); there is no CPU fallback" % LIB_PATH)
+    import torch  # noqa: F401  (libtorch must be loaded before the extension)
+    from . import _binding
+    return _binding
