@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py - headline benchmark of the B200-native Gaussian rasterizer hot path.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun, one rank per GPU)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+Workload (BASELINE.json metric: "fwd+bwd rasterize ms/view @1080p 3M Gaussians; train views/s at 1-8 GPUs"):
+config C3 - 3,000,000 synthetic Gaussians, SH degree 3, 1920x1080, cameras on the SURVEY 8(d) ring.
+A step = every rank renders `--views-per-step` views forward+backward through the drop-in
+GaussianRasterizer API over the full (replicated) Gaussian set, gradients accumulating in one flat
+buffer, followed for N>1 by one NCCL all-reduce of that buffer (weak scaling: per-GPU work is fixed).
+value = total views/s over all ranks (ms/view on one GPU = 1000 / value at N=1).
+
+Prints ONE JSON line (rank 0).  `--impl reference` times the reference algorithm's CPU restatement
+(oracle/, all host threads) on a bounded tile sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "structured-gaussian-splatting_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "fwd+bwd rasterize views/s @1080p 3M Gaussians SH3 (ms/view = 1000*n_gpus/value)"
+UNIT = "views/s"
+WORKLOAD = "C3: 3M Gaussians, SH degree 3, 1920x1080, fwd+bwd via GaussianRasterizer API"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--views-per-step", type=int, default=4)
+    ap.add_argument("--config", default="C3")
+    ap.add_argument("--gaussians", type=int, default=0, help="override P (debug only; makes the number invalid)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples SM clock and throttle reasons with NVML every 100 ms while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons, self._stop, self.max_mhz = index, [], set(), threading.Event(), None
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        if self.nv is not None:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t is not None:
+            self._t.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------ CPU baseline
+def cpu_sample(spec, P, tile_stride, cam_k=0):
+    """The oracle (CPU restatement of the reference algorithm, OpenMP over all host threads) on a bounded
+    sample: preprocess + binning of the FULL scene, blending forward/backward on every `tile_stride`-th
+    tile; the blending time is scaled by tile_stride ("extrapolated").  Returns (est. seconds/view, info)."""
+    import numpy as np
+    import oracle
+    from gsr_b200 import synth
+    sc = synth.spec_scene(spec, P=P)
+    cam = synth.make_camera(cam_k, 64, spec.W, spec.H, spec.radius, spec.fovx_deg)
+    bg = synth.spec_background(spec)
+    go = synth.grad_image(spec.W, spec.H).numpy()
+    kw = dict(shs=sc["shs"].numpy(), scales=sc["scales"].numpy(), rotations=sc["rotations"].numpy(),
+              viewmatrix=cam.viewmatrix.numpy(), projmatrix=cam.projmatrix.numpy(), campos=cam.campos.numpy(), bg=bg.numpy(),
+              W=spec.W, H=spec.H, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, sh_degree=spec.D)
+    m, o = sc["means3D"].numpy(), sc["opacities"].numpy()
+    t0 = time.perf_counter()
+    st = oracle.forward(m, o, blend=False, **kw)
+    t_pre = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    oracle.blend_forward(st, tile_first=0, tile_stride=tile_stride)
+    t_bf = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    oracle.backward(st, go, tile_first=0, tile_stride=1 << 30)        # tile 0 only: the per-Gaussian part
+    t_pb = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    oracle.backward(st, go, tile_first=0, tile_stride=tile_stride)
+    t_bb = max(0.0, time.perf_counter() - t0 - t_pb)
+    est = t_pre + t_pb + tile_stride * (t_bf + t_bb)
+    info = dict(R=int(st.R), preprocess_bin_s=round(t_pre, 3), blend_fwd_sample_s=round(t_bf, 3),
+                blend_bwd_sample_s=round(t_bb, 3), pre_bwd_s=round(t_pb, 3), tile_stride=tile_stride)
+    return est, info
+
+
+def run_reference_arm(args, spec, P):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    cores = oracle.num_threads()
+    stride = 64
+    for _ in range(args.warmup):
+        cpu_sample(spec, P, 1 << 12)                 # warm-up on a tiny tile sample (page-in, OpenMP pool)
+    t = []
+    info = None
+    for _ in range(args.steps):
+        est, info = cpu_sample(spec, P, stride)
+        t.append(est)
+    sec_per_view = sum(t) / len(t)
+    value = 1.0 / sec_per_view
+    sample = ("full preprocess+binning of the scene, blending fwd+bwd on every %d-th tile scaled x%d (extrapolated), "
+              "1 view per step" % (stride, stride))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": sec_per_view * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "P": P, "W": spec.W, "H": spec.H, "sh_degree": spec.D, "views_per_step": 1},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "detail": info},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "the reference rasterizer has no CPU implementation; this is the oracle/ C restatement of its algorithm"}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def stage_bytes(P, Pv, R, N, tiles, M):
+    """Algorithmic bytes per launch of each stage."""
+    return {
+        "preprocess": 44 * P + (12 * M + 4) * Pv + 49 * P + 4 * P,     # inputs + SH of visible + 48 B record, 1 B clamp + radii
+        "depth_order": 100 * P,
+        "tile_split": 52 * R + 8 * tiles,
+        "blend_forward": 40 * R + 20 * N,
+        "blend_backward": 80 * R + 32 * N,
+        "preprocess_backward": (111 + 64 + 24 * M) * Pv + 4 * (14 + 3 * M) * (P - Pv),
+    }
+
+
+def main():
+    args = parse_args()
+    from gsr_b200 import synth
+    spec = synth.CONFIGS[args.config]
+    P = args.gaussians or spec.P
+    if args.impl == "reference":
+        run_reference_arm(args, spec, P)
+        return
+
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import diff_gaussian_rasterization as dgr
+    from gsr_b200 import dp
+    C = dgr._C
+
+    V = 64
+    vps = args.views_per_step
+    scene = synth.spec_scene(spec, P=P)
+    params = dp.make_leaf_params(scene, dev)
+    flat = dp.FlatGrads(params)
+    cams = [synth.make_camera(k, V, spec.W, spec.H, spec.radius, spec.fovx_deg).to(dev) for k in range(V)]
+    bg = synth.spec_background(spec, dev)
+    go = synth.grad_image(spec.W, spec.H, device=dev)
+    M = (spec.D + 1) ** 2
+    N = spec.W * spec.H
+    tiles = ((spec.W + 15) // 16) * ((spec.H + 15) // 16)
+
+    def my_views(step):
+        # view k of the step goes to rank k mod world; camera ids walk round the ring
+        return [(step * vps * world + j * world + rank) % V for j in range(vps)]
+
+    stats = {"R": 0, "Pv": 0, "views": 0}
+
+    def step_device(step, collect=False):
+        flat.zero_()
+        for k in my_views(step):
+            color, radii, _ = dp.render_view(dgr, params, cams[k], bg, spec.D)
+            color.backward(go)
+            if collect:
+                stats["Pv"] += int((radii > 0).sum())
+                stats["views"] += 1
+        flat.all_reduce()
+
+    # e2e: host buffers in, host scalar out.  Per view: camera + ground-truth image from pinned host memory,
+    # forward, L1 loss against it, backward, loss read back to the host (train.py:91-106).
+    target_host = torch.rand(3, spec.H, spec.W, generator=torch.Generator().manual_seed(3)).pin_memory()
+    cam_host = [torch.cat([c.viewmatrix.reshape(-1), c.projmatrix.reshape(-1), c.campos.reshape(-1)]).cpu().pin_memory()
+                for c in cams]
+    h2d_view = target_host.numel() * 4 + cam_host[0].numel() * 4
+    d2h_view = 4
+
+    def step_e2e(step):
+        flat.zero_()
+        for k in my_views(step):
+            tgt = target_host.to(dev, non_blocking=True)
+            cm = cam_host[k].to(dev, non_blocking=True)
+            cam = synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cm[:16].view(4, 4), cm[16:32].view(4, 4), cm[32:35])
+            color, radii, _ = dp.render_view(dgr, params, cam, bg, spec.D)
+            loss = (color - tgt).abs().mean()
+            loss.backward()
+            _ = float(loss.item())          # device -> host read of the step's result
+        flat.all_reduce()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, first_step):
+        barrier()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(first_step + i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- device-resident timing (value) with per-stage events and clock sampling
+    for i in range(args.warmup):
+        step_device(i)
+    torch.cuda.synchronize()
+    step_device(args.warmup, collect=True)           # untimed: realised P_v for the byte counts
+    C.timing_reset(); C.timing_enable(True); C.reset_launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms_total = timed(step_device, args.steps, args.warmup + 1)
+    clocks = sampler.stop()
+    C.timing_enable(False)
+    launches = int(C.launch_count())
+    stage_rows = C.timing_collect()
+    views_total = args.steps * vps * world
+    value = views_total / (ms_total * 1e-3)
+
+    # ---- e2e timing
+    e2e = None
+    if not args.no_e2e:
+        for i in range(min(2, args.warmup)):
+            step_e2e(i)
+        ms_e2e = timed(step_e2e, args.steps, args.warmup)
+        e2e = {"value": views_total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
+               "d2h_bytes_per_step": d2h_view * vps, "ms_per_step": ms_e2e / args.steps}
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        Pv = stats["Pv"] / max(1, stats["views"])
+        # realised R of one representative view
+        R = probe_R(C, params, cams[my_views(0)[0]], bg, spec.D)
+        sb = stage_bytes(P, Pv, R, N, tiles, M)
+        stages = {}
+        dom, dom_ms = None, -1.0
+        for name, ms, calls in stage_rows:
+            if calls == 0 or name not in sb:
+                continue
+            avg = ms / calls
+            gbs = sb[name] / (avg * 1e-3) / 1e9
+            stages[name] = {"ms": round(avg, 4), "algo_bytes": int(sb[name]), "GBps": round(gbs, 1), "frac_hbm": round(gbs / peak, 4)}
+            if avg > dom_ms:
+                dom, dom_ms = name, avg
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+        except Exception:
+            pass
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": stages[dom]["GBps"], "peak": peak, "peak_source": peak_src,
+                    "unit": "GB/s", "frac": stages[dom]["frac_hbm"], "traffic": traffic,
+                    "note": "blending stages are FP32/MUFU/atomic bound (no dense contraction, no tensor cores); "
+                            "the HBM fraction is reported as the contract asks, per-stage figures in `stages`"}
+        cpu_baseline = None
+        if world == 1 and not args.no_cpu_baseline:
+            import oracle
+            est, info = cpu_sample(spec, P, 64)
+            cpu_baseline = {"value": 1.0 / est, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+                            "sample": "full preprocess+binning, blending fwd+bwd on every 64th tile scaled x64 (extrapolated), 1 view",
+                            "detail": info}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_total / args.steps, "ms_per_view": ms_total / args.steps / vps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "P": P, "W": spec.W, "H": spec.H, "sh_degree": spec.D, "views_per_step": vps * world,
+                           "views_per_gpu_per_step": vps, "R_per_view": R, "visible_per_view": int(Pv),
+                           "parallelism": "view-sharded dp%d, one NCCL all-reduce of %d MB per step" % (world, flat.nbytes() >> 20),
+                           "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
+                                 ((flat.nbytes() + 48 * P + 20 * R) / 1e9)},
+                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches,
+                "clocks": clocks}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def probe_R(C, params, cam, bg, D):
+    """num_rendered of one view through the raw binding (untimed)."""
+    import torch
+    e = torch.Tensor([])
+    with torch.no_grad():
+        out = C.rasterize_gaussians(bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], 1.0, e,
+                                    cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, params["shs"], D,
+                                    cam.campos, False, False)
+    return int(out[0])
+
+
+if __name__ == "__main__":
+    main()

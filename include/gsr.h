@@ -162,6 +162,20 @@ const char* gsr_strerror(int code);
 const char* gsr_last_cuda_error(void);
 int gsr_abi_version(void);
 
+/*
+ * Per-stage device timing (bench.py's roofline leg).  When enabled, every stage of gsr_forward /
+ * gsr_backward is bracketed by cudaEvents recorded on the caller's stream; gsr_timing_collect()
+ * synchronises those events and adds the elapsed times to per-stage totals.
+ * Stage ids: 0 preprocess, 1 depth_order, 2 tile_split, 3 blend_forward, 4 blend_backward,
+ * 5 preprocess_backward, 6 dist2.   ms / calls may be NULL.
+ */
+#define GSR_NUM_STAGES 7
+void gsr_timing_enable(int on);
+int  gsr_timing_collect(void);
+int  gsr_timing_read(int stage, double* ms_total, unsigned long long* calls);
+void gsr_timing_reset(void);
+const char* gsr_stage_name(int stage);
+
 /* kernel-launch counter (all launches made by this library since the last reset) */
 void gsr_reset_launch_count(void);
 unsigned long long gsr_launch_count(void);

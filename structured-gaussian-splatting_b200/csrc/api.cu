@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 namespace gsr {
 
@@ -26,6 +27,35 @@ int env_int(const char* name, int dflt)
 {
     const char* v = getenv(name);
     return v && *v ? atoi(v) : dflt;
+}
+
+// ------------------------------------------------------------------ per-stage event timing
+static bool g_timing = false;
+struct Pending { int stage; cudaEvent_t a, b; };
+static std::vector<Pending> g_pending;
+static std::vector<cudaEvent_t> g_pool;
+static double g_stage_ms[GSR_NUM_STAGES];
+static unsigned long long g_stage_calls[GSR_NUM_STAGES];
+static cudaEvent_t g_open[GSR_NUM_STAGES];
+
+static cudaEvent_t get_event()
+{
+    if (!g_pool.empty()) { cudaEvent_t e = g_pool.back(); g_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+void stage_begin(int stage, cudaStream_t s)
+{
+    if (!g_timing) return;
+    g_open[stage] = get_event();
+    cudaEventRecord(g_open[stage], s);
+}
+void stage_end(int stage, cudaStream_t s)
+{
+    if (!g_timing || !g_open[stage]) return;
+    cudaEvent_t b = get_event();
+    cudaEventRecord(b, s);
+    g_pending.push_back(Pending{stage, g_open[stage], b});
+    g_open[stage] = nullptr;
 }
 
 // ------------------------------------------------------------------ blob layouts
@@ -143,9 +173,13 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     GSR_CUDA(cudaMemsetAsync(g.hdr, 0, sizeof(BlobHeader), s));
 
     int rc;
+    stage_begin(0, s);
     if ((rc = launch_preprocess(*a, g, s))) return rc;
+    stage_end(0, s);
     GSR_STAGE(a->debug, s, "preprocess");
+    stage_begin(1, s);
     if ((rc = launch_depth_order(a->P, g, s))) return rc;
+    stage_end(1, s);
     GSR_STAGE(a->debug, s, "depth_order");
 
     // the binning blob is sized from R: one blocking read-back, like rasterizer_impl.cu:280-281
@@ -161,12 +195,16 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     BinView b = bin_view(bblob, R);
     GSR_LAUNCH(init_headers_kernel, 1, 32, 0, s, g.hdr, b.hdr, im.hdr, a->P, R, a->W, a->H);
 
+    stage_begin(2, s);
     if (env_int("GSR_SORT", 0) == 1) rc = launch_tile_split_cub(a->P, R, a->W, a->H, g, b, im, s);
     else rc = launch_tile_split(a->P, R, a->W, a->H, g, b, im, s);
     if (rc) return rc;
+    stage_end(2, s);
     GSR_STAGE(a->debug, s, "tile_split");
 
+    stage_begin(3, s);
     if ((rc = launch_blend_forward(a->W, a->H, a->background, g, b, im, a->out_color, s))) return rc;
+    stage_end(3, s);
     GSR_STAGE(a->debug, s, "blend_forward");
     if (a->debug && a->prefiltered) {
         int err = 0;
@@ -203,11 +241,15 @@ int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream_)
                 return GSR_EBLOB;
     }
     float* accum = (float*)a->accum;
-    GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(a->P), s));
     int rc;
+    stage_begin(4, s);
+    GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(a->P), s));
     if ((rc = launch_blend_backward(a->W, a->H, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
+    stage_end(4, s);
     GSR_STAGE(a->debug, s, "blend_backward");
+    stage_begin(5, s);
     if ((rc = launch_preprocess_backward(*a, g, accum, s))) return rc;
+    stage_end(5, s);
     GSR_STAGE(a->debug, s, "preprocess_backward");
     return GSR_OK;
 }
@@ -225,7 +267,10 @@ int gsr_dist2(int P, const float* points, float* out, GsrAlloc scratch, gsr_stre
 {
     if (P < 0 || (P > 0 && (!points || !out || !scratch.fn))) return GSR_EINVAL;
     if (P == 0) return GSR_OK;
-    return launch_dist2(P, points, out, scratch, (cudaStream_t)stream);
+    stage_begin(6, (cudaStream_t)stream);
+    int rc = launch_dist2(P, points, out, scratch, (cudaStream_t)stream);
+    stage_end(6, (cudaStream_t)stream);
+    return rc;
 }
 
 int gsr_export_binning(const void* geom_blob, const void* binning_blob, const void* img_blob, int P, int R, int W, int H,
@@ -263,6 +308,37 @@ const char* gsr_strerror(int code)
 }
 const char* gsr_last_cuda_error(void) { return g_last_cuda_error; }
 int gsr_abi_version(void) { return GSR_ABI_VERSION; }
+
+void gsr_timing_enable(int on) { g_timing = on != 0; }
+void gsr_timing_reset(void)
+{
+    for (int i = 0; i < GSR_NUM_STAGES; i++) { g_stage_ms[i] = 0; g_stage_calls[i] = 0; }
+}
+int gsr_timing_collect(void)
+{
+    for (auto& p : g_pending) {
+        GSR_CUDA(cudaEventSynchronize(p.b));
+        float ms = 0.f;
+        GSR_CUDA(cudaEventElapsedTime(&ms, p.a, p.b));
+        g_stage_ms[p.stage] += ms; g_stage_calls[p.stage]++;
+        g_pool.push_back(p.a); g_pool.push_back(p.b);
+    }
+    g_pending.clear();
+    return GSR_OK;
+}
+int gsr_timing_read(int stage, double* ms_total, unsigned long long* calls)
+{
+    if (stage < 0 || stage >= GSR_NUM_STAGES) return GSR_EINVAL;
+    if (ms_total) *ms_total = g_stage_ms[stage];
+    if (calls) *calls = g_stage_calls[stage];
+    return GSR_OK;
+}
+const char* gsr_stage_name(int stage)
+{
+    static const char* n[GSR_NUM_STAGES] = {"preprocess", "depth_order", "tile_split", "blend_forward", "blend_backward",
+                                            "preprocess_backward", "dist2"};
+    return stage >= 0 && stage < GSR_NUM_STAGES ? n[stage] : "?";
+}
 void gsr_reset_launch_count(void) { g_launches = 0; }
 unsigned long long gsr_launch_count(void) { return g_launches; }
 

@@ -42,6 +42,10 @@ int record_cuda_error(cudaError_t e, const char* where);
         }                                                                        \
     } while (0)
 
+// optional per-stage event timing (api.cu)
+void stage_begin(int stage, cudaStream_t s);
+void stage_end(int stage, cudaStream_t s);
+
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
@@ -143,6 +147,11 @@ int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const
 // comparison arm only (bench / tests): the reference's formulation, cub::DeviceRadixSort on 64-bit keys
 int launch_tile_split_cub(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
 size_t cub_sort_scratch_bytes(long long R);
+
+// generic stable radix sort of (u32 key, identity value) pairs on the low 8*npass key bits (sort.cu)
+size_t radix_hist_words(uint32_t n);
+int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n, int npass,
+                          uint32_t* hist_and_totals, cudaStream_t s);
 
 // blend.cu
 int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,

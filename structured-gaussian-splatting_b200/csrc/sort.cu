@@ -165,6 +165,28 @@ static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t
     return GSR_OK;
 }
 
+// stable LSD sort of n (key, value) pairs on key bits [0, 8*npass); values start as identity.
+// K0, K1, V0: n-word ping-pong buffers; result values land in vals_out (keys are not kept).
+size_t radix_hist_words(uint32_t n) { return align_up((size_t)RS_NB * cdiv(n > 0 ? n : 1, RS_TILE), 64) + RS_NB; }
+int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n, int npass,
+                          uint32_t* hist_and_totals, cudaStream_t s)
+{
+    uint32_t* hist = hist_and_totals;
+    uint32_t* totals = hist + align_up((size_t)RS_NB * cdiv(n > 0 ? n : 1, RS_TILE), 64);
+    // choose the value ping-pong so that the LAST pass writes vals_out
+    uint32_t* Vb[2] = {(npass & 1) ? vals_out : V0, (npass & 1) ? V0 : vals_out};
+    uint32_t* Kb[2] = {K0, K1};
+    const uint32_t* kin = keys;
+    const uint32_t* vin = nullptr;
+    for (int p = 0; p < npass; p++) {
+        const bool last = p == npass - 1;
+        int rc = radix_pass(kin, vin, last ? nullptr : Kb[p & 1], Vb[p & 1], n, 8 * p, 8, hist, totals, s);
+        if (rc) return rc;
+        kin = Kb[p & 1]; vin = Vb[p & 1];
+    }
+    return GSR_OK;
+}
+
 // ------------------------------------------------------------------ exclusive scan of tile counts in depth order
 constexpr int SC_TILE = 4096;   // items per block, 256 threads x 16
 

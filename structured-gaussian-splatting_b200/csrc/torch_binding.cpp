@@ -14,6 +14,7 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <tuple>
 #include <string>
+#include <vector>
 #include "../../include/gsr.h"
 
 namespace {
@@ -203,4 +204,16 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
     m.def("launch_count", []() { return (unsigned long long)gsr_launch_count(); });
     m.def("reset_launch_count", []() { gsr_reset_launch_count(); });
     m.def("abi_version", []() { return gsr_abi_version(); });
+    m.def("timing_enable", [](bool on) { gsr_timing_enable(on ? 1 : 0); });
+    m.def("timing_reset", []() { gsr_timing_reset(); });
+    m.def("timing_collect", []() {
+        check(gsr_timing_collect(), "timing_collect");
+        std::vector<std::tuple<std::string, double, unsigned long long>> out;
+        for (int i = 0; i < GSR_NUM_STAGES; i++) {
+            double ms = 0; unsigned long long n = 0;
+            gsr_timing_read(i, &ms, &n);
+            out.emplace_back(gsr_stage_name(i), ms, n);
+        }
+        return out;
+    });
 }

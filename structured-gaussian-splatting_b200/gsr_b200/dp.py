@@ -1,0 +1,93 @@
+"""View-sharded data-parallel rasterisation step (BASELINE.json config 5).
+
+One process per GPU (torchrun).  Every rank holds the full Gaussian replica, renders its slice of the
+step's cameras (view k goes to rank k mod world), accumulates parameter gradients locally in ONE flat
+fp32 buffer, and the buffer is summed across ranks with a single NCCL all-reduce over NVLink/NVSwitch.
+The reference has no multi-GPU code; this is the layer its train.py would call instead of a
+single-view `render() ... loss.backward()`.
+
+Flat layout (floats per Gaussian: 3 + 3 + 4 + 1 + 3*M):
+    means3D P*3 | scales P*3 | rotations P*4 | opacities P*1 | shs P*M*3
+Each parameter's .grad is a view into the buffer, so autograd accumulates in place and no
+flatten / unflatten copy happens before the collective.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Iterable, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+PARAM_ORDER = ("means3D", "scales", "rotations", "opacities", "shs")
+
+
+def shard_views(n_views: int, rank: int, world: int) -> List[int]:
+    """Views owned by `rank`: k with k mod world == rank."""
+    return [k for k in range(n_views) if k % world == rank]
+
+
+class FlatGrads:
+    """Owns the flat gradient buffer and binds each parameter's .grad to its slice."""
+
+    def __init__(self, params: Dict[str, torch.Tensor]):
+        self.params = params
+        self.names = [n for n in PARAM_ORDER if n in params]
+        total = sum(params[n].numel() for n in self.names)
+        ref = params[self.names[0]]
+        self.flat = torch.zeros(total, dtype=torch.float32, device=ref.device)
+        self.slices = {}
+        o = 0
+        for n in self.names:
+            k = params[n].numel()
+            self.slices[n] = (o, o + k)
+            params[n].grad = self.flat[o:o + k].view_as(params[n])
+            o += k
+
+    def zero_(self):
+        self.flat.zero_()
+
+    def grad(self, name: str) -> torch.Tensor:
+        a, b = self.slices[name]
+        return self.flat[a:b].view_as(self.params[name])
+
+    def nbytes(self) -> int:
+        return self.flat.numel() * 4
+
+    def all_reduce(self, group=None, async_op: bool = False):
+        """Sum over ranks (no-op for world size 1)."""
+        if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+            return None
+        return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+
+def make_leaf_params(scene: Dict[str, torch.Tensor], device) -> Dict[str, torch.Tensor]:
+    return {k: scene[k].to(device).clone().requires_grad_(True) for k in PARAM_ORDER if k in scene}
+
+
+def render_view(rasterizer_mod, params, cam, bg, sh_degree: int, scale_modifier: float = 1.0):
+    """One forward through the drop-in API, exactly as gaussian_renderer.render() calls it
+    (gaussian_renderer/__init__.py:36-93).  Returns (color[3,H,W], radii, means2D grad sink)."""
+    rs = rasterizer_mod.GaussianRasterizationSettings(
+        image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=bg,
+        scale_modifier=scale_modifier, viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, sh_degree=sh_degree,
+        campos=cam.campos, prefiltered=False, debug=False)
+    means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+    color, radii = rasterizer_mod.GaussianRasterizer(rs)(
+        means3D=params["means3D"], means2D=means2D, opacities=params["opacities"], shs=params["shs"],
+        scales=params["scales"], rotations=params["rotations"])
+    return color, radii, means2D
+
+
+def dp_step(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
+            loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None):
+    """Renders this rank's views, back-propagates `loss_fn(color, view_id)` for each into the flat
+    buffer, then all-reduces it.  Returns the summed local loss (a device scalar)."""
+    flat.zero_()
+    total = None
+    for k in view_ids:
+        color, _radii, _m2d = render_view(rasterizer_mod, params, cams[k], bg, sh_degree)
+        loss = loss_fn(color, k)
+        loss.backward()
+        total = loss.detach() if total is None else total + loss.detach()
+    flat.all_reduce(group)
+    return total
