@@ -127,11 +127,142 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     }
 }
 
+// ------------------------------------------------------------------------------------------ sub-tile culling
+// Each warp owns an 8x4 pixel sub-tile (2 x 4 sub-tiles per 16x16 tile).  Before a batch is blended, the
+// thread that gathered entry t decides for which of the 8 sub-tiles the entry can possibly be blended:
+// alpha >= 1/255 needs  q(d) = 0.5*(A dx^2 + C dy^2) + B dx dy <= ln(255*opacity) =: tau, and that ellipse
+// lies inside the axis-aligned box |dx| <= sqrt(2 tau C / det), |dy| <= sqrt(2 tau A / det), det = AC - B^2.
+// A sub-tile whose pixel-centre rectangle misses that box cannot contain a pixel the reference would blend,
+// so dropping the entry for that warp leaves every result bit-identical.  tau is inflated for the rounding
+// of the per-pixel fp32 power (error <= ~1e-6 * q * AC/det), of logf/sqrtf/division, and the box by 1e-3 px;
+// ill-conditioned conics (AC/det > 1e4) are never culled.
+__device__ __forceinline__ uint32_t subtile_mask(const float4 a, const float4 c, float X0, float Y0)
+{
+    const float o = c.y;
+    if (o < 1.0f / 255.0f) return 0u;                 // alpha = min(0.99, o*exp(p<=0)) <= o < 1/255 everywhere
+    const float A = a.z, B = a.w, C = c.x;
+    const float det = A * C - B * B;
+    const float kappa = A * C / det;
+    if (!(kappa <= 1.0e4f) || !(det > 0.f)) return 0xFFu;
+    float tau = (__logf(255.0f * o) + 1.0e-3f) * (1.0f + 2.0e-6f * kappa) * 1.0002f;
+    const float inv = 1.0f / det;
+    const float hx = sqrtf(2.0f * tau * C * inv) * 1.0001f + 1.0e-3f;
+    const float hy = sqrtf(2.0f * tau * A * inv) * 1.0001f + 1.0e-3f;
+    const float xlo = a.x - hx, xhi = a.x + hx, ylo = a.y - hy, yhi = a.y + hy;
+    uint32_t xm = 0, ym = 0;
+    if (xhi >= X0 && xlo <= X0 + 7.0f) xm |= 1u;
+    if (xhi >= X0 + 8.0f && xlo <= X0 + 15.0f) xm |= 2u;
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+        if (yhi >= Y0 + 4.0f * r && ylo <= Y0 + 4.0f * r + 3.0f) ym |= 1u << r;
+    // warp w: sx = w & 1, sy = w >> 1
+    uint32_t m = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++)
+        if (((xm >> (w & 1)) & 1u) && ((ym >> (w >> 1)) & 1u)) m |= 1u << w;
+    return m;
+}
+
+__global__ void __launch_bounds__(BL_THREADS)
+blend_fwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                      int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                      float* __restrict__ out)
+{
+    __shared__ BlendStage stage[2];
+    __shared__ uint32_t bits[2][8][8];     // [buffer][consumer warp][chunk of 32 entries]
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(blockIdx.y * GSR_TILE);
+    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    bool done = !inside;
+
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
+
+    float T = 1.0f;
+    uint32_t last_contributor = 0;
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+
+    uint32_t id_next = 0;
+    {
+        const bool v0 = (int)threadIdx.x < total;
+        const uint32_t id0 = v0 ? vals[range.x + threadIdx.x] : 0;
+        stage_gather(stage[0], rec, id0, v0);
+        const int p1 = BL_THREADS + threadIdx.x;
+        if (p1 < total) id_next = vals[range.x + p1];
+    }
+    for (int i = 0; i < rounds; i++) {
+        const int buf = i & 1;
+        cp_async_wait<0>();       // my own entry of batch i has landed: classify it
+        {
+            uint32_t m = 0;
+            if (i * BL_THREADS + (int)threadIdx.x < total) m = subtile_mask(stage[buf].q0[threadIdx.x], stage[buf].q1[threadIdx.x], X0, Y0);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
+                if (lane == k) bits[buf][k][wid] = bk;
+            }
+        }
+        // barrier: batch i (records + masks) visible to all, everyone has left batch i-1
+        const int num_done = __syncthreads_count(done);
+        if (num_done == BL_THREADS) break;
+        {
+            const int p1 = (i + 1) * BL_THREADS + threadIdx.x;
+            stage_gather(stage[buf ^ 1], rec, id_next, p1 < total);
+            const int p2 = p1 + BL_THREADS;
+            if (p2 < total) id_next = vals[range.x + p2];
+        }
+        if (__all_sync(0xffffffffu, done)) continue;       // this warp's pixels are finished; keep helping with the gathers
+        const BlendStage& st = stage[buf];
+#pragma unroll 1
+        for (int cch = 0; cch < 8; cch++) {
+            uint32_t m = bits[buf][wid][cch];
+            while (m) {
+                const int j = cch * 32 + __ffs(m) - 1;
+                m &= m - 1;
+                if (done) continue;
+                const float4 a = st.q0[j];
+                const float4 c = st.q1[j];
+                const float dx = a.x - pxf, dy = a.y - pyf;
+                const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
+                if (power > 0.0f) continue;
+                const float alpha = fminf(0.99f, c.y * expf(power));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) { done = true; continue; }
+                C0 += c.z * alpha * T;
+                C1 += c.w * alpha * T;
+                C2 += st.b[j] * alpha * T;
+                T = test_T;
+                last_contributor = (uint32_t)(i * BL_THREADS + j + 1);
+            }
+            if (__all_sync(0xffffffffu, done)) break;
+        }
+    }
+    cp_async_wait<0>();
+    if (inside) {
+        const size_t pix = (size_t)W * py + px;
+        final_T[pix] = T;
+        n_contrib[pix] = last_contributor;
+        const size_t HW = (size_t)H * W;
+        out[pix] = C0 + T * bg[0];
+        out[HW + pix] = C1 + T * bg[1];
+        out[2 * HW + pix] = C2 + T * bg[2];
+    }
+}
+
 int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                          float* out_color, cudaStream_t s)
 {
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
-    GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
+    if (env_int("GSR_BLEND", 2) == 1)
+        GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
+    else
+        GSR_LAUNCH(blend_fwd_cull_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+                   out_color);
     return GSR_OK;
 }
 
@@ -269,12 +400,149 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     }
 }
 
+// Backward with the same sub-tile culling as the forward (8x4 pixels per warp).  The list is truncated to the
+// largest n_contrib of the tile, a warp additionally ignores entries at or beyond its own largest n_contrib,
+// and only (warp, entry) pairs that survive both filters are evaluated, reduced and committed.
+__global__ void __launch_bounds__(BL_THREADS)
+blend_bwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                      int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
+                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, float* __restrict__ accum)
+{
+    __shared__ BlendStageBwd stage[2];
+    __shared__ uint32_t bits[2][8][8];
+    __shared__ int s_warp_last[8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(blockIdx.y * GSR_TILE);
+    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t pix = (size_t)W * py + px;
+    const size_t HW = (size_t)H * W;
+
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+
+    const float T_final = inside ? final_T[pix] : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
+    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
+    const float bg_dot = bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2;
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;
+    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+    int warp_last = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+    if (lane == 0) s_warp_last[wid] = warp_last;
+    __syncthreads();
+    int total = 0;                                   // truncated list length = largest n_contrib of the tile
+#pragma unroll
+    for (int k = 0; k < 8; k++) total = max(total, s_warp_last[k]);
+    total = min(total, (int)(range.y - range.x));
+    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
+    const uint32_t list_end = range.x + total;
+
+    const int col8 = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+
+    // back to front: slot t of batch i holds list position total-1-(i*256+t)
+    auto gather = [&](BlendStageBwd& st, int batch) {
+        const int p = batch * BL_THREADS + threadIdx.x;
+        if (p < total) {
+            const uint32_t id = vals[list_end - 1 - p];
+            st.id[threadIdx.x] = id;
+            const SplatRec* r = rec + id;
+            cp_async16(&st.q0[threadIdx.x], &r->q0);
+            cp_async16(&st.q1[threadIdx.x], &r->q1);
+            cp_async4(&st.b[threadIdx.x], &r->q2);
+        }
+        cp_async_commit();
+    };
+    gather(stage[0], 0);
+    for (int i = 0; i < rounds; i++) {
+        const int buf = i & 1;
+        cp_async_wait<0>();
+        {
+            uint32_t m = 0;
+            const int p = i * BL_THREADS + (int)threadIdx.x;
+            if (p < total) {
+                m = subtile_mask(stage[buf].q0[threadIdx.x], stage[buf].q1[threadIdx.x], X0, Y0);
+                const int pos = total - 1 - p;
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    if (pos >= s_warp_last[k]) m &= ~(1u << k);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
+                if (lane == k) bits[buf][k][wid] = bk;
+            }
+        }
+        __syncthreads();
+        if (i + 1 < rounds) gather(stage[buf ^ 1], i + 1);
+        const BlendStageBwd& st = stage[buf];
+#pragma unroll 1
+        for (int cch = 0; cch < 8; cch++) {
+            uint32_t m = bits[buf][wid][cch];
+            while (m) {
+                const int j = cch * 32 + __ffs(m) - 1;
+                m &= m - 1;
+                const int pos = total - 1 - (i * BL_THREADS + j);
+                const float4 a = st.q0[j];
+                const float4 c = st.q1[j];
+                const float dx = a.x - pxf, dy = a.y - pyf;
+                const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, c.y * G);
+                const bool live = pos < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                if (!__any_sync(0xffffffffu, live)) continue;
+
+                float g0 = 0.f, g1 = 0.f, g2 = 0.f, gmx = 0.f, gmy = 0.f, gcx = 0.f, gcy = 0.f, gcw = 0.f, gop = 0.f;
+                if (live) {
+                    T = T / (1.f - alpha);
+                    const float dchannel_dcolor = alpha * T;
+                    const float col2 = st.b[j];
+                    float dL_dalpha = 0.0f;
+                    acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = c.z; dL_dalpha += (c.z - acc0) * dp0;
+                    acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = c.w; dL_dalpha += (c.w - acc1) * dp1;
+                    acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = col2; dL_dalpha += (col2 - acc2) * dp2;
+                    g0 = dchannel_dcolor * dp0; g1 = dchannel_dcolor * dp1; g2 = dchannel_dcolor * dp2;
+                    dL_dalpha *= T;
+                    last_alpha = alpha;
+                    dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
+                    const float dL_dG = c.y * dL_dalpha;
+                    const float gdx = G * dx, gdy = G * dy;
+                    const float dG_ddelx = -gdx * a.z - gdy * a.w;
+                    const float dG_ddely = -gdy * c.x - gdx * a.w;
+                    gmx = dL_dG * dG_ddelx * ddelx_dx;
+                    gmy = dL_dG * dG_ddely * ddely_dy;
+                    gcx = -0.5f * gdx * dx * dL_dG;
+                    gcy = -0.5f * gdx * dy * dL_dG;
+                    gcw = -0.5f * gdy * dy * dL_dG;
+                    gop = G * dL_dalpha;
+                }
+                const float r8 = butterfly8(g0, g1, g2, gmx, gmy, gcx, gcy, gcw, lane);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) gop += __shfl_xor_sync(0xffffffffu, gop, o);
+                float* row = accum + (size_t)st.id[j] * 12;
+                if ((lane & 3) == 0) atomicAdd(row + col8, r8);
+                else if (lane == 1) atomicAdd(row + 8, gop);
+            }
+        }
+    }
+}
+
 int launch_blend_backward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                           const float* dL_dpix, float* accum, cudaStream_t s)
 {
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
-    GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
-               accum);
+    if (env_int("GSR_BLEND", 2) == 1)
+        GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
+                   accum);
+    else
+        GSR_LAUNCH(blend_bwd_cull_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+                   dL_dpix, accum);
     return GSR_OK;
 }
 
