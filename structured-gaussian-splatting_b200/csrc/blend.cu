@@ -268,6 +268,35 @@ int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const
 
 // ------------------------------------------------------------------------------------------ backward
 
+// Per-pixel contribution of one blended entry to the per-Gaussian sums (restates backward.cu:494-556).
+// Instead of the reference's nine final gradient terms the lanes produce MOMENTS of w = dL/dG * G:
+//   g0..g2 = alpha*T*dL/dpix (colour), gmx = w dx, gmy = w dy, gcx = w dx^2, gcy = w dx dy, gcw = w dy^2, gop = w
+// The conic / opacity factors are constant per Gaussian, so they are applied once per Gaussian in
+// preprocess_bwd (dL/dmean2D.x = -W/2 (A gmx + B gmy), dL/dconic = -1/2 (gcx, gcy, gcw), dL/dopacity = gop / o).
+// 1/(1-alpha) is one MUFU.RCP (alpha <= 0.99) instead of two IEEE divisions: gradients carry a 1e-3 tolerance.
+__device__ __forceinline__ void bwd_live_math(float alpha, float araw, float dx, float dy, float c0, float c1, float c2,
+                                              float dp0, float dp1, float dp2, float tfb, float& T, float& last_alpha,
+                                              float& acc0, float& acc1, float& acc2, float& lc0, float& lc1, float& lc2,
+                                              float& g0, float& g1, float& g2, float& gmx, float& gmy, float& gcx, float& gcy,
+                                              float& gcw, float& gop)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f - alpha));
+    T *= r;
+    const float at = alpha * T;
+    acc0 = fmaf(last_alpha, lc0 - acc0, acc0); lc0 = c0;
+    acc1 = fmaf(last_alpha, lc1 - acc1, acc1); lc1 = c1;
+    acc2 = fmaf(last_alpha, lc2 - acc2, acc2); lc2 = c2;
+    float dL_dalpha = (c0 - acc0) * dp0 + (c1 - acc1) * dp1 + (c2 - acc2) * dp2;
+    g0 = at * dp0; g1 = at * dp1; g2 = at * dp2;
+    last_alpha = alpha;
+    dL_dalpha = fmaf(dL_dalpha, T, -tfb * r);
+    const float w = araw * dL_dalpha;          // dL/dG * G = opacity * dL/dalpha * G  (no zeroing when alpha was clamped)
+    gmx = w * dx; gmy = w * dy;
+    gcx = gmx * dx; gcy = gmx * dy; gcw = gmy * dy;
+    gop = w;
+}
+
 // reduces 8 per-lane values over the warp with a transposing butterfly: afterwards lane L holds the
 // warp total of value ((L>>4)&1)*4 + ((L>>3)&1)*2 + ((L>>2)&1)  (replicated over the low two lane bits)
 __device__ __forceinline__ float butterfly8(float v0, float v1, float v2, float v3, float v4, float v5, float v6, float v7,
@@ -296,7 +325,7 @@ struct BlendStageBwd {
     uint32_t id[BL_THREADS];
 };
 
-// accumulator row layout (12 floats per Gaussian): 0-2 dL/dcolour, 3-4 dL/dmean2D (NDC), 5-7 dL/dconic (x, y, w), 8 dL/dopacity
+// accumulator row layout (12 floats per Gaussian): 0-2 dL/dcolour, 3-4 sum w*(dx,dy), 5-7 sum w*(dx^2, dx dy, dy^2), 8 sum w
 __global__ void __launch_bounds__(BL_THREADS)
 blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                  int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
@@ -320,10 +349,9 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     const int last_contributor = inside ? (int)n_contrib[pix] : 0;
     float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
     if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
-    const float bg_dot = bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2;
+    const float tfb = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
     float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;       // accum_rec
     float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;     // backward.cu:460-461
 
     // the warp only has work in list positions below the largest n_contrib of its lanes
     int warp_last = last_contributor;
@@ -361,34 +389,15 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
             const float4 c = st.q1[j];
             const float dx = a.x - pxf, dy = a.y - pyf;
             const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
-            const float G = expf(power);
-            const float alpha = fminf(0.99f, c.y * G);
+            const float araw = c.y * expf(power);
+            const float alpha = fminf(0.99f, araw);
             const bool live = contributor < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
             if (!__any_sync(0xffffffffu, live)) continue;
 
             float g0 = 0.f, g1 = 0.f, g2 = 0.f, gmx = 0.f, gmy = 0.f, gcx = 0.f, gcy = 0.f, gcw = 0.f, gop = 0.f;
             if (live) {
-                T = T / (1.f - alpha);
-                const float dchannel_dcolor = alpha * T;
-                const float col2 = st.b[j];
-                float dL_dalpha = 0.0f;
-                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = c.z; dL_dalpha += (c.z - acc0) * dp0;
-                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = c.w; dL_dalpha += (c.w - acc1) * dp1;
-                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = col2; dL_dalpha += (col2 - acc2) * dp2;
-                g0 = dchannel_dcolor * dp0; g1 = dchannel_dcolor * dp1; g2 = dchannel_dcolor * dp2;
-                dL_dalpha *= T;
-                last_alpha = alpha;
-                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
-                const float dL_dG = c.y * dL_dalpha;
-                const float gdx = G * dx, gdy = G * dy;
-                const float dG_ddelx = -gdx * a.z - gdy * a.w;
-                const float dG_ddely = -gdy * c.x - gdx * a.w;
-                gmx = dL_dG * dG_ddelx * ddelx_dx;
-                gmy = dL_dG * dG_ddely * ddely_dy;
-                gcx = -0.5f * gdx * dx * dL_dG;
-                gcy = -0.5f * gdx * dy * dL_dG;
-                gcw = -0.5f * gdy * dy * dL_dG;
-                gop = G * dL_dalpha;
+                bwd_live_math(alpha, araw, dx, dy, c.z, c.w, st.b[j], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                              lc0, lc1, lc2, g0, g1, g2, gmx, gmy, gcx, gcy, gcw, gop);
             }
             const float r8 = butterfly8(g0, g1, g2, gmx, gmy, gcx, gcy, gcw, lane);
 #pragma unroll
@@ -427,10 +436,9 @@ blend_bwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const int last_contributor = inside ? (int)n_contrib[pix] : 0;
     float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
     if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
-    const float bg_dot = bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2;
+    const float tfb = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
     float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;
     float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
     int warp_last = last_contributor;
 #pragma unroll
@@ -493,34 +501,15 @@ blend_bwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 const float4 c = st.q1[j];
                 const float dx = a.x - pxf, dy = a.y - pyf;
                 const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
-                const float G = expf(power);
-                const float alpha = fminf(0.99f, c.y * G);
+                const float araw = c.y * expf(power);
+                const float alpha = fminf(0.99f, araw);
                 const bool live = pos < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                 if (!__any_sync(0xffffffffu, live)) continue;
 
                 float g0 = 0.f, g1 = 0.f, g2 = 0.f, gmx = 0.f, gmy = 0.f, gcx = 0.f, gcy = 0.f, gcw = 0.f, gop = 0.f;
                 if (live) {
-                    T = T / (1.f - alpha);
-                    const float dchannel_dcolor = alpha * T;
-                    const float col2 = st.b[j];
-                    float dL_dalpha = 0.0f;
-                    acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = c.z; dL_dalpha += (c.z - acc0) * dp0;
-                    acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = c.w; dL_dalpha += (c.w - acc1) * dp1;
-                    acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = col2; dL_dalpha += (col2 - acc2) * dp2;
-                    g0 = dchannel_dcolor * dp0; g1 = dchannel_dcolor * dp1; g2 = dchannel_dcolor * dp2;
-                    dL_dalpha *= T;
-                    last_alpha = alpha;
-                    dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
-                    const float dL_dG = c.y * dL_dalpha;
-                    const float gdx = G * dx, gdy = G * dy;
-                    const float dG_ddelx = -gdx * a.z - gdy * a.w;
-                    const float dG_ddely = -gdy * c.x - gdx * a.w;
-                    gmx = dL_dG * dG_ddelx * ddelx_dx;
-                    gmy = dL_dG * dG_ddely * ddely_dy;
-                    gcx = -0.5f * gdx * dx * dL_dG;
-                    gcy = -0.5f * gdx * dy * dL_dG;
-                    gcw = -0.5f * gdy * dy * dL_dG;
-                    gop = G * dL_dalpha;
+                    bwd_live_math(alpha, araw, dx, dy, c.z, c.w, st.b[j], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                                  lc0, lc1, lc2, g0, g1, g2, gmx, gmy, gcx, gcy, gcw, gop);
                 }
                 const float r8 = butterfly8(g0, g1, g2, gmx, gmy, gcx, gcy, gcw, lane);
 #pragma unroll

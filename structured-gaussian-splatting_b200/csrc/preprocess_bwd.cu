@@ -8,7 +8,8 @@
 // empty() and no 300 B/Gaussian memset is needed.
 //
 // Input is the packed accumulator row written by the blending backward (12 floats per Gaussian:
-// 0-2 dL/dcolour, 3-4 dL/dmean2D, 5-7 dL/dconic x,y,w, 8 dL/dopacity).  cov3D is recomputed from
+// 0-2 dL/dcolour, 3-4 sum w*(dx,dy), 5-7 sum w*(dx^2, dx dy, dy^2), 8 sum w, with w = dL/dG * G), turned
+// into dL/dmean2D, dL/dconic, dL/dopacity here with the Gaussian's conic and opacity.  cov3D is recomputed from
 // scale/rotation instead of being saved by the forward.  Gradients are fp32 with a 1e-3 relative
 // tolerance, so the arithmetic here is free to use a cheaper operation order than the reference.
 #include "gsr_common.cuh"
@@ -26,7 +27,8 @@ struct PreBwdArgs {
     const float* rots;
     const float* cov_pre;
     float mod;
-    const float* accum;      // [P,12]
+    const float* accum;      // [P,12] moment rows written by the blending backward
+    const SplatRec* rec;     // forward records: conic and opacity turn the moments into gradients
     float* dL_dmean2D;       // [P,3]
     float* dL_dopacity;      // [P]
     float* dL_dcolor;        // [P,3] or null
@@ -96,10 +98,14 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, Camer
     const float4* ar = reinterpret_cast<const float4*>(a.accum + (size_t)12 * idx);
     const float4 A0 = ar[0], A1 = ar[1], A2 = ar[2];
     const float dcol[3] = {A0.x, A0.y, A0.z};
-    const float g2x = A0.w, g2y = A1.x;
-    const float dcon_x = A1.y, dcon_y = A1.z, dcon_w = A1.w;
+    // moments -> gradients (backward.cu:536-551 with the per-Gaussian constants factored out of the pixel sums)
+    const float4 r0 = a.rec[idx].q0, r1 = a.rec[idx].q1;
+    const float cA = r0.z, cB = r0.w, cC = r1.x, opac = r1.y;
+    const float g2x = -0.5f * cam.W * (cA * A0.w + cB * A1.x);
+    const float g2y = -0.5f * cam.H * (cC * A1.x + cB * A0.w);
+    const float dcon_x = -0.5f * A1.y, dcon_y = -0.5f * A1.z, dcon_w = -0.5f * A1.w;
     a.dL_dmean2D[3 * idx] = g2x; a.dL_dmean2D[3 * idx + 1] = g2y; a.dL_dmean2D[3 * idx + 2] = 0.f;
-    a.dL_dopacity[idx] = A2.x;
+    a.dL_dopacity[idx] = opac > 0.f ? A2.x / opac : 0.f;
     if (a.dL_dcolor) { a.dL_dcolor[3 * idx] = dcol[0]; a.dL_dcolor[3 * idx + 1] = dcol[1]; a.dL_dcolor[3 * idx + 2] = dcol[2]; }
 
     const float3 p = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
@@ -321,7 +327,7 @@ int launch_preprocess_backward(const GsrBwdArgs& a, const GeomView& g, const flo
     k.P = a.P; k.D = a.D; k.M = a.M;
     k.means = a.means3D; k.radii = a.radii; k.shs = a.shs; k.clamped = g.clamped;
     k.scales = a.scales; k.rots = a.rotations; k.cov_pre = a.cov3D_precomp; k.mod = a.scale_modifier;
-    k.accum = accum;
+    k.accum = accum; k.rec = g.rec;
     k.dL_dmean2D = a.dL_dmean2D; k.dL_dopacity = a.dL_dopacity; k.dL_dcolor = a.dL_dcolor;
     k.dL_dmean3D = a.dL_dmean3D; k.dL_dcov3D = a.dL_dcov3D; k.dL_dsh = a.shs ? a.dL_dsh : nullptr;
     k.dL_dscale = a.cov3D_precomp ? nullptr : a.dL_dscale;

@@ -75,6 +75,10 @@ __global__ void __launch_bounds__(RS_THREADS) radix_rowscan_kernel(uint32_t* __r
 
 // ------------------------------------------------------------------ radix pass: ranked scatter
 // vals_in == nullptr means "identity" (value = item index).  keys_out may be nullptr.
+// One warp match-any per item gives its stable rank inside the warp's run; per-warp digit counts are
+// scanned across the CTA; the 4096 items are first placed in digit order in shared memory and then
+// written out so that consecutive threads write consecutive addresses inside each digit run
+// (full 32-byte sectors instead of 4-byte scattered stores).
 __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_t* __restrict__ keys_in,
                                                                    const uint32_t* __restrict__ vals_in,
                                                                    uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
@@ -83,16 +87,21 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
                                                                    int nblocks)
 {
     __shared__ uint32_t wcount[RS_WARPS][RS_NB];
-    __shared__ uint32_t dbase[RS_NB];
+    __shared__ uint32_t lbase[RS_NB];       // CTA-local exclusive offset of each digit
+    __shared__ uint32_t gdelta[RS_NB];      // global position of local slot lp of digit d = gdelta[d] + lp
     __shared__ uint32_t warp_sum[RS_WARPS];
+    __shared__ uint32_t skey[RS_TILE];
+    __shared__ uint32_t sval[RS_TILE];
     const uint32_t nb = 1u << bits, mask = nb - 1;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t t = threadIdx.x;
 
-    for (uint32_t i = threadIdx.x; i < RS_WARPS * RS_NB; i += RS_THREADS) (&wcount[0][0])[i] = 0;
-    // global digit bases: exclusive scan of totals (<= 256 entries, one per thread)
+    for (uint32_t i = t; i < RS_WARPS * RS_NB; i += RS_THREADS) (&wcount[0][0])[i] = 0;
+    // global digit bases for this CTA: exclusive scan of totals + this CTA's row prefix
+    uint32_t gscan = 0;
     {
-        const uint32_t t = threadIdx.x < nb ? totals[threadIdx.x] : 0;
-        uint32_t inc = t;
+        const uint32_t v = t < nb ? totals[t] : 0;
+        uint32_t inc = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
@@ -100,15 +109,16 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
         }
         if (lane == 31) warp_sum[w] = inc;
         __syncthreads();
-        uint32_t wbase = 0;
-        for (int i = 0; i < w; i++) wbase += warp_sum[i];
-        if (threadIdx.x < nb) dbase[threadIdx.x] = wbase + inc - t + hist[(size_t)threadIdx.x * nblocks + blockIdx.x];
+        uint32_t wb = 0;
+        for (int i = 0; i < w; i++) wb += warp_sum[i];
+        if (t < nb) gscan = wb + inc - v + hist[(size_t)t * nblocks + blockIdx.x];
     }
     __syncthreads();
 
-    // each warp owns a contiguous run of 32*IPT items, walked in order (i, lane)
+    // phase 1: each warp walks its contiguous run of 32*IPT items in order (i, lane)
     const uint32_t wbase_idx = blockIdx.x * RS_TILE + w * (32 * RS_IPT);
     uint32_t key[RS_IPT];
+    uint32_t loff[RS_IPT];      // rank of the item among the warp's items with the same digit
 #pragma unroll
     for (int i = 0; i < RS_IPT; i++) {
         const uint32_t idx = wbase_idx + i * 32 + lane;
@@ -119,37 +129,63 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
         const uint32_t idx = wbase_idx + i * 32 + lane;
         const bool valid = idx < n;
         const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-            const uint32_t d = (key[i] >> shift) & mask;
-            const uint32_t peers = __match_any_sync(vmask, d);
-            if ((peers & ((1u << lane) - 1)) == 0) wcount[w][d] += __popc(peers);
-        }
-        __syncwarp();
-    }
-    __syncthreads();
-    // per digit: turn per-warp counts into per-warp global start positions
-    if (threadIdx.x < nb) {
-        uint32_t run = dbase[threadIdx.x];
-#pragma unroll
-        for (int i = 0; i < RS_WARPS; i++) { uint32_t c = wcount[i][threadIdx.x]; wcount[i][threadIdx.x] = run; run += c; }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < RS_IPT; i++) {
-        const uint32_t idx = wbase_idx + i * 32 + lane;
-        const bool valid = idx < n;
-        const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+        loff[i] = 0;
         if (valid) {
             const uint32_t d = (key[i] >> shift) & mask;
             const uint32_t peers = __match_any_sync(vmask, d);
             const uint32_t rank = __popc(peers & ((1u << lane) - 1));
-            const uint32_t pos = wcount[w][d] + rank;
-            if (keys_out) keys_out[pos] = key[i];
-            vals_out[pos] = vals_in ? vals_in[idx] : idx;
-            __syncwarp(vmask);
-            if (rank == 0) wcount[w][d] += __popc(peers);
+            const int leader = __ffs(peers) - 1;
+            uint32_t old = 0;
+            if (lane == leader) { old = wcount[w][d]; wcount[w][d] = old + __popc(peers); }
+            old = __shfl_sync(peers, old, leader);
+            loff[i] = old + rank;
         }
         __syncwarp();
+    }
+    __syncthreads();
+    // phase 2: per digit, exclusive prefix over warps; then exclusive scan over digits
+    {
+        uint32_t tot = 0;
+        if (t < nb) {
+#pragma unroll
+            for (int i = 0; i < RS_WARPS; i++) { uint32_t c = wcount[i][t]; wcount[i][t] = tot; tot += c; }
+        }
+        uint32_t inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        if (lane == 31) warp_sum[w] = inc;
+        __syncthreads();
+        uint32_t wb = 0;
+        for (int i = 0; i < w; i++) wb += warp_sum[i];
+        if (t < nb) { const uint32_t lb = wb + inc - tot; lbase[t] = lb; gdelta[t] = gscan - lb; }
+    }
+    __syncthreads();
+    // phase 3: place items in digit order in shared memory
+#pragma unroll
+    for (int i = 0; i < RS_IPT; i++) {
+        const uint32_t idx = wbase_idx + i * 32 + lane;
+        if (idx < n) {
+            const uint32_t d = (key[i] >> shift) & mask;
+            const uint32_t lp = lbase[d] + wcount[w][d] + loff[i];
+            skey[lp] = key[i];
+            sval[lp] = vals_in ? vals_in[idx] : idx;
+        }
+    }
+    __syncthreads();
+    // phase 4: coalesced write-out
+    const uint32_t n_blk = min((uint32_t)RS_TILE, n - blockIdx.x * RS_TILE);
+#pragma unroll
+    for (int i = 0; i < RS_IPT; i++) {
+        const uint32_t lp = i * RS_THREADS + t;
+        if (lp < n_blk) {
+            const uint32_t k = skey[lp];
+            const uint32_t gpos = gdelta[(k >> shift) & mask] + lp;
+            if (keys_out) keys_out[gpos] = k;
+            vals_out[gpos] = sval[lp];
+        }
     }
 }
 
@@ -344,29 +380,61 @@ int launch_depth_order(int P, const GeomView& g, cudaStream_t s)
 }
 
 // ------------------------------------------------------------------ instance emission (in depth order)
+// Warp-cooperative: a warp takes 32 consecutive Gaussians of the depth order, and its lanes write the
+// warp's instances with consecutive lanes on consecutive output slots (coalesced), finding the owner of
+// slot t with a 5-step binary search over the lanes' offsets (shuffles).  Row-major over each
+// Gaussian's tile rect, exactly the order of duplicateWithKeys (rasterizer_impl.cu:98-109).
 __global__ void __launch_bounds__(256) emit_instances_kernel(int P, int gx, int gy, const uint32_t* __restrict__ order,
                                                              const uint32_t* __restrict__ offs, const SplatRec* __restrict__ rec,
                                                              uint32_t* __restrict__ tile_ids, uint32_t* __restrict__ gauss_ids)
 {
+    const int lane = threadIdx.x & 31;
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= P) return;
-    const uint32_t g = order[k];
-    const float4 q2 = rec[g].q2;
-    const int rad = __float_as_int(q2.z);
-    if (rad <= 0) return;
-    const float4 q0 = rec[g].q0;
-    // same rect as preprocess (auxiliary.h:46-56)
-    const int x0 = min(gx, max(0, (int)((q0.x - rad) / GSR_TILE)));
-    const int y0 = min(gy, max(0, (int)((q0.y - rad) / GSR_TILE)));
-    const int x1 = min(gx, max(0, (int)((q0.x + rad + GSR_TILE - 1) / GSR_TILE)));
-    const int y1 = min(gy, max(0, (int)((q0.y + rad + GSR_TILE - 1) / GSR_TILE)));
-    uint32_t off = offs[k];
-    for (int y = y0; y < y1; y++)
-        for (int x = x0; x < x1; x++) {
-            tile_ids[off] = (uint32_t)(y * gx + x);
-            gauss_ids[off] = g;
-            off++;
+    uint32_t g = 0, off = 0xFFFFFFFFu;
+    int x0 = 0, y0 = 0, wdt = 1, cnt = 0;
+    if (k < P) {
+        g = order[k];
+        off = offs[k];
+        const float4 q2 = rec[g].q2;
+        const int rad = __float_as_int(q2.z);
+        if (rad > 0) {
+            const float4 q0 = rec[g].q0;
+            // same rect as preprocess (auxiliary.h:46-56)
+            x0 = min(gx, max(0, (int)((q0.x - rad) / GSR_TILE)));
+            y0 = min(gy, max(0, (int)((q0.y - rad) / GSR_TILE)));
+            const int x1 = min(gx, max(0, (int)((q0.x + rad + GSR_TILE - 1) / GSR_TILE)));
+            const int y1 = min(gy, max(0, (int)((q0.y + rad + GSR_TILE - 1) / GSR_TILE)));
+            wdt = max(1, x1 - x0);
+            cnt = (x1 - x0) * (y1 - y0);
         }
+    }
+    const uint32_t off0 = __shfl_sync(0xffffffffu, off, 0);
+    if (off0 == 0xFFFFFFFFu) return;                       // whole warp beyond P
+    const uint32_t rel = off - off0;                       // lanes beyond P carry a huge value: never owners
+    // total instances of this warp = end offset of the last lane
+    const uint32_t my_end = (k < P) ? rel + (uint32_t)cnt : 0u;
+    uint32_t total = my_end;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total = max(total, __shfl_xor_sync(0xffffffffu, total, o));
+    for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t t = base + lane;
+        int lo = 0;
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) {
+            const uint32_t v = __shfl_sync(0xffffffffu, rel, lo + s);     // lo + s <= 31 always
+            if (v <= t) lo += s;
+        }
+        const uint32_t orel = __shfl_sync(0xffffffffu, rel, lo);
+        const int ox0 = __shfl_sync(0xffffffffu, x0, lo), oy0 = __shfl_sync(0xffffffffu, y0, lo);
+        const int ow = __shfl_sync(0xffffffffu, wdt, lo);
+        const uint32_t og = __shfl_sync(0xffffffffu, g, lo);
+        if (t < total) {
+            const uint32_t j = t - orel;
+            const uint32_t row = j / (uint32_t)ow, col = j - row * (uint32_t)ow;
+            tile_ids[off0 + t] = (uint32_t)((oy0 + (int)row) * gx + ox0 + (int)col);
+            gauss_ids[off0 + t] = og;
+        }
+    }
 }
 
 // ------------------------------------------------------------------ tile ranges from the sorted tile ids
