@@ -132,7 +132,14 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
         loff[i] = 0;
         if (valid) {
             const uint32_t d = (key[i] >> shift) & mask;
-            const uint32_t peers = __match_any_sync(vmask, d);
+            // lanes holding the same digit, from 8 ballots (match.any is microcoded and far slower)
+            uint32_t peers = vmask;
+#pragma unroll
+            for (int b = 0; b < 8; b++) {
+                const bool bit = (d >> b) & 1u;
+                const uint32_t bal = __ballot_sync(vmask, bit);
+                peers &= bit ? bal : ~bal;
+            }
             const uint32_t rank = __popc(peers & ((1u << lane) - 1));
             const int leader = __ffs(peers) - 1;
             uint32_t old = 0;
