@@ -130,36 +130,50 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 // ------------------------------------------------------------------------------------------ sub-tile culling
 // Each warp owns an 8x4 pixel sub-tile (2 x 4 sub-tiles per 16x16 tile).  Before a batch is blended, the
 // thread that gathered entry t decides for which of the 8 sub-tiles the entry can possibly be blended:
-// alpha >= 1/255 needs  q(d) = 0.5*(A dx^2 + C dy^2) + B dx dy <= ln(255*opacity) =: tau, and that ellipse
-// lies inside the axis-aligned box |dx| <= sqrt(2 tau C / det), |dy| <= sqrt(2 tau A / det), det = AC - B^2.
-// A sub-tile whose pixel-centre rectangle misses that box cannot contain a pixel the reference would blend,
-// so dropping the entry for that warp leaves every result bit-identical.  tau is inflated for the rounding
-// of the per-pixel fp32 power (error <= ~1e-6 * q * AC/det), of logf/sqrtf/division, and the box by 1e-3 px;
+// alpha >= 1/255 needs  q(d) = 0.5*(A dx^2 + C dy^2) + B dx dy <= ln(255*opacity) =: tau.  The test is exact up
+// to rounding: q is a convex quadratic, so its minimum over the sub-tile's pixel-centre rectangle is attained
+// either on the vertical edge nearest the centre (u = cu) at the clamped 1-D minimiser v* = -B cu / C, or on the
+// nearest horizontal edge (v = cv) at u* = -B cv / A (both candidates are points of the rectangle, so taking
+// the smaller never under-estimates; when the centre is inside both are 0).  A sub-tile whose minimum exceeds
+// tau cannot contain a pixel the reference would blend, so dropping the entry for that warp leaves every
+// result bit-identical.  tau is inflated for the rounding of the per-pixel fp32 power (error <= ~1e-6 * q *
+// AC/det), of the approximate log / reciprocals and of this evaluation; the rectangle grows by 1e-3 px;
 // ill-conditioned conics (AC/det > 1e4) are never culled.
+__device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
 __device__ __forceinline__ uint32_t subtile_mask(const float4 a, const float4 c, float X0, float Y0)
 {
     const float o = c.y;
     if (o < 1.0f / 255.0f) return 0u;                 // alpha = min(0.99, o*exp(p<=0)) <= o < 1/255 everywhere
     const float A = a.z, B = a.w, C = c.x;
     const float det = A * C - B * B;
-    const float kappa = A * C / det;
-    if (!(kappa <= 1.0e4f) || !(det > 0.f)) return 0xFFu;
-    float tau = (__logf(255.0f * o) + 1.0e-3f) * (1.0f + 2.0e-6f * kappa) * 1.0002f;
-    const float inv = 1.0f / det;
-    const float hx = sqrtf(2.0f * tau * C * inv) * 1.0001f + 1.0e-3f;
-    const float hy = sqrtf(2.0f * tau * A * inv) * 1.0001f + 1.0e-3f;
-    const float xlo = a.x - hx, xhi = a.x + hx, ylo = a.y - hy, yhi = a.y + hy;
-    uint32_t xm = 0, ym = 0;
-    if (xhi >= X0 && xlo <= X0 + 7.0f) xm |= 1u;
-    if (xhi >= X0 + 8.0f && xlo <= X0 + 15.0f) xm |= 2u;
+    const float kappa = A * C * rcp_fast(det);
+    if (!(kappa <= 1.0e4f) || !(det > 0.f) || !(A > 0.f) || !(C > 0.f)) return 0xFFu;
+    const float tau = (__logf(255.0f * o) + 1.0e-3f) * (1.0f + 6.0e-6f * kappa) * 1.0004f;
+    const float nBC = -B * rcp_fast(C), nBA = -B * rcp_fast(A);
+    const float hA = 0.5f * A, hC = 0.5f * C;
+    float u0[2], u1[2], vst[2], qa[2], bu[2];
 #pragma unroll
-    for (int r = 0; r < 4; r++)
-        if (yhi >= Y0 + 4.0f * r && ylo <= Y0 + 4.0f * r + 3.0f) ym |= 1u << r;
-    // warp w: sx = w & 1, sy = w >> 1
+    for (int sx = 0; sx < 2; sx++) {
+        u0[sx] = (X0 + 8.0f * sx - 1.0e-3f) - a.x; u1[sx] = u0[sx] + 7.002f;
+        const float cu = fminf(fmaxf(0.0f, u0[sx]), u1[sx]);
+        vst[sx] = nBC * cu; qa[sx] = hA * cu * cu; bu[sx] = B * cu;
+    }
     uint32_t m = 0;
 #pragma unroll
-    for (int w = 0; w < 8; w++)
-        if (((xm >> (w & 1)) & 1u) && ((ym >> (w >> 1)) & 1u)) m |= 1u << w;
+    for (int sy = 0; sy < 4; sy++) {
+        const float v0 = (Y0 + 4.0f * sy - 1.0e-3f) - a.y, v1 = v0 + 3.002f;
+        const float cv = fminf(fmaxf(0.0f, v0), v1);
+        const float ust = nBA * cv, qc = hC * cv * cv, bv = B * cv;
+#pragma unroll
+        for (int sx = 0; sx < 2; sx++) {
+            const float vs = fminf(fmaxf(vst[sx], v0), v1);
+            const float q1 = fmaf(vs, fmaf(hC, vs, bu[sx]), qa[sx]);
+            const float us = fminf(fmaxf(ust, u0[sx]), u1[sx]);
+            const float q2 = fmaf(us, fmaf(hA, us, bv), qc);
+            if (fminf(q1, q2) <= tau) m |= 1u << (sy * 2 + sx);       // warp w: sx = w & 1, sy = w >> 1
+        }
+    }
     return m;
 }
 
@@ -254,10 +268,109 @@ blend_fwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     }
 }
 
+// ------------------------------------------------------------------------------------------ statistics (debug hook)
+// Counts what the culled forward does, to size the kernels' work (scripts/exp_blend.py): not on the product path.
+//  0 entries staged (until the tile is done)   1 (warp, entry) pairs evaluated   2 lanes not done at evaluation
+//  3 lanes with power <= 0   4 lanes with alpha >= 1/255   5 lanes blended   6 (warp, entry) pairs with >= 1 lane passing alpha
+//  7 (half-warp 8x2, entry) pairs with >= 1 lane passing alpha   8 (quarter 4x2.. lanes 8-groups) likewise   9 batches
+__device__ unsigned long long g_blend_stats[16];
+
+__global__ void __launch_bounds__(BL_THREADS)
+blend_stats_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec, int W, int H)
+{
+    __shared__ BlendStage stage;
+    __shared__ uint32_t bits[8][8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(blockIdx.y * GSR_TILE);
+    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    bool done = !inside;
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
+    float T = 1.0f;
+    unsigned long long c[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < rounds; i++) {
+        uint32_t n44[2] = {0, 0}, n82[2] = {0, 0}, n42[4] = {0, 0, 0, 0};
+        const int num_done = __syncthreads_count(done);
+        if (num_done == BL_THREADS) break;
+        const int p = i * BL_THREADS + (int)threadIdx.x;
+        uint32_t m = 0;
+        if (p < total) {
+            const SplatRec r = rec[vals[range.x + p]];
+            stage.q0[threadIdx.x] = r.q0; stage.q1[threadIdx.x] = r.q1; stage.b[threadIdx.x] = r.q2.x;
+            m = subtile_mask(r.q0, r.q1, X0, Y0);
+            c[0]++;
+        }
+        if (threadIdx.x == 0) c[9]++;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
+            if (lane == k) bits[k][wid] = bk;
+        }
+        __syncthreads();
+        for (int cch = 0; cch < 8; cch++) {
+            uint32_t mm = bits[wid][cch];
+            if (__all_sync(0xffffffffu, done)) mm = 0;
+            while (mm) {
+                const int j = cch * 32 + __ffs(mm) - 1;
+                mm &= mm - 1;
+                if (__all_sync(0xffffffffu, done)) break;
+                if (lane == 0) c[1]++;
+                bool pass = false;
+                if (!done) {
+                    c[2]++;
+                    const float4 a = stage.q0[j];
+                    const float4 q = stage.q1[j];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = -0.5f * (a.z * dx * dx + q.x * dy * dy) - a.w * dx * dy;
+                    if (!(power > 0.0f)) {
+                        c[3]++;
+                        const float alpha = fminf(0.99f, q.y * expf(power));
+                        if (!(alpha < 1.0f / 255.0f)) {
+                            c[4]++;
+                            pass = true;
+                            const float test_T = T * (1 - alpha);
+                            if (test_T < 0.0001f) done = true;
+                            else { c[5]++; T = test_T; }
+                        }
+                    }
+                }
+                const uint32_t pb = __ballot_sync(0xffffffffu, pass);
+                if (lane == 0) {
+                    c[6] += pb != 0;
+                    c[7] += ((pb & 0xFFFFu) != 0) + ((pb >> 16) != 0);
+                    c[8] += ((pb & 0xFFu) != 0) + (((pb >> 8) & 0xFFu) != 0) + (((pb >> 16) & 0xFFu) != 0) + ((pb >> 24) != 0);
+                }
+                n44[0] += (pb & 0x0F0F0F0Fu) != 0; n44[1] += (pb & 0xF0F0F0F0u) != 0;
+                n82[0] += (pb & 0x0000FFFFu) != 0; n82[1] += (pb & 0xFFFF0000u) != 0;
+                n42[0] += (pb & 0x00000F0Fu) != 0; n42[1] += (pb & 0x0000F0F0u) != 0;
+                n42[2] += (pb & 0x0F0F0000u) != 0; n42[3] += (pb & 0xF0F00000u) != 0;
+            }
+        }
+        if (lane == 0) {
+            c[10] += max(n44[0], n44[1]); c[11] += max(n82[0], n82[1]);
+            c[12] += max(max(n42[0], n42[1]), max(n42[2], n42[3]));
+            c[13] += n44[0] + n44[1];
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < 14; k++) {
+        unsigned long long v = c[k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0 && v) atomicAdd(&g_blend_stats[k], v);
+    }
+}
+
 int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                          float* out_color, cudaStream_t s)
 {
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
+    if (env_int("GSR_BLEND_STATS", 0) == 1)
+        GSR_LAUNCH(blend_stats_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H);
     if (env_int("GSR_BLEND", 2) == 1)
         GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
     else
@@ -536,3 +649,14 @@ int launch_blend_backward(int W, int H, const float* bg, const GeomView& g, cons
 }
 
 }  // namespace gsr
+
+// debug hook (not declared in include/gsr.h): reads and optionally clears the counters of blend_stats_kernel
+extern "C" int gsr_debug_blend_stats(unsigned long long* out16, int reset)
+{
+    if (out16 && cudaMemcpyFromSymbol(out16, gsr::g_blend_stats, sizeof(unsigned long long) * 16) != cudaSuccess) return GSR_ECUDA;
+    if (reset) {
+        unsigned long long z[16] = {0};
+        if (cudaMemcpyToSymbol(gsr::g_blend_stats, z, sizeof z) != cudaSuccess) return GSR_ECUDA;
+    }
+    return GSR_OK;
+}
