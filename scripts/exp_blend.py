@@ -46,7 +46,8 @@ def main():
     lib.gsr_debug_blend_stats(st, 1)
     names = ["entries_staged", "warp_entries", "lanes_active", "lanes_power_ok", "lanes_alpha_ok", "lanes_blended",
              "warp_entries_exact", "half_entries_exact", "quarter_entries_exact", "batches",
-             "iters_two_4x4", "iters_two_8x2", "iters_four_4x2", "block44_entries_exact"]
+             "iters_two_4x4", "iters_two_8x2", "iters_four_4x2", "block44_entries_exact",
+             "sum_batch_max_warp", "sum_tile_max_warp"]
     print("stats:", {n: int(st[i]) for i, n in enumerate(names)}, flush=True)
 
     base = None
@@ -65,11 +66,11 @@ def main():
                 bool(torch.equal(img, base[0])), float((img - base[0]).abs().max()),
                 bool(np.array_equal(ex["n_contrib"], base[1]["n_contrib"])), bool(np.array_equal(ex["final_T"], base[1]["final_T"])))
         print(msg, flush=True)
-    os.environ["GSR_BLEND"] = "2"
+    os.environ["GSR_BLEND"] = "0"
     a, f = util.raw_forward(C, sc, cam, bg, spec.D)
     gbase = None
     for v in bvars:
-        os.environ["GSR_BLEND_BWD"] = str(v)
+        os.environ["GSR_BLEND"] = str(v)
         g = [x.clone() for x in util.raw_backward(C, a, f, go)]
         t = stage_ms(lambda: util.raw_backward(C, a, f, go))
         msg = "bwd variant %d: blend_backward %.4f ms  preprocess_backward %.4f ms" % (v, t["blend_backward"], t["preprocess_backward"])

@@ -177,10 +177,61 @@ __device__ __forceinline__ uint32_t subtile_mask(const float4 a, const float4 c,
     return m;
 }
 
-__global__ void __launch_bounds__(BL_THREADS)
-blend_fwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
-                      int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                      float* __restrict__ out)
+// ------------------------------------------------------------------------------------------ forward with sub-tile culling
+// Staging as in blend_fwd_kernel plus the sub-tile masks; the per-warp entry loop takes up to UMAX surviving entries per trip:
+// their alphas (independent of the pixel's running state) are evaluated side by side, which doubles the
+// instruction-level parallelism of the latency chain LDS -> power -> expf, halves the loop overhead, and the
+// sequential part (T test, colour accumulation) is predicated instead of branched.  Arithmetic per pixel is
+// unchanged (same expressions, same order), so every output is bit-identical to variants 1 and 2.
+__device__ __forceinline__ float entry_alpha(const float4 a, const float4 c, float pxf, float pyf, bool& ok)
+{
+    const float dx = a.x - pxf, dy = a.y - pyf;
+    const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
+    const float alpha = fminf(0.99f, c.y * expf(power));
+    ok = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+    return alpha;
+}
+
+__device__ __forceinline__ void blend_step(float alpha, bool ok, float r, float g, float b, uint32_t pos, bool& done, float& T,
+                                           float& C0, float& C1, float& C2, uint32_t& last)
+{
+    const float test_T = T * (1 - alpha);
+    const bool v = ok && !done;
+    const bool stop = v && (test_T < 0.0001f);
+    done = done || stop;
+    if (v && !stop) {
+        C0 += r * alpha * T;
+        C1 += g * alpha * T;
+        C2 += b * alpha * T;
+        T = test_T;
+        last = pos;
+    }
+}
+
+// U surviving entries of chunk `jb` (taken from the low set bits of m) in one trip
+template <int U>
+__device__ __forceinline__ void blend_trip(const BlendStage& st, uint32_t& m, int jb, uint32_t pos_base, float pxf, float pyf,
+                                           bool& done, float& T, float& C0, float& C1, float& C2, uint32_t& last)
+{
+    int j[U];
+    float4 a[U], c[U];
+    float b[U], al[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) { j[u] = jb + __ffs(m) - 1; m &= m - 1; }
+#pragma unroll
+    for (int u = 0; u < U; u++) { a[u] = st.q0[j[u]]; c[u] = st.q1[j[u]]; b[u] = st.b[j[u]]; }
+#pragma unroll
+    for (int u = 0; u < U; u++) al[u] = entry_alpha(a[u], c[u], pxf, pyf, ok[u]);
+#pragma unroll
+    for (int u = 0; u < U; u++) blend_step(al[u], ok[u], c[u].z, c[u].w, b[u], pos_base + j[u], done, T, C0, C1, C2, last);
+}
+
+template <int UMAX, int MINB>
+__global__ void __launch_bounds__(BL_THREADS, MINB)
+blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                    int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                    float* __restrict__ out)
 {
     __shared__ BlendStage stage[2];
     __shared__ uint32_t bits[2][8][8];     // [buffer][consumer warp][chunk of 32 entries]
@@ -220,7 +271,6 @@ blend_fwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 if (lane == k) bits[buf][k][wid] = bk;
             }
         }
-        // barrier: batch i (records + masks) visible to all, everyone has left batch i-1
         const int num_done = __syncthreads_count(done);
         if (num_done == BL_THREADS) break;
         {
@@ -229,30 +279,21 @@ blend_fwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const int p2 = p1 + BL_THREADS;
             if (p2 < total) id_next = vals[range.x + p2];
         }
-        if (__all_sync(0xffffffffu, done)) continue;       // this warp's pixels are finished; keep helping with the gathers
+        if (__all_sync(0xffffffffu, done)) continue;
         const BlendStage& st = stage[buf];
+        const uint32_t pos_base = (uint32_t)(i * BL_THREADS) + 1u;
 #pragma unroll 1
         for (int cch = 0; cch < 8; cch++) {
             uint32_t m = bits[buf][wid][cch];
-            while (m) {
-                const int j = cch * 32 + __ffs(m) - 1;
-                m &= m - 1;
-                if (done) continue;
-                const float4 a = st.q0[j];
-                const float4 c = st.q1[j];
-                const float dx = a.x - pxf, dy = a.y - pyf;
-                const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, c.y * expf(power));
-                if (alpha < 1.0f / 255.0f) continue;
-                const float test_T = T * (1 - alpha);
-                if (test_T < 0.0001f) { done = true; continue; }
-                C0 += c.z * alpha * T;
-                C1 += c.w * alpha * T;
-                C2 += st.b[j] * alpha * T;
-                T = test_T;
-                last_contributor = (uint32_t)(i * BL_THREADS + j + 1);
-            }
+            if (m == 0) continue;
+            const int jb = cch * 32;
+            do {
+                const int n = __popc(m);
+                if (UMAX >= 4 && n >= 4) blend_trip<4>(st, m, jb, pos_base, pxf, pyf, done, T, C0, C1, C2, last_contributor);
+                else if (UMAX >= 3 && n == 3) blend_trip<3>(st, m, jb, pos_base, pxf, pyf, done, T, C0, C1, C2, last_contributor);
+                else if (UMAX >= 2 && n >= 2) blend_trip<2>(st, m, jb, pos_base, pxf, pyf, done, T, C0, C1, C2, last_contributor);
+                else blend_trip<1>(st, m, jb, pos_base, pxf, pyf, done, T, C0, C1, C2, last_contributor);
+            } while (m);
             if (__all_sync(0xffffffffu, done)) break;
         }
     }
@@ -291,9 +332,11 @@ blend_stats_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
     const int total = (int)(range.y - range.x);
     const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
     float T = 1.0f;
-    unsigned long long c[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned long long c[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    __shared__ uint32_t wcnt[8];
+    uint32_t tile_cnt = 0;
     for (int i = 0; i < rounds; i++) {
-        uint32_t n44[2] = {0, 0}, n82[2] = {0, 0}, n42[4] = {0, 0, 0, 0};
+        uint32_t n44[2] = {0, 0}, n82[2] = {0, 0}, n42[4] = {0, 0, 0, 0}, nw = 0;
         const int num_done = __syncthreads_count(done);
         if (num_done == BL_THREADS) break;
         const int p = i * BL_THREADS + (int)threadIdx.x;
@@ -319,6 +362,7 @@ blend_stats_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
                 mm &= mm - 1;
                 if (__all_sync(0xffffffffu, done)) break;
                 if (lane == 0) c[1]++;
+                nw++;
                 bool pass = false;
                 if (!done) {
                     c[2]++;
@@ -354,11 +398,25 @@ blend_stats_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
             c[10] += max(n44[0], n44[1]); c[11] += max(n82[0], n82[1]);
             c[12] += max(max(n42[0], n42[1]), max(n42[2], n42[3]));
             c[13] += n44[0] + n44[1];
+            wcnt[wid] = nw;
         }
+        tile_cnt += nw;
         __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t mx = 0;
+            for (int k = 0; k < 8; k++) mx = max(mx, wcnt[k]);
+            c[14] += mx;                      // per-batch critical path (slowest warp)
+        }
+    }
+    if (lane == 0) wcnt[wid] = tile_cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t mx = 0;
+        for (int k = 0; k < 8; k++) mx = max(mx, wcnt[k]);
+        c[15] += mx;                          // per-tile critical path if warps never waited for each other
     }
 #pragma unroll
-    for (int k = 0; k < 14; k++) {
+    for (int k = 0; k < 16; k++) {
         unsigned long long v = c[k];
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
         if (lane == 0 && v) atomicAdd(&g_blend_stats[k], v);
@@ -371,10 +429,10 @@ int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
     if (env_int("GSR_BLEND_STATS", 0) == 1)
         GSR_LAUNCH(blend_stats_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H);
-    if (env_int("GSR_BLEND", 2) == 1)
+    if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
     else
-        GSR_LAUNCH(blend_fwd_cull_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+        GSR_LAUNCH((blend_fwd_v3_kernel<4, 4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
                    out_color);
     return GSR_OK;
 }
@@ -522,13 +580,51 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     }
 }
 
-// Backward with the same sub-tile culling as the forward (8x4 pixels per warp).  The list is truncated to the
-// largest n_contrib of the tile, a warp additionally ignores entries at or beyond its own largest n_contrib,
-// and only (warp, entry) pairs that survive both filters are evaluated, reduced and committed.
-__global__ void __launch_bounds__(BL_THREADS)
-blend_bwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
-                      int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
-                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, float* __restrict__ accum)
+// ------------------------------------------------------------------------------------------ backward with sub-tile culling
+// Same tiles / sub-tiles / culling as the forward; the list is truncated to the largest n_contrib of the tile, a warp
+// additionally ignores entries at or beyond its own largest n_contrib.
+// Two surviving entries per trip: both alphas are evaluated side by side (instruction-level parallelism on the
+// LDS -> power -> expf chain), the per-pixel state update stays sequential, and the two entries' 8 + 8 values
+// go through ONE 16-value transposing butterfly (16 + 5 shuffles for two entries instead of 2 x 14).
+struct PixState {
+    float T, last_alpha, acc0, acc1, acc2, lc0, lc1, lc2;
+};
+struct EntryHead {
+    float dx, dy, araw, alpha;
+    bool live;
+};
+__device__ __forceinline__ EntryHead bwd_head(const float4 a, const float4 c, float pxf, float pyf, int pos, int last_contributor)
+{
+    EntryHead h;
+    h.dx = a.x - pxf; h.dy = a.y - pyf;
+    const float power = -0.5f * (a.z * h.dx * h.dx + c.x * h.dy * h.dy) - a.w * h.dx * h.dy;
+    h.araw = c.y * expf(power);
+    h.alpha = fminf(0.99f, h.araw);
+    h.live = pos < last_contributor && !(power > 0.0f) && !(h.alpha < 1.0f / 255.0f);
+    return h;
+}
+
+// lane L ends up with the warp total of v[((L>>4)&1)*8 + ((L>>3)&1)*4 + ((L>>2)&1)*2 + ((L>>1)&1)]
+__device__ __forceinline__ float butterfly16(const float* v, int lane)
+{
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+    float a[8], c[4], d[2];
+#pragma unroll
+    for (int k = 0; k < 8; k++) a[k] = (b4 ? v[k + 8] : v[k]) + __shfl_xor_sync(0xffffffffu, b4 ? v[k] : v[k + 8], 16);
+#pragma unroll
+    for (int k = 0; k < 4; k++) c[k] = (b3 ? a[k + 4] : a[k]) + __shfl_xor_sync(0xffffffffu, b3 ? a[k] : a[k + 4], 8);
+#pragma unroll
+    for (int k = 0; k < 2; k++) d[k] = (b2 ? c[k + 2] : c[k]) + __shfl_xor_sync(0xffffffffu, b2 ? c[k] : c[k + 2], 4);
+    float e = (b1 ? d[1] : d[0]) + __shfl_xor_sync(0xffffffffu, b1 ? d[0] : d[1], 2);
+    e += __shfl_xor_sync(0xffffffffu, e, 1);
+    return e;
+}
+
+template <int MINB>
+__global__ void __launch_bounds__(BL_THREADS, MINB)
+blend_bwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                    int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
+                    const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, float* __restrict__ accum)
 {
     __shared__ BlendStageBwd stage[2];
     __shared__ uint32_t bits[2][8][8];
@@ -558,7 +654,7 @@ blend_bwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
     if (lane == 0) s_warp_last[wid] = warp_last;
     __syncthreads();
-    int total = 0;                                   // truncated list length = largest n_contrib of the tile
+    int total = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) total = max(total, s_warp_last[k]);
     total = min(total, (int)(range.y - range.x));
@@ -566,8 +662,8 @@ blend_bwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const uint32_t list_end = range.x + total;
 
     const int col8 = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    const int col16 = (lane >> 1) & 7, ent16 = lane >> 4;
 
-    // back to front: slot t of batch i holds list position total-1-(i*256+t)
     auto gather = [&](BlendStageBwd& st, int batch) {
         const int p = batch * BL_THREADS + threadIdx.x;
         if (p < total) {
@@ -603,33 +699,56 @@ blend_bwd_cull_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         __syncthreads();
         if (i + 1 < rounds) gather(stage[buf ^ 1], i + 1);
         const BlendStageBwd& st = stage[buf];
+        const int pos_top = total - 1 - i * BL_THREADS;
 #pragma unroll 1
         for (int cch = 0; cch < 8; cch++) {
             uint32_t m = bits[buf][wid][cch];
+            const int jb = cch * 32;
             while (m) {
-                const int j = cch * 32 + __ffs(m) - 1;
+                const int j0 = jb + __ffs(m) - 1;
                 m &= m - 1;
-                const int pos = total - 1 - (i * BL_THREADS + j);
-                const float4 a = st.q0[j];
-                const float4 c = st.q1[j];
-                const float dx = a.x - pxf, dy = a.y - pyf;
-                const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
-                const float araw = c.y * expf(power);
-                const float alpha = fminf(0.99f, araw);
-                const bool live = pos < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                if (!__any_sync(0xffffffffu, live)) continue;
-
-                float g0 = 0.f, g1 = 0.f, g2 = 0.f, gmx = 0.f, gmy = 0.f, gcx = 0.f, gcy = 0.f, gcw = 0.f, gop = 0.f;
-                if (live) {
-                    bwd_live_math(alpha, araw, dx, dy, c.z, c.w, st.b[j], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
-                                  lc0, lc1, lc2, g0, g1, g2, gmx, gmy, gcx, gcy, gcw, gop);
-                }
-                const float r8 = butterfly8(g0, g1, g2, gmx, gmy, gcx, gcy, gcw, lane);
+                if (m) {
+                    const int j1 = jb + __ffs(m) - 1;
+                    m &= m - 1;
+                    const float4 a0 = st.q0[j0], c0 = st.q1[j0], a1 = st.q0[j1], c1 = st.q1[j1];
+                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
+                    const EntryHead h1 = bwd_head(a1, c1, pxf, pyf, pos_top - j1, last_contributor);
+                    const bool any0 = __any_sync(0xffffffffu, h0.live), any1 = __any_sync(0xffffffffu, h1.live);
+                    if (!any0 && !any1) continue;
+                    float v[16], gop0 = 0.f, gop1 = 0.f;
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) gop += __shfl_xor_sync(0xffffffffu, gop, o);
-                float* row = accum + (size_t)st.id[j] * 12;
-                if ((lane & 3) == 0) atomicAdd(row + col8, r8);
-                else if (lane == 1) atomicAdd(row + 8, gop);
+                    for (int k = 0; k < 16; k++) v[k] = 0.f;
+                    if (h0.live)
+                        bwd_live_math(h0.alpha, h0.araw, h0.dx, h0.dy, c0.z, c0.w, st.b[j0], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1,
+                                      acc2, lc0, lc1, lc2, v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], gop0);
+                    if (h1.live)
+                        bwd_live_math(h1.alpha, h1.araw, h1.dx, h1.dy, c1.z, c1.w, st.b[j1], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1,
+                                      acc2, lc0, lc1, lc2, v[8], v[9], v[10], v[11], v[12], v[13], v[14], v[15], gop1);
+                    const float e = butterfly16(v, lane);
+                    float g = (ent16 ? gop1 : gop0) + __shfl_xor_sync(0xffffffffu, ent16 ? gop0 : gop1, 16);
+#pragma unroll
+                    for (int o = 8; o > 0; o >>= 1) g += __shfl_xor_sync(0xffffffffu, g, o);
+                    const bool mine = ent16 ? any1 : any0;
+                    float* row = accum + (size_t)st.id[ent16 ? j1 : j0] * 12;
+                    if (mine) {
+                        if ((lane & 1) == 0) atomicAdd(row + col16, e);
+                        else if ((lane & 15) == 1) atomicAdd(row + 8, g);
+                    }
+                } else {
+                    const float4 a0 = st.q0[j0], c0 = st.q1[j0];
+                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
+                    if (!__any_sync(0xffffffffu, h0.live)) continue;
+                    float g0 = 0.f, g1 = 0.f, g2 = 0.f, gmx = 0.f, gmy = 0.f, gcx = 0.f, gcy = 0.f, gcw = 0.f, gop = 0.f;
+                    if (h0.live)
+                        bwd_live_math(h0.alpha, h0.araw, h0.dx, h0.dy, c0.z, c0.w, st.b[j0], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1,
+                                      acc2, lc0, lc1, lc2, g0, g1, g2, gmx, gmy, gcx, gcy, gcw, gop);
+                    const float r8 = butterfly8(g0, g1, g2, gmx, gmy, gcx, gcy, gcw, lane);
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) gop += __shfl_xor_sync(0xffffffffu, gop, o);
+                    float* row = accum + (size_t)st.id[j0] * 12;
+                    if ((lane & 3) == 0) atomicAdd(row + col8, r8);
+                    else if (lane == 1) atomicAdd(row + 8, gop);
+                }
             }
         }
     }
@@ -639,11 +758,11 @@ int launch_blend_backward(int W, int H, const float* bg, const GeomView& g, cons
                           const float* dL_dpix, float* accum, cudaStream_t s)
 {
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
-    if (env_int("GSR_BLEND", 2) == 1)
+    if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
                    accum);
     else
-        GSR_LAUNCH(blend_bwd_cull_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+        GSR_LAUNCH((blend_bwd_v3_kernel<4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
                    dL_dpix, accum);
     return GSR_OK;
 }
