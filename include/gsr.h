@@ -40,7 +40,7 @@ extern "C" {
 #define GSR_ECHANNELS  -4   /* neither shs nor colors_precomp given (reference: "For non-RGB, provide precomputed Gaussian colors!") */
 #define GSR_ECOV       -5   /* neither (scales, rotations) nor cov3D_precomp given */
 #define GSR_EBLOB      -6   /* a state blob handed to backward does not carry our magic / sizes */
-#define GSR_ETOOBIG    -7   /* image has more than 65535 tiles per axis or R >= 2^31 */
+#define GSR_ETOOBIG    -7   /* image has more than 65535 tiles per axis or R >= 2^30 */
 
 /* CUDA stream handle (== cudaStream_t) without dragging in cuda headers. */
 typedef struct CUstream_st* gsr_stream_t;

@@ -30,6 +30,8 @@ int env_int(const char* name, int dflt)
 }
 
 // ------------------------------------------------------------------ per-stage event timing
+static uint32_t* g_R_host = nullptr;        // pinned landing slot of the R read-back
+static cudaEvent_t g_R_event = nullptr;
 static bool g_timing = false;
 struct Pending { int stage; cudaEvent_t a, b; };
 static std::vector<Pending> g_pending;
@@ -62,7 +64,7 @@ void stage_end(int stage, cudaStream_t s)
 static size_t geom_fixed_bytes(int P)
 {
     const size_t Pp = (size_t)(P > 0 ? P : 1);
-    return sizeof(BlobHeader) + align_up(Pp * sizeof(SplatRec)) + align_up(Pp) + align_up(Pp * 4) + align_up((Pp + 1) * 4);
+    return sizeof(BlobHeader) + align_up(Pp * sizeof(SplatRec)) + align_up(Pp) + align_up(Pp * 4);
 }
 GeomView geom_view(void* blob, int P)
 {
@@ -73,7 +75,6 @@ GeomView geom_view(void* blob, int P)
     g.rec = (SplatRec*)p; p += align_up(Pp * sizeof(SplatRec));
     g.clamped = (uint8_t*)p; p += align_up(Pp);
     g.order = (uint32_t*)p; p += align_up(Pp * 4);
-    g.offs = (uint32_t*)p; p += align_up((Pp + 1) * 4);
     g.scratch = (uint32_t*)p;
     g.scratch_bytes = geom_scratch_bytes(P);
     return g;
@@ -98,7 +99,8 @@ ImgView img_view(void* blob, int W, int H)
     v.hdr = (BlobHeader*)p; p += sizeof(BlobHeader);
     v.ranges = (uint2*)p; p += align_up((tiles ? tiles : 1) * sizeof(uint2));
     v.final_T = (float*)p; p += align_up((N ? N : 1) * 4);
-    v.n_contrib = (uint32_t*)p;
+    v.n_contrib = (uint32_t*)p; p += align_up((N ? N : 1) * 4);
+    v.tile_diff = (int*)p;
     return v;
 }
 
@@ -134,7 +136,9 @@ size_t gsr_img_bytes(int W, int H)
 {
     const size_t tiles = (size_t)((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
     const size_t N = (size_t)W * H;
-    return sizeof(BlobHeader) + align_up((tiles ? tiles : 1) * sizeof(uint2)) + 2 * align_up((N ? N : 1) * 4);
+    const size_t gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
+    return sizeof(BlobHeader) + align_up((tiles ? tiles : 1) * sizeof(uint2)) + 2 * align_up((N ? N : 1) * 4) +
+           align_up((gx + 1) * (gy + 1) * sizeof(int));
 }
 size_t gsr_binning_bytes(int P, int R, int W, int H)
 {
@@ -171,22 +175,34 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     GeomView g = geom_view(gblob, a->P);
     ImgView im = img_view(iblob, a->W, a->H);
     GSR_CUDA(cudaMemsetAsync(g.hdr, 0, sizeof(BlobHeader), s));
+    const GeomScratch sc = carve_geom_scratch(g.scratch, a->P);
+    GSR_CUDA(cudaMemsetAsync(sc.ctl, 0, sc.ctl_words * 4, s));       // counters, histograms, look-back words
+    GSR_CUDA(cudaMemsetAsync(im.tile_diff, 0, sizeof(int) * (size_t)(gx + 1) * (gy + 1), s));
 
     int rc;
     stage_begin(0, s);
     if ((rc = launch_preprocess(*a, g, s))) return rc;
     stage_end(0, s);
     GSR_STAGE(a->debug, s, "preprocess");
+
+    // R (sum of tiles touched) is accumulated by preprocess: start its read-back now and wait for it only after
+    // the depth sort has been queued, so the host's launch work overlaps the device
+    if (!g_R_host) {
+        GSR_CUDA(cudaHostAlloc((void**)&g_R_host, 64, cudaHostAllocDefault));
+        GSR_CUDA(cudaEventCreateWithFlags(&g_R_event, cudaEventDisableTiming));
+    }
+    GSR_CUDA(cudaMemcpyAsync(g_R_host, sc.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    GSR_CUDA(cudaEventRecord(g_R_event, s));
+
     stage_begin(1, s);
-    if ((rc = launch_depth_order(a->P, g, s))) return rc;
+    if ((rc = launch_depth_order(a->P, a->W, a->H, g, im, s))) return rc;
     stage_end(1, s);
     GSR_STAGE(a->debug, s, "depth_order");
 
-    // the binning blob is sized from R: one blocking read-back, like rasterizer_impl.cu:280-281
-    uint32_t R_host = 0;
-    GSR_CUDA(cudaMemcpyAsync(&R_host, g.offs + a->P, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-    GSR_CUDA(cudaStreamSynchronize(s));
-    if (R_host >= 0x80000000u) return GSR_ETOOBIG;
+    // the binning blob is sized from R: the one blocking wait of the forward, like rasterizer_impl.cu:280-281
+    GSR_CUDA(cudaEventSynchronize(g_R_event));
+    const uint32_t R_host = *g_R_host;
+    if (R_host >= 0x40000000u) return GSR_ETOOBIG;
     const int R = (int)R_host;
     *num_rendered = R;
 
@@ -208,7 +224,7 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     GSR_STAGE(a->debug, s, "blend_forward");
     if (a->debug && a->prefiltered) {
         int err = 0;
-        GSR_CUDA(cudaMemcpy(&err, &g.hdr->pad[0], sizeof(int), cudaMemcpyDeviceToHost));
+        GSR_CUDA(cudaMemcpy(&err, sc.counters + 8, sizeof(int), cudaMemcpyDeviceToHost));
         if (err) return GSR_EINVAL;
     }
     return GSR_OK;

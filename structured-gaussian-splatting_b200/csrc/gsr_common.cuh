@@ -71,8 +71,7 @@ struct GeomView {              // views into the geometry blob
     SplatRec*   rec;           // [P]
     uint8_t*    clamped;       // [P] bit c set <=> SH colour channel c was clamped to 0
     uint32_t*   order;         // [P] Gaussian ids sorted by (depth bits, id); culled last
-    uint32_t*   offs;          // [P+1] exclusive scan of tiles_touched in `order` sequence; offs[P] = R
-    uint32_t*   scratch;       // sort / scan scratch, only live inside forward
+    uint32_t*   scratch;       // sort / scan scratch (GeomScratch), only live inside forward
     size_t      scratch_bytes;
 };
 struct BinView {
@@ -86,8 +85,23 @@ struct ImgView {
     uint2*      ranges;        // [tiles]
     float*      final_T;       // [W*H]
     uint32_t*   n_contrib;     // [W*H]
+    int*        tile_diff;     // [(gy+1)*(gx+1)] 2-D difference array of the tile rects (zeroed before preprocess), only live inside forward
 };
 
+// layout of GeomView::scratch (sort.cu).  The control block [ctl, ctl + ctl_words) must be zero before preprocess runs.
+struct GeomScratch {
+    uint32_t* ctl;
+    size_t    ctl_words;
+    uint32_t* counters;        // [64]: 0 = R (sum of tiles touched, accumulated by preprocess), 1 = emit ticket, 8 = prefiltered-violated flag
+    uint32_t* tile_hist;       // [4][256] digit histograms of the tile-split passes (counted by emit_instances_kernel)
+    unsigned long long* emit_status;   // [ceil(P/256)] look-back words of the fused tile-count scan
+    uint32_t* radix_ctl;       // digit histograms, tickets and look-back words of the four depth passes
+    uint32_t* depthkey;        // [P] float bits of the view-space depth, 0xFFFFFFFF for culled Gaussians (written by preprocess)
+    ushort4*  rect;            // [P] tile rect (x0, y0, x1, y1) of every Gaussian, all zero when culled (written by preprocess)
+    uint32_t *K0, *K1, *V0;    // [P] ping-pong buffers of the depth sort
+    size_t    total_words;
+};
+GeomScratch carve_geom_scratch(uint32_t* scratch, int P);
 size_t geom_scratch_bytes(int P);
 size_t bin_scratch_bytes(long long R);
 GeomView geom_view(void* blob, int P);
@@ -140,18 +154,19 @@ int launch_mark_visible(int P, const float* means, const float* view, uint8_t* p
 int launch_preprocess_backward(const GsrBwdArgs& a, const GeomView& g, const float* accum, cudaStream_t s);
 
 // sort.cu
-// sorts Gaussian ids by depth bits (stable) into g.order and scans tile counts into g.offs
-int launch_depth_order(int P, const GeomView& g, cudaStream_t s);
+// sorts Gaussian ids by depth bits (stable) into g.order; counts instances per tile -> tile ranges, split-pass histograms
+int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im, cudaStream_t s);
 // emits instances in depth order, splits them stably by tile id, writes vals + tile ranges
 int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
 // comparison arm only (bench / tests): the reference's formulation, cub::DeviceRadixSort on 64-bit keys
 int launch_tile_split_cub(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
 size_t cub_sort_scratch_bytes(long long R);
 
-// generic stable radix sort of (u32 key, identity value) pairs on the low 8*npass key bits (sort.cu)
-size_t radix_hist_words(uint32_t n);
-int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n, int npass,
-                          uint32_t* hist_and_totals, cudaStream_t s);
+// generic stable radix sort of (u32 key, identity value) pairs on all 32 key bits (sort.cu); ctl = radix_ctl_words(n)
+// words of control state, zeroed by the call unless ctl_zeroed
+size_t radix_ctl_words(uint32_t n);
+int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n,
+                          uint32_t* ctl, bool ctl_zeroed, cudaStream_t s);
 
 // blend.cu
 int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,

@@ -208,7 +208,7 @@ int launch_dist2(int P, const float* points, float* out, GsrAlloc scratch, cudaS
 {
     const int nbox = cdiv(P, KB);
     const size_t Pa = align_up((size_t)P, 64);
-    const size_t words = 64 + 5 * Pa + radix_hist_words(P) + 4 * Pa /*float4 sorted*/ + 8 * (size_t)nbox + 64;
+    const size_t words = 64 + 5 * Pa + radix_ctl_words((uint32_t)P) + 4 * Pa /*float4 sorted*/ + 8 * (size_t)nbox + 64;
     uint32_t* base = (uint32_t*)scratch.fn(scratch.ctx, words * 4);
     if (!base) return GSR_ENOMEM;
     uint32_t* mm = base;
@@ -218,13 +218,13 @@ int launch_dist2(int P, const float* points, float* out, GsrAlloc scratch, cudaS
     uint32_t* V0 = K1 + Pa;
     uint32_t* order = V0 + Pa;
     uint32_t* hist = order + Pa;
-    float4* sorted = reinterpret_cast<float4*>(hist + radix_hist_words(P));
+    float4* sorted = reinterpret_cast<float4*>(hist + radix_ctl_words((uint32_t)P));
     KnnBox* boxes = reinterpret_cast<KnnBox*>(reinterpret_cast<uint32_t*>(sorted) + 4 * Pa);
 
     GSR_CUDA(cudaMemsetAsync(mm, 0, 64 * 4, s));
     GSR_LAUNCH(knn_bounds_kernel, cdiv(P, 256), 256, 0, s, P, points, mm);
     GSR_LAUNCH(knn_morton_kernel, cdiv(P, 256), 256, 0, s, P, points, mm, codes);
-    int rc = radix_sort_by_key_u32(codes, K0, K1, V0, order, (uint32_t)P, 4, hist, s);
+    int rc = radix_sort_by_key_u32(codes, K0, K1, V0, order, (uint32_t)P, hist, false, s);
     if (rc) return rc;
     GSR_LAUNCH(knn_gather_boxes_kernel, nbox, KB, 0, s, P, points, order, sorted, boxes);
     GSR_LAUNCH(knn_search_kernel, nbox, KB, 0, s, P, nbox, sorted, boxes, out);

@@ -132,6 +132,9 @@ struct PreArgs {
     int* radii;
     SplatRec* rec;
     uint8_t* clamped;
+    uint32_t* depthkey; // [P] sort key of the depth pass
+    ushort4* rect;      // [P] tile rect
+    uint32_t* total;    // sum of tiles touched (R)
     int* err;          // device flag: prefiltered violated
 };
 
@@ -148,6 +151,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
     out.q2 = make_float4(0.f, __uint_as_float(0xFFFFFFFFu), __int_as_float(0), __uint_as_float(0u));
     int radius_out = 0;
     uint32_t clamp_bits = 0;
+    ushort4 rect_out = make_ushort4(0, 0, 0, 0);
 
     const float3 p = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
     const float3 p_view = xform4x3(p, cam.view);
@@ -203,6 +207,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
                 out.q1 = make_float4(conic.z, a.opac[idx], rgb[0], rgb[1]);
                 out.q2 = make_float4(rgb[2], p_view.z, __int_as_float((int)my_radius), __uint_as_float(area));
                 radius_out = (int)my_radius;
+                rect_out = make_ushort4((unsigned short)x0, (unsigned short)y0, (unsigned short)x1, (unsigned short)y1);
             }
         }
     } else if (a.prefiltered) {
@@ -211,6 +216,13 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
     a.radii[idx] = radius_out;
     a.rec[idx] = out;
     a.clamped[idx] = (uint8_t)clamp_bits;
+    a.depthkey[idx] = __float_as_uint(out.q2.y);
+    a.rect[idx] = rect_out;
+    // R = sum of tiles touched: one atomic per warp that has any
+    uint32_t tiles = __float_as_uint(out.q2.w);
+    const unsigned am = __activemask();
+    tiles = __reduce_add_sync(am, tiles);
+    if (tiles && (int)(threadIdx.x & 31) == __ffs(am) - 1) atomicAdd(a.total, tiles);
 }
 
 int launch_preprocess(const GsrFwdArgs& a, const GeomView& g, cudaStream_t s)
@@ -221,7 +233,9 @@ int launch_preprocess(const GsrFwdArgs& a, const GeomView& g, cudaStream_t s)
     k.means = a.means3D; k.shs = a.shs; k.colors_pre = a.colors_precomp; k.opac = a.opacities;
     k.scales = a.scales; k.rots = a.rotations; k.cov_pre = a.cov3D_precomp; k.mod = a.scale_modifier;
     k.prefiltered = a.prefiltered; k.radii = a.radii; k.rec = g.rec; k.clamped = g.clamped;
-    k.err = reinterpret_cast<int*>(&g.hdr->pad[0]);
+    const GeomScratch sc = carve_geom_scratch(g.scratch, a.P);
+    k.depthkey = sc.depthkey; k.rect = sc.rect; k.total = sc.counters;
+    k.err = reinterpret_cast<int*>(sc.counters + 8);
     GSR_LAUNCH(preprocess_fwd_kernel, cdiv(a.P, 256), 256, 0, s, k, cam);
     return GSR_OK;
 }

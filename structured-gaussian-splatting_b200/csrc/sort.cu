@@ -1,10 +1,10 @@
 // sort.cu - binning: depth ordering of Gaussians, instance emission, stable split by tile, tile ranges.
 //
 // Replaces (reference: submodules/diff-gaussian-rasterization/cuda_rasterizer/rasterizer_impl.cu):
-//   cub::DeviceScan::InclusiveSum            :277      -> scan_* kernels (over the depth-ordered tile counts)
+//   cub::DeviceScan::InclusiveSum            :277      -> fused into emit_instances_kernel (decoupled look-back)
 //   duplicateWithKeys                        :70-111   -> emit_instances_kernel
-//   cub::DeviceRadixSort::SortPairs (u64)    :303-308  -> radix_* kernels, see below
-//   identifyTileRanges (+ cudaMemset)        :116-138,310-318 -> tile_ranges_kernel
+//   cub::DeviceRadixSort::SortPairs (u64)    :303-308  -> radix_onesweep_kernel, see below
+//   identifyTileRanges (+ cudaMemset)        :116-138,310-318 -> tile_count_kernel + tile_prefix_kernel
 //
 // The reference sorts R (tile<<32 | depth) 64-bit keys with 6 radix passes over 12 B pairs (~152 B per
 // instance of HBM traffic).  We produce the IDENTICAL sequence with far less traffic by trimming the
@@ -15,108 +15,124 @@
 // A stable sort by (tile) of a sequence already ordered by (depth, id) is ordered by (tile, depth, id),
 // which is exactly what a stable sort on tile<<32|depth of the id-major emission gives.
 //
-// Each radix pass is three launches: per-block digit histogram, per-digit scan over blocks, ranked
-// scatter (warp match-any ranking keeps the pass stable).
+// Every radix pass is ONE launch ("onesweep"): the digit histograms of all passes are known up front
+// (radix_hist4_kernel for the depth bits, tile_prefix_kernel for the tile digits), and the per-block digit offsets come from a decoupled look-back over per-block status words
+// instead of a separate histogram + scan launch per pass.  Blocks take their tile by atomic ticket, so
+// a block only ever waits for blocks that are already running.
 #include "gsr_common.cuh"
 
 namespace gsr {
 
-constexpr int RS_THREADS = 256;
+constexpr int RS_THREADS = 512;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_IPT = 16;                         // items per thread
+constexpr int RS_IPT = 8;                          // items per thread
 constexpr int RS_TILE = RS_THREADS * RS_IPT;       // items per block (4096)
 constexpr int RS_NB = 256;                         // max bins (8-bit digits)
 
-// ------------------------------------------------------------------ radix pass: histogram
-__global__ void __launch_bounds__(RS_THREADS) radix_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, int shift,
-                                                                int bits, uint32_t* __restrict__ hist, int nblocks)
+constexpr uint32_t ST_AGG = 1u << 30, ST_INC = 2u << 30, ST_VAL = (1u << 30) - 1;   // look-back status word
+
+__device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
+__device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
+__device__ __forceinline__ unsigned long long ld_volatile64(const unsigned long long* p)
 {
-    __shared__ uint32_t sh[RS_NB];
-    const uint32_t nb = 1u << bits, mask = nb - 1;
-    for (uint32_t i = threadIdx.x; i < nb; i += RS_THREADS) sh[i] = 0;
-    __syncthreads();
-    const uint32_t base = blockIdx.x * RS_TILE;
-#pragma unroll
-    for (int i = 0; i < RS_IPT; i++) {
-        const uint32_t idx = base + i * RS_THREADS + threadIdx.x;
-        if (idx < n) atomicAdd(&sh[(keys[idx] >> shift) & mask], 1u);
-    }
-    __syncthreads();
-    for (uint32_t d = threadIdx.x; d < nb; d += RS_THREADS) hist[(size_t)d * nblocks + blockIdx.x] = sh[d];
+    return *reinterpret_cast<const volatile unsigned long long*>(p);
+}
+__device__ __forceinline__ void st_volatile64(unsigned long long* p, unsigned long long v)
+{
+    *reinterpret_cast<volatile unsigned long long*>(p) = v;
 }
 
-// ------------------------------------------------------------------ radix pass: scan each digit row over blocks
-// one CTA per digit; hist[d][*] becomes the exclusive prefix over blocks, totals[d] the row sum
-__global__ void __launch_bounds__(RS_THREADS) radix_rowscan_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ totals,
-                                                                   int nblocks)
+// exclusive scan over the block's NW warps (one value per thread); warp_sum is NW words of shared memory
+template <int NW>
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_sum, uint32_t* total = nullptr)
 {
-    __shared__ uint32_t warp_sum[RS_WARPS];
-    uint32_t* row = hist + (size_t)blockIdx.x * nblocks;
-    const int per = (nblocks + RS_THREADS - 1) / RS_THREADS;
-    const int j0 = threadIdx.x * per, j1 = min(nblocks, j0 + per);
-    uint32_t s = 0;
-    for (int j = j0; j < j1; j++) s += row[j];
-    // block exclusive scan of s
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    uint32_t inc = s;
+    uint32_t inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += t;
+        const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
     }
+    __syncthreads();                       // warp_sum may still be read from a previous use
     if (lane == 31) warp_sum[w] = inc;
     __syncthreads();
-    uint32_t wbase = 0;
-    for (int i = 0; i < w; i++) wbase += warp_sum[i];
-    uint32_t run = wbase + inc - s;
-    for (int j = j0; j < j1; j++) { uint32_t v = row[j]; row[j] = run; run += v; }
-    if (threadIdx.x == RS_THREADS - 1) totals[blockIdx.x] = wbase + inc;
+    uint32_t wb = 0, all = 0;
+#pragma unroll
+    for (int i = 0; i < NW; i++) { const uint32_t s = warp_sum[i]; if (i < w) wb += s; all += s; }
+    if (total) *total = all;
+    return wb + inc - v;
 }
 
-// ------------------------------------------------------------------ radix pass: ranked scatter
-// vals_in == nullptr means "identity" (value = item index).  keys_out may be nullptr.
-// One warp match-any per item gives its stable rank inside the warp's run; per-warp digit counts are
-// scanned across the CTA; the 4096 items are first placed in digit order in shared memory and then
-// written out so that consecutive threads write consecutive addresses inside each digit run
-// (full 32-byte sectors instead of 4-byte scattered stores).
-__global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_t* __restrict__ keys_in,
-                                                                   const uint32_t* __restrict__ vals_in,
-                                                                   uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                                                                   uint32_t n, int shift, int bits,
-                                                                   const uint32_t* __restrict__ hist, const uint32_t* __restrict__ totals,
-                                                                   int nblocks)
+// ------------------------------------------------------------------ digit histograms of all four depth passes
+// one read of the keys; shared-memory atomics; a few hundred blocks flush 4 x 256 counters each
+__global__ void __launch_bounds__(RS_THREADS) radix_hist4_kernel(const uint32_t* __restrict__ keys, uint32_t n,
+                                                                 uint32_t* __restrict__ ghist)
 {
-    __shared__ uint32_t wcount[RS_WARPS][RS_NB];
-    __shared__ uint32_t lbase[RS_NB];       // CTA-local exclusive offset of each digit
-    __shared__ uint32_t gdelta[RS_NB];      // global position of local slot lp of digit d = gdelta[d] + lp
-    __shared__ uint32_t warp_sum[RS_WARPS];
+    __shared__ uint32_t sh[4 * RS_NB];
+    for (int i = threadIdx.x; i < 4 * RS_NB; i += RS_THREADS) sh[i] = 0;
+    __syncthreads();
+    const uint32_t n4 = n >> 2;
+    const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+    for (uint32_t i = blockIdx.x * RS_THREADS + threadIdx.x; i < n4; i += gridDim.x * RS_THREADS) {
+        const uint4 k = k4[i];
+        const uint32_t kk[4] = {k.x, k.y, k.z, k.w};
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            atomicAdd(&sh[kk[c] & 255u], 1u);
+            atomicAdd(&sh[256 + ((kk[c] >> 8) & 255u)], 1u);
+            atomicAdd(&sh[512 + ((kk[c] >> 16) & 255u)], 1u);
+            atomicAdd(&sh[768 + (kk[c] >> 24)], 1u);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3u)) {
+        const uint32_t k = keys[(n4 << 2) + threadIdx.x];
+        atomicAdd(&sh[k & 255u], 1u);
+        atomicAdd(&sh[256 + ((k >> 8) & 255u)], 1u);
+        atomicAdd(&sh[512 + ((k >> 16) & 255u)], 1u);
+        atomicAdd(&sh[768 + (k >> 24)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 4 * RS_NB; i += RS_THREADS)
+        if (sh[i]) atomicAdd(&ghist[i], sh[i]);
+}
+
+// ------------------------------------------------------------------ one LSD pass in one launch
+// keys_in[n] (+ vals_in[n], nullptr = identity) -> keys_out (may be nullptr) / vals_out, stable on digit
+// (key >> shift) & (2^BITS - 1).  ghist[2^BITS] = global digit counts of this pass, status[nblocks][2^BITS] and
+// *ticket zeroed by the caller.
+//  phase 1  each warp walks its contiguous run of 32*IPT items; 8 ballots give the lanes holding the same digit,
+//           hence the item's stable rank inside the warp's run (match.any is microcoded and far slower)
+//  phase 2  thread d owns digit d: prefix over warps, publish the block's count, look back over the preceding
+//           blocks' status words for the exclusive prefix, publish the inclusive one
+//  phase 3  items are placed in digit order in shared memory, phase 4 writes them out so that consecutive
+//           threads write consecutive addresses inside each digit run (full sectors, not 4-byte scatters)
+template <int BITS>
+__global__ void __launch_bounds__(RS_THREADS) radix_onesweep_kernel(const uint32_t* __restrict__ keys_in,
+                                                                    const uint32_t* __restrict__ vals_in,
+                                                                    uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                                    uint32_t n, int shift, const uint32_t* __restrict__ ghist,
+                                                                    uint32_t* __restrict__ status, uint32_t* __restrict__ ticket)
+{
+    constexpr uint32_t NB = 1u << BITS, MASK = NB - 1;
     __shared__ uint32_t skey[RS_TILE];
     __shared__ uint32_t sval[RS_TILE];
-    const uint32_t nb = 1u << bits, mask = nb - 1;
+    uint32_t (*wcount)[NB] = reinterpret_cast<uint32_t (*)[NB]>(sval);     // [RS_WARPS][NB], dead before sval is written
+    static_assert(RS_WARPS * NB <= RS_TILE, "wcount must fit in sval");
+    __shared__ uint32_t lbase[NB];          // CTA-local exclusive offset of each digit
+    __shared__ uint32_t gdelta[NB];         // global position of local slot lp of digit d = gdelta[d] + lp
+    __shared__ uint32_t warp_sum[RS_WARPS];
+    __shared__ uint32_t s_blk;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t t = threadIdx.x;
 
-    for (uint32_t i = t; i < RS_WARPS * RS_NB; i += RS_THREADS) (&wcount[0][0])[i] = 0;
-    // global digit bases for this CTA: exclusive scan of totals + this CTA's row prefix
-    uint32_t gscan = 0;
-    {
-        const uint32_t v = t < nb ? totals[t] : 0;
-        uint32_t inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += u;
-        }
-        if (lane == 31) warp_sum[w] = inc;
-        __syncthreads();
-        uint32_t wb = 0;
-        for (int i = 0; i < w; i++) wb += warp_sum[i];
-        if (t < nb) gscan = wb + inc - v + hist[(size_t)t * nblocks + blockIdx.x];
-    }
+    if (t == 0) s_blk = atomicAdd(ticket, 1u);
+    for (uint32_t i = t; i < RS_WARPS * NB; i += RS_THREADS) sval[i] = 0;
     __syncthreads();
+    const uint32_t blk = s_blk;
 
-    // phase 1: each warp walks its contiguous run of 32*IPT items in order (i, lane)
-    const uint32_t wbase_idx = blockIdx.x * RS_TILE + w * (32 * RS_IPT);
+    // phase 1
+    const uint32_t wbase_idx = blk * RS_TILE + w * (32 * RS_IPT);
+    const uint32_t lt_mask = (1u << lane) - 1;
     uint32_t key[RS_IPT];
     uint32_t loff[RS_IPT];      // rank of the item among the warp's items with the same digit
 #pragma unroll
@@ -128,375 +144,410 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
     for (int i = 0; i < RS_IPT; i++) {
         const uint32_t idx = wbase_idx + i * 32 + lane;
         const bool valid = idx < n;
-        const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
-        loff[i] = 0;
-        if (valid) {
-            const uint32_t d = (key[i] >> shift) & mask;
-            // lanes holding the same digit, from 8 ballots (match.any is microcoded and far slower)
-            uint32_t peers = vmask;
+        const uint32_t d = (key[i] >> shift) & MASK;
+        uint32_t peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
-            for (int b = 0; b < 8; b++) {
-                const bool bit = (d >> b) & 1u;
-                const uint32_t bal = __ballot_sync(vmask, bit);
-                peers &= bit ? bal : ~bal;
-            }
-            const uint32_t rank = __popc(peers & ((1u << lane) - 1));
-            const int leader = __ffs(peers) - 1;
-            uint32_t old = 0;
-            if (lane == leader) { old = wcount[w][d]; wcount[w][d] = old + __popc(peers); }
-            old = __shfl_sync(peers, old, leader);
-            loff[i] = old + rank;
+        for (int b = 0; b < BITS; b++) {
+            const bool bit = (d >> b) & 1u;
+            const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+            peers &= bal ^ (bit ? 0u : 0xFFFFFFFFu);
         }
+        const uint32_t old = wcount[w][d];
         __syncwarp();
+        const uint32_t cnt = __popc(peers), rank = __popc(peers & lt_mask);
+        if (valid && rank == cnt - 1) wcount[w][d] = old + cnt;
+        __syncwarp();
+        loff[i] = old + rank;
     }
     __syncthreads();
-    // phase 2: per digit, exclusive prefix over warps; then exclusive scan over digits
-    {
-        uint32_t tot = 0;
-        if (t < nb) {
+
+    // phase 2
+    uint32_t tot = 0, excl = 0;
+    if (t < NB) {
 #pragma unroll
-            for (int i = 0; i < RS_WARPS; i++) { uint32_t c = wcount[i][t]; wcount[i][t] = tot; tot += c; }
-        }
-        uint32_t inc = tot;
+        for (int i = 0; i < RS_WARPS; i++) { const uint32_t c = wcount[i][t]; wcount[i][t] = tot; tot += c; }
+        uint32_t* mine = status + (size_t)blk * NB + t;
+        if (blk == 0) st_volatile(mine, ST_INC | tot);
+        else {
+            st_volatile(mine, ST_AGG | tot);
+            // four predecessors per round trip to L2; consumed nearest first
+            bool found = false;
+            for (int k = (int)blk - 1; !found; k -= 4) {
+                uint32_t sv[4];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += u;
+                for (int j = 0; j < 4; j++) sv[j] = k - j >= 0 ? ld_volatile(status + (size_t)(k - j) * NB + t) : ST_INC;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (found) break;
+                    uint32_t v = sv[j];
+                    while ((v >> 30) == 0) v = ld_volatile(status + (size_t)(k - j) * NB + t);
+                    excl += v & ST_VAL;
+                    found = (v & ST_INC) != 0;
+                }
+            }
+            st_volatile(mine, ST_INC | (excl + tot));
         }
-        if (lane == 31) warp_sum[w] = inc;
-        __syncthreads();
-        uint32_t wb = 0;
-        for (int i = 0; i < w; i++) wb += warp_sum[i];
-        if (t < nb) { const uint32_t lb = wb + inc - tot; lbase[t] = lb; gdelta[t] = gscan - lb; }
     }
+    const uint32_t gbase = block_excl_scan<RS_WARPS>(t < NB ? ghist[t] : 0u, warp_sum);
+    const uint32_t lb = block_excl_scan<RS_WARPS>(tot, warp_sum);
+    if (t < NB) { lbase[t] = lb; gdelta[t] = gbase + excl - lb; }
     __syncthreads();
-    // phase 3: place items in digit order in shared memory
+
+    // phase 3: place items in digit order in shared memory (all value loads are issued before the first store;
+    // the slots are computed before wcount's storage is reused for the values)
+    uint32_t val[RS_IPT];
 #pragma unroll
     for (int i = 0; i < RS_IPT; i++) {
         const uint32_t idx = wbase_idx + i * 32 + lane;
-        if (idx < n) {
-            const uint32_t d = (key[i] >> shift) & mask;
-            const uint32_t lp = lbase[d] + wcount[w][d] + loff[i];
-            skey[lp] = key[i];
-            sval[lp] = vals_in ? vals_in[idx] : idx;
-        }
+        val[i] = (vals_in && idx < n) ? vals_in[idx] : idx;
+        const uint32_t d = (key[i] >> shift) & MASK;
+        loff[i] += lbase[d] + wcount[w][d];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < RS_IPT; i++) {
+        const uint32_t idx = wbase_idx + i * 32 + lane;
+        if (idx < n) { skey[loff[i]] = key[i]; sval[loff[i]] = val[i]; }
     }
     __syncthreads();
     // phase 4: coalesced write-out
-    const uint32_t n_blk = min((uint32_t)RS_TILE, n - blockIdx.x * RS_TILE);
+    const uint32_t n_blk = min((uint32_t)RS_TILE, n - blk * RS_TILE);
 #pragma unroll
     for (int i = 0; i < RS_IPT; i++) {
         const uint32_t lp = i * RS_THREADS + t;
         if (lp < n_blk) {
             const uint32_t k = skey[lp];
-            const uint32_t gpos = gdelta[(k >> shift) & mask] + lp;
+            const uint32_t gpos = gdelta[(k >> shift) & MASK] + lp;
             if (keys_out) keys_out[gpos] = k;
             vals_out[gpos] = sval[lp];
         }
     }
 }
 
-// one LSD pass over (keys, vals); hist needs 256 * nblocks u32, totals 256 u32
+// one pass; bits in 1..8
 static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t n,
-                      int shift, int bits, uint32_t* hist, uint32_t* totals, cudaStream_t s)
+                      int shift, int bits, const uint32_t* ghist, uint32_t* status, uint32_t* ticket, cudaStream_t s)
 {
     const int nblocks = cdiv(n, RS_TILE);
-    GSR_LAUNCH(radix_hist_kernel, nblocks, RS_THREADS, 0, s, keys_in, n, shift, bits, hist, nblocks);
-    GSR_LAUNCH(radix_rowscan_kernel, 1 << bits, RS_THREADS, 0, s, hist, totals, nblocks);
-    GSR_LAUNCH(radix_scatter_kernel, nblocks, RS_THREADS, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, bits, hist,
-               totals, nblocks);
+#define GSR_PASS(B)                                                                                                      \
+    case B:                                                                                                              \
+        GSR_LAUNCH(radix_onesweep_kernel<B>, nblocks, RS_THREADS, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, ghist, \
+                   status, ticket);                                                                                      \
+        break;
+    switch (bits) {
+        GSR_PASS(1) GSR_PASS(2) GSR_PASS(3) GSR_PASS(4) GSR_PASS(5) GSR_PASS(6) GSR_PASS(7) GSR_PASS(8)
+    default: return GSR_EINVAL;
+    }
+#undef GSR_PASS
     return GSR_OK;
 }
 
-// stable LSD sort of n (key, value) pairs on key bits [0, 8*npass); values start as identity.
+// stable LSD sort of n (key, value) pairs on all 32 key bits; values start as identity.
 // K0, K1, V0: n-word ping-pong buffers; result values land in vals_out (keys are not kept).
-size_t radix_hist_words(uint32_t n) { return align_up((size_t)RS_NB * cdiv(n > 0 ? n : 1, RS_TILE), 64) + RS_NB; }
-int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n, int npass,
-                          uint32_t* hist_and_totals, cudaStream_t s)
+// ctl: radix_ctl_words(n) words (digit histograms, tickets, look-back status), zeroed here.
+size_t radix_ctl_words(uint32_t n) { return 4 * RS_NB + 64 + (size_t)4 * RS_NB * cdiv(n > 0 ? n : 1, RS_TILE); }
+int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n,
+                          uint32_t* ctl, bool ctl_zeroed, cudaStream_t s)
 {
-    uint32_t* hist = hist_and_totals;
-    uint32_t* totals = hist + align_up((size_t)RS_NB * cdiv(n > 0 ? n : 1, RS_TILE), 64);
-    // choose the value ping-pong so that the LAST pass writes vals_out
-    uint32_t* Vb[2] = {(npass & 1) ? vals_out : V0, (npass & 1) ? V0 : vals_out};
+    const int nblocks = cdiv(n, RS_TILE);
+    uint32_t* ghist = ctl;
+    uint32_t* tickets = ctl + 4 * RS_NB;
+    uint32_t* status = tickets + 64;
+    if (!ctl_zeroed) GSR_CUDA(cudaMemsetAsync(ctl, 0, radix_ctl_words(n) * 4, s));
+    GSR_LAUNCH(radix_hist4_kernel, min(cdiv(n, 4 * RS_THREADS * 4), 148 * 4), RS_THREADS, 0, s, keys, n, ghist);
+    uint32_t* Vb[2] = {V0, vals_out};       // 4 passes: the last one writes vals_out
     uint32_t* Kb[2] = {K0, K1};
     const uint32_t* kin = keys;
     const uint32_t* vin = nullptr;
-    for (int p = 0; p < npass; p++) {
-        const bool last = p == npass - 1;
-        int rc = radix_pass(kin, vin, last ? nullptr : Kb[p & 1], Vb[p & 1], n, 8 * p, 8, hist, totals, s);
+    for (int p = 0; p < 4; p++) {
+        const bool last = p == 3;
+        int rc = radix_pass(kin, vin, last ? nullptr : Kb[p & 1], Vb[p & 1], n, 8 * p, 8, ghist + p * RS_NB,
+                            status + (size_t)p * RS_NB * nblocks, tickets + p, s);
         if (rc) return rc;
         kin = Kb[p & 1]; vin = Vb[p & 1];
     }
     return GSR_OK;
 }
 
-// ------------------------------------------------------------------ exclusive scan of tile counts in depth order
-constexpr int SC_TILE = 4096;   // items per block, 256 threads x 16
-
-__global__ void __launch_bounds__(256) scan_reduce_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles,
-                                                          uint32_t n, uint32_t* __restrict__ block_sums)
+// ------------------------------------------------------------------ geometry scratch layout
+GeomScratch carve_geom_scratch(uint32_t* p, int P)
 {
-    __shared__ uint32_t ws[8];
-    uint32_t s = 0;
-    const uint32_t base = blockIdx.x * SC_TILE;
-#pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const uint32_t idx = base + i * 256 + threadIdx.x;
-        if (idx < n) s += tiles[order[idx]];
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t t = 0;
-        for (int i = 0; i < 8; i++) t += ws[i];
-        block_sums[blockIdx.x] = t;
-    }
-}
-
-// single CTA: exclusive scan of block_sums in place; writes the grand total to *total and *offs_end
-__global__ void __launch_bounds__(1024) scan_spine_kernel(uint32_t* __restrict__ block_sums, int nb, uint32_t* __restrict__ total,
-                                                          uint32_t* __restrict__ offs_end)
-{
-    __shared__ uint32_t ws[32];
-    __shared__ uint32_t carry_s, chunk_s;
-    if (threadIdx.x == 0) carry_s = 0;
-    __syncthreads();
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int base = 0; base < nb; base += 1024) {
-        const int j = base + threadIdx.x;
-        const uint32_t v = j < nb ? block_sums[j] : 0;
-        uint32_t inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) ws[w] = inc;
-        __syncthreads();
-        if (w == 0) {
-            const uint32_t x = ws[lane];
-            uint32_t xi = x;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                uint32_t t = __shfl_up_sync(0xffffffffu, xi, o);
-                if (lane >= o) xi += t;
-            }
-            ws[lane] = xi - x;               // exclusive warp bases
-            if (lane == 31) chunk_s = xi;    // chunk total
-        }
-        __syncthreads();
-        const uint32_t carry = carry_s;
-        if (j < nb) block_sums[j] = carry + ws[w] + inc - v;
-        __syncthreads();
-        if (threadIdx.x == 0) carry_s = carry + chunk_s;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) { *total = carry_s; *offs_end = carry_s; }
-}
-
-__global__ void __launch_bounds__(256) scan_apply_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles,
-                                                         uint32_t n, const uint32_t* __restrict__ block_sums,
-                                                         uint32_t* __restrict__ offs)
-{
-    __shared__ uint32_t ws[8];
-    // thread t owns 16 consecutive items so the scan order is the item order
-    const uint32_t base = blockIdx.x * SC_TILE + threadIdx.x * 16;
-    uint32_t v[16];
-    uint32_t s = 0;
-#pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const uint32_t idx = base + i;
-        v[i] = idx < n ? tiles[order[idx]] : 0;
-        s += v[i];
-    }
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    uint32_t inc = s;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += t;
-    }
-    if (lane == 31) ws[w] = inc;
-    __syncthreads();
-    uint32_t run = block_sums[blockIdx.x] + inc - s;
-    for (int i = 0; i < w; i++) run += ws[i];
-#pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const uint32_t idx = base + i;
-        if (idx < n) offs[idx] = run;
-        run += v[i];
-    }
-}
-
-// ------------------------------------------------------------------ depth ordering
-// scratch layout (u32 words): depthkey[P] tiles[P] K0[P] K1[P] V0[P] hist[256*nblk] totals[256] bsum[nscan] total[1]
-struct GeomScratch {
-    uint32_t *depthkey, *tiles, *K0, *K1, *V0, *hist, *totals, *bsum, *total;
-};
-static GeomScratch carve_geom_scratch(uint32_t* p, int P)
-{
+    const size_t Pp = (size_t)(P > 0 ? P : 1);
+    const size_t Pa = align_up(Pp, 64);
     GeomScratch g;
-    const size_t Pa = align_up((size_t)P, 64);
+    g.ctl = p;
+    g.counters = p;
+    g.tile_hist = p + 64;
+    g.emit_status = reinterpret_cast<unsigned long long*>(p + 64 + 4 * RS_NB);
+    g.radix_ctl = p + 64 + 4 * RS_NB + 2 * align_up((size_t)cdiv(Pp, 256), 32);
+    g.ctl_words = align_up(64 + 4 * RS_NB + 2 * align_up((size_t)cdiv(Pp, 256), 32) + radix_ctl_words((uint32_t)Pp), 64);
+    p += g.ctl_words;
     g.depthkey = p; p += Pa;
-    g.tiles = p; p += Pa;
     g.K0 = p; p += Pa;
     g.K1 = p; p += Pa;
     g.V0 = p; p += Pa;
-    g.hist = p; p += align_up((size_t)RS_NB * cdiv(P, RS_TILE), 64);
-    g.totals = p; p += RS_NB;
-    g.bsum = p; p += align_up((size_t)cdiv(P, SC_TILE) + 1, 64);
-    g.total = p; p += 64;
+    g.rect = reinterpret_cast<ushort4*>(p); p += 2 * Pa;
+    g.total_words = g.ctl_words + 6 * Pa;
     return g;
 }
-size_t geom_scratch_bytes(int P)
+size_t geom_scratch_bytes(int P) { return carve_geom_scratch(nullptr, P).total_words * 4; }
+
+// ------------------------------------------------------------------ tile-id digits of the split passes
+struct TileDigits {
+    int npass;
+    int shift[4], bits[4];
+};
+static TileDigits tile_digits(uint32_t tiles)
 {
-    const size_t Pa = align_up((size_t)(P > 0 ? P : 1), 64);
-    return 4 * (5 * Pa + align_up((size_t)RS_NB * cdiv(P > 0 ? P : 1, RS_TILE), 64) + RS_NB +
-                align_up((size_t)cdiv(P > 0 ? P : 1, SC_TILE) + 1, 64) + 64);
+    // bits = position of the highest set bit + 1 (what the reference's getHigherMsb computes, rasterizer_impl.cu:35-50)
+    int tb = 0;
+    while (tb < 32 && (tiles >> tb)) tb++;
+    if (tb == 0) tb = 1;
+    TileDigits d;
+    d.npass = (tb + 7) / 8;
+    int shift = 0;
+    for (int p = 0; p < 4; p++) { d.shift[p] = 0; d.bits[p] = 0; }
+    for (int p = 0; p < d.npass; p++) {
+        d.bits[p] = (tb - shift + (d.npass - p) - 1) / (d.npass - p);      // balanced digits, e.g. 13 -> 7 + 6
+        d.shift[p] = shift;
+        shift += d.bits[p];
+    }
+    return d;
 }
 
-// pulls the depth bits and tile count out of the packed records (coalesced 16 B loads of q2)
-__global__ void __launch_bounds__(256) extract_keys_kernel(int P, const SplatRec* __restrict__ rec, uint32_t* __restrict__ depthkey,
-                                                           uint32_t* __restrict__ tiles)
+// ------------------------------------------------------------------ instances per tile -> tile ranges, split histograms
+// Every visible Gaussian adds +1 over its tile rect: four corner updates of a 2-D difference array (shared-memory
+// atomics, one flush per block); the 2-D prefix sum of that array is the number of instances of every tile.  Its
+// exclusive scan in tile-id order IS the reference's tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138:
+// empty tiles stay (0,0)), and the digit histograms the split passes need are marginals of it - no pass over
+// the R instances is needed for either.
+template <bool SMEM>
+__global__ void __launch_bounds__(1024) tile_count_kernel(int P, const ushort4* __restrict__ rect, int gx1, int cells,
+                                                          int* __restrict__ diff)
 {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P) return;
-    const float4 q2 = rec[idx].q2;
-    depthkey[idx] = __float_as_uint(q2.y);
-    tiles[idx] = __float_as_uint(q2.w);
+    extern __shared__ int sd[];
+    if (SMEM) {
+        for (int i = threadIdx.x; i < cells; i += 1024) sd[i] = 0;
+        __syncthreads();
+    }
+    for (int k = blockIdx.x * 1024 + threadIdx.x; k < P; k += gridDim.x * 1024) {
+        const ushort4 r = rect[k];
+        if (r.x == r.z || r.y == r.w) continue;
+        if (SMEM) {
+            atomicAdd(&sd[r.y * gx1 + r.x], 1); atomicAdd(&sd[r.y * gx1 + r.z], -1);
+            atomicAdd(&sd[r.w * gx1 + r.x], -1); atomicAdd(&sd[r.w * gx1 + r.z], 1);
+        } else {
+            atomicAdd(&diff[r.y * gx1 + r.x], 1); atomicAdd(&diff[r.y * gx1 + r.z], -1);
+            atomicAdd(&diff[r.w * gx1 + r.x], -1); atomicAdd(&diff[r.w * gx1 + r.z], 1);
+        }
+    }
+    if (SMEM) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < cells; i += 1024)
+            if (sd[i]) atomicAdd(&diff[i], sd[i]);
+    }
 }
 
-int launch_depth_order(int P, const GeomView& g, cudaStream_t s)
+// single block: 2-D prefix of the difference array, exclusive scan over tile ids, ranges, digit histograms
+template <bool SMEM>
+__global__ void __launch_bounds__(1024) tile_prefix_kernel(int gx, int gy, int* __restrict__ diff, uint2* __restrict__ ranges,
+                                                           uint32_t* __restrict__ tile_hist, TileDigits td)
 {
-    GeomScratch sc = carve_geom_scratch(g.scratch, P);
-    GSR_LAUNCH(extract_keys_kernel, cdiv(P, 256), 256, 0, s, P, g.rec, sc.depthkey, sc.tiles);
-    // 4 x 8-bit stable passes over the 32 depth bits; values start as identity
-    int rc;
-    if ((rc = radix_pass(sc.depthkey, nullptr, sc.K0, sc.V0, P, 0, 8, sc.hist, sc.totals, s))) return rc;
-    if ((rc = radix_pass(sc.K0, sc.V0, sc.K1, g.order, P, 8, 8, sc.hist, sc.totals, s))) return rc;
-    if ((rc = radix_pass(sc.K1, g.order, sc.K0, sc.V0, P, 16, 8, sc.hist, sc.totals, s))) return rc;
-    if ((rc = radix_pass(sc.K0, sc.V0, nullptr, g.order, P, 24, 8, sc.hist, sc.totals, s))) return rc;
-    // exclusive scan of tile counts in that order -> offs[0..P], total
-    const int nb = cdiv(P, SC_TILE);
-    GSR_LAUNCH(scan_reduce_kernel, nb, 256, 0, s, g.order, sc.tiles, (uint32_t)P, sc.bsum);
-    GSR_LAUNCH(scan_spine_kernel, 1, 1024, 0, s, sc.bsum, nb, sc.total, g.offs + P);
-    GSR_LAUNCH(scan_apply_kernel, nb, 256, 0, s, g.order, sc.tiles, (uint32_t)P, sc.bsum, g.offs);
-    return GSR_OK;
+    extern __shared__ int sd[];
+    __shared__ uint32_t warp_sum[32];
+    __shared__ uint32_t sh[4 * RS_NB];
+    const int gx1 = gx + 1, cells = gx1 * (gy + 1), t = threadIdx.x;
+    int* d = SMEM ? sd : diff;
+    if (SMEM)
+        for (int i = t; i < cells; i += 1024) sd[i] = diff[i];
+    for (int i = t; i < 4 * RS_NB; i += 1024) sh[i] = 0;
+    __syncthreads();
+    for (int x = t; x <= gx; x += 1024) {            // prefix down the columns
+        int acc = 0;
+        for (int y = 0; y <= gy; y++) { acc += d[y * gx1 + x]; d[y * gx1 + x] = acc; }
+    }
+    __syncthreads();
+    for (int y = t; y <= gy; y += 1024) {            // prefix along the rows: d[y][x] = instances of tile (x, y)
+        int acc = 0;
+        for (int x = 0; x <= gx; x++) { acc += d[y * gx1 + x]; d[y * gx1 + x] = acc; }
+    }
+    __syncthreads();
+    const int ntiles = gx * gy, per = (ntiles + 1023) / 1024;
+    const int i0 = min(ntiles, t * per), i1 = min(ntiles, i0 + per);
+    uint32_t mine = 0;
+    for (int i = i0; i < i1; i++) mine += (uint32_t)d[(i / gx) * gx1 + (i % gx)];
+    uint32_t start = block_excl_scan<32>(mine, warp_sum);
+    for (int i = i0; i < i1; i++) {
+        const uint32_t c = (uint32_t)d[(i / gx) * gx1 + (i % gx)];
+        ranges[i] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
+        start += c;
+        if (c)
+            for (int p = 0; p < td.npass; p++) atomicAdd(&sh[p * RS_NB + (((uint32_t)i >> td.shift[p]) & ((1u << td.bits[p]) - 1))], c);
+    }
+    __syncthreads();
+    for (int i = t; i < 4 * RS_NB; i += 1024) tile_hist[i] = sh[i];
+}
+
+int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im, cudaStream_t s)
+{
+    const GeomScratch sc = carve_geom_scratch(g.scratch, P);
+    const int gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
+    const int cells = (gx + 1) * (gy + 1);
+    const size_t smem = (size_t)cells * sizeof(int);
+    const TileDigits td = tile_digits((uint32_t)(gx * gy));
+    // instances per tile (depends on preprocess only): ranges + histograms of the tile split
+    if (smem <= 160 * 1024) {
+        if (smem > 40 * 1024) {
+            GSR_CUDA(cudaFuncSetAttribute(tile_count_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            GSR_CUDA(cudaFuncSetAttribute(tile_prefix_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        }
+        GSR_LAUNCH(tile_count_kernel<true>, min(cdiv(P, 4096), 148), 1024, smem, s, P, sc.rect, gx + 1, cells, im.tile_diff);
+        GSR_LAUNCH(tile_prefix_kernel<true>, 1, 1024, smem, s, gx, gy, im.tile_diff, im.ranges, sc.tile_hist, td);
+    } else {
+        GSR_LAUNCH(tile_count_kernel<false>, min(cdiv(P, 4096), 592), 1024, 0, s, P, sc.rect, gx + 1, cells, im.tile_diff);
+        GSR_LAUNCH(tile_prefix_kernel<false>, 1, 1024, 0, s, gx, gy, im.tile_diff, im.ranges, sc.tile_hist, td);
+    }
+    // depth keys were written by preprocess; the control block was zeroed before it
+    return radix_sort_by_key_u32(sc.depthkey, sc.K0, sc.K1, sc.V0, g.order, (uint32_t)P, sc.radix_ctl, true, s);
 }
 
 // ------------------------------------------------------------------ instance emission (in depth order)
-// Warp-cooperative: a warp takes 32 consecutive Gaussians of the depth order, and its lanes write the
-// warp's instances with consecutive lanes on consecutive output slots (coalesced), finding the owner of
-// slot t with a 5-step binary search over the lanes' offsets (shuffles).  Row-major over each
-// Gaussian's tile rect, exactly the order of duplicateWithKeys (rasterizer_impl.cu:98-109).
-__global__ void __launch_bounds__(256) emit_instances_kernel(int P, int gx, int gy, const uint32_t* __restrict__ order,
-                                                             const uint32_t* __restrict__ offs, const SplatRec* __restrict__ rec,
-                                                             uint32_t* __restrict__ tile_ids, uint32_t* __restrict__ gauss_ids)
+// Chunks of 256 depth-ordered Gaussians, taken by ticket.  The exclusive prefix of the tile counts (the reference's
+// InclusiveSum) is fused in: block scan + decoupled look-back over 64-bit per-chunk status words.  Emission is
+// warp-cooperative: a warp takes 32 consecutive Gaussians and its lanes write the warp's instances with consecutive
+// lanes on consecutive output slots (coalesced), finding the owner of slot t with a 5-step binary search over
+// the lanes' offsets (shuffles).  Row-major over each Gaussian's tile rect, exactly the order of duplicateWithKeys
+// (rasterizer_impl.cu:98-109).
+constexpr unsigned long long ES_AGG = 1ull << 62, ES_INC = 2ull << 62, ES_VAL = (1ull << 62) - 1;
+
+constexpr int EM_SUB = 4;                       // sub-rounds of 256 Gaussians per chunk (one look-back per chunk)
+constexpr int EM_CHUNK = 256 * EM_SUB;
+
+__global__ void __launch_bounds__(256) emit_instances_kernel(int P, int gx, const uint32_t* __restrict__ order,
+                                                             const ushort4* __restrict__ rect, uint32_t* __restrict__ tile_ids,
+                                                             uint32_t* __restrict__ gauss_ids,
+                                                             unsigned long long* __restrict__ estatus, uint32_t* __restrict__ ticket)
 {
+    __shared__ uint32_t warp_sum[8];
+    __shared__ uint32_t s_chunk, s_base;
     const int lane = threadIdx.x & 31;
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t g = 0, off = 0xFFFFFFFFu;
-    int x0 = 0, y0 = 0, wdt = 1, cnt = 0;
-    if (k < P) {
-        g = order[k];
-        off = offs[k];
-        const float4 q2 = rec[g].q2;
-        const int rad = __float_as_int(q2.z);
-        if (rad > 0) {
-            const float4 q0 = rec[g].q0;
-            // same rect as preprocess (auxiliary.h:46-56)
-            x0 = min(gx, max(0, (int)((q0.x - rad) / GSR_TILE)));
-            y0 = min(gy, max(0, (int)((q0.y - rad) / GSR_TILE)));
-            const int x1 = min(gx, max(0, (int)((q0.x + rad + GSR_TILE - 1) / GSR_TILE)));
-            const int y1 = min(gy, max(0, (int)((q0.y + rad + GSR_TILE - 1) / GSR_TILE)));
-            wdt = max(1, x1 - x0);
-            cnt = (x1 - x0) * (y1 - y0);
-        }
-    }
-    const uint32_t off0 = __shfl_sync(0xffffffffu, off, 0);
-    if (off0 == 0xFFFFFFFFu) return;                       // whole warp beyond P
-    const uint32_t rel = off - off0;                       // lanes beyond P carry a huge value: never owners
-    // total instances of this warp = end offset of the last lane
-    const uint32_t my_end = (k < P) ? rel + (uint32_t)cnt : 0u;
-    uint32_t total = my_end;
+    const int nchunks = (P + EM_CHUNK - 1) / EM_CHUNK;
+    while (true) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_chunk = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const int c = (int)s_chunk;
+        if (c >= nchunks) break;
+        uint32_t g[EM_SUB];
+        int x0[EM_SUB], y0[EM_SUB], wdt[EM_SUB], cnt[EM_SUB];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) total = max(total, __shfl_xor_sync(0xffffffffu, total, o));
-    for (uint32_t base = 0; base < total; base += 32) {
-        const uint32_t t = base + lane;
-        int lo = 0;
+        for (int r = 0; r < EM_SUB; r++) {
+            const int k = c * EM_CHUNK + r * 256 + threadIdx.x;
+            g[r] = k < P ? order[k] : 0xFFFFFFFFu;
+        }
 #pragma unroll
-        for (int s = 16; s > 0; s >>= 1) {
-            const uint32_t v = __shfl_sync(0xffffffffu, rel, lo + s);     // lo + s <= 31 always
-            if (v <= t) lo += s;
+        for (int r = 0; r < EM_SUB; r++) {
+            const ushort4 q = g[r] != 0xFFFFFFFFu ? rect[g[r]] : make_ushort4(0, 0, 0, 0);
+            x0[r] = q.x; y0[r] = q.y;
+            wdt[r] = max(1, (int)q.z - (int)q.x);
+            cnt[r] = ((int)q.z - (int)q.x) * ((int)q.w - (int)q.y);
         }
-        const uint32_t orel = __shfl_sync(0xffffffffu, rel, lo);
-        const int ox0 = __shfl_sync(0xffffffffu, x0, lo), oy0 = __shfl_sync(0xffffffffu, y0, lo);
-        const int ow = __shfl_sync(0xffffffffu, wdt, lo);
-        const uint32_t og = __shfl_sync(0xffffffffu, g, lo);
-        if (t < total) {
-            const uint32_t j = t - orel;
-            const uint32_t row = j / (uint32_t)ow, col = j - row * (uint32_t)ow;
-            tile_ids[off0 + t] = (uint32_t)((oy0 + (int)row) * gx + ox0 + (int)col);
-            gauss_ids[off0 + t] = og;
+        // exclusive offsets inside the chunk (sub-round major = depth order), chunk total
+        uint32_t excl[EM_SUB], run = 0;
+#pragma unroll
+        for (int r = 0; r < EM_SUB; r++) {
+            uint32_t tot;
+            excl[r] = run + block_excl_scan<8>((uint32_t)cnt[r], warp_sum, &tot);
+            run += tot;
+        }
+        if (threadIdx.x == 0) {
+            unsigned long long base = 0;
+            if (c == 0) st_volatile64(estatus, ES_INC | run);
+            else {
+                st_volatile64(estatus + c, ES_AGG | run);
+                for (int j = c - 1;; j--) {
+                    unsigned long long v;
+                    do { v = ld_volatile64(estatus + j); } while ((v >> 62) == 0);
+                    base += v & ES_VAL;
+                    if (v & ES_INC) break;
+                }
+                st_volatile64(estatus + c, ES_INC | (base + run));
+            }
+            s_base = (uint32_t)base;
+        }
+        __syncthreads();
+        const uint32_t chunk_base = s_base;
+#pragma unroll
+        for (int r = 0; r < EM_SUB; r++) {
+            const uint32_t off = chunk_base + excl[r];
+            const uint32_t off0 = __shfl_sync(0xffffffffu, off, 0);
+            const uint32_t rel = off - off0;
+            // total instances of this warp = end offset of the last lane
+            const uint32_t total = __shfl_sync(0xffffffffu, rel + (uint32_t)cnt[r], 31);
+            for (uint32_t base = 0; base < total; base += 32) {
+                const uint32_t t = base + lane;
+                int lo = 0;
+#pragma unroll
+                for (int s = 16; s > 0; s >>= 1) {
+                    const uint32_t v = __shfl_sync(0xffffffffu, rel, lo + s);     // lo + s <= 31 always
+                    if (v <= t) lo += s;
+                }
+                const uint32_t orel = __shfl_sync(0xffffffffu, rel, lo);
+                const int ox0 = __shfl_sync(0xffffffffu, x0[r], lo), oy0 = __shfl_sync(0xffffffffu, y0[r], lo);
+                const int ow = __shfl_sync(0xffffffffu, wdt[r], lo);
+                const uint32_t og = __shfl_sync(0xffffffffu, g[r], lo);
+                if (t < total) {
+                    const uint32_t j = t - orel;
+                    const uint32_t row = j / (uint32_t)ow, col = j - row * (uint32_t)ow;
+                    tile_ids[off0 + t] = (uint32_t)((oy0 + (int)row) * gx + ox0 + (int)col);
+                    gauss_ids[off0 + t] = og;
+                }
+            }
         }
     }
 }
 
-// ------------------------------------------------------------------ tile ranges from the sorted tile ids
-__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t R, const uint32_t* __restrict__ tile_sorted, uint2* __restrict__ ranges)
+// scratch layout (u32 words): T0[R] G0[R] T1[R] G1[R] status[sum over passes of nblk * 2^bits] tickets[64]
+static size_t bin_status_words(long long R)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= R) return;
-    const uint32_t cur = tile_sorted[i];
-    if (i == 0) ranges[cur].x = 0;
-    else {
-        const uint32_t prev = tile_sorted[i - 1];
-        if (cur != prev) { ranges[prev].y = i; ranges[cur].x = i; }
-    }
-    if (i == R - 1) ranges[cur].y = R;
+    return (size_t)4 * RS_NB * cdiv(R > 0 ? R : 1, RS_TILE) + 64;       // worst case: 4 passes of 8 bits
 }
-
-// host: position of the highest set bit + 1 (what the reference's getHigherMsb computes, rasterizer_impl.cu:35-50)
-static int tile_bits(uint32_t tiles)
-{
-    int b = 0;
-    while (b < 32 && (tiles >> b)) b++;
-    return b;
-}
-
-// scratch layout (u32 words): T0[R] G0[R] T1[R] G1[R] hist[256*nblk] totals[256]
 size_t bin_scratch_bytes(long long R)
 {
     const size_t Ra = align_up((size_t)(R > 0 ? R : 1), 64);
-    return 4 * (4 * Ra + align_up((size_t)RS_NB * cdiv(R > 0 ? R : 1, RS_TILE), 64) + RS_NB);
+    return 4 * (4 * Ra + bin_status_words(R));
 }
 
 int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s)
 {
     const int gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
-    GSR_CUDA(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)gx * gy, s));
+    (void)im;                            // ranges were written by tile_prefix_kernel
     if (R <= 0) return GSR_OK;
+    if (R >= (1ll << 30)) return GSR_ETOOBIG;
+    const GeomScratch sc = carve_geom_scratch(g.scratch, P);
     const size_t Ra = align_up((size_t)R, 64);
     uint32_t* T[2] = {b.scratch, b.scratch + 2 * Ra};
     uint32_t* G[2] = {b.scratch + Ra, b.scratch + 3 * Ra};
-    uint32_t* hist = b.scratch + 4 * Ra;
-    uint32_t* totals = hist + align_up((size_t)RS_NB * cdiv(R, RS_TILE), 64);
+    uint32_t* status = b.scratch + 4 * Ra;
+    const TileDigits td = tile_digits((uint32_t)(gx * gy));
+    const int nblk = cdiv(R, RS_TILE);
+    size_t status_words = 64;
+    for (int p = 0; p < td.npass; p++) status_words += (size_t)nblk << td.bits[p];
+    GSR_CUDA(cudaMemsetAsync(status, 0, status_words * 4, s));
+    uint32_t* tickets = status;          // first 64 words
+    uint32_t* st = status + 64;
 
-    GSR_LAUNCH(emit_instances_kernel, cdiv(P, 256), 256, 0, s, P, gx, gy, g.order, g.offs, g.rec, T[0], G[0]);
-
-    const int tb = tile_bits((uint32_t)(gx * gy));
-    const int npass = tb <= 8 ? 1 : (tb + 7) / 8;
-    int shift = 0, cur = 0;
-    for (int p = 0; p < npass; p++) {
-        const int bits = (tb - shift + (npass - p) - 1) / (npass - p);    // balanced digits, e.g. 13 -> 7 + 6
-        const bool last = p == npass - 1;
-        int rc = radix_pass(T[cur], G[cur], T[cur ^ 1], last ? b.vals : G[cur ^ 1], (uint32_t)R, shift, bits, hist, totals, s);
+    GSR_LAUNCH(emit_instances_kernel, min(cdiv(P, EM_CHUNK), 148 * 8), 256, 0, s, P, gx, g.order, sc.rect, T[0], G[0], sc.emit_status,
+               sc.counters + 1);
+    int cur = 0;
+    for (int p = 0; p < td.npass; p++) {
+        const bool last = p == td.npass - 1;
+        int rc = radix_pass(T[cur], G[cur], last ? nullptr : T[cur ^ 1], last ? b.vals : G[cur ^ 1], (uint32_t)R, td.shift[p], td.bits[p],
+                            sc.tile_hist + p * RS_NB, st, tickets + p, s);
         if (rc) return rc;
-        shift += bits; cur ^= 1;
+        st += (size_t)nblk << td.bits[p];
+        cur ^= 1;
     }
-    GSR_LAUNCH(tile_ranges_kernel, cdiv(R, 256), 256, 0, s, (uint32_t)R, T[cur], im.ranges);
     return GSR_OK;
 }
 
