@@ -45,6 +45,8 @@ def parse_args():
     ap.add_argument("--gaussians", type=int, default=0, help="override P (debug only; makes the number invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--plain-autograd", action="store_true",
+                    help="sum the views' gradients through autograd (.grad += per parameter) instead of in the backward kernels")
     return ap.parse_args()
 
 
@@ -211,11 +213,20 @@ def main():
 
     stats = {"R": 0, "Pv": 0, "views": 0}
 
+    fused = not args.plain_autograd
+
+    def grad_mode(i):
+        # view 0 of the step overwrites the flat gradient buffer, the following views add to it (in the kernels)
+        return dgr.set_grad_mode(("overwrite" if i == 0 else "accumulate") if fused else None)
+
     def step_device(step, collect=False):
-        flat.zero_()
-        for k in my_views(step):
+        if not fused:
+            flat.zero_()
+        for i, k in enumerate(my_views(step)):
+            prev = grad_mode(i)
             color, radii, _ = dp.render_view(dgr, params, cams[k], bg, spec.D)
             color.backward(go)
+            dgr.set_grad_mode(prev)
             if collect:
                 stats["Pv"] += int((radii > 0).sum())
                 stats["views"] += 1
@@ -230,14 +241,17 @@ def main():
     d2h_view = 4
 
     def step_e2e(step):
-        flat.zero_()
-        for k in my_views(step):
+        if not fused:
+            flat.zero_()
+        for i, k in enumerate(my_views(step)):
+            prev = grad_mode(i)
             tgt = target_host.to(dev, non_blocking=True)
             cm = cam_host[k].to(dev, non_blocking=True)
             cam = synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cm[:16].view(4, 4), cm[16:32].view(4, 4), cm[32:35])
             color, radii, _ = dp.render_view(dgr, params, cam, bg, spec.D)
             loss = (color - tgt).abs().mean()
             loss.backward()
+            dgr.set_grad_mode(prev)
             _ = float(loss.item())          # device -> host read of the step's result
         flat.all_reduce()
 
@@ -327,6 +341,7 @@ def main():
                 "config": {"workload": WORKLOAD, "P": P, "W": spec.W, "H": spec.H, "sh_degree": spec.D, "views_per_step": vps * world,
                            "views_per_gpu_per_step": vps, "R_per_view": R, "visible_per_view": int(Pv),
                            "parallelism": "view-sharded dp%d, one NCCL all-reduce of %d MB per step" % (world, flat.nbytes() >> 20),
+                           "grad_sum": "in the backward kernels (set_grad_mode)" if fused else "autograd .grad +=",
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat.nbytes() + 48 * P + 20 * R) / 1e9)},
                 "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches,

@@ -122,7 +122,17 @@ typedef struct GsrBwdArgs {
     float* dL_dscale;            /* [P,3];   required iff scales != NULL */
     float* dL_drot;              /* [P,4];   required iff rotations != NULL */
     int    debug;
+    /* GSR_ACC_* bits.  A flagged output is ACCUMULATED: rows of visible Gaussians are added to what the buffer
+       holds, rows of culled Gaussians are left untouched (multi-view steps sum parameter gradients in place
+       instead of through one extra elementwise add per output and view).  0 = overwrite everything (reference). */
+    unsigned accumulate;
 } GsrBwdArgs;
+
+#define GSR_ACC_MEAN3D   1u
+#define GSR_ACC_OPACITY  2u
+#define GSR_ACC_SH       4u
+#define GSR_ACC_SCALE    8u
+#define GSR_ACC_ROT     16u
 
 int gsr_backward(const GsrBwdArgs* args, gsr_stream_t stream);
 

@@ -37,10 +37,19 @@ struct PreBwdArgs {
     float* dL_dsh;           // [P,M,3] or null
     float* dL_dscale;        // [P,3] or null
     float* dL_drot;          // [P,4] or null
+    unsigned acc;            // GSR_ACC_* bits: add to the existing contents (visible rows only) instead of overwriting
+    int sh_done;             // the SH part (dL_dsh, its share of dL_dmean3D) was done by sh_bwd_m16_kernel
 };
 
-__device__ __forceinline__ void store_sh_grads(float* __restrict__ dst, const float* g, int nfloats, int total_floats)
+// out = v, or out += v when accumulating
+__device__ __forceinline__ void put(float* p, float v, bool acc) { *p = acc ? *p + v : v; }
+
+__device__ __forceinline__ void store_sh_grads(float* __restrict__ dst, const float* g, int nfloats, int total_floats, bool acc = false)
 {
+    if (acc) {      // read-modify-write of the live coefficients only
+        for (int i = 0; i < nfloats; i++) dst[i] += g[i];
+        return;
+    }
     // g holds nfloats live values, the rest of the row is zero
     const bool vec = ((((size_t)dst) & 15) == 0) && (total_floats % 4 == 0);
     if (vec) {
@@ -65,7 +74,8 @@ __device__ __forceinline__ void store_sh_grads(float* __restrict__ dst, const fl
     }
 }
 
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, CameraArgs ca)
+template <bool WITH_SH>
+__global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(PreBwdArgs a, CameraArgs ca)
 {
     __shared__ Camera cam;
     load_camera(cam, ca);
@@ -73,22 +83,24 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, Camer
     if (idx >= a.P) return;
     const int M3f = 3 * a.M;
 
+    const bool acc_m = a.acc & GSR_ACC_MEAN3D, acc_o = a.acc & GSR_ACC_OPACITY, acc_sh = a.acc & GSR_ACC_SH,
+               acc_s = a.acc & GSR_ACC_SCALE, acc_r = a.acc & GSR_ACC_ROT;
     if (!(a.radii[idx] > 0)) {
-        // culled: every owned gradient row is zero
+        // culled: every owned gradient row is zero (left untouched when accumulating)
         a.dL_dmean2D[3 * idx] = 0.f; a.dL_dmean2D[3 * idx + 1] = 0.f; a.dL_dmean2D[3 * idx + 2] = 0.f;
-        a.dL_dopacity[idx] = 0.f;
-        a.dL_dmean3D[3 * idx] = 0.f; a.dL_dmean3D[3 * idx + 1] = 0.f; a.dL_dmean3D[3 * idx + 2] = 0.f;
+        if (!acc_o) a.dL_dopacity[idx] = 0.f;
+        if (!acc_m && !a.sh_done) { a.dL_dmean3D[3 * idx] = 0.f; a.dL_dmean3D[3 * idx + 1] = 0.f; a.dL_dmean3D[3 * idx + 2] = 0.f; }
         if (a.dL_dcolor) { a.dL_dcolor[3 * idx] = 0.f; a.dL_dcolor[3 * idx + 1] = 0.f; a.dL_dcolor[3 * idx + 2] = 0.f; }
         if (a.dL_dcov3D) {
 #pragma unroll
             for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * (size_t)idx + k] = 0.f;
         }
-        if (a.dL_dsh) {
+        if (WITH_SH && a.dL_dsh && !acc_sh && !a.sh_done) {
             float z[1] = {0.f};
             store_sh_grads(a.dL_dsh + (size_t)M3f * idx, z, 0, M3f);
         }
-        if (a.dL_dscale) { a.dL_dscale[3 * idx] = 0.f; a.dL_dscale[3 * idx + 1] = 0.f; a.dL_dscale[3 * idx + 2] = 0.f; }
-        if (a.dL_drot) {
+        if (a.dL_dscale && !acc_s) { a.dL_dscale[3 * idx] = 0.f; a.dL_dscale[3 * idx + 1] = 0.f; a.dL_dscale[3 * idx + 2] = 0.f; }
+        if (a.dL_drot && !acc_r) {
             a.dL_drot[4 * idx] = 0.f; a.dL_drot[4 * idx + 1] = 0.f; a.dL_drot[4 * idx + 2] = 0.f; a.dL_drot[4 * idx + 3] = 0.f;
         }
         return;
@@ -105,7 +117,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, Camer
     const float g2y = -0.5f * cam.H * (cC * A1.x + cB * A0.w);
     const float dcon_x = -0.5f * A1.y, dcon_y = -0.5f * A1.z, dcon_w = -0.5f * A1.w;
     a.dL_dmean2D[3 * idx] = g2x; a.dL_dmean2D[3 * idx + 1] = g2y; a.dL_dmean2D[3 * idx + 2] = 0.f;
-    a.dL_dopacity[idx] = opac > 0.f ? A2.x / opac : 0.f;
+    put(a.dL_dopacity + idx, opac > 0.f ? A2.x / opac : 0.f, acc_o);
     if (a.dL_dcolor) { a.dL_dcolor[3 * idx] = dcol[0]; a.dL_dcolor[3 * idx + 1] = dcol[1]; a.dL_dcolor[3 * idx + 2] = dcol[2]; }
 
     const float3 p = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
@@ -210,7 +222,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, Camer
     }
 
     // ---- SH backward (backward.cu:20-139)
-    if (a.shs) {
+    if (WITH_SH && a.shs && !a.sh_done) {
         const float ox = p.x - cam.cam[0], oy = p.y - cam.cam[1], oz = p.z - cam.cam[2];
         const float s2 = ox * ox + oy * oy + oz * oz;
         const float len = sqrtf(s2);
@@ -277,7 +289,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, Camer
         // dL/dsh[k][ch] = basis_k * dL/dRGB[ch]; reuse f as the output row
 #pragma unroll
         for (int k = 0; k < 16; k++) { f[3 * k] = w[k] * dRGB[0]; f[3 * k + 1] = w[k] * dRGB[1]; f[3 * k + 2] = w[k] * dRGB[2]; }
-        store_sh_grads(a.dL_dsh + (size_t)M3f * idx, f, 3 * ncoef, M3f);
+        store_sh_grads(a.dL_dsh + (size_t)M3f * idx, f, 3 * ncoef, M3f, acc_sh);
 
         const float ddx = gx[0] * dRGB[0] + gx[1] * dRGB[1] + gx[2] * dRGB[2];
         const float ddy = gy[0] * dRGB[0] + gy[1] * dRGB[1] + gy[2] * dRGB[2];
@@ -288,7 +300,10 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, Camer
         dmy += (-ox * oy * ddx + (s2 - oy * oy) * ddy - oz * oy * ddz) * inv;
         dmz += (-ox * oz * ddx - oy * oz * ddy + (s2 - oz * oz) * ddz) * inv;
     }
-    a.dL_dmean3D[3 * idx] = dmx; a.dL_dmean3D[3 * idx + 1] = dmy; a.dL_dmean3D[3 * idx + 2] = dmz;
+    {
+        const bool add = acc_m || a.sh_done;       // sh_bwd_m16_kernel has already written its share
+        put(a.dL_dmean3D + 3 * idx, dmx, add); put(a.dL_dmean3D + 3 * idx + 1, dmy, add); put(a.dL_dmean3D + 3 * idx + 2, dmz, add);
+    }
 
     // ---- cov3D -> scale / rotation (backward.cu:278-341; no quaternion-normalisation Jacobian)
     if (a.dL_dscale) {
@@ -304,7 +319,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, Camer
 #pragma unroll
         for (int k = 0; k < 3; k++) dsv[k] = Rt.c[k][0] * dMt.c[k][0] + Rt.c[k][1] * dMt.c[k][1] + Rt.c[k][2] * dMt.c[k][2];
         // parity quirk: like the reference (backward.cu:322-325) this is the gradient w.r.t. mod*scale, NOT multiplied by mod
-        a.dL_dscale[3 * idx] = dsv[0]; a.dL_dscale[3 * idx + 1] = dsv[1]; a.dL_dscale[3 * idx + 2] = dsv[2];
+        put(a.dL_dscale + 3 * idx, dsv[0], acc_s); put(a.dL_dscale + 3 * idx + 1, dsv[1], acc_s); put(a.dL_dscale + 3 * idx + 2, dsv[2], acc_s);
         const float sv[3] = {sc.x, sc.y, sc.z};
 #pragma unroll
         for (int k = 0; k < 3; k++)
@@ -312,11 +327,156 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreBwdArgs a, Camer
             for (int j = 0; j < 3; j++) dMt.c[k][j] *= sv[k];
         const float r = q.x, x = q.y, y = q.z, z = q.w;
 #define D_(i, j) dMt.c[i][j]
-        a.dL_drot[4 * idx + 0] = 2 * z * (D_(0, 1) - D_(1, 0)) + 2 * y * (D_(2, 0) - D_(0, 2)) + 2 * x * (D_(1, 2) - D_(2, 1));
-        a.dL_drot[4 * idx + 1] = 2 * y * (D_(1, 0) + D_(0, 1)) + 2 * z * (D_(2, 0) + D_(0, 2)) + 2 * r * (D_(1, 2) - D_(2, 1)) - 4 * x * (D_(2, 2) + D_(1, 1));
-        a.dL_drot[4 * idx + 2] = 2 * x * (D_(1, 0) + D_(0, 1)) + 2 * r * (D_(2, 0) - D_(0, 2)) + 2 * z * (D_(1, 2) + D_(2, 1)) - 4 * y * (D_(2, 2) + D_(0, 0));
-        a.dL_drot[4 * idx + 3] = 2 * r * (D_(0, 1) - D_(1, 0)) + 2 * x * (D_(2, 0) + D_(0, 2)) + 2 * y * (D_(1, 2) + D_(2, 1)) - 4 * z * (D_(1, 1) + D_(0, 0));
+        put(a.dL_drot + 4 * idx + 0, 2 * z * (D_(0, 1) - D_(1, 0)) + 2 * y * (D_(2, 0) - D_(0, 2)) + 2 * x * (D_(1, 2) - D_(2, 1)), acc_r);
+        put(a.dL_drot + 4 * idx + 1, 2 * y * (D_(1, 0) + D_(0, 1)) + 2 * z * (D_(2, 0) + D_(0, 2)) + 2 * r * (D_(1, 2) - D_(2, 1)) - 4 * x * (D_(2, 2) + D_(1, 1)), acc_r);
+        put(a.dL_drot + 4 * idx + 2, 2 * x * (D_(1, 0) + D_(0, 1)) + 2 * r * (D_(2, 0) - D_(0, 2)) + 2 * z * (D_(1, 2) + D_(2, 1)) - 4 * y * (D_(2, 2) + D_(0, 0)), acc_r);
+        put(a.dL_drot + 4 * idx + 3, 2 * r * (D_(0, 1) - D_(1, 0)) + 2 * x * (D_(2, 0) + D_(0, 2)) + 2 * y * (D_(1, 2) + D_(2, 1)) - 4 * z * (D_(1, 1) + D_(0, 0)), acc_r);
 #undef D_
+    }
+}
+
+// ------------------------------------------------------------------ SH backward, 16 coefficients per Gaussian
+// One lane per Gaussian for the arithmetic, but the 192-byte SH rows travel through shared memory: a warp loads the
+// 32 rows it owns as 12 fully coalesced float4 loads per lane (6 KB contiguous), each lane then walks ITS row in
+// four chunks of 4 coefficients (3 x LDS.128, rows padded to 13 float4 so the 8 lanes of a phase hit distinct
+// banks), overwrites the chunk with dL/dsh = basis_k * dL/dRGB, and the rows go back out coalesced (added to
+// the destination when accumulating).  The direction gradient sum_k dbasis_k/d(x,y,z) * (sh_k . dL/dRGB) stays in
+// registers; dnormvdv (auxiliary.h:107-117) turns it into this part of dL/dmean3D.  Restates backward.cu:20-139.
+constexpr int SHB_WARPS = 4;
+constexpr int SHB_ROW4 = 13;            // padded row length in float4
+
+// basis and derivative of coefficients 4*J .. 4*J+3 (constants auxiliary.h:22-39, signs forward.cu:30-59)
+template <int J>
+__device__ __forceinline__ void sh_chunk(int D, float x, float y, float z, float* w, float* bx, float* by, float* bz)
+{
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+#pragma unroll
+    for (int k = 0; k < 4; k++) { w[k] = 0.f; bx[k] = 0.f; by[k] = 0.f; bz[k] = 0.f; }
+    if (J == 0) {
+        w[0] = GSR_SH_C0;
+        if (D > 0) {
+            w[1] = -GSR_SH_C1 * y; by[1] = -GSR_SH_C1;
+            w[2] = GSR_SH_C1 * z; bz[2] = GSR_SH_C1;
+            w[3] = -GSR_SH_C1 * x; bx[3] = -GSR_SH_C1;
+        }
+    } else if (J == 1) {
+        if (D > 1) {
+            w[0] = GSR_SH_C2_0 * xy; bx[0] = GSR_SH_C2_0 * y; by[0] = GSR_SH_C2_0 * x;
+            w[1] = GSR_SH_C2_1 * yz; by[1] = GSR_SH_C2_1 * z; bz[1] = GSR_SH_C2_1 * y;
+            w[2] = GSR_SH_C2_2 * (2.f * zz - xx - yy); bx[2] = GSR_SH_C2_2 * -2.f * x; by[2] = GSR_SH_C2_2 * -2.f * y; bz[2] = GSR_SH_C2_2 * 4.f * z;
+            w[3] = GSR_SH_C2_3 * xz; bx[3] = GSR_SH_C2_3 * z; bz[3] = GSR_SH_C2_3 * x;
+        }
+    } else if (J == 2) {
+        if (D > 1) { w[0] = GSR_SH_C2_4 * (xx - yy); bx[0] = GSR_SH_C2_4 * 2.f * x; by[0] = GSR_SH_C2_4 * -2.f * y; }
+        if (D > 2) {
+            w[1] = GSR_SH_C3_0 * y * (3.f * xx - yy); bx[1] = GSR_SH_C3_0 * 6.f * xy; by[1] = GSR_SH_C3_0 * 3.f * (xx - yy);
+            w[2] = GSR_SH_C3_1 * xy * z; bx[2] = GSR_SH_C3_1 * yz; by[2] = GSR_SH_C3_1 * xz; bz[2] = GSR_SH_C3_1 * xy;
+            w[3] = GSR_SH_C3_2 * y * (4.f * zz - xx - yy); bx[3] = GSR_SH_C3_2 * -2.f * xy;
+            by[3] = GSR_SH_C3_2 * (-3.f * yy + 4.f * zz - xx); bz[3] = GSR_SH_C3_2 * 8.f * yz;
+        }
+    } else {
+        if (D > 2) {
+            w[0] = GSR_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy); bx[0] = GSR_SH_C3_3 * -6.f * xz; by[0] = GSR_SH_C3_3 * -6.f * yz;
+            bz[0] = GSR_SH_C3_3 * 3.f * (2.f * zz - xx - yy);
+            w[1] = GSR_SH_C3_4 * x * (4.f * zz - xx - yy); bx[1] = GSR_SH_C3_4 * (-3.f * xx + 4.f * zz - yy); by[1] = GSR_SH_C3_4 * -2.f * xy;
+            bz[1] = GSR_SH_C3_4 * 8.f * xz;
+            w[2] = GSR_SH_C3_5 * z * (xx - yy); bx[2] = GSR_SH_C3_5 * 2.f * xz; by[2] = GSR_SH_C3_5 * -2.f * yz; bz[2] = GSR_SH_C3_5 * (xx - yy);
+            w[3] = GSR_SH_C3_6 * x * (xx - 3.f * yy); bx[3] = GSR_SH_C3_6 * 3.f * (xx - yy); by[3] = GSR_SH_C3_6 * -6.f * xy;
+        }
+    }
+}
+
+template <int J>
+__device__ __forceinline__ void sh_chunk_apply(float4* row, int D, float x, float y, float z, float dR, float dG, float dB, float& ddx,
+                                               float& ddy, float& ddz)
+{
+    float w[4], bx[4], by[4], bz[4];
+    sh_chunk<J>(D, x, y, z, w, bx, by, bz);
+    const float4 s0 = row[3 * J], s1 = row[3 * J + 1], s2 = row[3 * J + 2];
+    const float f[12] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w, s2.x, s2.y, s2.z, s2.w};
+    float g[12];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float sd = f[3 * k] * dR + f[3 * k + 1] * dG + f[3 * k + 2] * dB;
+        ddx += bx[k] * sd; ddy += by[k] * sd; ddz += bz[k] * sd;
+        g[3 * k] = w[k] * dR; g[3 * k + 1] = w[k] * dG; g[3 * k + 2] = w[k] * dB;
+    }
+    row[3 * J] = make_float4(g[0], g[1], g[2], g[3]);
+    row[3 * J + 1] = make_float4(g[4], g[5], g[6], g[7]);
+    row[3 * J + 2] = make_float4(g[8], g[9], g[10], g[11]);
+}
+
+__global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D, const float* __restrict__ means,
+                                                                    const int* __restrict__ radii, const float* __restrict__ shs,
+                                                                    const uint8_t* __restrict__ clamped, const float* __restrict__ accum,
+                                                                    const float* __restrict__ campos, float* __restrict__ dL_dsh,
+                                                                    float* __restrict__ dL_dmean3D, unsigned acc)
+{
+    __shared__ float4 rows[SHB_WARPS][32 * SHB_ROW4];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int g0 = (blockIdx.x * SHB_WARPS + w) * 32;
+    if (g0 >= P) return;
+    const int nrow = min(32, P - g0);
+    const bool acc_sh = acc & GSR_ACC_SH, acc_m = acc & GSR_ACC_MEAN3D;
+    float4* my = rows[w];
+    const int gid = g0 + lane;
+    const bool visible = lane < nrow && radii[gid] > 0;
+    const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
+    // stage in (rows of culled Gaussians are not needed)
+    const float4* src = reinterpret_cast<const float4*>(shs) + (size_t)g0 * 12;
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+        const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
+        if ((vis_mask >> r) & 1u) my[r * SHB_ROW4 + c] = __ldg(src + e);
+    }
+    __syncwarp();
+    if (visible) {
+        const float4 A0 = *reinterpret_cast<const float4*>(accum + (size_t)12 * gid);
+        const uint32_t cl = clamped[gid];
+        const float dR = (cl & 1) ? 0.f : A0.x, dG = (cl & 2) ? 0.f : A0.y, dB = (cl & 4) ? 0.f : A0.z;
+        const float ox = means[3 * (size_t)gid] - campos[0], oy = means[3 * (size_t)gid + 1] - campos[1],
+                    oz = means[3 * (size_t)gid + 2] - campos[2];
+        const float sq = ox * ox + oy * oy + oz * oz;
+        const float rl = rsqrtf(sq);
+        const float x = ox * rl, y = oy * rl, z = oz * rl;
+        float ddx = 0.f, ddy = 0.f, ddz = 0.f;
+        float4* row = my + lane * SHB_ROW4;
+        sh_chunk_apply<0>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+        sh_chunk_apply<1>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+        sh_chunk_apply<2>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+        sh_chunk_apply<3>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+        const float inv = rl * rl * rl;          // 1 / |o|^3
+        put(dL_dmean3D + 3 * (size_t)gid, ((sq - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * inv, acc_m);
+        put(dL_dmean3D + 3 * (size_t)gid + 1, (-ox * oy * ddx + (sq - oy * oy) * ddy - oz * oy * ddz) * inv, acc_m);
+        put(dL_dmean3D + 3 * (size_t)gid + 2, (-ox * oz * ddx - oy * oz * ddy + (sq - oz * oz) * ddz) * inv, acc_m);
+    } else if (lane < nrow && !acc_m) {
+        dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f;
+    }
+    __syncwarp();
+    // stage out
+    float4* dst = reinterpret_cast<float4*>(dL_dsh) + (size_t)g0 * 12;
+    if (acc_sh) {
+        // all twelve reads of the destination are issued before the first dependent store
+        float4 o[12];
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane, r = e / 12;
+            o[i] = (r < nrow && ((vis_mask >> r) & 1u)) ? dst[e] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
+            if (r < nrow && ((vis_mask >> r) & 1u)) {
+                const float4 v = my[r * SHB_ROW4 + c];
+                dst[e] = make_float4(o[i].x + v.x, o[i].y + v.y, o[i].z + v.z, o[i].w + v.w);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
+            if (r < nrow) dst[e] = ((vis_mask >> r) & 1u) ? my[r * SHB_ROW4 + c] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
     }
 }
 
@@ -332,7 +492,15 @@ int launch_preprocess_backward(const GsrBwdArgs& a, const GeomView& g, const flo
     k.dL_dmean3D = a.dL_dmean3D; k.dL_dcov3D = a.dL_dcov3D; k.dL_dsh = a.shs ? a.dL_dsh : nullptr;
     k.dL_dscale = a.cov3D_precomp ? nullptr : a.dL_dscale;
     k.dL_drot = a.cov3D_precomp ? nullptr : a.dL_drot;
-    GSR_LAUNCH(preprocess_bwd_kernel, cdiv(a.P, 256), 256, 0, s, k, cam);
+    k.acc = a.accumulate;
+    k.sh_done = 0;
+    if (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && env_int("GSR_SH_SPLIT", 1)) {
+        GSR_LAUNCH(sh_bwd_m16_kernel, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs, g.clamped, accum, a.cam_pos,
+                   a.dL_dsh, a.dL_dmean3D, a.accumulate);
+        k.sh_done = 1;
+    }
+    if (k.sh_done || !a.shs) GSR_LAUNCH(preprocess_bwd_kernel<false>, cdiv(a.P, 256), 256, 0, s, k, cam);
+    else GSR_LAUNCH(preprocess_bwd_kernel<true>, cdiv(a.P, 256), 256, 0, s, k, cam);
     return GSR_OK;
 }
 

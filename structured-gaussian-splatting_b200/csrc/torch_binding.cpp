@@ -86,14 +86,19 @@ rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3
 }
 
 std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
-rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
-                             const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
-                             const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
-                             const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
-                             const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
-                             const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
-                             const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug)
+rasterize_gaussians_backward_into(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                                  const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
+                                  const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                                  const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                                  const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                                  const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
+                                  const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
+                                  const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
+                                  const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate)
 {
+    // Extension of the reference entry point: a non-empty `into_*` tensor (contiguous fp32 CUDA, same element count as
+    // the gradient) receives that gradient directly - overwritten, or added to when `accumulate` - and the
+    // corresponding slot of the returned tuple is an empty tensor.
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
     const c10::cuda::CUDAGuard guard(means3D.device());
     const int P = (int)means3D.size(0);
@@ -106,14 +111,28 @@ rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tenso
 
     // the core writes every element of every gradient it is given: no zero-fill (reference: nine torch::zeros)
     auto alloc = [&](std::initializer_list<int64_t> shape) { return P == 0 ? torch::zeros(shape, f32) : torch::empty(shape, f32); };
-    torch::Tensor dL_dmeans3D = alloc({P, 3});
+    unsigned acc_bits = 0;
+    auto target = [&](const torch::Tensor& into, int64_t numel, unsigned bit) -> float* {
+        if (into.numel() == 0) return nullptr;
+        TORCH_CHECK(into.is_cuda() && into.scalar_type() == torch::kFloat32 && into.is_contiguous() && into.numel() == numel,
+                    "gradient target must be a contiguous fp32 CUDA tensor with the gradient's element count");
+        if (accumulate) acc_bits |= bit;
+        return into.data_ptr<float>();
+    };
+    float* t_m3 = target(into_means3D, (int64_t)P * 3, GSR_ACC_MEAN3D);
+    float* t_op = target(into_opacity, (int64_t)P, GSR_ACC_OPACITY);
+    float* t_sh = target(into_sh, (int64_t)P * M * 3, GSR_ACC_SH);
+    float* t_sc = has_sr ? target(into_scales, (int64_t)P * 3, GSR_ACC_SCALE) : nullptr;
+    float* t_rt = has_sr ? target(into_rotations, (int64_t)P * 4, GSR_ACC_ROT) : nullptr;
+    auto none = [&]() { return torch::empty({0}, f32); };
+    torch::Tensor dL_dmeans3D = t_m3 ? none() : alloc({P, 3});
     torch::Tensor dL_dmeans2D = alloc({P, 3});
-    torch::Tensor dL_dcolors = want_colors ? alloc({P, 3}) : torch::empty({0}, f32);
-    torch::Tensor dL_dopacity = alloc({P, 1});
-    torch::Tensor dL_dcov3D = want_cov ? alloc({P, 6}) : torch::empty({0}, f32);
-    torch::Tensor dL_dsh = alloc({P, M, 3});
-    torch::Tensor dL_dscales = has_sr ? alloc({P, 3}) : torch::empty({0}, f32);
-    torch::Tensor dL_drotations = has_sr ? alloc({P, 4}) : torch::empty({0}, f32);
+    torch::Tensor dL_dcolors = want_colors ? alloc({P, 3}) : none();
+    torch::Tensor dL_dopacity = t_op ? none() : alloc({P, 1});
+    torch::Tensor dL_dcov3D = want_cov ? alloc({P, 6}) : none();
+    torch::Tensor dL_dsh = t_sh ? none() : alloc({P, M, 3});
+    torch::Tensor dL_dscales = (has_sr && !t_sc) ? alloc({P, 3}) : none();
+    torch::Tensor dL_drotations = (has_sr && !t_rt) ? alloc({P, 4}) : none();
 
     if (P != 0) {
         torch::Tensor accum = torch::empty({(long long)(gsr_bwd_accum_bytes(P) / sizeof(float))}, f32);
@@ -131,17 +150,34 @@ rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tenso
         a.dL_dpix = dpix.ptr();
         a.accum = accum.data_ptr();
         a.dL_dmean2D = dL_dmeans2D.data_ptr<float>();
-        a.dL_dopacity = dL_dopacity.data_ptr<float>();
-        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>();
+        a.dL_dopacity = t_op ? t_op : dL_dopacity.data_ptr<float>();
+        a.dL_dmean3D = t_m3 ? t_m3 : dL_dmeans3D.data_ptr<float>();
         a.dL_dcolor = want_colors ? dL_dcolors.data_ptr<float>() : nullptr;
         a.dL_dcov3D = want_cov ? dL_dcov3D.data_ptr<float>() : nullptr;
-        a.dL_dsh = M > 0 ? dL_dsh.data_ptr<float>() : nullptr;
-        a.dL_dscale = has_sr ? dL_dscales.data_ptr<float>() : nullptr;
-        a.dL_drot = has_sr ? dL_drotations.data_ptr<float>() : nullptr;
+        a.dL_dsh = M > 0 ? (t_sh ? t_sh : dL_dsh.data_ptr<float>()) : nullptr;
+        a.dL_dscale = has_sr ? (t_sc ? t_sc : dL_dscales.data_ptr<float>()) : nullptr;
+        a.dL_drot = has_sr ? (t_rt ? t_rt : dL_drotations.data_ptr<float>()) : nullptr;
         a.debug = debug;
+        a.accumulate = acc_bits;
         check(gsr_backward(&a, current_stream()), "rasterize_gaussians_backward");
     }
     return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+}
+
+// the reference's entry point (rasterize_points.h:40-62): every gradient freshly allocated
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                             const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
+                             const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                             const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                             const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                             const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
+                             const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug)
+{
+    const torch::Tensor e = torch::empty({0});
+    return rasterize_gaussians_backward_into(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                             viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer,
+                                             R, binningBuffer, imageBuffer, debug, e, e, e, e, e, false);
 }
 
 torch::Tensor mark_visible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix)
@@ -198,6 +234,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
 {
     m.def("rasterize_gaussians", &rasterize_gaussians);
     m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
+    m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into);
     m.def("mark_visible", &mark_visible);
     m.def("distCUDA2", &distCUDA2);
     m.def("export_binning", &export_binning);

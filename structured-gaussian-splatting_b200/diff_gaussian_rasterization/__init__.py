@@ -34,6 +34,33 @@ def _call_with_snapshot(fn, args, debug, dump_name, stage):
         raise
 
 
+# ---- extension (off by default): gradients straight into the leaf parameters' .grad buffers -------------------
+# A multi-view step sums the parameter gradients of its views.  Through plain autograd every view costs one
+# elementwise `grad += new` per parameter (3 x 236 B per Gaussian at SH degree 3) on top of the backward's own
+# writes.  With a mode set here, an input that IS a leaf parameter with a preallocated contiguous fp32 .grad gets
+# its gradient written (mode "overwrite") or added (mode "accumulate") by the backward kernels themselves, and
+# autograd receives None for it.  Inputs that are not such leaves (the reference trainer passes activations)
+# are unaffected, as is everything when the mode is None.
+_GRAD_MODE = None
+
+
+def set_grad_mode(mode):
+    """None (reference behaviour), "overwrite" or "accumulate"; returns the previous mode."""
+    global _GRAD_MODE
+    if mode not in (None, "overwrite", "accumulate"):
+        raise ValueError("grad mode must be None, 'overwrite' or 'accumulate'")
+    prev, _GRAD_MODE = _GRAD_MODE, mode
+    return prev
+
+
+def _grad_target(t):
+    g = getattr(t, "grad", None)
+    if (t.numel() != 0 and t.is_leaf and t.requires_grad and g is not None and g.is_cuda and g.dtype == torch.float32
+            and g.is_contiguous() and g.numel() == t.numel()):
+        return g
+    return None
+
+
 class GaussianRasterizationSettings(NamedTuple):
     image_height: int
     image_width: int
@@ -61,6 +88,9 @@ class _RasterizeGaussians(torch.autograd.Function):
             _C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward")
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
+        ctx.grad_mode = _GRAD_MODE
+        if _GRAD_MODE is not None:
+            ctx.grad_targets = tuple(_grad_target(t) for t in (means3D, opacities, sh, scales, rotations))
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
                               binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
@@ -75,11 +105,26 @@ class _RasterizeGaussians(torch.autograd.Function):
         args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix,
                 rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, sh, rs.sh_degree, rs.campos, geomBuffer,
                 ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
-        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
-         grad_rotations) = _call_with_snapshot(_C.rasterize_gaussians_backward, args, rs.debug, "snapshot_bw.dump", "backward")
+        if ctx.grad_mode is None:
+            (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+             grad_rotations) = _call_with_snapshot(_C.rasterize_gaussians_backward, args, rs.debug, "snapshot_bw.dump", "backward")
+        else:
+            empty = torch.Tensor([])
+            into = tuple(empty if t is None else t for t in ctx.grad_targets)
+            (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+             grad_rotations) = _call_with_snapshot(_C.rasterize_gaussians_backward_into,
+                                                   args + into + (ctx.grad_mode == "accumulate",), rs.debug, "snapshot_bw.dump",
+                                                   "backward")
+            t_m3, t_op, t_sh, t_sc, t_rt = ctx.grad_targets
+            # written in place by the kernels: autograd gets None for these inputs
+            grad_means3D = None if t_m3 is not None else grad_means3D
+            grad_opacities = None if t_op is not None else grad_opacities
+            grad_sh = None if t_sh is not None else grad_sh
+            grad_scales = None if t_sc is not None else grad_scales
+            grad_rotations = None if t_rt is not None else grad_rotations
 
         def present(g, inp):      # absent inputs (0-element sentinels) get no gradient
-            return g if inp.numel() != 0 else None
+            return g if (g is not None and inp.numel() != 0) else None
 
         return (grad_means3D, grad_means2D, present(grad_sh, sh), present(grad_colors_precomp, colors_precomp),
                 grad_opacities, present(grad_scales, scales), present(grad_rotations, rotations),

@@ -78,16 +78,34 @@ def render_view(rasterizer_mod, params, cam, bg, sh_degree: int, scale_modifier:
     return color, radii, means2D
 
 
+def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
+                   loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], fused: bool = True):
+    """Renders the given views and back-propagates `loss_fn(color, view_id)` of each into the flat buffer.
+    fused=True: the backward kernels write the first view's gradients straight into the buffer and ADD the following
+    views' (diff_gaussian_rasterization.set_grad_mode) - no zero-fill, no per-view elementwise adds.
+    fused=False: plain autograd accumulation into the zeroed buffer (what the reference API alone offers)."""
+    total = None
+    views = list(view_ids)
+    if not views or not fused or not hasattr(rasterizer_mod, "set_grad_mode"):
+        flat.zero_()
+        fused = False
+    for i, k in enumerate(views):
+        prev = rasterizer_mod.set_grad_mode(("overwrite" if i == 0 else "accumulate")) if fused else None
+        try:
+            color, _radii, _m2d = render_view(rasterizer_mod, params, cams[k], bg, sh_degree)
+            loss = loss_fn(color, k)
+            loss.backward()
+        finally:
+            if fused:
+                rasterizer_mod.set_grad_mode(prev)
+        total = loss.detach() if total is None else total + loss.detach()
+    return total
+
+
 def dp_step(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
-            loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None):
+            loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None, fused: bool = True):
     """Renders this rank's views, back-propagates `loss_fn(color, view_id)` for each into the flat
     buffer, then all-reduces it.  Returns the summed local loss (a device scalar)."""
-    flat.zero_()
-    total = None
-    for k in view_ids:
-        color, _radii, _m2d = render_view(rasterizer_mod, params, cams[k], bg, sh_degree)
-        loss = loss_fn(color, k)
-        loss.backward()
-        total = loss.detach() if total is None else total + loss.detach()
+    total = backward_views(rasterizer_mod, params, flat, cams, bg, sh_degree, loss_fn, view_ids, fused)
     flat.all_reduce(group)
     return total
