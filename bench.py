@@ -160,15 +160,20 @@ def run_reference_arm(args, spec, P):
 
 
 # ------------------------------------------------------------------------------------------ our arm
-def stage_bytes(P, Pv, R, N, tiles, M):
-    """Algorithmic bytes per launch of each stage (DESIGN.md section 4)."""
+def stage_bytes(P, Pv, R, N, tiles, M, accumulate_frac=0.0):
+    """Algorithmic bytes per launch of each stage (DESIGN.md section 3)."""
     return {
-        "preprocess": 44 * P + (12 * M + 4) * Pv + 49 * P + 4 * P,     # inputs + SH of visible + 48 B record, 1 B clamp + radii
-        "depth_order": 100 * P,
-        "tile_split": 52 * R + 8 * tiles,
+        # inputs (44 B) + SH of the visible ones + 48 B record, clamp byte, radii, depth key, tile rect
+        "preprocess": 44 * P + (12 * M + 4) * Pv + (48 + 1 + 4 + 4 + 8) * P,
+        # digit histograms (4P) + four passes over (key, id) pairs (first reads keys only, last writes ids only) + tile rects (8P)
+        "depth_order": 4 * P + (4 * 16 - 8) * P + 8 * P + 8 * tiles,
+        # emission: order + rect in, (tile, id) out; pass 1: 8R in, 8R out; pass 2: 8R in, 4R out
+        "tile_split": 12 * P + 8 * R + 16 * R + 12 * R,
         "blend_forward": 40 * R + 20 * N,
         "blend_backward": 80 * R + 32 * N,
-        "preprocess_backward": (111 + 64 + 24 * M) * Pv + 4 * (14 + 3 * M) * (P - Pv),
+        # every owned gradient written once (zeros for culled rows) + inputs; accumulating also reads the old gradients
+        "preprocess_backward": (111 + 64 + 24 * M) * Pv + 4 * (14 + 3 * M) * (P - Pv) * (1.0 - accumulate_frac)
+                               + accumulate_frac * 4 * (11 + 3 * M) * Pv,
     }
 
 
@@ -308,7 +313,7 @@ def main():
         Pv = stats["Pv"] / max(1, stats["views"])
         # realised R of one representative view
         R = probe_R(C, params, cams[my_views(0)[0]], bg, spec.D)
-        sb = stage_bytes(P, Pv, R, N, tiles, M)
+        sb = stage_bytes(P, Pv, R, N, tiles, M, accumulate_frac=(vps - 1) / vps if fused else 0.0)
         stages = {}
         dom, dom_ms = None, -1.0
         for name, ms, calls in stage_rows:
