@@ -754,6 +754,277 @@ blend_bwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     }
 }
 
+// ------------------------------------------------------------------------------------------ backward, tensor-core reduction
+// The per-Gaussian sums of blend_bwd_v3 cost a 16-value butterfly (21 shuffles, 30 selects, 21 adds) per pair of
+// entries: 40 % of the kernel's instructions.  They are linear in two per-lane scalars of the entry,
+//   w  = dL/dG * G   and   at = alpha * T,
+// with coefficients that do not depend on the entry: the pixel's offset inside the warp's 8x4 sub-tile
+// (lx, ly in 0..7 x 0..3) for the six moments of w, and the pixel's dL/dpixel for the three colour sums.  So a warp
+// parks (w, at) of each surviving entry in a shared-memory slot (two STS) and, every 8 entries, reduces all of them
+// over the 32 lanes with the tensor cores (mma.sync m16n8k8 tf32, fp32 accumulate, K = the 32 lanes in 4 steps):
+//   A[16 x 32]  rows 0-7 = w of slots 0-7, rows 8-15 = at of slots 0-7          (split hi + lo: two MMAs)
+//   B1[32 x 8]  columns (1, lx, lx', ...) = the moment matrix (small integers: exact in tf32)   -> D1 rows 0-7
+//   B2[32 x 8]  columns (hi, lo) of dL/dpixel r, g, b                                           -> D2 rows 8-15
+// The hi/lo splits keep ~21 mantissa bits (error < 1e-6; the gradients carry a 1e-3 tolerance).  The slot array is
+// stored in A-fragment order, so one LDS.128 per k-step is the whole A operand.  The moments about the sub-tile origin
+// are shifted to the Gaussian's centre (dx = u - lx, u = mean.x - origin.x) and committed with the same RED.ADDs
+// into the same accumulator rows as before (two of them as 8-byte vector REDs).
+constexpr int RED_SLOTS = 8;
+constexpr int RED_KSTRIDE = 144;      // floats per k-step of the slot array: 8 slots x 16 + 16 (STS of one slot: 2-way conflicts only)
+struct __align__(16) WarpRed {
+    float a[4 * RED_KSTRIDE];         // [k-step s][slot][t][b][w | at]   (lane = 8t + 2s + b)
+    float2 b2[4][32];                 // B2 fragments: [k-step][lane (g, t)] = column g of dL/dpixel at lanes 8t+2s, 8t+2s+1
+    float4 meta[RED_SLOTS];           // mean.x, mean.y, Gaussian id (bits)
+};
+struct __align__(16) BwdSmemV4 {
+    BlendStageBwd stage[2];
+    WarpRed red[8];
+    float2 b1[4][32];                 // B1 fragments (moment matrix), same for all warps
+    uint32_t bits[2][8][8];
+    int warp_last[8];
+};
+
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
+{
+    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ float fsel(bool c, float a, float b)       // branch-free select (the compiler may not turn it into a jump)
+{
+    float r;
+    asm("{ .reg .pred p; setp.ne.s32 p, %3, 0; selp.f32 %0, %1, %2, p; }" : "=f"(r) : "f"(a), "f"(b), "r"((int)c));
+    return r;
+}
+__device__ __forceinline__ void red_add_v2(float* addr, float x, float y)
+{
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(x), "f"(y) : "memory");
+}
+
+// Reduces slots [0, cnt) of the warp over its 32 lanes and commits them.  Fragment layout of m16n8k8 (g = lane >> 2,
+// t = lane & 3): A rows g / g+8 at k = t / t+4, B column g at k = t / t+4, D rows g / g+8, columns 2t, 2t+1.
+// k-step s maps k = t to lane 8t + 2s and k = t+4 to lane 8t + 2s + 1.
+__device__ __forceinline__ void red_flush(WarpRed& R, const float2 (*b1)[32], int cnt, int lane, float X0s, float Y0s,
+                                          float* __restrict__ accum)
+{
+    __syncwarp();
+    const int g = lane >> 2, t = lane & 3;
+    float d1[4] = {0.f, 0.f, 0.f, 0.f}, d2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        const float4 av = *reinterpret_cast<const float4*>(&R.a[s * RED_KSTRIDE + 4 * lane]);
+        const float2 m = b1[s][lane];
+        const float2 q = R.b2[s][lane];
+        const float x[4] = {av.x, av.y, av.z, av.w};
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {      // x = hi + lo, hi exact in tf32 (the tensor core ignores the 13 low mantissa bits)
+            hi[k] = __float_as_uint(x[k]) & 0xffffe000u;
+            lo[k] = __float_as_uint(x[k] - __uint_as_float(hi[k]));
+        }
+        mma_tf32(d1, hi, __float_as_uint(m.x), __float_as_uint(m.y));
+        mma_tf32(d1, lo, __float_as_uint(m.x), __float_as_uint(m.y));
+        mma_tf32(d2, hi, __float_as_uint(q.x), __float_as_uint(q.y));
+        mma_tf32(d2, lo, __float_as_uint(q.x), __float_as_uint(q.y));
+    }
+    // lane (g, t): d1[0], d1[1] = moments 2t, 2t+1 of slot g about the sub-tile origin (S0 Sx | Sy Sxx | Sxy Syy | - -),
+    //              d2[2] + d2[3] = colour sum t of slot g
+    const float4 me = R.meta[g];
+    const int q0 = lane & ~3;
+    const float S0 = __shfl_sync(0xffffffffu, d1[0], q0);
+    const float Sx = __shfl_sync(0xffffffffu, d1[1], q0);
+    const float Sy = __shfl_sync(0xffffffffu, d1[0], q0 + 1);
+    const float u = me.x - X0s, v = me.y - Y0s;          // dx = u - lx, dy = v - ly
+    const float a1 = fmaf(u, S0, -Sx);                   // sum w dx
+    const float a2 = fmaf(v, S0, -Sy);                   // sum w dy
+    const float o3 = fmaf(u, a1 - Sx, d1[1]);            // sum w dx^2  = Sxx - 2u Sx + u^2 S0
+    const float o4 = fmaf(-v, Sx, fmaf(u, a2, d1[0]));   // sum w dx dy = Sxy - u Sy - v Sx + uv S0
+    const float o5 = fmaf(v, a2 - Sy, d1[1]);            // sum w dy^2  = Syy - 2v Sy + v^2 S0
+    const float out0 = fsel(t == 0, d1[0], fsel(t == 1, a2, o4));
+    const float out1 = fsel(t == 0, a1, fsel(t == 1, o3, o5));
+    const float col = d2[2] + d2[3];
+    if (g < cnt && t < 3) {
+        float* row = accum + (size_t)__float_as_uint(me.z) * 12;
+        if (t == 0) { atomicAdd(row + 8, out0); atomicAdd(row + 3, out1); }
+        else red_add_v2(row + 2 + 2 * t, out0, out1);    // t = 1: columns 4, 5   t = 2: columns 6, 7
+        atomicAdd(row + t, col);
+    }
+    __syncwarp();
+}
+
+// per-pixel state update of one blended entry (restates backward.cu:494-556); returns w = dL/dG * G and at = alpha * T
+__device__ __forceinline__ void bwd_live_wa(float alpha, float araw, float c0, float c1, float c2, float dp0, float dp1, float dp2,
+                                            float tfb, float& T, float& last_alpha, float& acc0, float& acc1, float& acc2,
+                                            float& lc0, float& lc1, float& lc2, float& w, float& at)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f - alpha));
+    T *= r;
+    at = alpha * T;
+    acc0 = fmaf(last_alpha, lc0 - acc0, acc0); lc0 = c0;
+    acc1 = fmaf(last_alpha, lc1 - acc1, acc1); lc1 = c1;
+    acc2 = fmaf(last_alpha, lc2 - acc2, acc2); lc2 = c2;
+    float dL_dalpha = (c0 - acc0) * dp0 + (c1 - acc1) * dp1 + (c2 - acc2) * dp2;
+    last_alpha = alpha;
+    dL_dalpha = fmaf(dL_dalpha, T, -tfb * r);
+    w = araw * dL_dalpha;
+}
+
+template <int MINB>
+__global__ void __launch_bounds__(BL_THREADS, MINB)
+blend_bwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                    int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
+                    const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, float* __restrict__ accum)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BwdSmemV4& S = *reinterpret_cast<BwdSmemV4*>(smem_raw);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    WarpRed& R = S.red[wid];
+    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(blockIdx.y * GSR_TILE);
+    const float X0s = X0 + (float)((wid & 1) * 8), Y0s = Y0 + (float)((wid >> 1) * 4);
+    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t pix = (size_t)W * py + px;
+    const size_t HW = (size_t)H * W;
+
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+
+    const float T_final = inside ? final_T[pix] : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
+    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
+    const float tfb = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;
+    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
+
+    // constant operands of the reduction in B-fragment order: the moment matrix (whole block) and this warp's
+    // dL/dpixel columns (r_hi, r_lo, g_hi, g_lo, b_hi, b_lo, 0, 0)
+    if (threadIdx.x < 128) {
+        const int s = threadIdx.x >> 5, l = threadIdx.x & 31, n = l >> 2;
+        const float ly = (float)(l & 3), lx0 = (float)(2 * s), lx1 = lx0 + 1.f;
+        float2 m;
+        m.x = n == 0 ? 1.f : n == 1 ? lx0 : n == 2 ? ly : n == 3 ? lx0 * lx0 : n == 4 ? lx0 * ly : n == 5 ? ly * ly : 0.f;
+        m.y = n == 0 ? 1.f : n == 1 ? lx1 : n == 2 ? ly : n == 3 ? lx1 * lx1 : n == 4 ? lx1 * ly : n == 5 ? ly * ly : 0.f;
+        S.b1[s][l] = m;
+    }
+    const int tL = lane >> 3, sL = (lane >> 1) & 3, bL = lane & 1;      // this pixel is k index tL + 4 bL of k-step sL
+    {
+        const float d[3] = {dp0, dp1, dp2};
+        float* col = reinterpret_cast<float*>(&R.b2[sL][tL]) + bL;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const float hi = __uint_as_float(__float_as_uint(d[c]) & 0xffffe000u);
+            col[(2 * c) * 8] = hi;                 // column n lives at lane index 4n + tL: 8 floats apart
+            col[(2 * c + 1) * 8] = d[c] - hi;
+        }
+        col[6 * 8] = 0.f;
+        col[7 * 8] = 0.f;
+    }
+    float2* const slot0 = reinterpret_cast<float2*>(&R.a[sL * RED_KSTRIDE + tL * 4 + bL * 2]);   // slot c: slot0 + 8 c
+
+    int warp_last = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+    if (lane == 0) S.warp_last[wid] = warp_last;
+    __syncthreads();
+    int total = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) total = max(total, S.warp_last[k]);
+    total = min(total, (int)(range.y - range.x));
+    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
+    const uint32_t list_end = range.x + total;
+
+    auto gather = [&](BlendStageBwd& st, int batch) {
+        const int p = batch * BL_THREADS + threadIdx.x;
+        if (p < total) {
+            const uint32_t id = vals[list_end - 1 - p];
+            st.id[threadIdx.x] = id;
+            const SplatRec* r = rec + id;
+            cp_async16(&st.q0[threadIdx.x], &r->q0);
+            cp_async16(&st.q1[threadIdx.x], &r->q1);
+            cp_async4(&st.b[threadIdx.x], &r->q2);
+        }
+        cp_async_commit();
+    };
+    gather(S.stage[0], 0);
+    int cnt = 0;                  // filled reduction slots of this warp (warp-uniform)
+    for (int i = 0; i < rounds; i++) {
+        const int buf = i & 1;
+        cp_async_wait<0>();
+        {
+            uint32_t m = 0;
+            const int p = i * BL_THREADS + (int)threadIdx.x;
+            if (p < total) {
+                m = subtile_mask(S.stage[buf].q0[threadIdx.x], S.stage[buf].q1[threadIdx.x], X0, Y0);
+                const int pos = total - 1 - p;
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    if (pos >= S.warp_last[k]) m &= ~(1u << k);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
+                if (lane == k) S.bits[buf][k][wid] = bk;
+            }
+        }
+        __syncthreads();
+        if (i + 1 < rounds) gather(S.stage[buf ^ 1], i + 1);
+        const BlendStageBwd& st = S.stage[buf];
+        const int pos_top = total - 1 - i * BL_THREADS;
+#pragma unroll 1
+        for (int cch = 0; cch < 8; cch++) {
+            uint32_t m = S.bits[buf][wid][cch];
+            const int jb = cch * 32;
+            while (m) {
+                if (cnt >= RED_SLOTS - 1) { red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum); cnt = 0; }
+                const int j0 = jb + __ffs(m) - 1;
+                m &= m - 1;
+                if (m) {
+                    const int j1 = jb + __ffs(m) - 1;
+                    m &= m - 1;
+                    const float4 a0 = st.q0[j0], c0 = st.q1[j0], a1 = st.q0[j1], c1 = st.q1[j1];
+                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
+                    const EntryHead h1 = bwd_head(a1, c1, pxf, pyf, pos_top - j1, last_contributor);
+                    const bool any0 = __any_sync(0xffffffffu, h0.live), any1 = __any_sync(0xffffffffu, h1.live);
+                    if (any0) {
+                        float wv = 0.f, atv = 0.f;
+                        if (h0.live)
+                            bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, st.b[j0], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                                        lc0, lc1, lc2, wv, atv);
+                        slot0[8 * cnt] = make_float2(wv, atv);
+                        if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, __uint_as_float(st.id[j0]), 0.f);
+                        cnt++;
+                    }
+                    if (any1) {
+                        float wv = 0.f, atv = 0.f;
+                        if (h1.live)
+                            bwd_live_wa(h1.alpha, h1.araw, c1.z, c1.w, st.b[j1], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                                        lc0, lc1, lc2, wv, atv);
+                        slot0[8 * cnt] = make_float2(wv, atv);
+                        if (lane == 0) R.meta[cnt] = make_float4(a1.x, a1.y, __uint_as_float(st.id[j1]), 0.f);
+                        cnt++;
+                    }
+                } else {
+                    const float4 a0 = st.q0[j0], c0 = st.q1[j0];
+                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
+                    if (!__any_sync(0xffffffffu, h0.live)) continue;
+                    float wv = 0.f, atv = 0.f;
+                    if (h0.live)
+                        bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, st.b[j0], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                                    lc0, lc1, lc2, wv, atv);
+                    slot0[8 * cnt] = make_float2(wv, atv);
+                    if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, __uint_as_float(st.id[j0]), 0.f);
+                    cnt++;
+                }
+            }
+        }
+    }
+    if (cnt) red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum);
+}
+
 int launch_blend_backward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                           const float* dL_dpix, float* accum, cudaStream_t s)
 {
@@ -761,9 +1032,23 @@ int launch_blend_backward(int W, int H, const float* bg, const GeomView& g, cons
     if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
                    accum);
-    else
+    else if (env_int("GSR_BLEND", 0) == 3)
         GSR_LAUNCH((blend_bwd_v3_kernel<4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
                    dL_dpix, accum);
+    else {
+        static bool attr_set = false;
+        if (!attr_set) {
+            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v4_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV4)));
+            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v4_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV4)));
+            attr_set = true;
+        }
+        if (env_int("GSR_BWD_MINB", 4) == 3)
+            GSR_LAUNCH((blend_bwd_v4_kernel<3>), grid, BL_THREADS, sizeof(BwdSmemV4), s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T,
+                       im.n_contrib, dL_dpix, accum);
+        else
+            GSR_LAUNCH((blend_bwd_v4_kernel<4>), grid, BL_THREADS, sizeof(BwdSmemV4), s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T,
+                       im.n_contrib, dL_dpix, accum);
+    }
     return GSR_OK;
 }
 
