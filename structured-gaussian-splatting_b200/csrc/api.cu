@@ -142,10 +142,12 @@ size_t gsr_img_bytes(int W, int H)
 }
 size_t gsr_binning_bytes(int P, int R, int W, int H)
 {
-    (void)P; (void)W; (void)H;
+    (void)P;
     const size_t Rp = (size_t)(R > 0 ? R : 1);
     size_t scratch = bin_scratch_bytes(R);
     if (env_int("GSR_SORT", 0) == 1) { size_t c = cub_sort_scratch_bytes(R); if (c > scratch) scratch = c; }
+    const size_t planes = 8 * 4 * blend_plane_words(R, W, H);      // written by the forward blending into the dead sort scratch
+    if (planes > scratch) scratch = planes;
     return sizeof(BlobHeader) + align_up(Rp * 4) + scratch;
 }
 size_t gsr_bwd_accum_bytes(int P) { return (size_t)(P > 0 ? P : 1) * 12 * sizeof(float); }
@@ -219,7 +221,7 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     GSR_STAGE(a->debug, s, "tile_split");
 
     stage_begin(3, s);
-    if ((rc = launch_blend_forward(a->W, a->H, a->background, g, b, im, a->out_color, s))) return rc;
+    if ((rc = launch_blend_forward(R, a->W, a->H, a->background, g, b, im, a->out_color, s))) return rc;
     stage_end(3, s);
     GSR_STAGE(a->debug, s, "blend_forward");
     if (a->debug && a->prefiltered) {
@@ -260,7 +262,7 @@ int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream_)
     int rc;
     stage_begin(4, s);
     GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(a->P), s));
-    if ((rc = launch_blend_backward(a->W, a->H, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
+    if ((rc = launch_blend_backward(a->R, a->W, a->H, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
     stage_end(4, s);
     GSR_STAGE(a->debug, s, "blend_backward");
     stage_begin(5, s);

@@ -231,7 +231,7 @@ template <int UMAX, int MINB>
 __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                    float* __restrict__ out)
+                    float* __restrict__ out, uint32_t* __restrict__ planes, uint32_t plane_words)
 {
     __shared__ BlendStage stage[2];
     __shared__ uint32_t bits[2][8][8];     // [buffer][consumer warp][chunk of 32 entries]
@@ -243,8 +243,11 @@ blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     const float pxf = (float)px, pyf = (float)py;
     bool done = !inside;
 
-    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+    const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
+    // classification words are kept for the backward: plane k (sub-tile k), word (range.x >> 5) + 16 tile + chunk
+    uint32_t* const plane = planes + (size_t)lane * plane_words + (range.x >> 5) + 16u * tile + wid;
     const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
 
     float T = 1.0f;
@@ -268,7 +271,7 @@ blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
 #pragma unroll
             for (int k = 0; k < 8; k++) {
                 const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
-                if (lane == k) bits[buf][k][wid] = bk;
+                if (lane == k) { bits[buf][k][wid] = bk; plane[i * 8] = bk; }
             }
         }
         const int num_done = __syncthreads_count(done);
@@ -423,17 +426,29 @@ blend_stats_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
     }
 }
 
-int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+// classification words kept for the backward (in the binning blob's sort scratch, dead once the tile split is done):
+// 8 planes (one per sub-tile of a tile) of (R >> 5) + 16 tiles + 16 words
+size_t blend_plane_words(long long R, int W, int H)
+{
+    const size_t tiles = (size_t)((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
+    return (size_t)((R > 0 ? R : 0) >> 5) + 16 * tiles + 16;
+}
+
+int launch_blend_forward(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                          float* out_color, cudaStream_t s)
 {
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
+    const uint32_t pw = (uint32_t)blend_plane_words(R, W, H);
     if (env_int("GSR_BLEND_STATS", 0) == 1)
         GSR_LAUNCH(blend_stats_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H);
     if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
+    else if (env_int("GSR_FWD_MINB", 4) == 3)
+        GSR_LAUNCH((blend_fwd_v3_kernel<4, 3>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+                   out_color, b.scratch, pw);
     else
         GSR_LAUNCH((blend_fwd_v3_kernel<4, 4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   out_color);
+                   out_color, b.scratch, pw);
     return GSR_OK;
 }
 
@@ -599,6 +614,22 @@ __device__ __forceinline__ EntryHead bwd_head(const float4 a, const float4 c, fl
     h.dx = a.x - pxf; h.dy = a.y - pyf;
     const float power = -0.5f * (a.z * h.dx * h.dx + c.x * h.dy * h.dy) - a.w * h.dx * h.dy;
     h.araw = c.y * expf(power);
+    h.alpha = fminf(0.99f, h.araw);
+    h.live = pos < last_contributor && !(power > 0.0f) && !(h.alpha < 1.0f / 255.0f);
+    return h;
+}
+
+// v5 head: exp through ex2.approx(power * log2 e) - relative error ~4e-7 instead of expf's 1 ulp, 2 instructions instead
+// of 8.  Only the backward uses it (gradients carry a 1e-3 tolerance); the forward keeps expf, its skip decisions and
+// n_contrib are part of the bit-exact contract.
+__device__ __forceinline__ EntryHead bwd_head_fast(const float4 a, const float4 c, float pxf, float pyf, int pos, int last_contributor)
+{
+    EntryHead h;
+    h.dx = a.x - pxf; h.dy = a.y - pyf;
+    const float power = -0.5f * (a.z * h.dx * h.dx + c.x * h.dy * h.dy) - a.w * h.dx * h.dy;
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(power * 1.4426950408889634f));
+    h.araw = c.y * e;
     h.alpha = fminf(0.99f, h.araw);
     h.live = pos < last_contributor && !(power > 0.0f) && !(h.alpha < 1.0f / 255.0f);
     return h;
@@ -776,8 +807,13 @@ struct __align__(16) WarpRed {
     float2 b2[4][32];                 // B2 fragments: [k-step][lane (g, t)] = column g of dL/dpixel at lanes 8t+2s, 8t+2s+1
     float4 meta[RED_SLOTS];           // mean.x, mean.y, Gaussian id (bits)
 };
+struct BlendStageBwd4 {
+    float4 q0[BL_THREADS];
+    float4 q1[BL_THREADS];
+    float2 bi[BL_THREADS];            // colour b, Gaussian id (bits): one LDS.64 at the top of a trip
+};
 struct __align__(16) BwdSmemV4 {
-    BlendStageBwd stage[2];
+    BlendStageBwd4 stage[2];
     WarpRed red[8];
     float2 b1[4][32];                 // B1 fragments (moment matrix), same for all warps
     uint32_t bits[2][8][8];
@@ -937,15 +973,15 @@ blend_bwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
     const uint32_t list_end = range.x + total;
 
-    auto gather = [&](BlendStageBwd& st, int batch) {
+    auto gather = [&](BlendStageBwd4& st, int batch) {
         const int p = batch * BL_THREADS + threadIdx.x;
         if (p < total) {
             const uint32_t id = vals[list_end - 1 - p];
-            st.id[threadIdx.x] = id;
+            st.bi[threadIdx.x].y = __uint_as_float(id);
             const SplatRec* r = rec + id;
             cp_async16(&st.q0[threadIdx.x], &r->q0);
             cp_async16(&st.q1[threadIdx.x], &r->q1);
-            cp_async4(&st.b[threadIdx.x], &r->q2);
+            cp_async4(&st.bi[threadIdx.x].x, &r->q2);
         }
         cp_async_commit();
     };
@@ -972,7 +1008,7 @@ blend_bwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
         }
         __syncthreads();
         if (i + 1 < rounds) gather(S.stage[buf ^ 1], i + 1);
-        const BlendStageBwd& st = S.stage[buf];
+        const BlendStageBwd4& st = S.stage[buf];
         const int pos_top = total - 1 - i * BL_THREADS;
 #pragma unroll 1
         for (int cch = 0; cch < 8; cch++) {
@@ -986,37 +1022,39 @@ blend_bwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                     const int j1 = jb + __ffs(m) - 1;
                     m &= m - 1;
                     const float4 a0 = st.q0[j0], c0 = st.q1[j0], a1 = st.q0[j1], c1 = st.q1[j1];
+                    const float2 e0 = st.bi[j0], e1 = st.bi[j1];
                     const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
                     const EntryHead h1 = bwd_head(a1, c1, pxf, pyf, pos_top - j1, last_contributor);
                     const bool any0 = __any_sync(0xffffffffu, h0.live), any1 = __any_sync(0xffffffffu, h1.live);
                     if (any0) {
                         float wv = 0.f, atv = 0.f;
                         if (h0.live)
-                            bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, st.b[j0], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                            bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
                                         lc0, lc1, lc2, wv, atv);
                         slot0[8 * cnt] = make_float2(wv, atv);
-                        if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, __uint_as_float(st.id[j0]), 0.f);
+                        if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, e0.y, 0.f);
                         cnt++;
                     }
                     if (any1) {
                         float wv = 0.f, atv = 0.f;
                         if (h1.live)
-                            bwd_live_wa(h1.alpha, h1.araw, c1.z, c1.w, st.b[j1], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                            bwd_live_wa(h1.alpha, h1.araw, c1.z, c1.w, e1.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
                                         lc0, lc1, lc2, wv, atv);
                         slot0[8 * cnt] = make_float2(wv, atv);
-                        if (lane == 0) R.meta[cnt] = make_float4(a1.x, a1.y, __uint_as_float(st.id[j1]), 0.f);
+                        if (lane == 0) R.meta[cnt] = make_float4(a1.x, a1.y, e1.y, 0.f);
                         cnt++;
                     }
                 } else {
                     const float4 a0 = st.q0[j0], c0 = st.q1[j0];
+                    const float2 e0 = st.bi[j0];
                     const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
                     if (!__any_sync(0xffffffffu, h0.live)) continue;
                     float wv = 0.f, atv = 0.f;
                     if (h0.live)
-                        bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, st.b[j0], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                        bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
                                     lc0, lc1, lc2, wv, atv);
                     slot0[8 * cnt] = make_float2(wv, atv);
-                    if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, __uint_as_float(st.id[j0]), 0.f);
+                    if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, e0.y, 0.f);
                     cnt++;
                 }
             }
@@ -1025,17 +1063,222 @@ blend_bwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     if (cnt) red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum);
 }
 
-int launch_blend_backward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+// ------------------------------------------------------------------------------------------ backward, warp-autonomous
+// blend_bwd_v4 spends 19 % of its warp-time at the per-batch block barrier (the eight sub-tiles of a tile do not carry
+// the same number of surviving entries) and re-runs the sub-tile classification the forward already did.  Here the
+// forward exports its classification - one word per (sub-tile, 32 list entries), `planes` - and every warp walks the
+// tile list on its own, back to front, 32 entries per step: lanes whose bit is set gather their record with cp.async
+// into a warp-private ring (so a record is fetched once per sub-tile that needs it, as before), NS - 1 steps ahead of the
+// blending; there is no block barrier after the prologue and no classification.  Blending, reduction (red_flush) and
+// arithmetic are those of v4.
+template <int NS>
+struct __align__(16) WarpRing {
+    float4 q0[NS][32];
+    float4 q1[NS][32];
+    float2 bi[NS][32];                // colour b, Gaussian id (bits)
+};
+template <int NS>
+struct __align__(16) BwdSmemV5 {
+    WarpRing<NS> ring[8];
+    WarpRed red[8];
+    float2 b1[4][32];
+};
+
+template <int NS, int MINB>
+__global__ void __launch_bounds__(BL_THREADS, MINB)
+blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                    const uint32_t* __restrict__ planes, uint32_t plane_words, int W, int H, const float* __restrict__ bg,
+                    const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
+                    float* __restrict__ accum)
+{
+    constexpr int D = NS - 1;          // gather distance in steps
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BwdSmemV5<NS>& S = *reinterpret_cast<BwdSmemV5<NS>*>(smem_raw);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    WarpRed& R = S.red[wid];
+    WarpRing<NS>& Q = S.ring[wid];
+    const float X0s = (float)(blockIdx.x * GSR_TILE + (wid & 1) * 8), Y0s = (float)(blockIdx.y * GSR_TILE + (wid >> 1) * 4);
+    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t pix = (size_t)W * py + px;
+    const size_t HW = (size_t)H * W;
+    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+    const uint2 range = ranges[tile];
+
+    const float T_final = inside ? final_T[pix] : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
+    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
+    const float tfb = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;
+    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
+
+    // constant operands of the reduction (see blend_bwd_v4_kernel)
+    if (threadIdx.x < 128) {
+        const int s = threadIdx.x >> 5, l = threadIdx.x & 31, n = l >> 2;
+        const float ly = (float)(l & 3), lx0 = (float)(2 * s), lx1 = lx0 + 1.f;
+        float2 m;
+        m.x = n == 0 ? 1.f : n == 1 ? lx0 : n == 2 ? ly : n == 3 ? lx0 * lx0 : n == 4 ? lx0 * ly : n == 5 ? ly * ly : 0.f;
+        m.y = n == 0 ? 1.f : n == 1 ? lx1 : n == 2 ? ly : n == 3 ? lx1 * lx1 : n == 4 ? lx1 * ly : n == 5 ? ly * ly : 0.f;
+        S.b1[s][l] = m;
+    }
+    const int tL = lane >> 3, sL = (lane >> 1) & 3, bL = lane & 1;
+    {
+        const float d[3] = {dp0, dp1, dp2};
+        float* col = reinterpret_cast<float*>(&R.b2[sL][tL]) + bL;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const float hi = __uint_as_float(__float_as_uint(d[c]) & 0xffffe000u);
+            col[(2 * c) * 8] = hi;
+            col[(2 * c + 1) * 8] = d[c] - hi;
+        }
+        col[6 * 8] = 0.f;
+        col[7 * 8] = 0.f;
+    }
+    float2* const slot0 = reinterpret_cast<float2*>(&R.a[sL * RED_KSTRIDE + tL * 4 + bL * 2]);
+
+    int warp_last = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+    warp_last = min(warp_last, (int)(range.y - range.x));
+    __syncthreads();                       // b1 is visible; the only block barrier
+    const int nch = (warp_last + 31) >> 5; // chunks of 32 list entries this warp has work in
+    if (nch == 0) return;
+    const uint32_t* plane = planes + (size_t)wid * plane_words + (range.x >> 5) + 16u * tile;
+    const uint32_t* tvals = vals + range.x;
+    // step s = 0 .. nch-1 handles chunk nch-1-s (back to front).  The classification words of 32 consecutive steps sit
+    // in one register per lane: wA = block of the step whose mask is extracted next, wB = the block after it.
+    auto load_words = [&](int blk) -> uint32_t {
+        const int s = blk * 32 + lane;
+        return s < nch ? plane[nch - 1 - s] : 0u;
+    };
+    uint32_t wA = load_words(0), wB = load_words(1);
+    int blkA = 0;
+    auto load_id = [&](int s, uint32_t m) -> uint32_t { return ((m >> lane) & 1u) ? tvals[(nch - 1 - s) * 32 + lane] : 0u; };
+    auto issue = [&](int s, uint32_t m, uint32_t id) {
+        if ((m >> lane) & 1u) {
+            const int k = s % NS;
+            const SplatRec* r = rec + id;
+            cp_async16(&Q.q0[k][lane], &r->q0);
+            cp_async16(&Q.q1[k][lane], &r->q1);
+            cp_async4(&Q.bi[k][lane].x, &r->q2);
+            Q.bi[k][lane].y = __uint_as_float(id);
+        }
+        cp_async_commit();
+    };
+    uint32_t mq[D + 2];                // masks of steps s .. s+D+1
+#pragma unroll
+    for (int k = 0; k < D + 2; k++) {
+        const uint32_t w = __shfl_sync(0xffffffffu, wA, k);
+        mq[k] = k < nch ? w : 0u;
+    }
+    uint32_t idc = load_id(0, mq[0]);
+#pragma unroll
+    for (int k = 0; k < D; k++) {
+        const uint32_t idn = load_id(k + 1, mq[k + 1]);
+        issue(k, mq[k], idc);
+        idc = idn;
+    }
+    int cnt = 0;                       // filled reduction slots (warp-uniform)
+    for (int s = 0; s < nch; s++) {
+        const uint32_t idn = load_id(s + D + 1, mq[D + 1]);     // ids of step s+D+1 (mask is 0 beyond the end)
+        issue(s + D, mq[D], idc);                               // records of step s+D
+        idc = idn;
+        cp_async_wait<D>();                                     // my records of step s have landed
+        __syncwarp();
+        const int kq = s % NS;
+        const int cbase = (nch - 1 - s) * 32;
+        uint32_t m = mq[0];
+        while (m) {
+            if (cnt >= RED_SLOTS - 1) { red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum); cnt = 0; }
+            const int j0 = 31 - __clz(m);
+            m ^= 1u << j0;
+            if (m) {
+                const int j1 = 31 - __clz(m);
+                m ^= 1u << j1;
+                const float4 a0 = Q.q0[kq][j0], c0 = Q.q1[kq][j0], a1 = Q.q0[kq][j1], c1 = Q.q1[kq][j1];
+                const float2 e0 = Q.bi[kq][j0], e1 = Q.bi[kq][j1];
+                const EntryHead h0 = bwd_head_fast(a0, c0, pxf, pyf, cbase + j0, last_contributor);
+                const EntryHead h1 = bwd_head_fast(a1, c1, pxf, pyf, cbase + j1, last_contributor);
+                const bool any0 = __any_sync(0xffffffffu, h0.live), any1 = __any_sync(0xffffffffu, h1.live);
+                if (any0) {
+                    float wv = 0.f, atv = 0.f;
+                    if (h0.live)
+                        bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                                    lc0, lc1, lc2, wv, atv);
+                    slot0[8 * cnt] = make_float2(wv, atv);
+                    if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, e0.y, 0.f);
+                    cnt++;
+                }
+                if (any1) {
+                    float wv = 0.f, atv = 0.f;
+                    if (h1.live)
+                        bwd_live_wa(h1.alpha, h1.araw, c1.z, c1.w, e1.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                                    lc0, lc1, lc2, wv, atv);
+                    slot0[8 * cnt] = make_float2(wv, atv);
+                    if (lane == 0) R.meta[cnt] = make_float4(a1.x, a1.y, e1.y, 0.f);
+                    cnt++;
+                }
+            } else {
+                const float4 a0 = Q.q0[kq][j0], c0 = Q.q1[kq][j0];
+                const float2 e0 = Q.bi[kq][j0];
+                const EntryHead h0 = bwd_head_fast(a0, c0, pxf, pyf, cbase + j0, last_contributor);
+                if (!__any_sync(0xffffffffu, h0.live)) continue;
+                float wv = 0.f, atv = 0.f;
+                if (h0.live)
+                    bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
+                                lc0, lc1, lc2, wv, atv);
+                slot0[8 * cnt] = make_float2(wv, atv);
+                if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, e0.y, 0.f);
+                cnt++;
+            }
+        }
+        // masks move up one step; extract the mask of step s+D+2 (its block becomes wA when it starts a new one)
+#pragma unroll
+        for (int k = 0; k < D + 1; k++) mq[k] = mq[k + 1];
+        const int sn = s + D + 2;
+        if ((sn >> 5) != blkA) { wA = wB; blkA++; wB = load_words(blkA + 1); }
+        const uint32_t wn = __shfl_sync(0xffffffffu, wA, sn & 31);
+        mq[D + 1] = sn < nch ? wn : 0u;
+        __syncwarp();                  // everyone has left ring slot kq before the next step's gather overwrites it
+    }
+    if (cnt) red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum);
+}
+
+int launch_blend_backward(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                           const float* dL_dpix, float* accum, cudaStream_t s)
 {
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
+    const uint32_t pw = (uint32_t)blend_plane_words(R, W, H);
+    const int variant = env_int("GSR_BLEND", 0);       // 0: v5 (needs the planes of blend_fwd_v3), 1 / 3 / 4: comparison arms
     if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
                    accum);
     else if (env_int("GSR_BLEND", 0) == 3)
         GSR_LAUNCH((blend_bwd_v3_kernel<4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
                    dL_dpix, accum);
-    else {
+    else if (variant == 0) {
+        static bool attr5_set = false;
+        if (!attr5_set) {
+            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
+            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
+            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<4>)));
+            attr5_set = true;
+        }
+        const int ns = env_int("GSR_BWD_NS", 2), minb = env_int("GSR_BWD_MINB", 3);
+        if (ns == 4)
+            GSR_LAUNCH((blend_bwd_v5_kernel<4, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<4>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum);
+        else if (minb == 3)
+            GSR_LAUNCH((blend_bwd_v5_kernel<2, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum);
+        else
+            GSR_LAUNCH((blend_bwd_v5_kernel<2, 4>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum);
+    } else {
         static bool attr_set = false;
         if (!attr_set) {
             GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v4_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV4)));

@@ -169,9 +169,10 @@ int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint
                           uint32_t* ctl, bool ctl_zeroed, cudaStream_t s);
 
 // blend.cu
-int launch_blend_forward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+size_t blend_plane_words(long long R, int W, int H);
+int launch_blend_forward(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                          float* out_color, cudaStream_t s);
-int launch_blend_backward(int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+int launch_blend_backward(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                           const float* dL_dpix, float* accum, cudaStream_t s);
 
 // knn.cu
