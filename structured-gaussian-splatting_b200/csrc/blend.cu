@@ -1071,6 +1071,24 @@ blend_bwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
 // into a warp-private ring (so a record is fetched once per sub-tile that needs it, as before), NS - 1 steps ahead of the
 // blending; there is no block barrier after the prologue and no classification.  Blending, reduction (red_flush) and
 // arithmetic are those of v4.
+// Per-pixel state update of one blended entry in suffix-sum form.  With e = dL/dpixel . colour and
+// Sd = sum over the entries behind this one of e_k alpha_k T_k (+ T_final dL/dpixel . background),
+//   dL/dalpha = T e - Sd / (1 - alpha)
+// which is the reference's (colour - accum_rec) . dL/dpixel * T - T_final/(1 - alpha) bg . dL/dpixel (backward.cu:494-533)
+// with accum_rec written out as Sd / T_next: 11 operations and two state registers (T, Sd) instead of 23 and eight.
+__device__ __forceinline__ void bwd_live_sd(float alpha, float araw, float c0, float c1, float c2, float dp0, float dp1, float dp2,
+                                            float& T, float& Sd, float& w, float& at)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f - alpha));
+    T *= r;
+    const float e = fmaf(c2, dp2, fmaf(c1, dp1, c0 * dp0));
+    at = alpha * T;
+    const float dL_dalpha = fmaf(T, e, -(Sd * r));
+    Sd = fmaf(e, at, Sd);
+    w = araw * dL_dalpha;
+}
+
 template <int NS>
 struct __align__(16) WarpRing {
     float4 q0[NS][32];
@@ -1112,9 +1130,7 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     const int last_contributor = inside ? (int)n_contrib[pix] : 0;
     float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
     if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
-    const float tfb = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
+    float Sd = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);     // see bwd_live_sd
 
     // constant operands of the reduction (see blend_bwd_v4_kernel)
     if (threadIdx.x < 128) {
@@ -1207,8 +1223,7 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                 if (any0) {
                     float wv = 0.f, atv = 0.f;
                     if (h0.live)
-                        bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
-                                    lc0, lc1, lc2, wv, atv);
+                        bwd_live_sd(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, T, Sd, wv, atv);
                     slot0[8 * cnt] = make_float2(wv, atv);
                     if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, e0.y, 0.f);
                     cnt++;
@@ -1216,8 +1231,7 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                 if (any1) {
                     float wv = 0.f, atv = 0.f;
                     if (h1.live)
-                        bwd_live_wa(h1.alpha, h1.araw, c1.z, c1.w, e1.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
-                                    lc0, lc1, lc2, wv, atv);
+                        bwd_live_sd(h1.alpha, h1.araw, c1.z, c1.w, e1.x, dp0, dp1, dp2, T, Sd, wv, atv);
                     slot0[8 * cnt] = make_float2(wv, atv);
                     if (lane == 0) R.meta[cnt] = make_float4(a1.x, a1.y, e1.y, 0.f);
                     cnt++;
@@ -1229,8 +1243,7 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                 if (!__any_sync(0xffffffffu, h0.live)) continue;
                 float wv = 0.f, atv = 0.f;
                 if (h0.live)
-                    bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
-                                lc0, lc1, lc2, wv, atv);
+                    bwd_live_sd(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, T, Sd, wv, atv);
                 slot0[8 * cnt] = make_float2(wv, atv);
                 if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, e0.y, 0.f);
                 cnt++;
@@ -1268,7 +1281,7 @@ int launch_blend_backward(long long R, int W, int H, const float* bg, const Geom
             GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<4>)));
             attr5_set = true;
         }
-        const int ns = env_int("GSR_BWD_NS", 2), minb = env_int("GSR_BWD_MINB", 3);
+        const int ns = env_int("GSR_BWD_NS", 2), minb = env_int("GSR_BWD_MINB", 4);
         if (ns == 4)
             GSR_LAUNCH((blend_bwd_v5_kernel<4, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<4>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
                        bg, im.final_T, im.n_contrib, dL_dpix, accum);
