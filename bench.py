@@ -37,7 +37,7 @@ WORKLOAD = "C3: 3M Gaussians, SH degree 3, 1920x1080, fwd+bwd via GaussianRaster
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--views-per-step", type=int, default=4)
@@ -52,7 +52,7 @@ def parse_args():
 
 # ------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
-    """Samples SM clock and throttle reasons with NVML every 100 ms while the timed region runs."""
+    """Samples SM clock and throttle reasons with NVML every 10 ms while the timed region runs."""
 
     def __init__(self, index: int):
         self.index, self.samples, self.reasons, self._stop, self.max_mhz = index, [], set(), threading.Event(), None
@@ -81,7 +81,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.01)
 
     def start(self):
         if self.nv is not None:
