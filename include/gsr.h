@@ -149,6 +149,16 @@ int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const
 int gsr_dist2(int P, const float* points, float* out, GsrAlloc scratch, gsr_stream_t stream);
 
 /*
+ * Fused L1 image loss (forward + gradient in one pass): replaces utils/loss_utils.py:17-18
+ * `torch.abs(network_output - gt).mean()` and its autograd backward.
+ *   *loss_sum = sum_i |image[i] - target[i]|         (device scalar, zeroed by the call)
+ *   grad[i]   = grad_scale * sign(image[i] - target[i])   (0 where equal; grad may be NULL)
+ * image, target and grad must be 16-byte aligned device pointers of n floats.
+ */
+int gsr_l1_loss(const float* image, const float* target, size_t n, float grad_scale, float* loss_sum,
+                float* grad, gsr_stream_t stream);
+
+/*
  * Test hook for the bit-exact integer contract: reconstructs, from our private
  * blobs, the arrays the reference keeps in BinningState / ImageState:
  *   keys[R]   = (tile << 32) | float_bits(depth)   sorted

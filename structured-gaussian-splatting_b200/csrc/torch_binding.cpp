@@ -230,8 +230,25 @@ export_binning(const torch::Tensor& geomBuffer, const torch::Tensor& binningBuff
     return std::make_tuple(keys, vals, ranges, ncontrib, finalT);
 }
 
+// fused L1 loss: returns (sum |image - target| as a 1-element tensor, dL/dimage for loss = mean |image - target|)
+std::tuple<torch::Tensor, torch::Tensor> l1_loss(const torch::Tensor& image, const torch::Tensor& target)
+{
+    TORCH_CHECK(image.is_cuda() && target.is_cuda(), "l1_loss: CUDA tensors expected");
+    TORCH_CHECK(image.numel() == target.numel(), "l1_loss: size mismatch");
+    const c10::cuda::CUDAGuard guard(image.device());
+    F32 a(image), b(target);
+    const size_t n = (size_t)image.numel();
+    auto f32 = image.options().dtype(torch::kFloat32);
+    torch::Tensor sum = torch::empty({1}, f32);
+    torch::Tensor grad = torch::empty(image.sizes(), f32);
+    check(gsr_l1_loss(a.ptr(), b.ptr(), n, n ? 1.0f / (float)n : 0.f, sum.data_ptr<float>(), grad.data_ptr<float>(), current_stream()),
+          "l1_loss");
+    return std::make_tuple(sum, grad);
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
 {
+    m.def("l1_loss", &l1_loss);
     m.def("rasterize_gaussians", &rasterize_gaussians);
     m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
     m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into);
