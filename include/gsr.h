@@ -88,6 +88,19 @@ typedef struct GsrFwdArgs {
 int gsr_forward(const GsrFwdArgs* args, GsrAlloc geom, GsrAlloc binning, GsrAlloc img,
                 gsr_stream_t stream, int* num_rendered);
 
+/*
+ * Batched forward: n_views cameras over ONE Gaussian set in a single pass (the reference
+ * renders one view per call, train_lgm.py:111-120).  Same argument struct with these per-view extensions:
+ *   viewmatrix [n_views,16], projmatrix [n_views,16], cam_pos [n_views,3]  (W, H, tan_fov*, background shared)
+ *   out_color  [n_views,3,H,W], radii [n_views,P]
+ * Every view's result is identical to a gsr_forward call with that camera; depth sort, tile split and blending run once
+ * over all (Gaussian, view) pairs, and the host is blocked once.  colors_precomp / cov3D_precomp must be NULL when
+ * n_views > 1.  *num_rendered is the total over the views.  The blobs belong to gsr_backward_batched with the same n_views;
+ * the image blob is obtained with gsr_img_bytes_batched bytes.
+ */
+int gsr_forward_batched(const GsrFwdArgs* args, int n_views, GsrAlloc geom, GsrAlloc binning, GsrAlloc img,
+                        gsr_stream_t stream, int* num_rendered);
+
 typedef struct GsrBwdArgs {
     int P, D, M, R, W, H;
     const float* background;
@@ -136,6 +149,13 @@ typedef struct GsrBwdArgs {
 
 int gsr_backward(const GsrBwdArgs* args, gsr_stream_t stream);
 
+/*
+ * Backward of gsr_forward_batched: radii [n_views,P], dL_dpix [n_views,3,H,W], camera arrays as in the forward,
+ * accum = gsr_bwd_accum_bytes(n_views * P) bytes; dL_dmean2D is per view [n_views,P,3]; every other gradient is the
+ * SUM over the views ([P,...]: view 0 overwrites - or accumulates when `accumulate` says so - and the others add).
+ */
+int gsr_backward_batched(const GsrBwdArgs* args, int n_views, gsr_stream_t stream);
+
 /* present[i] = (view-space z of means3D[i] > 0.2).  `present` is uint8 (bool). */
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, gsr_stream_t stream);
@@ -175,6 +195,7 @@ int gsr_export_binning(const void* geom_blob, const void* binning_blob, const vo
 /* bytes the three blobs need (geom, img are known up-front; binning needs R) */
 size_t gsr_geom_bytes(int P);
 size_t gsr_img_bytes(int W, int H);
+size_t gsr_img_bytes_batched(int W, int H, int n_views);
 size_t gsr_binning_bytes(int P, int R, int W, int H);
 size_t gsr_bwd_accum_bytes(int P);
 

@@ -90,10 +90,12 @@ BinView bin_view(void* blob, long long R)
     b.scratch_bytes = bin_scratch_bytes(R);
     return b;
 }
-ImgView img_view(void* blob, int W, int H)
+ImgView img_view(void* blob, int W, int H, int V)
 {
-    const size_t tiles = (size_t)((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
-    const size_t N = (size_t)W * H;
+    // V views are stacked vertically: tile row v * gy + ty belongs to view v (every view is padded to whole tiles)
+    const size_t gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (size_t)((H + GSR_TILE - 1) / GSR_TILE) * (V > 0 ? V : 1);
+    const size_t tiles = gx * gy;
+    const size_t N = (size_t)W * H * (V > 0 ? V : 1);
     ImgView v;
     char* p = (char*)blob;
     v.hdr = (BlobHeader*)p; p += sizeof(BlobHeader);
@@ -132,14 +134,16 @@ using namespace gsr;
 extern "C" {
 
 size_t gsr_geom_bytes(int P) { return geom_fixed_bytes(P) + geom_scratch_bytes(P); }
-size_t gsr_img_bytes(int W, int H)
+size_t gsr_img_bytes_batched(int W, int H, int n_views)
 {
-    const size_t tiles = (size_t)((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
-    const size_t N = (size_t)W * H;
-    const size_t gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
+    const size_t V = n_views > 0 ? n_views : 1;
+    const size_t gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (size_t)((H + GSR_TILE - 1) / GSR_TILE) * V;
+    const size_t tiles = gx * gy;
+    const size_t N = (size_t)W * H * V;
     return sizeof(BlobHeader) + align_up((tiles ? tiles : 1) * sizeof(uint2)) + 2 * align_up((N ? N : 1) * 4) +
            align_up((gx + 1) * (gy + 1) * sizeof(int));
 }
+size_t gsr_img_bytes(int W, int H) { return gsr_img_bytes_batched(W, H, 1); }
 size_t gsr_binning_bytes(int P, int R, int W, int H)
 {
     (void)P;
@@ -152,18 +156,23 @@ size_t gsr_binning_bytes(int P, int R, int W, int H)
 }
 size_t gsr_bwd_accum_bytes(int P) { return (size_t)(P > 0 ? P : 1) * 12 * sizeof(float); }
 
-int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream_, int* num_rendered)
+// V views of ONE Gaussian set in one pass: the views are stacked into a tall image (tile row v * gy + ty), every
+// (Gaussian, view) pair is a "virtual Gaussian" v * P + g with its own record, and depth sort, tile split and blending
+// run once over all of them.  V = 1 is the reference's single-view call.
+static int forward_impl(const GsrFwdArgs* a, int V, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream_, int* num_rendered)
 {
     cudaStream_t s = (cudaStream_t)stream_;
     if (!a || !num_rendered || !geom.fn || !binning.fn || !img.fn) return GSR_EINVAL;
     *num_rendered = 0;
-    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3) return GSR_EINVAL;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3 || V < 1) return GSR_EINVAL;
     if (!a->out_color || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
     const int gx = (a->W + GSR_TILE - 1) / GSR_TILE, gy = (a->H + GSR_TILE - 1) / GSR_TILE;
-    if (gx > 65535 || gy > 65535) return GSR_ETOOBIG;
+    if (gx > 65535 || (long long)gy * V > 65535 || (long long)a->P * V >= (1ll << 31)) return GSR_ETOOBIG;
+    const int Pv = a->P * V;                    // virtual Gaussians
+    const int gyT = gy * V, HT = gyT * GSR_TILE; // the tall image in whole tiles
     if (a->P == 0) {
         // reference binding returns the zero-filled image without calling the core (rasterize_points.cu:81)
-        GSR_CUDA(cudaMemsetAsync(a->out_color, 0, sizeof(float) * 3 * (size_t)a->W * a->H, s));
+        GSR_CUDA(cudaMemsetAsync(a->out_color, 0, sizeof(float) * 3 * (size_t)a->W * a->H * V, s));
         return GSR_OK;
     }
     if (!a->means3D || !a->opacities || !a->radii) return GSR_EINVAL;
@@ -171,19 +180,19 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     if (a->shs && !a->colors_precomp && (!a->cam_pos || a->M < (a->D + 1) * (a->D + 1))) return GSR_EINVAL;
     if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return GSR_ECOV;
 
-    void* gblob = geom.fn(geom.ctx, gsr_geom_bytes(a->P));
-    void* iblob = img.fn(img.ctx, gsr_img_bytes(a->W, a->H));
+    void* gblob = geom.fn(geom.ctx, gsr_geom_bytes(Pv));
+    void* iblob = img.fn(img.ctx, gsr_img_bytes_batched(a->W, a->H, V));
     if (!gblob || !iblob) return GSR_ENOMEM;
-    GeomView g = geom_view(gblob, a->P);
-    ImgView im = img_view(iblob, a->W, a->H);
+    GeomView g = geom_view(gblob, Pv);
+    ImgView im = img_view(iblob, a->W, a->H, V);
     GSR_CUDA(cudaMemsetAsync(g.hdr, 0, sizeof(BlobHeader), s));
-    const GeomScratch sc = carve_geom_scratch(g.scratch, a->P);
+    const GeomScratch sc = carve_geom_scratch(g.scratch, Pv);
     GSR_CUDA(cudaMemsetAsync(sc.ctl, 0, sc.ctl_words * 4, s));       // counters, histograms, look-back words
-    GSR_CUDA(cudaMemsetAsync(im.tile_diff, 0, sizeof(int) * (size_t)(gx + 1) * (gy + 1), s));
+    GSR_CUDA(cudaMemsetAsync(im.tile_diff, 0, sizeof(int) * (size_t)(gx + 1) * (gyT + 1), s));
 
     int rc;
     stage_begin(0, s);
-    if ((rc = launch_preprocess(*a, g, s))) return rc;
+    if ((rc = launch_preprocess(*a, V, g, s))) return rc;
     stage_end(0, s);
     GSR_STAGE(a->debug, s, "preprocess");
 
@@ -197,7 +206,7 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     GSR_CUDA(cudaEventRecord(g_R_event, s));
 
     stage_begin(1, s);
-    if ((rc = launch_depth_order(a->P, a->W, a->H, g, im, s))) return rc;
+    if ((rc = launch_depth_order(Pv, a->W, HT, g, im, s))) return rc;
     stage_end(1, s);
     GSR_STAGE(a->debug, s, "depth_order");
 
@@ -208,20 +217,20 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     const int R = (int)R_host;
     *num_rendered = R;
 
-    void* bblob = binning.fn(binning.ctx, gsr_binning_bytes(a->P, R, a->W, a->H));
+    void* bblob = binning.fn(binning.ctx, gsr_binning_bytes(Pv, R, a->W, HT));
     if (!bblob) return GSR_ENOMEM;
     BinView b = bin_view(bblob, R);
-    GSR_LAUNCH(init_headers_kernel, 1, 32, 0, s, g.hdr, b.hdr, im.hdr, a->P, R, a->W, a->H);
+    GSR_LAUNCH(init_headers_kernel, 1, 32, 0, s, g.hdr, b.hdr, im.hdr, Pv, R, a->W, a->H);
 
     stage_begin(2, s);
-    if (env_int("GSR_SORT", 0) == 1) rc = launch_tile_split_cub(a->P, R, a->W, a->H, g, b, im, s);
-    else rc = launch_tile_split(a->P, R, a->W, a->H, g, b, im, s);
+    if (env_int("GSR_SORT", 0) == 1) rc = launch_tile_split_cub(Pv, R, a->W, HT, g, b, im, s);
+    else rc = launch_tile_split(Pv, R, a->W, HT, g, b, im, s);
     if (rc) return rc;
     stage_end(2, s);
     GSR_STAGE(a->debug, s, "tile_split");
 
     stage_begin(3, s);
-    if ((rc = launch_blend_forward(R, a->W, a->H, a->background, g, b, im, a->out_color, s))) return rc;
+    if ((rc = launch_blend_forward(R, a->W, a->H, V, a->background, g, b, im, a->out_color, s))) return rc;
     stage_end(3, s);
     GSR_STAGE(a->debug, s, "blend_forward");
     if (a->debug && a->prefiltered) {
@@ -232,11 +241,22 @@ int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc i
     return GSR_OK;
 }
 
-int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream_)
+int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream, int* num_rendered)
+{
+    return forward_impl(a, 1, geom, binning, img, stream, num_rendered);
+}
+int gsr_forward_batched(const GsrFwdArgs* a, int n_views, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream,
+                        int* num_rendered)
+{
+    if (n_views > 1 && a && (a->colors_precomp || a->cov3D_precomp)) return GSR_EINVAL;   // per-view accumulation of their gradients is not wired
+    return forward_impl(a, n_views, geom, binning, img, stream, num_rendered);
+}
+
+static int backward_impl(const GsrBwdArgs* a, int V, gsr_stream_t stream_)
 {
     cudaStream_t s = (cudaStream_t)stream_;
     if (!a) return GSR_EINVAL;
-    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->R < 0 || a->D < 0 || a->D > 3) return GSR_EINVAL;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->R < 0 || a->D < 0 || a->D > 3 || V < 1) return GSR_EINVAL;
     if (a->P == 0) return GSR_OK;
     if (!a->means3D || !a->radii || !a->dL_dpix || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
     if (!a->geom_blob || !a->binning_blob || !a->img_blob || !a->accum) return GSR_EBLOB;
@@ -244,9 +264,10 @@ int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream_)
     if (a->shs && (!a->dL_dsh || !a->cam_pos)) return GSR_EINVAL;
     if (!a->cov3D_precomp && (!a->scales || !a->rotations || !a->dL_dscale || !a->dL_drot)) return GSR_ECOV;
 
-    GeomView g = geom_view(const_cast<void*>(a->geom_blob), a->P);
+    const int Pv = a->P * V;
+    GeomView g = geom_view(const_cast<void*>(a->geom_blob), Pv);
     BinView b = bin_view(const_cast<void*>(a->binning_blob), a->R);
-    ImgView im = img_view(const_cast<void*>(a->img_blob), a->W, a->H);
+    ImgView im = img_view(const_cast<void*>(a->img_blob), a->W, a->H, V);
     if (a->debug) {
         BlobHeader h[3];
         GSR_CUDA(cudaMemcpyAsync(&h[0], g.hdr, sizeof(BlobHeader), cudaMemcpyDeviceToHost, s));
@@ -254,22 +275,42 @@ int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream_)
         GSR_CUDA(cudaMemcpyAsync(&h[2], im.hdr, sizeof(BlobHeader), cudaMemcpyDeviceToHost, s));
         GSR_CUDA(cudaStreamSynchronize(s));
         for (int k = 0; k < 3; k++)
-            if (h[k].magic != GSR_MAGIC || h[k].kind != (uint32_t)(k + 1) || h[k].P != a->P || h[k].R != a->R || h[k].W != a->W ||
+            if (h[k].magic != GSR_MAGIC || h[k].kind != (uint32_t)(k + 1) || h[k].P != Pv || h[k].R != a->R || h[k].W != a->W ||
                 h[k].H != a->H)
                 return GSR_EBLOB;
     }
     float* accum = (float*)a->accum;
     int rc;
     stage_begin(4, s);
-    GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(a->P), s));
-    if ((rc = launch_blend_backward(a->R, a->W, a->H, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
+    GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(Pv), s));
+    if ((rc = launch_blend_backward(a->R, a->W, a->H, V, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
     stage_end(4, s);
     GSR_STAGE(a->debug, s, "blend_backward");
     stage_begin(5, s);
-    if ((rc = launch_preprocess_backward(*a, g, accum, s))) return rc;
+    for (int v = 0; v < V; v++) {
+        // per-Gaussian backward of view v over its slice of the virtual Gaussians; the views after the first add to
+        // what the first wrote (dL/dmean2D stays per view)
+        GsrBwdArgs av = *a;
+        GeomView gv = g;
+        const size_t o = (size_t)v * a->P;
+        gv.rec = g.rec + o; gv.clamped = g.clamped + o;
+        av.radii = a->radii + o;
+        av.viewmatrix = a->viewmatrix + 16 * v; av.projmatrix = a->projmatrix + 16 * v;
+        if (a->cam_pos) av.cam_pos = a->cam_pos + 3 * v;
+        av.dL_dmean2D = a->dL_dmean2D + 3 * o;
+        if (v > 0) av.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
+        if ((rc = launch_preprocess_backward(av, gv, accum + 12 * o, s))) return rc;
+    }
     stage_end(5, s);
     GSR_STAGE(a->debug, s, "preprocess_backward");
     return GSR_OK;
+}
+
+int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream) { return backward_impl(a, 1, stream); }
+int gsr_backward_batched(const GsrBwdArgs* a, int n_views, gsr_stream_t stream)
+{
+    if (n_views > 1 && a && (a->colors_precomp || a->cov3D_precomp)) return GSR_EINVAL;
+    return backward_impl(a, n_views, stream);
 }
 
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,

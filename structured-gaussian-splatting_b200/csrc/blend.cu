@@ -231,14 +231,16 @@ template <int UMAX, int MINB>
 __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                    float* __restrict__ out, uint32_t* __restrict__ planes, uint32_t plane_words)
+                    float* __restrict__ out, uint32_t* __restrict__ planes, uint32_t plane_words, int gyv)
 {
     __shared__ BlendStage stage[2];
     __shared__ uint32_t bits[2][8][8];     // [buffer][consumer warp][chunk of 32 entries]
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(blockIdx.y * GSR_TILE);
+    // batched calls stack the views' tile rows: tile row blockIdx.y = view * gyv + by; pixel coordinates stay per view
+    const uint32_t view = blockIdx.y / (uint32_t)gyv, by = blockIdx.y - view * (uint32_t)gyv;
+    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(by * GSR_TILE);
     const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
-    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const uint32_t py = by * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const float pxf = (float)px, pyf = (float)py;
     bool done = !inside;
@@ -302,13 +304,14 @@ blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     }
     cp_async_wait<0>();
     if (inside) {
-        const size_t pix = (size_t)W * py + px;
-        final_T[pix] = T;
-        n_contrib[pix] = last_contributor;
         const size_t HW = (size_t)H * W;
-        out[pix] = C0 + T * bg[0];
-        out[HW + pix] = C1 + T * bg[1];
-        out[2 * HW + pix] = C2 + T * bg[2];
+        const size_t pix = (size_t)W * py + px;
+        final_T[view * HW + pix] = T;
+        n_contrib[view * HW + pix] = last_contributor;
+        float* o = out + 3 * view * HW + pix;
+        o[0] = C0 + T * bg[0];
+        o[HW] = C1 + T * bg[1];
+        o[2 * HW] = C2 + T * bg[2];
     }
 }
 
@@ -434,21 +437,23 @@ size_t blend_plane_words(long long R, int W, int H)
     return (size_t)((R > 0 ? R : 0) >> 5) + 16 * tiles + 16;
 }
 
-int launch_blend_forward(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+int launch_blend_forward(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                          float* out_color, cudaStream_t s)
 {
-    const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
-    const uint32_t pw = (uint32_t)blend_plane_words(R, W, H);
+    const int gyv = (H + GSR_TILE - 1) / GSR_TILE;
+    const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, gyv * V);
+    const uint32_t pw = (uint32_t)blend_plane_words(R, W, gyv * V * GSR_TILE);
+    if (V > 1 && (env_int("GSR_BLEND", 0) != 0 || env_int("GSR_BLEND_STATS", 0) != 0)) return GSR_EINVAL;   // comparison arms are single-view
     if (env_int("GSR_BLEND_STATS", 0) == 1)
         GSR_LAUNCH(blend_stats_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H);
     if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
     else if (env_int("GSR_FWD_MINB", 4) == 3)
         GSR_LAUNCH((blend_fwd_v3_kernel<4, 3>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   out_color, b.scratch, pw);
+                   out_color, b.scratch, pw, gyv);
     else
         GSR_LAUNCH((blend_fwd_v3_kernel<4, 4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   out_color, b.scratch, pw);
+                   out_color, b.scratch, pw, gyv);
     return GSR_OK;
 }
 
@@ -1093,7 +1098,7 @@ __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     const uint32_t* __restrict__ planes, uint32_t plane_words, int W, int H, const float* __restrict__ bg,
                     const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
-                    float* __restrict__ accum)
+                    float* __restrict__ accum, int gyv)
 {
     constexpr int D = NS - 1;          // gather distance in steps
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1101,13 +1106,15 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpRed& R = S.red[wid];
     WarpRing<NS>& Q = S.ring[wid];
-    const float X0s = (float)(blockIdx.x * GSR_TILE + (wid & 1) * 8), Y0s = (float)(blockIdx.y * GSR_TILE + (wid >> 1) * 4);
+    const uint32_t view = blockIdx.y / (uint32_t)gyv, by = blockIdx.y - view * (uint32_t)gyv;     // see blend_fwd_v3_kernel
+    const float X0s = (float)(blockIdx.x * GSR_TILE + (wid & 1) * 8), Y0s = (float)(by * GSR_TILE + (wid >> 1) * 4);
     const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
-    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const uint32_t py = by * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const float pxf = (float)px, pyf = (float)py;
-    const size_t pix = (size_t)W * py + px;
     const size_t HW = (size_t)H * W;
+    const size_t pix = view * HW + (size_t)W * py + px;
+    dL_dpix += 2 * view * HW;                   // [V][3][H][W]: channel c of this pixel is dL_dpix[c * HW + pix]
     const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
     const uint2 range = ranges[tile];
 
@@ -1247,11 +1254,13 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     if (cnt) red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum);
 }
 
-int launch_blend_backward(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+int launch_blend_backward(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                           const float* dL_dpix, float* accum, cudaStream_t s)
 {
-    const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, (H + GSR_TILE - 1) / GSR_TILE);
-    const uint32_t pw = (uint32_t)blend_plane_words(R, W, H);
+    const int gyv = (H + GSR_TILE - 1) / GSR_TILE;
+    const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, gyv * V);
+    const uint32_t pw = (uint32_t)blend_plane_words(R, W, gyv * V * GSR_TILE);
+    if (V > 1 && env_int("GSR_BLEND", 0) != 0) return GSR_EINVAL;        // comparison arms are single-view
     const int variant = env_int("GSR_BLEND", 0);       // 0: v5 (needs the planes of blend_fwd_v3), 1 / 3 / 4: comparison arms
     if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
@@ -1270,13 +1279,13 @@ int launch_blend_backward(long long R, int W, int H, const float* bg, const Geom
         const int ns = env_int("GSR_BWD_NS", 2), minb = env_int("GSR_BWD_MINB", 4);
         if (ns == 4)
             GSR_LAUNCH((blend_bwd_v5_kernel<4, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<4>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum);
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv);
         else if (minb == 3)
             GSR_LAUNCH((blend_bwd_v5_kernel<2, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum);
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv);
         else
             GSR_LAUNCH((blend_bwd_v5_kernel<2, 4>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum);
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv);
     } else {
         static bool attr_set = false;
         if (!attr_set) {

@@ -106,7 +106,7 @@ size_t geom_scratch_bytes(int P);
 size_t bin_scratch_bytes(long long R);
 GeomView geom_view(void* blob, int P);
 BinView  bin_view(void* blob, long long R);
-ImgView  img_view(void* blob, int W, int H);
+ImgView  img_view(void* blob, int W, int H, int V = 1);
 
 // ---------------------------------------------------------------- stage entry points (one per .cu)
 struct Camera {                // lives in shared memory of the per-Gaussian kernels
@@ -149,7 +149,7 @@ __device__ __forceinline__ void load_camera(Camera& cam, const CameraArgs& ca)
 #endif
 
 // preprocess.cu
-int launch_preprocess(const GsrFwdArgs& a, const GeomView& g, cudaStream_t s);
+int launch_preprocess(const GsrFwdArgs& a, int V, const GeomView& g, cudaStream_t s);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
 int launch_preprocess_backward(const GsrBwdArgs& a, const GeomView& g, const float* accum, cudaStream_t s);
 
@@ -170,9 +170,9 @@ int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint
 
 // blend.cu
 size_t blend_plane_words(long long R, int W, int H);
-int launch_blend_forward(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+int launch_blend_forward(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                          float* out_color, cudaStream_t s);
-int launch_blend_backward(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+int launch_blend_backward(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
                           const float* dL_dpix, float* accum, cudaStream_t s);
 
 // knn.cu

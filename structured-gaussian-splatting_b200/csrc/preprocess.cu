@@ -141,9 +141,16 @@ struct PreArgs {
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraArgs ca)
 {
     __shared__ Camera cam;
+    // blockIdx.y = view of a batched call (gsr_forward_batched): its camera, its slice v * P + idx of the per-view
+    // outputs, its band of tile rows in the stacked image
+    const int view = blockIdx.y;
+    ca.view += 16 * view;
+    if (ca.proj) ca.proj += 16 * view;
+    if (ca.cam) ca.cam += 3 * view;
     load_camera(cam, ca);
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P) return;
+    const size_t oidx = (size_t)view * a.P + idx;
 
     SplatRec out;
     out.q0 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -207,17 +214,18 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
                 out.q1 = make_float4(conic.z, a.opac[idx], rgb[0], rgb[1]);
                 out.q2 = make_float4(rgb[2], p_view.z, __int_as_float((int)my_radius), __uint_as_float(area));
                 radius_out = (int)my_radius;
-                rect_out = make_ushort4((unsigned short)x0, (unsigned short)y0, (unsigned short)x1, (unsigned short)y1);
+                const int yoff = view * cam.gy;
+                rect_out = make_ushort4((unsigned short)x0, (unsigned short)(y0 + yoff), (unsigned short)x1, (unsigned short)(y1 + yoff));
             }
         }
     } else if (a.prefiltered) {
         *a.err = 1;   // reference: printf + __trap (auxiliary.h:156-160); we flag it and report GSR_EINVAL in debug mode
     }
-    a.radii[idx] = radius_out;
-    a.rec[idx] = out;
-    a.clamped[idx] = (uint8_t)clamp_bits;
-    a.depthkey[idx] = __float_as_uint(out.q2.y);
-    a.rect[idx] = rect_out;
+    a.radii[oidx] = radius_out;
+    a.rec[oidx] = out;
+    a.clamped[oidx] = (uint8_t)clamp_bits;
+    a.depthkey[oidx] = __float_as_uint(out.q2.y);
+    a.rect[oidx] = rect_out;
     // R = sum of tiles touched: one atomic per warp that has any
     uint32_t tiles = __float_as_uint(out.q2.w);
     const unsigned am = __activemask();
@@ -225,7 +233,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
     if (tiles && (int)(threadIdx.x & 31) == __ffs(am) - 1) atomicAdd(a.total, tiles);
 }
 
-int launch_preprocess(const GsrFwdArgs& a, const GeomView& g, cudaStream_t s)
+int launch_preprocess(const GsrFwdArgs& a, int V, const GeomView& g, cudaStream_t s)
 {
     const CameraArgs cam = make_camera_args(a.viewmatrix, a.projmatrix, a.cam_pos, a.tan_fovx, a.tan_fovy, a.W, a.H);
     PreArgs k;
@@ -233,10 +241,10 @@ int launch_preprocess(const GsrFwdArgs& a, const GeomView& g, cudaStream_t s)
     k.means = a.means3D; k.shs = a.shs; k.colors_pre = a.colors_precomp; k.opac = a.opacities;
     k.scales = a.scales; k.rots = a.rotations; k.cov_pre = a.cov3D_precomp; k.mod = a.scale_modifier;
     k.prefiltered = a.prefiltered; k.radii = a.radii; k.rec = g.rec; k.clamped = g.clamped;
-    const GeomScratch sc = carve_geom_scratch(g.scratch, a.P);
+    const GeomScratch sc = carve_geom_scratch(g.scratch, a.P * V);
     k.depthkey = sc.depthkey; k.rect = sc.rect; k.total = sc.counters;
     k.err = reinterpret_cast<int*>(sc.counters + 8);
-    GSR_LAUNCH(preprocess_fwd_kernel, cdiv(a.P, 256), 256, 0, s, k, cam);
+    GSR_LAUNCH(preprocess_fwd_kernel, dim3(cdiv(a.P, 256), V), 256, 0, s, k, cam);
     return GSR_OK;
 }
 

@@ -230,6 +230,92 @@ export_binning(const torch::Tensor& geomBuffer, const torch::Tensor& binningBuff
     return std::make_tuple(keys, vals, ranges, ncontrib, finalT);
 }
 
+// Batched multi-view entry points (extension): V cameras over one Gaussian set per call.
+//   viewmatrices [V,4,4], projmatrices [V,4,4], camposs [V,3]  ->  colors [V,3,H,W], radii [V,P]
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_batched(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& opacity,
+                            const torch::Tensor& scales, const torch::Tensor& rotations, const float scale_modifier,
+                            const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices, const float tan_fovx,
+                            const float tan_fovy, const int image_height, const int image_width, const torch::Tensor& sh,
+                            const int degree, const torch::Tensor& camposs, const bool debug)
+{
+    if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
+    TORCH_CHECK(viewmatrices.ndimension() == 3 && projmatrices.sizes() == viewmatrices.sizes() && camposs.ndimension() == 2 &&
+                    camposs.size(0) == viewmatrices.size(0),
+                "viewmatrices / projmatrices must be [V,4,4] and camposs [V,3]");
+    TORCH_CHECK(sh.numel() != 0 && scales.numel() != 0 && rotations.numel() != 0, "batched rasterization takes shs, scales and rotations");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = (int)means3D.size(0), V = (int)viewmatrices.size(0);
+    const int H = image_height, W = image_width;
+    auto f32 = means3D.options().dtype(torch::kFloat32);
+    auto i32 = means3D.options().dtype(torch::kInt32);
+    auto u8 = means3D.options().dtype(torch::kByte);
+    torch::Tensor out_color = P == 0 ? torch::zeros({V, 3, H, W}, f32) : torch::empty({V, 3, H, W}, f32);
+    torch::Tensor radii = P == 0 ? torch::zeros({V, P}, i32) : torch::empty({V, P}, i32);
+    torch::Tensor geomBuffer = torch::empty({0}, u8), binningBuffer = torch::empty({0}, u8), imgBuffer = torch::empty({0}, u8);
+    int rendered = 0;
+    if (P != 0 && V != 0) {
+        F32 bg(background), m3(means3D), op(opacity), sc(scales), rot(rotations), vm(viewmatrices), pm(projmatrices), shs(sh), cam(camposs);
+        GsrFwdArgs a = {};
+        a.P = P; a.D = degree; a.M = (int)sh.size(1); a.W = W; a.H = H;
+        a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr(); a.opacities = op.ptr();
+        a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr();
+        a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.prefiltered = 0; a.debug = debug;
+        a.out_color = out_color.data_ptr<float>(); a.radii = radii.data_ptr<int>();
+        check(gsr_forward_batched(&a, V, GsrAlloc{resize_cb, &geomBuffer}, GsrAlloc{resize_cb, &binningBuffer},
+                                  GsrAlloc{resize_cb, &imgBuffer}, current_stream(), &rendered),
+              "rasterize_gaussians_batched");
+    }
+    return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer);
+}
+
+// returns (dL_dmeans2D [V,P,3], dL_dopacity [P,1], dL_dmeans3D [P,3], dL_dsh [P,M,3], dL_dscales [P,3], dL_drotations [P,4]),
+// all but the first summed over the views
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_batched_backward(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                                     const torch::Tensor& scales, const torch::Tensor& rotations, const float scale_modifier,
+                                     const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices, const float tan_fovx,
+                                     const float tan_fovy, const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                                     const torch::Tensor& camposs, const torch::Tensor& geomBuffer, const int R,
+                                     const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug)
+{
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
+    TORCH_CHECK(dL_dout_color.ndimension() == 4, "dL_dout_color must be [V,3,H,W]");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = (int)means3D.size(0), V = (int)dL_dout_color.size(0);
+    const int H = (int)dL_dout_color.size(2), W = (int)dL_dout_color.size(3);
+    const int M = (int)sh.size(1);
+    auto f32 = means3D.options().dtype(torch::kFloat32);
+    const bool live = P != 0 && V != 0;
+    auto alloc = [&](std::initializer_list<int64_t> shape) { return live ? torch::empty(shape, f32) : torch::zeros(shape, f32); };
+    torch::Tensor dL_dmeans2D = alloc({V, P, 3}), dL_dopacity = alloc({P, 1}), dL_dmeans3D = alloc({P, 3}), dL_dsh = alloc({P, M, 3}),
+                  dL_dscales = alloc({P, 3}), dL_drotations = alloc({P, 4});
+    if (live) {
+        torch::Tensor accum = torch::empty({(long long)(gsr_bwd_accum_bytes(P * V) / sizeof(float))}, f32);
+        F32 bg(background), m3(means3D), sc(scales), rot(rotations), vm(viewmatrices), pm(projmatrices), shs(sh), cam(camposs),
+            dpix(dL_dout_color);
+        torch::Tensor radii_c = radii.contiguous();
+        GsrBwdArgs a = {};
+        a.P = P; a.D = degree; a.M = M; a.R = R; a.W = W; a.H = H;
+        a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr();
+        a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr();
+        a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+        a.radii = radii_c.data_ptr<int>();
+        a.geom_blob = geomBuffer.data_ptr(); a.binning_blob = binningBuffer.data_ptr(); a.img_blob = imageBuffer.data_ptr();
+        a.dL_dpix = dpix.ptr();
+        a.accum = accum.data_ptr();
+        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>(); a.dL_dopacity = dL_dopacity.data_ptr<float>();
+        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>(); a.dL_dsh = dL_dsh.data_ptr<float>();
+        a.dL_dscale = dL_dscales.data_ptr<float>(); a.dL_drot = dL_drotations.data_ptr<float>();
+        a.debug = debug;
+        check(gsr_backward_batched(&a, V, current_stream()), "rasterize_gaussians_batched_backward");
+    }
+    return std::make_tuple(dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_dsh, dL_dscales, dL_drotations);
+}
+
 // fused L1 loss: returns (sum |image - target| as a 1-element tensor, dL/dimage for loss = mean |image - target|)
 std::tuple<torch::Tensor, torch::Tensor> l1_loss(const torch::Tensor& image, const torch::Tensor& target)
 {
@@ -249,6 +335,8 @@ std::tuple<torch::Tensor, torch::Tensor> l1_loss(const torch::Tensor& image, con
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
 {
     m.def("l1_loss", &l1_loss);
+    m.def("rasterize_gaussians_batched", &rasterize_gaussians_batched);
+    m.def("rasterize_gaussians_batched_backward", &rasterize_gaussians_batched_backward);
     m.def("rasterize_gaussians", &rasterize_gaussians);
     m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
     m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into);
