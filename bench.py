@@ -45,6 +45,8 @@ def parse_args():
     ap.add_argument("--gaussians", type=int, default=0, help="override P (debug only; makes the number invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--batched", action="store_true",
+                    help="render each rank's views of a step in ONE batched call (GaussianRasterizerBatched, row f1)")
     ap.add_argument("--plain-autograd", action="store_true",
                     help="sum the views' gradients through autograd (.grad += per parameter) instead of in the backward kernels")
     return ap.parse_args()
@@ -231,7 +233,32 @@ def main():
         # view 0 of the step overwrites the flat gradient buffer, the following views add to it (in the kernels)
         return dgr.set_grad_mode(("overwrite" if i == 0 else "accumulate") if fused else None)
 
+    if args.batched:
+        from diff_gaussian_rasterization.batched import BatchedRasterizationSettings, GaussianRasterizerBatched
+        vm_all = torch.stack([c.viewmatrix for c in cams]); pm_all = torch.stack([c.projmatrix for c in cams])
+        cp_all = torch.stack([c.campos for c in cams])
+        go_b = go.unsqueeze(0).expand(vps, -1, -1, -1).contiguous()
+
+    def render_batched(ks, vm, pm, cp):
+        rs = BatchedRasterizationSettings(spec.H, spec.W, cams[0].tanfovx, cams[0].tanfovy, bg, 1.0, vm, pm, spec.D, cp, False)
+        means2D = torch.zeros(len(ks), P, 3, device=dev, requires_grad=True)
+        return GaussianRasterizerBatched(rs)(params["means3D"], means2D, params["opacities"], params["shs"], params["scales"],
+                                             params["rotations"])
+
+    def step_device_batched(step, collect=False):
+        ks = torch.tensor(my_views(step), device=dev)
+        prev = dgr.set_grad_mode("overwrite")
+        color, radii = render_batched(ks, vm_all[ks], pm_all[ks], cp_all[ks])
+        color.backward(go_b)
+        dgr.set_grad_mode(prev)
+        if collect:
+            stats["Pv"] += int((radii > 0).sum())
+            stats["views"] += len(ks)
+        flat.all_reduce()
+
     def step_device(step, collect=False):
+        if args.batched:
+            return step_device_batched(step, collect)
         if not fused:
             flat.zero_()
         for i, k in enumerate(my_views(step)):
@@ -271,7 +298,36 @@ def main():
         tgt.record_stream(cur); cm.record_stream(cur)
         return tgt, cm
 
+    def prefetch_step(step):
+        with torch.cuda.stream(copy_stream):
+            ks = my_views(step)
+            tgt = [target_host.to(dev, non_blocking=True) for _ in ks]
+            cm = [cam_host[k].to(dev, non_blocking=True) for k in ks]
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        pending[("step", step)] = (tgt, cm, ev)
+
+    def step_e2e_batched(step):
+        if ("step", step) not in pending:
+            prefetch_step(step)
+        tgt, cm, ev = pending.pop(("step", step))
+        cur = torch.cuda.current_stream()
+        cur.wait_event(ev)
+        for t in tgt + cm:
+            t.record_stream(cur)
+        prefetch_step(step + 1)                      # next step's inputs travel while this one renders
+        cmat = torch.stack(cm)
+        prev = dgr.set_grad_mode("overwrite")
+        color, radii = render_batched(my_views(step), cmat[:, :16].reshape(-1, 4, 4), cmat[:, 16:32].reshape(-1, 4, 4), cmat[:, 32:35])
+        loss = losses.l1_loss(color, torch.stack(tgt))
+        loss.backward()
+        dgr.set_grad_mode(prev)
+        flat.all_reduce()
+        _ = float(loss.item())
+
     def step_e2e(step):
+        if args.batched:
+            return step_e2e_batched(step)
         if not fused:
             flat.zero_()
         views = my_views(step)
@@ -350,7 +406,7 @@ def main():
         for name, ms, calls in stage_rows:
             if calls == 0 or name not in sb:
                 continue
-            avg = ms / calls
+            avg = ms / calls / (vps if args.batched else 1)       # per view
             gbs = sb[name] / (avg * 1e-3) / 1e9
             stages[name] = {"ms": round(avg, 4), "algo_bytes": int(sb[name]), "GBps": round(gbs, 1), "frac_hbm": round(gbs / peak, 4)}
             if avg > dom_ms:
@@ -383,6 +439,7 @@ def main():
                            "views_per_gpu_per_step": vps, "R_per_view": R, "visible_per_view": int(Pv),
                            "parallelism": "view-sharded dp%d, one NCCL all-reduce of %d MB per step" % (world, flat.nbytes() >> 20),
                            "grad_sum": "in the backward kernels (set_grad_mode)" if fused else "autograd .grad +=",
+                           "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else "GaussianRasterizer: one call per view",
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat.nbytes() + 48 * P + 20 * R) / 1e9)},
                 "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches,

@@ -279,8 +279,12 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
                                      const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices, const float tan_fovx,
                                      const float tan_fovy, const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
                                      const torch::Tensor& camposs, const torch::Tensor& geomBuffer, const int R,
-                                     const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug)
+                                     const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
+                                     const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
+                                     const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate)
 {
+    // non-empty `into_*` (all five or none): the summed gradients are written (or, with `accumulate`, added) straight into
+    // these buffers - the parameters' .grad - and the corresponding returned tensors are empty
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
     TORCH_CHECK(dL_dout_color.ndimension() == 4, "dL_dout_color must be [V,3,H,W]");
     const c10::cuda::CUDAGuard guard(means3D.device());
@@ -290,8 +294,20 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
     auto f32 = means3D.options().dtype(torch::kFloat32);
     const bool live = P != 0 && V != 0;
     auto alloc = [&](std::initializer_list<int64_t> shape) { return live ? torch::empty(shape, f32) : torch::zeros(shape, f32); };
-    torch::Tensor dL_dmeans2D = alloc({V, P, 3}), dL_dopacity = alloc({P, 1}), dL_dmeans3D = alloc({P, 3}), dL_dsh = alloc({P, M, 3}),
-                  dL_dscales = alloc({P, 3}), dL_drotations = alloc({P, 4});
+    const bool into = into_means3D.numel() != 0;
+    if (into) {
+        auto ok = [&](const torch::Tensor& t, int64_t n) {
+            return t.is_cuda() && t.scalar_type() == torch::kFloat32 && t.is_contiguous() && t.numel() == n;
+        };
+        TORCH_CHECK(ok(into_means3D, (int64_t)P * 3) && ok(into_opacity, P) && ok(into_sh, (int64_t)P * M * 3) &&
+                        ok(into_scales, (int64_t)P * 3) && ok(into_rotations, (int64_t)P * 4),
+                    "gradient targets must be contiguous fp32 CUDA tensors with the gradients' element counts");
+    }
+    auto none = [&]() { return torch::empty({0}, f32); };
+    torch::Tensor dL_dmeans2D = alloc({V, P, 3});
+    torch::Tensor dL_dopacity = into ? none() : alloc({P, 1}), dL_dmeans3D = into ? none() : alloc({P, 3}),
+                  dL_dsh = into ? none() : alloc({P, M, 3}), dL_dscales = into ? none() : alloc({P, 3}),
+                  dL_drotations = into ? none() : alloc({P, 4});
     if (live) {
         torch::Tensor accum = torch::empty({(long long)(gsr_bwd_accum_bytes(P * V) / sizeof(float))}, f32);
         F32 bg(background), m3(means3D), sc(scales), rot(rotations), vm(viewmatrices), pm(projmatrices), shs(sh), cam(camposs),
@@ -307,10 +323,14 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
         a.geom_blob = geomBuffer.data_ptr(); a.binning_blob = binningBuffer.data_ptr(); a.img_blob = imageBuffer.data_ptr();
         a.dL_dpix = dpix.ptr();
         a.accum = accum.data_ptr();
-        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>(); a.dL_dopacity = dL_dopacity.data_ptr<float>();
-        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>(); a.dL_dsh = dL_dsh.data_ptr<float>();
-        a.dL_dscale = dL_dscales.data_ptr<float>(); a.dL_drot = dL_drotations.data_ptr<float>();
+        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>();
+        a.dL_dopacity = (into ? into_opacity : dL_dopacity).data_ptr<float>();
+        a.dL_dmean3D = (into ? into_means3D : dL_dmeans3D).data_ptr<float>();
+        a.dL_dsh = (into ? into_sh : dL_dsh).data_ptr<float>();
+        a.dL_dscale = (into ? into_scales : dL_dscales).data_ptr<float>();
+        a.dL_drot = (into ? into_rotations : dL_drotations).data_ptr<float>();
         a.debug = debug;
+        if (into && accumulate) a.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
         check(gsr_backward_batched(&a, V, current_stream()), "rasterize_gaussians_batched_backward");
     }
     return std::make_tuple(dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_dsh, dL_dscales, dL_drotations);

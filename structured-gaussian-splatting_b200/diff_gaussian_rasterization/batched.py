@@ -17,6 +17,8 @@ import torch
 import torch.nn as nn
 
 from . import _C
+from . import _grad_target
+import diff_gaussian_rasterization as _dgr
 
 
 class BatchedRasterizationSettings(NamedTuple):
@@ -41,6 +43,10 @@ class _RasterizeGaussiansBatched(torch.autograd.Function):
             rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree, rs.camposs, rs.debug)
         ctx.rs = rs
         ctx.R = R
+        # diff_gaussian_rasterization.set_grad_mode: write / add the summed gradients straight into the leaves' .grad
+        ctx.grad_mode = _dgr._GRAD_MODE
+        targets = tuple(_grad_target(t) for t in (means3D, opacities, sh, scales, rotations)) if ctx.grad_mode else ()
+        ctx.grad_targets = targets if targets and all(t is not None for t in targets) else None
         ctx.save_for_backward(means3D, scales, rotations, radii, sh, geom, binning, img)
         ctx.mark_non_differentiable(radii)
         return color, radii
@@ -51,7 +57,10 @@ class _RasterizeGaussiansBatched(torch.autograd.Function):
         means3D, scales, rotations, radii, sh, geom, binning, img = ctx.saved_tensors
         g2d, gop, g3d, gsh, gsc, grot = _C.rasterize_gaussians_batched_backward(
             rs.bg, means3D, radii, scales, rotations, rs.scale_modifier, rs.viewmatrices, rs.projmatrices, rs.tanfovx, rs.tanfovy,
-            grad_color, sh, rs.sh_degree, rs.camposs, geom, ctx.R, binning, img, rs.debug)
+            grad_color, sh, rs.sh_degree, rs.camposs, geom, ctx.R, binning, img, rs.debug,
+            *(ctx.grad_targets if ctx.grad_targets else (torch.Tensor([]),) * 5), ctx.grad_mode == "accumulate")
+        if ctx.grad_targets:
+            return None, g2d, None, None, None, None, None
         return g3d, g2d, gsh, gop, gsc, grot, None
 
 
