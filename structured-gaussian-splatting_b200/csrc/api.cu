@@ -287,19 +287,23 @@ static int backward_impl(const GsrBwdArgs* a, int V, gsr_stream_t stream_)
     stage_end(4, s);
     GSR_STAGE(a->debug, s, "blend_backward");
     stage_begin(5, s);
-    for (int v = 0; v < V; v++) {
-        // per-Gaussian backward of view v over its slice of the virtual Gaussians; the views after the first add to
-        // what the first wrote (dL/dmean2D stays per view)
-        GsrBwdArgs av = *a;
-        GeomView gv = g;
-        const size_t o = (size_t)v * a->P;
-        gv.rec = g.rec + o; gv.clamped = g.clamped + o;
-        av.radii = a->radii + o;
-        av.viewmatrix = a->viewmatrix + 16 * v; av.projmatrix = a->projmatrix + 16 * v;
-        if (a->cam_pos) av.cam_pos = a->cam_pos + 3 * v;
-        av.dL_dmean2D = a->dL_dmean2D + 3 * o;
-        if (v > 0) av.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
-        if ((rc = launch_preprocess_backward(av, gv, accum + 12 * o, s))) return rc;
+    if (V <= GSR_MAX_VIEWS) {
+        // one launch pair over all views: the per-view contributions are summed in registers (preprocess_bwd.cu)
+        if ((rc = launch_preprocess_backward(*a, V, g, accum, s))) return rc;
+    } else {
+        for (int v = 0; v < V; v++) {
+            // view by view over its slice of the virtual Gaussians; the views after the first add to what the first wrote
+            GsrBwdArgs av = *a;
+            GeomView gv = g;
+            const size_t o = (size_t)v * a->P;
+            gv.rec = g.rec + o; gv.clamped = g.clamped + o;
+            av.radii = a->radii + o;
+            av.viewmatrix = a->viewmatrix + 16 * v; av.projmatrix = a->projmatrix + 16 * v;
+            if (a->cam_pos) av.cam_pos = a->cam_pos + 3 * v;
+            av.dL_dmean2D = a->dL_dmean2D + 3 * o;
+            if (v > 0) av.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
+            if ((rc = launch_preprocess_backward(av, 1, gv, accum + 12 * o, s))) return rc;
+        }
     }
     stage_end(5, s);
     GSR_STAGE(a->debug, s, "preprocess_backward");

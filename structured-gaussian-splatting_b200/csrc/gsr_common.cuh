@@ -10,6 +10,7 @@
 
 #define GSR_TILE 16                 // reference config.h:16-17 (BLOCK_X = BLOCK_Y = 16), part of the bit-exact contract
 #define GSR_MAGIC 0x47535242u       // "GSRB"
+#define GSR_MAX_VIEWS 16            // views the fused per-Gaussian backward of a batched call handles in one launch
 
 namespace gsr {
 
@@ -151,7 +152,7 @@ __device__ __forceinline__ void load_camera(Camera& cam, const CameraArgs& ca)
 // preprocess.cu
 int launch_preprocess(const GsrFwdArgs& a, int V, const GeomView& g, cudaStream_t s);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
-int launch_preprocess_backward(const GsrBwdArgs& a, const GeomView& g, const float* accum, cudaStream_t s);
+int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, const float* accum, cudaStream_t s);
 
 // sort.cu
 // sorts Gaussian ids by depth bits (stable) into g.order; counts instances per tile -> tile ranges, split-pass histograms

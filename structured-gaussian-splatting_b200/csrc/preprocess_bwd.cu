@@ -38,6 +38,7 @@ struct PreBwdArgs {
     float* dL_dscale;        // [P,3] or null
     float* dL_drot;          // [P,4] or null
     unsigned acc;            // GSR_ACC_* bits: add to the existing contents (visible rows only) instead of overwriting
+    int V;                   // views of a batched call (<= GSR_MAX_VIEWS); per-view arrays are [V][P]
     int sh_done;             // the SH part (dL_dsh, its share of dL_dmean3D) was done by sh_bwd_m16_kernel
 };
 
@@ -74,20 +75,35 @@ __device__ __forceinline__ void store_sh_grads(float* __restrict__ dst, const fl
     }
 }
 
-template <bool WITH_SH>
-__global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(PreBwdArgs a, CameraArgs ca)
+template <bool WITH_SH, bool MULTI>
+__global__ void __launch_bounds__(256, WITH_SH ? 1 : (MULTI ? 3 : 4)) preprocess_bwd_kernel(PreBwdArgs a, CameraArgs ca)
 {
-    __shared__ Camera cam;
-    load_camera(cam, ca);
+    const int NV = MULTI ? a.V : 1;            // compile-time 1 for the single-view call: the view loops fold away
+    // a.V views of a batched call (1 for the reference's single-view call): view v owns slice v * P + idx of the per-view
+    // arrays (radii, records, clamp flags, accumulator rows, dL/dmean2D); the parameter gradients are summed over the
+    // views in registers and written once.
+    __shared__ Camera cams[MULTI ? GSR_MAX_VIEWS : 1];
+    for (int v = 0; v < NV; v++) {
+        CameraArgs cv = ca;
+        cv.view += 16 * v;
+        if (cv.proj) cv.proj += 16 * v;
+        if (cv.cam) cv.cam += 3 * v;
+        load_camera(cams[v], cv);
+    }
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P) return;
     const int M3f = 3 * a.M;
 
     const bool acc_m = a.acc & GSR_ACC_MEAN3D, acc_o = a.acc & GSR_ACC_OPACITY, acc_sh = a.acc & GSR_ACC_SH,
                acc_s = a.acc & GSR_ACC_SCALE, acc_r = a.acc & GSR_ACC_ROT;
-    if (!(a.radii[idx] > 0)) {
-        // culled: every owned gradient row is zero (left untouched when accumulating)
-        a.dL_dmean2D[3 * idx] = 0.f; a.dL_dmean2D[3 * idx + 1] = 0.f; a.dL_dmean2D[3 * idx + 2] = 0.f;
+    bool any_visible = false;
+    for (int v = 0; v < NV; v++) any_visible = any_visible || a.radii[(size_t)v * a.P + idx] > 0;
+    if (!any_visible) {
+        // culled in every view: every owned gradient row is zero (left untouched when accumulating)
+        for (int v = 0; v < NV; v++) {
+            float* m2 = a.dL_dmean2D + 3 * ((size_t)v * a.P + idx);
+            m2[0] = 0.f; m2[1] = 0.f; m2[2] = 0.f;
+        }
         if (!acc_o) a.dL_dopacity[idx] = 0.f;
         if (!acc_m && !a.sh_done) { a.dL_dmean3D[3 * idx] = 0.f; a.dL_dmean3D[3 * idx + 1] = 0.f; a.dL_dmean3D[3 * idx + 2] = 0.f; }
         if (a.dL_dcolor) { a.dL_dcolor[3 * idx] = 0.f; a.dL_dcolor[3 * idx + 1] = 0.f; a.dL_dcolor[3 * idx + 2] = 0.f; }
@@ -105,20 +121,6 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(Pr
         }
         return;
     }
-
-    // accumulator row: three 16-byte loads
-    const float4* ar = reinterpret_cast<const float4*>(a.accum + (size_t)12 * idx);
-    const float4 A0 = ar[0], A1 = ar[1], A2 = ar[2];
-    const float dcol[3] = {A0.x, A0.y, A0.z};
-    // moments -> gradients (backward.cu:536-551 with the per-Gaussian constants factored out of the pixel sums)
-    const float4 r0 = a.rec[idx].q0, r1 = a.rec[idx].q1;
-    const float cA = r0.z, cB = r0.w, cC = r1.x, opac = r1.y;
-    const float g2x = -0.5f * cam.W * (cA * A0.w + cB * A1.x);
-    const float g2y = -0.5f * cam.H * (cC * A1.x + cB * A0.w);
-    const float dcon_x = -0.5f * A1.y, dcon_y = -0.5f * A1.z, dcon_w = -0.5f * A1.w;
-    a.dL_dmean2D[3 * idx] = g2x; a.dL_dmean2D[3 * idx + 1] = g2y; a.dL_dmean2D[3 * idx + 2] = 0.f;
-    put(a.dL_dopacity + idx, opac > 0.f ? A2.x / opac : 0.f, acc_o);
-    if (a.dL_dcolor) { a.dL_dcolor[3 * idx] = dcol[0]; a.dL_dcolor[3 * idx + 1] = dcol[1]; a.dL_dcolor[3 * idx + 2] = dcol[2]; }
 
     const float3 p = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
 
@@ -145,6 +147,31 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(Pr
         c6[0] = Sig.c[0][0]; c6[1] = Sig.c[0][1]; c6[2] = Sig.c[0][2];
         c6[3] = Sig.c[1][1]; c6[4] = Sig.c[1][2]; c6[5] = Sig.c[2][2];
     }
+
+    // ---- per view
+    float s_dop = 0.f, s_dm[3] = {0.f, 0.f, 0.f}, s_dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    bool sh_written = false;
+    (void)sh_written;
+    for (int v = 0; v < NV; v++) {
+    const Camera& cam = cams[v];
+    const size_t vi = (size_t)v * a.P + idx;
+    if (!(a.radii[vi] > 0)) {
+        a.dL_dmean2D[3 * vi] = 0.f; a.dL_dmean2D[3 * vi + 1] = 0.f; a.dL_dmean2D[3 * vi + 2] = 0.f;
+        continue;
+    }
+    // accumulator row: three 16-byte loads
+    const float4* ar = reinterpret_cast<const float4*>(a.accum + (size_t)12 * vi);
+    const float4 A0 = ar[0], A1 = ar[1], A2 = ar[2];
+    const float dcol[3] = {A0.x, A0.y, A0.z};
+    // moments -> gradients (backward.cu:536-551 with the per-Gaussian constants factored out of the pixel sums)
+    const float4 r0 = a.rec[vi].q0, r1 = a.rec[vi].q1;
+    const float cA = r0.z, cB = r0.w, cC = r1.x, opac = r1.y;
+    const float g2x = -0.5f * cam.W * (cA * A0.w + cB * A1.x);
+    const float g2y = -0.5f * cam.H * (cC * A1.x + cB * A0.w);
+    const float dcon_x = -0.5f * A1.y, dcon_y = -0.5f * A1.z, dcon_w = -0.5f * A1.w;
+    a.dL_dmean2D[3 * vi] = g2x; a.dL_dmean2D[3 * vi + 1] = g2y; a.dL_dmean2D[3 * vi + 2] = 0.f;
+    s_dop += opac > 0.f ? A2.x / opac : 0.f;
+    if (a.dL_dcolor) { a.dL_dcolor[3 * idx] = dcol[0]; a.dL_dcolor[3 * idx + 1] = dcol[1]; a.dL_dcolor[3 * idx + 2] = dcol[2]; }
 
     // ---- cov2D backward (backward.cu:144-274)
     float3 t = xform4x3(p, cam.view);
@@ -227,7 +254,7 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(Pr
         const float s2 = ox * ox + oy * oy + oz * oz;
         const float len = sqrtf(s2);
         const float x = ox / len, y = oy / len, z = oz / len;
-        const uint32_t cl = a.clamped[idx];
+        const uint32_t cl = a.clamped[vi];
         const float dRGB[3] = {(cl & 1) ? 0.f : dcol[0], (cl & 2) ? 0.f : dcol[1], (cl & 4) ? 0.f : dcol[2]};
         const float* shp = a.shs + (size_t)M3f * idx;
         const bool vec = (((size_t)shp) & 15) == 0 && (M3f % 4 == 0);
@@ -289,7 +316,8 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(Pr
         // dL/dsh[k][ch] = basis_k * dL/dRGB[ch]; reuse f as the output row
 #pragma unroll
         for (int k = 0; k < 16; k++) { f[3 * k] = w[k] * dRGB[0]; f[3 * k + 1] = w[k] * dRGB[1]; f[3 * k + 2] = w[k] * dRGB[2]; }
-        store_sh_grads(a.dL_dsh + (size_t)M3f * idx, f, 3 * ncoef, M3f, acc_sh);
+        store_sh_grads(a.dL_dsh + (size_t)M3f * idx, f, 3 * ncoef, M3f, acc_sh || sh_written);
+        sh_written = true;
 
         const float ddx = gx[0] * dRGB[0] + gx[1] * dRGB[1] + gx[2] * dRGB[2];
         const float ddy = gy[0] * dRGB[0] + gy[1] * dRGB[1] + gy[2] * dRGB[2];
@@ -300,14 +328,21 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(Pr
         dmy += (-ox * oy * ddx + (s2 - oy * oy) * ddy - oz * oy * ddz) * inv;
         dmz += (-ox * oz * ddx - oy * oz * ddy + (s2 - oz * oz) * ddz) * inv;
     }
+    s_dm[0] += dmx; s_dm[1] += dmy; s_dm[2] += dmz;
+#pragma unroll
+    for (int k = 0; k < 6; k++) s_dcov[k] += dcov[k];
+    }   // views
+
+    put(a.dL_dopacity + idx, s_dop, acc_o);
     {
         const bool add = acc_m || a.sh_done;       // sh_bwd_m16_kernel has already written its share
-        put(a.dL_dmean3D + 3 * idx, dmx, add); put(a.dL_dmean3D + 3 * idx + 1, dmy, add); put(a.dL_dmean3D + 3 * idx + 2, dmz, add);
+        put(a.dL_dmean3D + 3 * idx, s_dm[0], add); put(a.dL_dmean3D + 3 * idx + 1, s_dm[1], add); put(a.dL_dmean3D + 3 * idx + 2, s_dm[2], add);
     }
 
     // ---- cov3D -> scale / rotation (backward.cu:278-341; no quaternion-normalisation Jacobian)
     if (a.dL_dscale) {
         // dL/dSigma symmetric with halved off-diagonals; dL/dM = 2 M dL/dSigma
+        const float* dcov = s_dcov;
         M3 dSig = m3_cols(dcov[0], 0.5f * dcov[1], 0.5f * dcov[2], 0.5f * dcov[1], dcov[3], 0.5f * dcov[4],
                           0.5f * dcov[2], 0.5f * dcov[4], dcov[5]);
         M3 M2;
@@ -480,11 +515,121 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D
     }
 }
 
-int launch_preprocess_backward(const GsrBwdArgs& a, const GeomView& g, const float* accum, cudaStream_t s)
+// ------------------------------------------------------------------ SH backward over the V views of a batched call
+// Same staging as sh_bwd_m16_kernel, but a row is read once and written once for ALL views: per chunk of 4 coefficients
+// the lane loops over the views it is visible in, adds basis_k(dir_v) * dL/dRGB_v into the chunk's output and applies
+// the direction gradient of that chunk to dL/dmean3D straight away (dnormvdv is linear in it), so no per-view state
+// survives the inner loop.  Replaces V read-modify-write passes over the 192-byte gradient rows.
+template <int J>
+__device__ __forceinline__ void sh_chunk_views(float4* row, int P, int V, int D, int gid, float px, float py, float pz,
+                                               const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
+                                               const float* __restrict__ accum, const float* __restrict__ campos, float* dm)
 {
+    const float4 s0 = row[3 * J], s1 = row[3 * J + 1], s2 = row[3 * J + 2];
+    const float f[12] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w, s2.x, s2.y, s2.z, s2.w};
+    float g[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) g[k] = 0.f;
+    for (int v = 0; v < V; v++) {
+        const size_t vi = (size_t)v * P + gid;
+        if (!(radii[vi] > 0)) continue;
+        const float4 A0 = *reinterpret_cast<const float4*>(accum + (size_t)12 * vi);
+        const uint32_t cl = clamped[vi];
+        const float dR = (cl & 1) ? 0.f : A0.x, dG = (cl & 2) ? 0.f : A0.y, dB = (cl & 4) ? 0.f : A0.z;
+        const float ox = px - campos[3 * v], oy = py - campos[3 * v + 1], oz = pz - campos[3 * v + 2];
+        const float sq = ox * ox + oy * oy + oz * oz;
+        const float rl = rsqrtf(sq);
+        float w[4], bx[4], by[4], bz[4];
+        sh_chunk<J>(D, ox * rl, oy * rl, oz * rl, w, bx, by, bz);
+        float ddx = 0.f, ddy = 0.f, ddz = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const float sd = f[3 * k] * dR + f[3 * k + 1] * dG + f[3 * k + 2] * dB;
+            ddx += bx[k] * sd; ddy += by[k] * sd; ddz += bz[k] * sd;
+            g[3 * k] += w[k] * dR; g[3 * k + 1] += w[k] * dG; g[3 * k + 2] += w[k] * dB;
+        }
+        const float inv = rl * rl * rl;
+        dm[0] += ((sq - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * inv;
+        dm[1] += (-ox * oy * ddx + (sq - oy * oy) * ddy - oz * oy * ddz) * inv;
+        dm[2] += (-ox * oz * ddx - oy * oz * ddy + (sq - oz * oz) * ddz) * inv;
+    }
+    row[3 * J] = make_float4(g[0], g[1], g[2], g[3]);
+    row[3 * J + 1] = make_float4(g[4], g[5], g[6], g[7]);
+    row[3 * J + 2] = make_float4(g[8], g[9], g[10], g[11]);
+}
+
+__global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P, int V, int D, const float* __restrict__ means,
+                                                                          const int* __restrict__ radii, const float* __restrict__ shs,
+                                                                          const uint8_t* __restrict__ clamped,
+                                                                          const float* __restrict__ accum,
+                                                                          const float* __restrict__ campos, float* __restrict__ dL_dsh,
+                                                                          float* __restrict__ dL_dmean3D, unsigned acc)
+{
+    __shared__ float4 rows[SHB_WARPS][32 * SHB_ROW4];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int g0 = (blockIdx.x * SHB_WARPS + w) * 32;
+    if (g0 >= P) return;
+    const int nrow = min(32, P - g0);
+    const bool acc_sh = acc & GSR_ACC_SH, acc_m = acc & GSR_ACC_MEAN3D;
+    float4* my = rows[w];
+    const int gid = g0 + lane;
+    bool visible = false;
+    if (lane < nrow)
+        for (int v = 0; v < V; v++) visible = visible || radii[(size_t)v * P + gid] > 0;
+    const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
+    const float4* src = reinterpret_cast<const float4*>(shs) + (size_t)g0 * 12;
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+        const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
+        if ((vis_mask >> r) & 1u) my[r * SHB_ROW4 + c] = __ldg(src + e);
+    }
+    __syncwarp();
+    if (visible) {
+        const float px = means[3 * (size_t)gid], py = means[3 * (size_t)gid + 1], pz = means[3 * (size_t)gid + 2];
+        float dm[3] = {0.f, 0.f, 0.f};
+        float4* row = my + lane * SHB_ROW4;
+        sh_chunk_views<0>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+        sh_chunk_views<1>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+        sh_chunk_views<2>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+        sh_chunk_views<3>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+        put(dL_dmean3D + 3 * (size_t)gid, dm[0], acc_m);
+        put(dL_dmean3D + 3 * (size_t)gid + 1, dm[1], acc_m);
+        put(dL_dmean3D + 3 * (size_t)gid + 2, dm[2], acc_m);
+    } else if (lane < nrow && !acc_m) {
+        dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f;
+    }
+    __syncwarp();
+    float4* dst = reinterpret_cast<float4*>(dL_dsh) + (size_t)g0 * 12;
+    if (acc_sh) {
+        float4 o[12];
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane, r = e / 12;
+            o[i] = (r < nrow && ((vis_mask >> r) & 1u)) ? dst[e] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
+            if (r < nrow && ((vis_mask >> r) & 1u)) {
+                const float4 v = my[r * SHB_ROW4 + c];
+                dst[e] = make_float4(o[i].x + v.x, o[i].y + v.y, o[i].z + v.z, o[i].w + v.w);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
+            if (r < nrow) dst[e] = ((vis_mask >> r) & 1u) ? my[r * SHB_ROW4 + c] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+}
+
+int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, const float* accum, cudaStream_t s)
+{
+    // a: the batched call's arguments (per-view arrays [V][...], cameras [V][16] / [V][3]); V <= GSR_MAX_VIEWS
     const CameraArgs cam = make_camera_args(a.viewmatrix, a.projmatrix, a.cam_pos, a.tan_fovx, a.tan_fovy, a.W, a.H);
     PreBwdArgs k;
-    k.P = a.P; k.D = a.D; k.M = a.M;
+    k.P = a.P; k.D = a.D; k.M = a.M; k.V = V;
     k.means = a.means3D; k.radii = a.radii; k.shs = a.shs; k.clamped = g.clamped;
     k.scales = a.scales; k.rots = a.rotations; k.cov_pre = a.cov3D_precomp; k.mod = a.scale_modifier;
     k.accum = accum; k.rec = g.rec;
@@ -495,12 +640,22 @@ int launch_preprocess_backward(const GsrBwdArgs& a, const GeomView& g, const flo
     k.acc = a.accumulate;
     k.sh_done = 0;
     if (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && env_int("GSR_SH_SPLIT", 1)) {
-        GSR_LAUNCH(sh_bwd_m16_kernel, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs, g.clamped, accum, a.cam_pos,
-                   a.dL_dsh, a.dL_dmean3D, a.accumulate);
+        if (V == 1)
+            GSR_LAUNCH(sh_bwd_m16_kernel, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs, g.clamped,
+                       accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate);
+        else
+            GSR_LAUNCH(sh_bwd_m16_views_kernel, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii, a.shs,
+                       g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate);
         k.sh_done = 1;
     }
-    if (k.sh_done || !a.shs) GSR_LAUNCH(preprocess_bwd_kernel<false>, cdiv(a.P, 256), 256, 0, s, k, cam);
-    else GSR_LAUNCH(preprocess_bwd_kernel<true>, cdiv(a.P, 256), 256, 0, s, k, cam);
+    const bool with_sh = !(k.sh_done || !a.shs);
+    if (V == 1) {
+        if (!with_sh) GSR_LAUNCH((preprocess_bwd_kernel<false, false>), cdiv(a.P, 256), 256, 0, s, k, cam);
+        else GSR_LAUNCH((preprocess_bwd_kernel<true, false>), cdiv(a.P, 256), 256, 0, s, k, cam);
+    } else {
+        if (!with_sh) GSR_LAUNCH((preprocess_bwd_kernel<false, true>), cdiv(a.P, 256), 256, 0, s, k, cam);
+        else GSR_LAUNCH((preprocess_bwd_kernel<true, true>), cdiv(a.P, 256), 256, 0, s, k, cam);
+    }
     return GSR_OK;
 }
 
