@@ -233,7 +233,7 @@ def main():
         # view 0 of the step overwrites the flat gradient buffer, the following views add to it (in the kernels)
         return dgr.set_grad_mode(("overwrite" if i == 0 else "accumulate") if fused else None)
 
-    if args.batched:
+    if True:
         from diff_gaussian_rasterization.batched import BatchedRasterizationSettings, GaussianRasterizerBatched
         vm_all = torch.stack([c.viewmatrix for c in cams]); pm_all = torch.stack([c.projmatrix for c in cams])
         cp_all = torch.stack([c.campos for c in cams])
@@ -390,6 +390,21 @@ def main():
                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps,
                "note": "per view: 24.9 MB target image + camera from pinned host memory on a copy stream one view ahead; loss read once per step"}
 
+    # ---- the same step through the batched entry point (one call per rank and step), reported next to the drop-in API's
+    batched_extra = None
+    if not args.batched:
+        for i in range(args.warmup):
+            step_device_batched(i)
+        ms_b = timed(step_device_batched, args.steps, args.warmup)
+        batched_extra = {"api": "GaussianRasterizerBatched (gsr_forward_batched): one call per rank and step",
+                         "value": views_total / (ms_b * 1e-3), "unit": UNIT, "ms_per_view": ms_b / args.steps / vps}
+        if not args.no_e2e:
+            for i in range(min(2, args.warmup)):
+                step_e2e_batched(i)
+            ms_be = timed(step_e2e_batched, args.steps, args.warmup)
+            batched_extra["e2e"] = {"value": views_total / (ms_be * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
+                                    "d2h_bytes_per_step": 4}
+
     if rank == 0:
         peaks = {}
         try:
@@ -442,7 +457,8 @@ def main():
                            "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else "GaussianRasterizer: one call per view",
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat.nbytes() + 48 * P + 20 * R) / 1e9)},
-                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches,
+                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "batched": batched_extra,
+                "gpu_launches": launches,
                 "clocks": clocks}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -108,9 +108,10 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
             if (alpha < 1.0f / 255.0f) continue;
             const float test_T = T * (1 - alpha);
             if (test_T < 0.0001f) { done = true; continue; }
-            C0 += c.z * alpha * T;
-            C1 += c.w * alpha * T;
-            C2 += st.b[j] * alpha * T;
+            const float at = alpha * T;     // colour weight; (c * alpha) * T in the reference, same value to 1 ulp
+            C0 = fmaf(c.z, at, C0);
+            C1 = fmaf(c.w, at, C1);
+            C2 = fmaf(st.b[j], at, C2);
             T = test_T;
             last_contributor = contributor;
         }
@@ -200,9 +201,10 @@ __device__ __forceinline__ void blend_step(float alpha, bool ok, float r, float 
     const bool stop = v && (test_T < 0.0001f);
     done = done || stop;
     if (v && !stop) {
-        C0 += r * alpha * T;
-        C1 += g * alpha * T;
-        C2 += b * alpha * T;
+        const float at = alpha * T;         // colour weight; (c * alpha) * T in the reference, same value to 1 ulp
+        C0 = fmaf(r, at, C0);
+        C1 = fmaf(g, at, C1);
+        C2 = fmaf(b, at, C2);
         T = test_T;
         last = pos;
     }
