@@ -148,9 +148,9 @@ __global__ void __launch_bounds__(RS_THREADS) radix_onesweep_kernel(const uint32
         uint32_t peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
         for (int b = 0; b < BITS; b++) {
-            const bool bit = (d >> b) & 1u;
+            const uint32_t bit = (d >> b) & 1u;
             const uint32_t bal = __ballot_sync(0xffffffffu, bit);
-            peers &= bal ^ (bit ? 0u : 0xFFFFFFFFu);
+            peers &= ~(bal ^ (0u - bit));          // bit set: keep the lanes that voted 1, else those that voted 0 (one LOP3)
         }
         const uint32_t old = wcount[w][d];
         __syncwarp();
