@@ -179,6 +179,19 @@ int gsr_l1_loss(const float* image, const float* target, size_t n, float grad_sc
                 float* grad, gsr_stream_t stream);
 
 /*
+ * Fused L1 + D-SSIM image loss (value and gradient from one call): replaces train.py:104-105
+ *   loss = (1 - lambda) * l1_loss(image, gt) + lambda * (1 - ssim(image, gt))
+ * with ssim() of utils/loss_utils.py:27-63 (11x11 Gaussian window, sigma 1.5, zero padding 5, depthwise, mean of the map)
+ * and the autograd backward of both.  image, target, grad: [C, H, W] float device arrays.
+ *   sums[0] = sum |image - target|,  sums[1] = sum ssim_map        (device, zeroed by the call)
+ *   grad    = k_l1 * sign(image - target) + k_ssim * d(sum ssim_map)/d image     (grad may be NULL: value only)
+ *   maps    = scratch of 3*C*H*W floats (the three partial-derivative maps), required when grad != NULL
+ * For the loss above: n = C*H*W, k_l1 = (1 - lambda)/n, k_ssim = -lambda/n, loss = (1-lambda) sums[0]/n + lambda (1 - sums[1]/n).
+ */
+int gsr_l1_ssim_loss(const float* image, const float* target, int C, int H, int W, float k_l1, float k_ssim,
+                     float* sums, float* maps, float* grad, gsr_stream_t stream);
+
+/*
  * Test hook for the bit-exact integer contract: reconstructs, from our private
  * blobs, the arrays the reference keeps in BinningState / ImageState:
  *   keys[R]   = (tile << 32) | float_bits(depth)   sorted

@@ -352,8 +352,31 @@ std::tuple<torch::Tensor, torch::Tensor> l1_loss(const torch::Tensor& image, con
     return std::make_tuple(sum, grad);
 }
 
+// fused L1 + D-SSIM: returns (sums[2] = {sum |x-y|, sum ssim_map}, dL/dimage) for
+// loss = (1 - lambda) mean|x-y| + lambda (1 - mean ssim_map); with_grad = false returns an empty gradient
+std::tuple<torch::Tensor, torch::Tensor> l1_ssim_loss(const torch::Tensor& image, const torch::Tensor& target, double lambda,
+                                                     bool with_grad)
+{
+    TORCH_CHECK(image.is_cuda() && target.is_cuda(), "l1_ssim_loss: CUDA tensors expected");
+    TORCH_CHECK(image.dim() == 3 && image.sizes() == target.sizes(), "l1_ssim_loss: two [C,H,W] images expected");
+    const c10::cuda::CUDAGuard guard(image.device());
+    F32 a(image), b(target);
+    const int C = (int)image.size(0), H = (int)image.size(1), W = (int)image.size(2);
+    const double n = (double)image.numel();
+    auto f32 = image.options().dtype(torch::kFloat32);
+    torch::Tensor sums = torch::empty({2}, f32);
+    torch::Tensor grad = with_grad ? torch::empty(image.sizes(), f32) : torch::empty({0}, f32);
+    torch::Tensor maps = with_grad ? torch::empty({3, C, H, W}, f32) : torch::empty({0}, f32);
+    check(gsr_l1_ssim_loss(a.ptr(), b.ptr(), C, H, W, n > 0 ? (float)((1.0 - lambda) / n) : 0.f, n > 0 ? (float)(-lambda / n) : 0.f,
+                           sums.data_ptr<float>(), with_grad ? maps.data_ptr<float>() : nullptr,
+                           with_grad ? grad.data_ptr<float>() : nullptr, current_stream()),
+          "l1_ssim_loss");
+    return std::make_tuple(sums, grad);
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
 {
+    m.def("l1_ssim_loss", &l1_ssim_loss);
     m.def("l1_loss", &l1_loss);
     m.def("rasterize_gaussians_batched", &rasterize_gaussians_batched);
     m.def("rasterize_gaussians_batched_backward", &rasterize_gaussians_batched_backward);

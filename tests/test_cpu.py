@@ -97,6 +97,20 @@ def test_sub_oracles_from_reference_python():
     assert np.abs(st.cov3d[vis] - g["cov6"][vis]).max() <= 1e-6 * max(1.0, np.abs(g["cov6"]).max())
 
 
+def test_loss_oracle_matches_reference_golden():
+    """oracle/loss_oracle.py (numpy) against the reference's own l1_loss / ssim + torch autograd
+    (utils/loss_utils.py:17-63, train.py:104-105), vectors from tests/golden/make_loss_golden.py"""
+    from oracle import loss_oracle
+    g = np.load(os.path.join(GOLDEN, "loss_l1_ssim.npz"))
+    lam = float(g["lambda_dssim"])
+    for k in "abc":
+        o = loss_oracle.l1_ssim(g[k + "_image"], g[k + "_target"], lam)
+        assert abs(o["l1"] - g[k + "_l1"]) <= 1e-6
+        assert abs(o["ssim"] - g[k + "_ssim"]) <= 1e-6
+        assert abs(o["loss"] - g[k + "_loss"]) <= 1e-6
+        assert np.abs(o["grad"] - g[k + "_grad"]).max() <= 5e-6 * np.abs(g[k + "_grad"]).max()
+
+
 # ------------------------------------------------------------------------------ the C-ABI library
 def test_cabi_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "gsr.h")).read()
