@@ -192,6 +192,37 @@ int gsr_l1_ssim_loss(const float* image, const float* target, int C, int H, int 
                      float* sums, float* maps, float* grad, gsr_stream_t stream);
 
 /*
+ * Fused Adam step over all parameter groups in one launch: replaces gaussians.optimizer.step() of train.py:138-140,
+ * i.e. torch.optim.Adam(l, lr=0.0, eps=1e-15) over the groups built at scene/gaussian_model.py:164-175
+ * (no weight decay, no amsgrad).  Same fp32 arithmetic as torch's foreach implementation:
+ *   m += (1-beta1)(g-m);  v = v*beta2 + (1-beta2) g*g;  p -= lr/(1-beta1^step) * m / (sqrt(v)/sqrt(1-beta2^step) + eps)
+ * `step` is the 1-based step count of that group AFTER this update (torch increments before use).
+ * `row` = elements per Gaussian in this group (3, 3, 45, 1, 3, 4 ...), used only with `visible`:
+ * visible == NULL is the reference's dense update; otherwise visible[P] (bytes, non-zero = update) restricts the
+ * update to flagged Gaussians (moments and parameters of the others are left untouched).
+ */
+typedef struct GsrAdamGroup {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    size_t n;                    /* number of floats */
+    int row;                     /* floats per Gaussian */
+    int step;                    /* >= 1 */
+    float lr;
+} GsrAdamGroup;
+int gsr_adam_step(const GsrAdamGroup* groups, int n_groups, double beta1, double beta2, double eps,
+                  const unsigned char* visible, gsr_stream_t stream);
+
+/*
+ * Densification statistics of one view (train.py:131-132, scene/gaussian_model.py:415-417) for the filter radii > 0:
+ *   max_radii2D[i] = max(max_radii2D[i], radii[i]);  xyz_gradient_accum[i] += |dL_dmean2D[i, :2]|;  denom[i] += 1
+ * dL_dmean2D is the [P,3] gradient of the rasterizer's means2D input (viewspace_point_tensor.grad).
+ */
+int gsr_densify_stats(int P, const int* radii, const float* dL_dmean2D, float* max_radii2D,
+                      float* xyz_gradient_accum, float* denom, gsr_stream_t stream);
+
+/*
  * Test hook for the bit-exact integer contract: reconstructs, from our private
  * blobs, the arrays the reference keeps in BinningState / ImageState:
  *   keys[R]   = (tile << 32) | float_bits(depth)   sorted

@@ -374,8 +374,70 @@ std::tuple<torch::Tensor, torch::Tensor> l1_ssim_loss(const torch::Tensor& image
     return std::make_tuple(sums, grad);
 }
 
+// fused Adam over several parameter groups (one launch); everything is updated in place
+void adam_step(std::vector<torch::Tensor> params, std::vector<torch::Tensor> grads, std::vector<torch::Tensor> exp_avgs,
+               std::vector<torch::Tensor> exp_avg_sqs, std::vector<int64_t> steps, std::vector<double> lrs, std::vector<int64_t> rows,
+               double beta1, double beta2, double eps, const torch::Tensor& visible)
+{
+    const size_t n = params.size();
+    TORCH_CHECK(grads.size() == n && exp_avgs.size() == n && exp_avg_sqs.size() == n && steps.size() == n && lrs.size() == n &&
+                rows.size() == n, "adam_step: list lengths differ");
+    if (n == 0) return;
+    const c10::cuda::CUDAGuard guard(params[0].device());
+    std::vector<torch::Tensor> keep;                       // contiguous copies of gradients, if any were needed
+    const unsigned char* vis = nullptr;
+    torch::Tensor visc;
+    if (visible.numel() > 0) {
+        TORCH_CHECK(visible.is_cuda() && (visible.scalar_type() == torch::kBool || visible.scalar_type() == torch::kUInt8),
+                    "adam_step: visible must be a CUDA bool / uint8 tensor");
+        visc = visible.contiguous();
+        vis = reinterpret_cast<const unsigned char*>(visc.data_ptr());
+    }
+    for (size_t base = 0; base < n; base += 8) {
+        GsrAdamGroup g[8];
+        const int cnt = (int)std::min<size_t>(8, n - base);
+        for (int i = 0; i < cnt; i++) {
+            const size_t k = base + i;
+            for (const torch::Tensor* t : {&params[k], &exp_avgs[k], &exp_avg_sqs[k]})
+                TORCH_CHECK(t->is_cuda() && t->scalar_type() == torch::kFloat32 && t->is_contiguous() && t->numel() == params[k].numel(),
+                            "adam_step: parameters and moments must be contiguous CUDA float32 tensors of one size");
+            TORCH_CHECK(grads[k].is_cuda() && grads[k].scalar_type() == torch::kFloat32 && grads[k].numel() == params[k].numel(),
+                        "adam_step: gradient must be a CUDA float32 tensor of the parameter's size");
+            torch::Tensor gc = grads[k].contiguous();
+            keep.push_back(gc);
+            if (vis) TORCH_CHECK(rows[k] >= 1 && params[k].numel() == visible.numel() * rows[k], "adam_step: visible does not match rows");
+            g[i].param = params[k].data_ptr<float>();
+            g[i].grad = gc.data_ptr<float>();
+            g[i].exp_avg = exp_avgs[k].data_ptr<float>();
+            g[i].exp_avg_sq = exp_avg_sqs[k].data_ptr<float>();
+            g[i].n = (size_t)params[k].numel();
+            g[i].row = (int)std::max<int64_t>(1, rows[k]);
+            g[i].step = (int)steps[k];
+            g[i].lr = (float)lrs[k];
+        }
+        check(gsr_adam_step(g, cnt, beta1, beta2, eps, vis, current_stream()), "adam_step");
+    }
+}
+
+void densify_stats(const torch::Tensor& radii, const torch::Tensor& dmean2D, torch::Tensor max_radii2D, torch::Tensor grad_accum,
+                   torch::Tensor denom)
+{
+    const int64_t P = radii.numel();
+    TORCH_CHECK(radii.is_cuda() && radii.scalar_type() == torch::kInt32 && radii.is_contiguous(), "densify_stats: radii must be CUDA int32");
+    TORCH_CHECK(dmean2D.is_cuda() && dmean2D.scalar_type() == torch::kFloat32 && dmean2D.is_contiguous() && dmean2D.numel() == 3 * P,
+                "densify_stats: dL/dmeans2D must be a contiguous CUDA float32 [P,3] tensor");
+    for (const torch::Tensor* t : {&max_radii2D, &grad_accum, &denom})
+        TORCH_CHECK(t->is_cuda() && t->scalar_type() == torch::kFloat32 && t->is_contiguous() && t->numel() == P,
+                    "densify_stats: statistics must be contiguous CUDA float32 tensors of P elements");
+    const c10::cuda::CUDAGuard guard(radii.device());
+    check(gsr_densify_stats((int)P, radii.data_ptr<int>(), dmean2D.data_ptr<float>(), max_radii2D.data_ptr<float>(),
+                            grad_accum.data_ptr<float>(), denom.data_ptr<float>(), current_stream()), "densify_stats");
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
 {
+    m.def("adam_step", &adam_step);
+    m.def("densify_stats", &densify_stats);
     m.def("l1_ssim_loss", &l1_ssim_loss);
     m.def("l1_loss", &l1_loss);
     m.def("rasterize_gaussians_batched", &rasterize_gaussians_batched);

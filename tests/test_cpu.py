@@ -111,6 +111,33 @@ def test_loss_oracle_matches_reference_golden():
         assert np.abs(o["grad"] - g[k + "_grad"]).max() <= 5e-6 * np.abs(g[k + "_grad"]).max()
 
 
+def test_optim_oracle_matches_torch_adam_golden():
+    """oracle/optim_oracle.py against torch.optim.Adam configured like scene/gaussian_model.py:164-175
+    (vectors from tests/golden/make_optim_golden.py); densify_stats against the torch expressions of train.py:131-132"""
+    from oracle import optim_oracle
+    g = np.load(os.path.join(GOLDEN, "optim_adam.npz"))
+    for n, lr in zip(g["names"], g["lrs"]):
+        p = g["p0_" + n].copy(); m = np.zeros_like(p); v = np.zeros_like(p)
+        for t in range(int(g["steps"])):
+            optim_oracle.adam_step(p, g["g%d_%s" % (t, n)], m, v, t + 1, float(lr))
+        assert np.abs(p - g["p_" + n]).max() <= 1e-7
+        assert np.abs(m - g["m_" + n]).max() <= 1e-6 * np.abs(m).max()
+        assert np.abs(v - g["v_" + n]).max() <= 1e-6 * np.abs(v).max()
+    rng = np.random.default_rng(0)
+    P = 200
+    radii = rng.integers(-1, 30, P).astype(np.int32); radii[radii < 5] = 0
+    dm = rng.standard_normal((P, 3)).astype(np.float32)
+    mr = rng.uniform(0, 20, P).astype(np.float32); acc = rng.uniform(0, 1, P).astype(np.float32); den = np.ones(P, np.float32)
+    tr, tm, ta, td = (torch.from_numpy(x.copy()) for x in (radii, mr, acc.reshape(P, 1), den.reshape(P, 1)))
+    vis = tr > 0
+    tm[vis] = torch.max(tm[vis], tr[vis].float())
+    ta[vis] += torch.norm(torch.from_numpy(dm)[vis, :2], dim=-1, keepdim=True)
+    td[vis] += 1
+    optim_oracle.densify_stats(radii, dm, mr, acc, den)
+    assert np.array_equal(mr, tm.numpy()) and np.array_equal(den, td.numpy().ravel())
+    assert np.abs(acc - ta.numpy().ravel()).max() <= 1e-6
+
+
 # ------------------------------------------------------------------------------ the C-ABI library
 def test_cabi_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "gsr.h")).read()
