@@ -223,6 +223,16 @@ int gsr_densify_stats(int P, const int* radii, const float* dL_dmean2D, float* m
                       float* xyz_gradient_accum, float* denom, gsr_stream_t stream);
 
 /*
+ * Column gather between the PLY record layout and the parameter tensors (scene/gaussian_model.py:201-266 save_ply / load_ply):
+ *   out[r * out_cols + j] = col_of_out[j] >= 0 ? in[r * in_cols + col_of_out[j]] : 0      for r < rows, j < out_cols <= 64
+ * in / out are device arrays; col_of_out is a HOST array of out_cols entries.  Loading: in = the file's vertex payload
+ * (62 floats per Gaussian at SH-3), one call per parameter tensor; saving: in = the parameters concatenated per Gaussian,
+ * out = the 62-column records (negative entries produce the zero normals); see gsr_b200/ply.py.
+ */
+int gsr_gather_columns(const float* in, int in_cols, float* out, int out_cols, const int* col_of_out, long long rows,
+                       gsr_stream_t stream);
+
+/*
  * Test hook for the bit-exact integer contract: reconstructs, from our private
  * blobs, the arrays the reference keeps in BinningState / ImageState:
  *   keys[R]   = (tile << 32) | float_bits(depth)   sorted

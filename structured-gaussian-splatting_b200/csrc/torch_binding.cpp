@@ -434,8 +434,22 @@ void densify_stats(const torch::Tensor& radii, const torch::Tensor& dmean2D, tor
                             grad_accum.data_ptr<float>(), denom.data_ptr<float>(), current_stream()), "densify_stats");
 }
 
+// out[r, j] = in[r, cols[j]] (cols[j] < 0: 0) for a [rows, in_cols] CUDA float tensor; returns [rows, len(cols)]
+torch::Tensor gather_columns(const torch::Tensor& in, std::vector<int> cols)
+{
+    TORCH_CHECK(in.is_cuda() && in.scalar_type() == torch::kFloat32 && in.dim() == 2 && in.is_contiguous(),
+                "gather_columns: contiguous CUDA float32 [rows, cols] tensor expected");
+    TORCH_CHECK(cols.size() <= 64, "gather_columns: at most 64 output columns");
+    const c10::cuda::CUDAGuard guard(in.device());
+    torch::Tensor out = torch::empty({in.size(0), (int64_t)cols.size()}, in.options());
+    check(gsr_gather_columns(in.data_ptr<float>(), (int)in.size(1), out.data_ptr<float>(), (int)cols.size(), cols.data(),
+                             (long long)in.size(0), current_stream()), "gather_columns");
+    return out;
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
 {
+    m.def("gather_columns", &gather_columns);
     m.def("adam_step", &adam_step);
     m.def("densify_stats", &densify_stats);
     m.def("l1_ssim_loss", &l1_ssim_loss);

@@ -138,6 +138,60 @@ def test_optim_oracle_matches_torch_adam_golden():
     assert np.abs(acc - ta.numpy().ravel()).max() <= 1e-6
 
 
+def _ply_model(P, deg, seed):
+    rng = np.random.default_rng(seed)
+    K = (deg + 1) ** 2 - 1
+    f = lambda *s: rng.standard_normal(s).astype(np.float32)
+    return dict(xyz=f(P, 3), features_dc=f(P, 1, 3), features_rest=f(P, K, 3), opacity=f(P, 1), scaling=f(P, 3), rotation=f(P, 4))
+
+
+def test_ply_header_and_column_maps_match_oracle(tmp_path):
+    """host side of gsr_b200.ply (header, column maps) against oracle/ply_oracle.py (scene/gaussian_model.py:187-266);
+    the device gather out[r, j] = in[r, col[j]] is emulated with numpy indexing here and run for real in the gpu tests"""
+    from gsr_b200 import ply
+    from oracle import ply_oracle
+    for deg, P in ((3, 41), (0, 5), (1, 0)):
+        m = _ply_model(P, deg, 7 + deg)
+        path = str(tmp_path / ("m%d.ply" % deg))
+        ply_oracle.save_ply(path, **m)
+        raw = open(path, "rb").read()
+        n, props, off, fmt = ply.parse_header(raw[:1 << 16])
+        K = (deg + 1) ** 2 - 1
+        assert (n, fmt, len(props)) == (P, "binary_little_endian", 17 + 3 * K) and all(t == "f4" for _, t in props)
+        assert raw[:off] == ply.format_header(P, ply.attribute_names(3 * K)) and len(raw) == off + 4 * P * len(props)
+        payload, names = ply.read_payload(path)
+        maps = ply.column_maps(names, deg)
+        ref = ply_oracle.load_ply(path, deg)
+        for k, cols in maps.items():
+            assert np.array_equal(payload[:, cols].reshape(ref[k].shape), ref[k]) and np.array_equal(ref[k], m[k])
+    with pytest.raises(ValueError):
+        ply.column_maps(ply.attribute_names(45), 2)                 # the reference's assert on the f_rest count
+    with pytest.raises(ValueError):
+        ply.parse_header(b"plx\nend_header\n")
+    # another exporter: reordered columns, a double and a uchar property, comments
+    P = 9
+    m = _ply_model(P, 1, 3)
+    names = ply.attribute_names(9)
+    order = list(reversed(names)) + ["extra"]
+    dt = np.dtype([(k, "<f8" if k == "opacity" else ("u1" if k == "extra" else "<f4")) for k in order])
+    el = np.zeros(P, dt)
+    flat = np.concatenate((m["xyz"], np.zeros((P, 3), np.float32), m["features_dc"].transpose(0, 2, 1).reshape(P, -1),
+                           m["features_rest"].transpose(0, 2, 1).reshape(P, -1), m["opacity"], m["scaling"], m["rotation"]), axis=1)
+    for i, k in enumerate(names):
+        el[k] = flat[:, i]
+    path = str(tmp_path / "other.ply")
+    with open(path, "wb") as f:
+        f.write(b"ply\nformat binary_little_endian 1.0\ncomment made elsewhere\nelement vertex %d\n" % P)
+        for k in order:
+            f.write(("property %s %s\n" % ("double" if k == "opacity" else ("uchar" if k == "extra" else "float"), k)).encode())
+        f.write(b"element face 0\nproperty list uchar int vertex_indices\nend_header\n")
+        f.write(el.tobytes())
+    payload, pn = ply.read_payload(path)
+    maps = ply.column_maps(pn, 1)
+    for k, cols in maps.items():
+        assert np.array_equal(payload[:, cols].reshape(m[k].shape), m[k])
+
+
 # ------------------------------------------------------------------------------ the C-ABI library
 def test_cabi_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "gsr.h")).read()
