@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 1
+#define GSR_ABI_VERSION 2
 
 /* error codes */
 #define GSR_OK          0
@@ -78,6 +78,10 @@ typedef struct GsrFwdArgs {
     int          debug;          /* 1: synchronise + check after every stage (CHECK_CUDA semantics, auxiliary.h:166-173) */
     float*       out_color;      /* [3,H,W] written for every pixel */
     int*         radii;          /* [P] written for every Gaussian (0 = culled) */
+    /* Split SH storage (ABI 2): when non-NULL, `shs` holds only the DC coefficient [P,1,3] and `shs_rest` the others
+       [P,M-1,3] - the reference model's two parameters _features_dc / _features_rest (scene/gaussian_model.py:151-152)
+       without the torch.cat of get_features (:119-122).  M stays the total count; M must be 16 (or 1: shs_rest ignored). */
+    const float* shs_rest;
 } GsrFwdArgs;
 
 /*
@@ -139,6 +143,9 @@ typedef struct GsrBwdArgs {
        holds, rows of culled Gaussians are left untouched (multi-view steps sum parameter gradients in place
        instead of through one extra elementwise add per output and view).  0 = overwrite everything (reference). */
     unsigned accumulate;
+    /* split SH storage as in GsrFwdArgs (ABI 2): dL_dsh is then [P,1,3] and dL_dsh_rest [P,M-1,3] */
+    const float* shs_rest;
+    float*       dL_dsh_rest;
 } GsrBwdArgs;
 
 #define GSR_ACC_MEAN3D   1u

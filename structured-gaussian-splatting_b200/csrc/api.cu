@@ -178,6 +178,7 @@ static int forward_impl(const GsrFwdArgs* a, int V, GsrAlloc geom, GsrAlloc binn
     if (!a->means3D || !a->opacities || !a->radii) return GSR_EINVAL;
     if (!a->shs && !a->colors_precomp) return GSR_ECHANNELS;
     if (a->shs && !a->colors_precomp && (!a->cam_pos || a->M < (a->D + 1) * (a->D + 1))) return GSR_EINVAL;
+    if (a->shs && a->shs_rest && a->M != 16 && a->M != 1) return GSR_EINVAL;       // split SH storage: M = 16 (or DC only)
     if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return GSR_ECOV;
 
     void* gblob = geom.fn(geom.ctx, gsr_geom_bytes(Pv));
@@ -262,6 +263,7 @@ static int backward_impl(const GsrBwdArgs* a, int V, gsr_stream_t stream_)
     if (!a->geom_blob || !a->binning_blob || !a->img_blob || !a->accum) return GSR_EBLOB;
     if (!a->dL_dmean2D || !a->dL_dopacity || !a->dL_dmean3D) return GSR_EINVAL;
     if (a->shs && (!a->dL_dsh || !a->cam_pos)) return GSR_EINVAL;
+    if (a->shs && a->shs_rest && a->M > 1 && (a->M != 16 || !a->dL_dsh_rest)) return GSR_EINVAL;
     if (!a->cov3D_precomp && (!a->scales || !a->rotations || !a->dL_dscale || !a->dL_drot)) return GSR_ECOV;
 
     const int Pv = a->P * V;

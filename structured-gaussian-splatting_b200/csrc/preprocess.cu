@@ -118,10 +118,20 @@ __device__ __forceinline__ void load_sh(const float* __restrict__ p, bool vec, f
     }
 }
 
+// split storage: DC coefficient at dc, coefficients 1.. at rest (45 floats per Gaussian, 4-byte aligned rows)
+template <int NREST>
+__device__ __forceinline__ void load_sh_split(const float* __restrict__ dc, const float* __restrict__ rest, float* f)
+{
+    f[0] = __ldg(dc); f[1] = __ldg(dc + 1); f[2] = __ldg(dc + 2);
+#pragma unroll
+    for (int i = 0; i < NREST; i++) f[3 + i] = __ldg(rest + i);
+}
+
 struct PreArgs {
     int P, D, M;
     const float* means;
     const float* shs;
+    const float* shs_rest;
     const float* colors_pre;
     const float* opac;
     const float* scales;
@@ -200,14 +210,25 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
                     float dx = p.x - cam.cam[0], dy = p.y - cam.cam[1], dz = p.z - cam.cam[2];
                     const float len = sqrtf(dx * dx + dy * dy + dz * dz);
                     dx = dx / len; dy = dy / len; dz = dz / len;
-                    const float* shp = a.shs + (size_t)3 * a.M * idx;
-                    const bool vec = (((size_t)shp) & 15) == 0;
                     float f[48];
-                    switch (a.D) {
-                    case 0: load_sh<3>(shp, false, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
-                    case 1: load_sh<12>(shp, vec, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
-                    case 2: load_sh<27>(shp, vec, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
-                    default: load_sh<48>(shp, vec, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
+                    if (a.shs_rest != nullptr) {
+                        const float* dc = a.shs + (size_t)3 * idx;
+                        const float* rest = a.shs_rest + (size_t)3 * (a.M - 1) * idx;
+                        switch (a.D) {
+                        case 0: load_sh_split<0>(dc, rest, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        case 1: load_sh_split<9>(dc, rest, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        case 2: load_sh_split<24>(dc, rest, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        default: load_sh_split<45>(dc, rest, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        }
+                    } else {
+                        const float* shp = a.shs + (size_t)3 * a.M * idx;
+                        const bool vec = (((size_t)shp) & 15) == 0;
+                        switch (a.D) {
+                        case 0: load_sh<3>(shp, false, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        case 1: load_sh<12>(shp, vec, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        case 2: load_sh<27>(shp, vec, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        default: load_sh<48>(shp, vec, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        }
                     }
                 }
                 out.q0 = make_float4(px, py, conic.x, conic.y);
@@ -238,7 +259,7 @@ int launch_preprocess(const GsrFwdArgs& a, int V, const GeomView& g, cudaStream_
     const CameraArgs cam = make_camera_args(a.viewmatrix, a.projmatrix, a.cam_pos, a.tan_fovx, a.tan_fovy, a.W, a.H);
     PreArgs k;
     k.P = a.P; k.D = a.D; k.M = a.M;
-    k.means = a.means3D; k.shs = a.shs; k.colors_pre = a.colors_precomp; k.opac = a.opacities;
+    k.means = a.means3D; k.shs = a.shs; k.shs_rest = (a.shs && a.M > 1) ? a.shs_rest : nullptr; k.colors_pre = a.colors_precomp; k.opac = a.opacities;
     k.scales = a.scales; k.rots = a.rotations; k.cov_pre = a.cov3D_precomp; k.mod = a.scale_modifier;
     k.prefiltered = a.prefiltered; k.radii = a.radii; k.rec = g.rec; k.clamped = g.clamped;
     const GeomScratch sc = carve_geom_scratch(g.scratch, a.P * V);

@@ -421,14 +421,48 @@ __device__ __forceinline__ void sh_chunk(int D, float x, float y, float z, float
     }
 }
 
-template <int J>
-__device__ __forceinline__ void sh_chunk_apply(float4* row, int D, float x, float y, float z, float dR, float dG, float dB, float& ddx,
+// a lane's SH row in shared memory: padded float4 rows (one [P,16,3] array) or the flat copies of the two split arrays
+struct RowPadded {
+    float4* row;
+    template <int J> __device__ __forceinline__ void load(float* f) const
+    {
+        const float4 s0 = row[3 * J], s1 = row[3 * J + 1], s2 = row[3 * J + 2];
+        f[0] = s0.x; f[1] = s0.y; f[2] = s0.z; f[3] = s0.w; f[4] = s1.x; f[5] = s1.y; f[6] = s1.z; f[7] = s1.w;
+        f[8] = s2.x; f[9] = s2.y; f[10] = s2.z; f[11] = s2.w;
+    }
+    template <int J> __device__ __forceinline__ void store(const float* g) const
+    {
+        row[3 * J] = make_float4(g[0], g[1], g[2], g[3]);
+        row[3 * J + 1] = make_float4(g[4], g[5], g[6], g[7]);
+        row[3 * J + 2] = make_float4(g[8], g[9], g[10], g[11]);
+    }
+};
+struct RowFlat {
+    float* dc;      // 3 floats of this lane (stride 3 between lanes)
+    float* rest;    // 45 floats of this lane (stride 45: odd, conflict-free scalar accesses)
+    template <int J> __device__ __forceinline__ void load(float* f) const
+    {
+#pragma unroll
+        for (int i = 0; i < 12; i++) f[i] = (12 * J + i < 3) ? dc[12 * J + i] : rest[12 * J + i - 3];
+    }
+    template <int J> __device__ __forceinline__ void store(const float* g) const
+    {
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            if (12 * J + i < 3) dc[12 * J + i] = g[i];
+            else rest[12 * J + i - 3] = g[i];
+        }
+    }
+};
+
+template <int J, class Row>
+__device__ __forceinline__ void sh_chunk_apply(const Row& row, int D, float x, float y, float z, float dR, float dG, float dB, float& ddx,
                                                float& ddy, float& ddz)
 {
     float w[4], bx[4], by[4], bz[4];
     sh_chunk<J>(D, x, y, z, w, bx, by, bz);
-    const float4 s0 = row[3 * J], s1 = row[3 * J + 1], s2 = row[3 * J + 2];
-    const float f[12] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w, s2.x, s2.y, s2.z, s2.w};
+    float f[12];
+    row.template load<J>(f);
     float g[12];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
@@ -436,16 +470,62 @@ __device__ __forceinline__ void sh_chunk_apply(float4* row, int D, float x, floa
         ddx += bx[k] * sd; ddy += by[k] * sd; ddz += bz[k] * sd;
         g[3 * k] = w[k] * dR; g[3 * k + 1] = w[k] * dG; g[3 * k + 2] = w[k] * dB;
     }
-    row[3 * J] = make_float4(g[0], g[1], g[2], g[3]);
-    row[3 * J + 1] = make_float4(g[4], g[5], g[6], g[7]);
-    row[3 * J + 2] = make_float4(g[8], g[9], g[10], g[11]);
+    row.template store<J>(g);
 }
 
+// ---- staging for SPLIT SH storage (GsrBwdArgs.shs_rest): the warp's 32 rows are two contiguous runs, 32 x 3 floats of DC
+// coefficients and 32 x 45 floats of the others (both 16-byte aligned at a multiple of 32 rows).  They are copied to shared
+// memory AS THEY LIE (128-bit accesses, no index arithmetic); a lane then walks its own row with scalar accesses - the row
+// strides 3 and 45 are odd, so those are bank-conflict free (RowFlat).  Lanes of culled Gaussians zero their row, so the way
+// out is a plain copy (or a plain add in accumulating mode).
+constexpr int SHB_FLAT_DC = 32 * 3;          // float offset of the f_rest copy inside the warp's buffer (96 + 1440 <= 32 * 52)
+
+__device__ __forceinline__ void flat_in(float* sm, const float* __restrict__ src, int n, int lane)
+{
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    float4* d4 = reinterpret_cast<float4*>(sm);
+    const int n4 = n >> 2;
+    for (int e = lane; e < n4; e += 32) d4[e] = __ldg(s4 + e);
+    for (int f = (n4 << 2) + lane; f < n; f += 32) sm[f] = __ldg(src + f);
+}
+
+__device__ __forceinline__ void flat_out(const float* sm, float* __restrict__ dst, int n, bool acc, int lane)
+{
+    const float4* s4 = reinterpret_cast<const float4*>(sm);
+    float4* d4 = reinterpret_cast<float4*>(dst);
+    const int n4 = n >> 2;
+    if (acc) {
+        for (int e0 = 0; e0 < n4; e0 += 128) {          // four loads in flight before the dependent stores
+            float4 o[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) { const int e = e0 + u * 32 + lane; if (e < n4) o[u] = d4[e]; }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int e = e0 + u * 32 + lane;
+                if (e < n4) { const float4 v = s4[e]; d4[e] = make_float4(o[u].x + v.x, o[u].y + v.y, o[u].z + v.z, o[u].w + v.w); }
+            }
+        }
+        for (int f = (n4 << 2) + lane; f < n; f += 32) dst[f] += sm[f];
+    } else {
+        for (int e = lane; e < n4; e += 32) d4[e] = s4[e];
+        for (int f = (n4 << 2) + lane; f < n; f += 32) dst[f] = sm[f];
+    }
+}
+
+__device__ __forceinline__ void flat_zero_row(const RowFlat& r)
+{
+    r.dc[0] = 0.f; r.dc[1] = 0.f; r.dc[2] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 45; i++) r.rest[i] = 0.f;
+}
+
+template <bool SPLIT>
 __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D, const float* __restrict__ means,
                                                                     const int* __restrict__ radii, const float* __restrict__ shs,
                                                                     const uint8_t* __restrict__ clamped, const float* __restrict__ accum,
                                                                     const float* __restrict__ campos, float* __restrict__ dL_dsh,
-                                                                    float* __restrict__ dL_dmean3D, unsigned acc)
+                                                                    float* __restrict__ dL_dmean3D, unsigned acc,
+                                                                    const float* __restrict__ shs_rest, float* __restrict__ dL_dsh_rest)
 {
     __shared__ float4 rows[SHB_WARPS][32 * SHB_ROW4];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -458,11 +538,18 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D
     const bool visible = lane < nrow && radii[gid] > 0;
     const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
     // stage in (rows of culled Gaussians are not needed)
-    const float4* src = reinterpret_cast<const float4*>(shs) + (size_t)g0 * 12;
+    float* const flat = reinterpret_cast<float*>(my);
+    const RowFlat frow{flat + lane * 3, flat + SHB_FLAT_DC + lane * 45};
+    if (SPLIT) {
+        flat_in(flat, shs + (size_t)g0 * 3, nrow * 3, lane);
+        flat_in(flat + SHB_FLAT_DC, shs_rest + (size_t)g0 * 45, nrow * 45, lane);
+    } else {
+        const float4* src = reinterpret_cast<const float4*>(shs) + (size_t)g0 * 12;
 #pragma unroll
-    for (int i = 0; i < 12; i++) {
-        const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
-        if ((vis_mask >> r) & 1u) my[r * SHB_ROW4 + c] = __ldg(src + e);
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
+            if ((vis_mask >> r) & 1u) my[r * SHB_ROW4 + c] = __ldg(src + e);
+        }
     }
     __syncwarp();
     if (visible) {
@@ -475,20 +562,33 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D
         const float rl = rsqrtf(sq);
         const float x = ox * rl, y = oy * rl, z = oz * rl;
         float ddx = 0.f, ddy = 0.f, ddz = 0.f;
-        float4* row = my + lane * SHB_ROW4;
-        sh_chunk_apply<0>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
-        sh_chunk_apply<1>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
-        sh_chunk_apply<2>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
-        sh_chunk_apply<3>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+        if (SPLIT) {
+            sh_chunk_apply<0>(frow, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+            sh_chunk_apply<1>(frow, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+            sh_chunk_apply<2>(frow, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+            sh_chunk_apply<3>(frow, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+        } else {
+            const RowPadded row{my + lane * SHB_ROW4};
+            sh_chunk_apply<0>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+            sh_chunk_apply<1>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+            sh_chunk_apply<2>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+            sh_chunk_apply<3>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
+        }
         const float inv = rl * rl * rl;          // 1 / |o|^3
         put(dL_dmean3D + 3 * (size_t)gid, ((sq - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * inv, acc_m);
         put(dL_dmean3D + 3 * (size_t)gid + 1, (-ox * oy * ddx + (sq - oy * oy) * ddy - oz * oy * ddz) * inv, acc_m);
         put(dL_dmean3D + 3 * (size_t)gid + 2, (-ox * oz * ddx - oy * oz * ddy + (sq - oz * oz) * ddz) * inv, acc_m);
-    } else if (lane < nrow && !acc_m) {
-        dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f;
+    } else if (lane < nrow) {
+        if (!acc_m) { dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f; }
+        if (SPLIT) flat_zero_row(frow);
     }
     __syncwarp();
     // stage out
+    if (SPLIT) {
+        flat_out(flat, dL_dsh + (size_t)g0 * 3, nrow * 3, acc_sh, lane);
+        flat_out(flat + SHB_FLAT_DC, dL_dsh_rest + (size_t)g0 * 45, nrow * 45, acc_sh, lane);
+        return;
+    }
     float4* dst = reinterpret_cast<float4*>(dL_dsh) + (size_t)g0 * 12;
     if (acc_sh) {
         // all twelve reads of the destination are issued before the first dependent store
@@ -520,13 +620,13 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D
 // the lane loops over the views it is visible in, adds basis_k(dir_v) * dL/dRGB_v into the chunk's output and applies
 // the direction gradient of that chunk to dL/dmean3D straight away (dnormvdv is linear in it), so no per-view state
 // survives the inner loop.  Replaces V read-modify-write passes over the 192-byte gradient rows.
-template <int J>
-__device__ __forceinline__ void sh_chunk_views(float4* row, int P, int V, int D, int gid, float px, float py, float pz,
+template <int J, class Row>
+__device__ __forceinline__ void sh_chunk_views(const Row& row, int P, int V, int D, int gid, float px, float py, float pz,
                                                const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
                                                const float* __restrict__ accum, const float* __restrict__ campos, float* dm)
 {
-    const float4 s0 = row[3 * J], s1 = row[3 * J + 1], s2 = row[3 * J + 2];
-    const float f[12] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w, s2.x, s2.y, s2.z, s2.w};
+    float f[12];
+    row.template load<J>(f);
     float g[12];
 #pragma unroll
     for (int k = 0; k < 12; k++) g[k] = 0.f;
@@ -553,17 +653,18 @@ __device__ __forceinline__ void sh_chunk_views(float4* row, int P, int V, int D,
         dm[1] += (-ox * oy * ddx + (sq - oy * oy) * ddy - oz * oy * ddz) * inv;
         dm[2] += (-ox * oz * ddx - oy * oz * ddy + (sq - oz * oz) * ddz) * inv;
     }
-    row[3 * J] = make_float4(g[0], g[1], g[2], g[3]);
-    row[3 * J + 1] = make_float4(g[4], g[5], g[6], g[7]);
-    row[3 * J + 2] = make_float4(g[8], g[9], g[10], g[11]);
+    row.template store<J>(g);
 }
 
+template <bool SPLIT>
 __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P, int V, int D, const float* __restrict__ means,
                                                                           const int* __restrict__ radii, const float* __restrict__ shs,
                                                                           const uint8_t* __restrict__ clamped,
                                                                           const float* __restrict__ accum,
                                                                           const float* __restrict__ campos, float* __restrict__ dL_dsh,
-                                                                          float* __restrict__ dL_dmean3D, unsigned acc)
+                                                                          float* __restrict__ dL_dmean3D, unsigned acc,
+                                                                          const float* __restrict__ shs_rest,
+                                                                          float* __restrict__ dL_dsh_rest)
 {
     __shared__ float4 rows[SHB_WARPS][32 * SHB_ROW4];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -577,28 +678,48 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P,
     if (lane < nrow)
         for (int v = 0; v < V; v++) visible = visible || radii[(size_t)v * P + gid] > 0;
     const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
-    const float4* src = reinterpret_cast<const float4*>(shs) + (size_t)g0 * 12;
+    float* const flat = reinterpret_cast<float*>(my);
+    const RowFlat frow{flat + lane * 3, flat + SHB_FLAT_DC + lane * 45};
+    if (SPLIT) {
+        flat_in(flat, shs + (size_t)g0 * 3, nrow * 3, lane);
+        flat_in(flat + SHB_FLAT_DC, shs_rest + (size_t)g0 * 45, nrow * 45, lane);
+    } else {
+        const float4* src = reinterpret_cast<const float4*>(shs) + (size_t)g0 * 12;
 #pragma unroll
-    for (int i = 0; i < 12; i++) {
-        const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
-        if ((vis_mask >> r) & 1u) my[r * SHB_ROW4 + c] = __ldg(src + e);
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane, r = e / 12, c = e - r * 12;
+            if ((vis_mask >> r) & 1u) my[r * SHB_ROW4 + c] = __ldg(src + e);
+        }
     }
     __syncwarp();
     if (visible) {
         const float px = means[3 * (size_t)gid], py = means[3 * (size_t)gid + 1], pz = means[3 * (size_t)gid + 2];
         float dm[3] = {0.f, 0.f, 0.f};
-        float4* row = my + lane * SHB_ROW4;
-        sh_chunk_views<0>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-        sh_chunk_views<1>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-        sh_chunk_views<2>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-        sh_chunk_views<3>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+        if (SPLIT) {
+            sh_chunk_views<0>(frow, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+            sh_chunk_views<1>(frow, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+            sh_chunk_views<2>(frow, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+            sh_chunk_views<3>(frow, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+        } else {
+            const RowPadded row{my + lane * SHB_ROW4};
+            sh_chunk_views<0>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+            sh_chunk_views<1>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+            sh_chunk_views<2>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+            sh_chunk_views<3>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+        }
         put(dL_dmean3D + 3 * (size_t)gid, dm[0], acc_m);
         put(dL_dmean3D + 3 * (size_t)gid + 1, dm[1], acc_m);
         put(dL_dmean3D + 3 * (size_t)gid + 2, dm[2], acc_m);
-    } else if (lane < nrow && !acc_m) {
-        dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f;
+    } else if (lane < nrow) {
+        if (!acc_m) { dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f; }
+        if (SPLIT) flat_zero_row(frow);
     }
     __syncwarp();
+    if (SPLIT) {
+        flat_out(flat, dL_dsh + (size_t)g0 * 3, nrow * 3, acc_sh, lane);
+        flat_out(flat + SHB_FLAT_DC, dL_dsh_rest + (size_t)g0 * 45, nrow * 45, acc_sh, lane);
+        return;
+    }
     float4* dst = reinterpret_cast<float4*>(dL_dsh) + (size_t)g0 * 12;
     if (acc_sh) {
         float4 o[12];
@@ -639,13 +760,23 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
     k.dL_drot = a.cov3D_precomp ? nullptr : a.dL_drot;
     k.acc = a.accumulate;
     k.sh_done = 0;
-    if (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && env_int("GSR_SH_SPLIT", 1)) {
+    const bool split = a.shs && a.shs_rest && a.M > 1;      // DC and the other coefficients in two arrays (M == 16, checked by the API)
+    if (split) {
+        if (((((size_t)a.shs) | ((size_t)a.dL_dsh) | ((size_t)a.shs_rest) | ((size_t)a.dL_dsh_rest)) & 15) != 0) return GSR_EINVAL;
         if (V == 1)
-            GSR_LAUNCH(sh_bwd_m16_kernel, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs, g.clamped,
-                       accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate);
+            GSR_LAUNCH(sh_bwd_m16_kernel<true>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs,
+                       g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate, a.shs_rest, a.dL_dsh_rest);
         else
-            GSR_LAUNCH(sh_bwd_m16_views_kernel, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii, a.shs,
-                       g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate);
+            GSR_LAUNCH(sh_bwd_m16_views_kernel<true>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii,
+                       a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate, a.shs_rest, a.dL_dsh_rest);
+        k.sh_done = 1;
+    } else if (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && env_int("GSR_SH_SPLIT", 1)) {
+        if (V == 1)
+            GSR_LAUNCH(sh_bwd_m16_kernel<false>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs,
+                       g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate, (const float*)nullptr, (float*)nullptr);
+        else
+            GSR_LAUNCH(sh_bwd_m16_views_kernel<false>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii,
+                       a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate, (const float*)nullptr, (float*)nullptr);
         k.sh_done = 1;
     }
     const bool with_sh = !(k.sh_done || !a.shs);

@@ -45,13 +45,15 @@ gsr_stream_t current_stream() { return reinterpret_cast<gsr_stream_t>(at::cuda::
 
 }  // namespace
 
+// `sh_rest` non-empty: split SH storage - `sh` is the model's _features_dc [P,1,3] and `sh_rest` its _features_rest [P,M-1,3]
+// (scene/gaussian_model.py:151-152), read in place instead of through the torch.cat of get_features (:119-122)
 std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
-rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
-                    const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
-                    const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
-                    const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
-                    const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
-                    const bool prefiltered, const bool debug)
+rasterize_gaussians_split(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                          const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                          const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                          const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+                          const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                          const bool prefiltered, const bool debug, const torch::Tensor& sh_rest)
 {
     if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
@@ -69,10 +71,15 @@ rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3
     if (P != 0) {
         int M = 0;
         if (sh.numel() != 0) M = (int)sh.size(1);
+        if (sh_rest.numel() != 0) {
+            TORCH_CHECK(sh.numel() != 0 && sh.size(1) == 1 && sh_rest.dim() == 3 && sh_rest.size(0) == P, "split SH: sh [P,1,3] and sh_rest [P,K,3] expected");
+            M = 1 + (int)sh_rest.size(1);
+        }
         F32 bg(background), m3(means3D), col(colors), op(opacity), sc(scales), rot(rotations), cov(cov3D_precomp), vm(viewmatrix),
-            pm(projmatrix), shs(sh), cam(campos);
+            pm(projmatrix), shs(sh), cam(campos), shr(sh_rest);
         GsrFwdArgs a = {};
         a.P = P; a.D = degree; a.M = M; a.W = W; a.H = H;
+        a.shs_rest = shr.ptr();
         a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr(); a.colors_precomp = col.ptr(); a.opacities = op.ptr();
         a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr(); a.cov3D_precomp = cov.ptr();
         a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
@@ -85,8 +92,24 @@ rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3
     return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer);
 }
 
-std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
-rasterize_gaussians_backward_into(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+// the reference's entry point (rasterize_points.h:18-38)
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                    const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                    const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                    const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+                    const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                    const bool prefiltered, const bool debug)
+{
+    return rasterize_gaussians_split(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                                     projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug,
+                                     torch::empty({0}));
+}
+
+// returns the reference's eight gradients plus dL_dsh_rest (empty unless sh_rest is given)
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+           torch::Tensor>
+rasterize_gaussians_backward_split(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
                                   const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
                                   const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
                                   const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
@@ -94,7 +117,8 @@ rasterize_gaussians_backward_into(const torch::Tensor& background, const torch::
                                   const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
                                   const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
                                   const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
-                                  const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate)
+                                  const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate,
+                                  const torch::Tensor& sh_rest, const torch::Tensor& into_sh_rest)
 {
     // Extension of the reference entry point: a non-empty `into_*` tensor (contiguous fp32 CUDA, same element count as
     // the gradient) receives that gradient directly - overwritten, or added to when `accumulate` - and the
@@ -105,6 +129,12 @@ rasterize_gaussians_backward_into(const torch::Tensor& background, const torch::
     const int H = (int)dL_dout_color.size(1), W = (int)dL_dout_color.size(2);
     int M = 0;
     if (sh.numel() != 0) M = (int)sh.size(1);
+    const bool split = sh_rest.numel() != 0;
+    const int Mdc = M;                                        // coefficients held by `sh` itself
+    if (split) {
+        TORCH_CHECK(M == 1 && sh_rest.dim() == 3 && sh_rest.size(0) == P, "split SH: sh [P,1,3] and sh_rest [P,K,3] expected");
+        M = 1 + (int)sh_rest.size(1);
+    }
     auto f32 = means3D.options().dtype(torch::kFloat32);
     const bool want_colors = colors.numel() != 0, want_cov = cov3D_precomp.numel() != 0;
     const bool has_sr = scales.numel() != 0 && rotations.numel() != 0;
@@ -121,7 +151,10 @@ rasterize_gaussians_backward_into(const torch::Tensor& background, const torch::
     };
     float* t_m3 = target(into_means3D, (int64_t)P * 3, GSR_ACC_MEAN3D);
     float* t_op = target(into_opacity, (int64_t)P, GSR_ACC_OPACITY);
-    float* t_sh = target(into_sh, (int64_t)P * M * 3, GSR_ACC_SH);
+    float* t_sh = target(into_sh, (int64_t)P * Mdc * 3, GSR_ACC_SH);
+    float* t_shr = split ? target(into_sh_rest, (int64_t)P * (M - 1) * 3, GSR_ACC_SH) : nullptr;
+    TORCH_CHECK(!split || !accumulate || ((t_sh != nullptr) == (t_shr != nullptr)),
+                "split SH: accumulate needs targets for both f_dc and f_rest or for neither");
     float* t_sc = has_sr ? target(into_scales, (int64_t)P * 3, GSR_ACC_SCALE) : nullptr;
     float* t_rt = has_sr ? target(into_rotations, (int64_t)P * 4, GSR_ACC_ROT) : nullptr;
     auto none = [&]() { return torch::empty({0}, f32); };
@@ -130,16 +163,19 @@ rasterize_gaussians_backward_into(const torch::Tensor& background, const torch::
     torch::Tensor dL_dcolors = want_colors ? alloc({P, 3}) : none();
     torch::Tensor dL_dopacity = t_op ? none() : alloc({P, 1});
     torch::Tensor dL_dcov3D = want_cov ? alloc({P, 6}) : none();
-    torch::Tensor dL_dsh = t_sh ? none() : alloc({P, M, 3});
+    torch::Tensor dL_dsh = t_sh ? none() : alloc({P, Mdc, 3});
+    torch::Tensor dL_dsh_rest = (split && !t_shr) ? alloc({P, M - 1, 3}) : none();
     torch::Tensor dL_dscales = (has_sr && !t_sc) ? alloc({P, 3}) : none();
     torch::Tensor dL_drotations = (has_sr && !t_rt) ? alloc({P, 4}) : none();
 
     if (P != 0) {
         torch::Tensor accum = torch::empty({(long long)(gsr_bwd_accum_bytes(P) / sizeof(float))}, f32);
         F32 bg(background), m3(means3D), col(colors), sc(scales), rot(rotations), cov(cov3D_precomp), vm(viewmatrix), pm(projmatrix),
-            shs(sh), cam(campos), dpix(dL_dout_color);
+            shs(sh), cam(campos), dpix(dL_dout_color), shr(sh_rest);
         torch::Tensor radii_c = radii.contiguous();
         GsrBwdArgs a = {};
+        a.shs_rest = shr.ptr();
+        a.dL_dsh_rest = split ? (t_shr ? t_shr : dL_dsh_rest.data_ptr<float>()) : nullptr;
         a.P = P; a.D = degree; a.M = M; a.R = R; a.W = W; a.H = H;
         a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr(); a.colors_precomp = col.ptr();
         a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr(); a.cov3D_precomp = cov.ptr();
@@ -161,7 +197,27 @@ rasterize_gaussians_backward_into(const torch::Tensor& background, const torch::
         a.accumulate = acc_bits;
         check(gsr_backward(&a, current_stream()), "rasterize_gaussians_backward");
     }
-    return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+    return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, dL_dsh_rest);
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_backward_into(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                                  const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
+                                  const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                                  const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                                  const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                                  const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
+                                  const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
+                                  const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
+                                  const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate)
+{
+    const torch::Tensor e = torch::empty({0});
+    auto r = rasterize_gaussians_backward_split(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                                viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer,
+                                                R, binningBuffer, imageBuffer, debug, into_means3D, into_opacity, into_sh, into_scales,
+                                                into_rotations, accumulate, e, e);
+    return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r), std::get<3>(r), std::get<4>(r), std::get<5>(r),
+                           std::get<6>(r), std::get<7>(r));
 }
 
 // the reference's entry point (rasterize_points.h:40-62): every gradient freshly allocated
@@ -457,6 +513,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
     m.def("rasterize_gaussians_batched", &rasterize_gaussians_batched);
     m.def("rasterize_gaussians_batched_backward", &rasterize_gaussians_batched_backward);
     m.def("rasterize_gaussians", &rasterize_gaussians);
+    m.def("rasterize_gaussians_split", &rasterize_gaussians_split);
+    m.def("rasterize_gaussians_backward_split", &rasterize_gaussians_backward_split);
     m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
     m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into);
     m.def("mark_visible", &mark_visible);

@@ -203,7 +203,7 @@ def test_cabi_exports_every_declared_symbol():
     for s in sorted(declared):
         assert hasattr(lib, s), "libgsr_b200.so does not export %s" % s
     lib.gsr_abi_version.restype = ctypes.c_int
-    assert lib.gsr_abi_version() == 1
+    assert lib.gsr_abi_version() == 2
     lib.gsr_strerror.restype = ctypes.c_char_p
     assert b"precomputed" in lib.gsr_strerror(-4)
     lib.gsr_geom_bytes.restype = ctypes.c_size_t
