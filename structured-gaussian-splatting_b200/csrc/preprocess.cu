@@ -118,13 +118,39 @@ __device__ __forceinline__ void load_sh(const float* __restrict__ p, bool vec, f
     }
 }
 
-// split storage: DC coefficient at dc, coefficients 1.. at rest (45 floats per Gaussian, 4-byte aligned rows)
+// split storage: DC coefficient at dc, coefficients 1.. in rows of 45 floats at rest_base (row idx starts 4-byte aligned, at
+// float offset 45 idx = idx mod 4 past a 16-byte boundary).  The row is fetched with the 128-bit loads that cover it
+// (12 of them for 45 floats, as many as the unsplit 48-float row needs) and shifted into place by a two-stage select
+// network on idx mod 4 - 45 scalar loads would ask the L1 for four times as many sectors.
 template <int NREST>
-__device__ __forceinline__ void load_sh_split(const float* __restrict__ dc, const float* __restrict__ rest, float* f)
+__device__ __forceinline__ void load_sh_split(const float* __restrict__ dc, const float* __restrict__ rest_base, size_t idx,
+                                              size_t P, bool vec, float* f)
 {
     f[0] = __ldg(dc); f[1] = __ldg(dc + 1); f[2] = __ldg(dc + 2);
+    if (NREST == 0) return;
+    constexpr int NV = (NREST + 3 + 3) / 4;            // float4s covering [row - 3, row + NREST)
+    const float* row = rest_base + 45 * idx;
+    const unsigned o = (unsigned)(idx & 3);            // floats between the 16-byte boundary below the row and the row
+    if (vec && 45 * idx - o + 4 * NV <= 45 * P) {
+        const float4* p4 = reinterpret_cast<const float4*>(row - o);
+        float t[4 * NV + 4];
 #pragma unroll
-    for (int i = 0; i < NREST; i++) f[3 + i] = __ldg(rest + i);
+        for (int i = 0; i < NV; i++) {
+            const float4 v = __ldg(p4 + i);
+            t[4 * i] = v.x; t[4 * i + 1] = v.y; t[4 * i + 2] = v.z; t[4 * i + 3] = v.w;
+        }
+#pragma unroll
+        for (int i = 4 * NV; i < 4 * NV + 4; i++) t[i] = 0.f;
+        const bool s1 = o & 1u, s2 = o & 2u;
+        float u[NREST + 2];
+#pragma unroll
+        for (int i = 0; i < NREST + 2; i++) u[i] = s1 ? t[i + 1] : t[i];
+#pragma unroll
+        for (int i = 0; i < NREST; i++) f[3 + i] = s2 ? u[i + 2] : u[i];
+    } else {
+#pragma unroll
+        for (int i = 0; i < NREST; i++) f[3 + i] = __ldg(row + i);
+    }
 }
 
 struct PreArgs {
@@ -212,13 +238,14 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
                     dx = dx / len; dy = dy / len; dz = dz / len;
                     float f[48];
                     if (a.shs_rest != nullptr) {
+                        // M == 16 here (the API rejects other split layouts): rows of 45 floats
                         const float* dc = a.shs + (size_t)3 * idx;
-                        const float* rest = a.shs_rest + (size_t)3 * (a.M - 1) * idx;
+                        const bool vec = (((size_t)a.shs_rest) & 15) == 0;
                         switch (a.D) {
-                        case 0: load_sh_split<0>(dc, rest, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        case 1: load_sh_split<9>(dc, rest, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        case 2: load_sh_split<24>(dc, rest, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        default: load_sh_split<45>(dc, rest, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        case 0: load_sh_split<0>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        case 1: load_sh_split<9>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        case 2: load_sh_split<24>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
+                        default: load_sh_split<45>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
                         }
                     } else {
                         const float* shp = a.shs + (size_t)3 * a.M * idx;
