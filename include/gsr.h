@@ -199,6 +199,21 @@ int gsr_l1_ssim_loss(const float* image, const float* target, int C, int H, int 
                      float* sums, float* maps, float* grad, gsr_stream_t stream);
 
 /*
+ * Parameter activations of the model, one launch per direction (scene/gaussian_model.py:33-40,100-125):
+ *   scales = exp(scaling_raw) [P,3];  rotations = rotation_raw / max(|rotation_raw|, 1e-12) [P,4];
+ *   opacities = 1 / (1 + exp(-opacity_raw)) [P]
+ * Any output (with its input) may be NULL.  The backward recomputes the activations from the raw parameters and writes
+ * (accumulate = 0) or adds (accumulate = 1) the raw parameters' gradients; a NULL gradient output skips that parameter.
+ * The [P,4] arrays must be 16-byte aligned.
+ */
+int gsr_activate_forward(int P, const float* scaling_raw, const float* rotation_raw, const float* opacity_raw,
+                         float* scales, float* rotations, float* opacities, gsr_stream_t stream);
+int gsr_activate_backward(int P, const float* scaling_raw, const float* rotation_raw, const float* opacity_raw,
+                          const float* dL_dscales, const float* dL_drotations, const float* dL_dopacities,
+                          float* dL_dscaling_raw, float* dL_drotation_raw, float* dL_dopacity_raw, int accumulate,
+                          gsr_stream_t stream);
+
+/*
  * Fused Adam step over all parameter groups in one launch: replaces gaussians.optimizer.step() of train.py:138-140,
  * i.e. torch.optim.Adam(l, lr=0.0, eps=1e-15) over the groups built at scene/gaussian_model.py:164-175
  * (no weight decay, no amsgrad).  Same fp32 arithmetic as torch's foreach implementation:

@@ -19,7 +19,7 @@ PKG = os.path.join(HERE, "gsr_b200")
 OBJ = os.path.join(HERE, "build")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-CU_SOURCES = ["api.cu", "preprocess.cu", "preprocess_bwd.cu", "sort.cu", "sort_cub.cu", "blend.cu", "knn.cu", "loss.cu", "ssim.cu", "optim.cu", "io.cu"]
+CU_SOURCES = ["api.cu", "preprocess.cu", "preprocess_bwd.cu", "sort.cu", "sort_cub.cu", "blend.cu", "knn.cu", "loss.cu", "ssim.cu", "optim.cu", "io.cu", "activate.cu"]
 HEADERS = ["gsr_common.cuh", "math3.cuh", os.path.join(INCLUDE, "gsr.h")]
 # nvcc defaults on purpose (-fmad=true, IEEE div/sqrt, no fast-math): the bit-exact integer contract
 # depends on the same fp32 rounding as the reference build (torch's BuildExtension adds no fast-math).

@@ -503,8 +503,54 @@ torch::Tensor gather_columns(const torch::Tensor& in, std::vector<int> cols)
     return out;
 }
 
+// (exp(scaling), normalize(rotation), sigmoid(opacity)) in one launch
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> activate(const torch::Tensor& scaling, const torch::Tensor& rotation,
+                                                                 const torch::Tensor& opacity)
+{
+    TORCH_CHECK(scaling.is_cuda() && rotation.is_cuda() && opacity.is_cuda(), "activate: CUDA tensors expected");
+    const int64_t P = scaling.size(0);
+    TORCH_CHECK(scaling.numel() == 3 * P && rotation.numel() == 4 * P && opacity.numel() == P, "activate: [P,3], [P,4], [P,1] expected");
+    const c10::cuda::CUDAGuard guard(scaling.device());
+    F32 s(scaling), q(rotation), o(opacity);
+    auto f32 = scaling.options().dtype(torch::kFloat32);
+    torch::Tensor so = torch::empty({P, 3}, f32), qo = torch::empty({P, 4}, f32), oo = torch::empty({P, 1}, f32);
+    check(gsr_activate_forward((int)P, s.ptr(), q.ptr(), o.ptr(), so.data_ptr<float>(), qo.data_ptr<float>(), oo.data_ptr<float>(),
+                               current_stream()), "activate");
+    return std::make_tuple(so, qo, oo);
+}
+
+// gradients of the raw parameters; a non-empty `into_*` (contiguous fp32, the leaf's .grad) is written / added to in place
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor>
+activate_backward(const torch::Tensor& scaling, const torch::Tensor& rotation, const torch::Tensor& opacity, const torch::Tensor& g_s,
+                  const torch::Tensor& g_q, const torch::Tensor& g_o, const torch::Tensor& into_s, const torch::Tensor& into_q,
+                  const torch::Tensor& into_o, bool accumulate)
+{
+    const int64_t P = scaling.size(0);
+    const c10::cuda::CUDAGuard guard(scaling.device());
+    F32 s(scaling), q(rotation), o(opacity), gs(g_s), gq(g_q), go(g_o);
+    auto f32 = scaling.options().dtype(torch::kFloat32);
+    const bool all_into = into_s.numel() && into_q.numel() && into_o.numel();
+    TORCH_CHECK(all_into || !(into_s.numel() || into_q.numel() || into_o.numel()), "activate_backward: give all three targets or none");
+    torch::Tensor ds, dq, dop;
+    if (all_into) {
+        for (const torch::Tensor* t : {&into_s, &into_q, &into_o})
+            TORCH_CHECK(t->is_cuda() && t->scalar_type() == torch::kFloat32 && t->is_contiguous(), "activate_backward: bad gradient target");
+        TORCH_CHECK(into_s.numel() == 3 * P && into_q.numel() == 4 * P && into_o.numel() == P, "activate_backward: target sizes");
+        ds = into_s; dq = into_q; dop = into_o;
+    } else {
+        ds = torch::empty({P, 3}, f32); dq = torch::empty({P, 4}, f32); dop = torch::empty({P, 1}, f32);
+    }
+    check(gsr_activate_backward((int)P, s.ptr(), q.ptr(), o.ptr(), gs.ptr(), gq.ptr(), go.ptr(), ds.data_ptr<float>(),
+                                dq.data_ptr<float>(), dop.data_ptr<float>(), (all_into && accumulate) ? 1 : 0, current_stream()),
+          "activate_backward");
+    if (all_into) { torch::Tensor e = torch::empty({0}, f32); return std::make_tuple(e, e, e); }
+    return std::make_tuple(ds, dq, dop);
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
 {
+    m.def("activate", &activate);
+    m.def("activate_backward", &activate_backward);
     m.def("gather_columns", &gather_columns);
     m.def("adam_step", &adam_step);
     m.def("densify_stats", &densify_stats);

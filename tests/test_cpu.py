@@ -192,6 +192,19 @@ def test_ply_header_and_column_maps_match_oracle(tmp_path):
         assert np.array_equal(payload[:, cols].reshape(m[k].shape), m[k])
 
 
+def test_activation_oracle_matches_torch_golden():
+    """oracle/activation_oracle.py against torch.exp / F.normalize / torch.sigmoid + autograd (the reference's activation
+    functions, scene/gaussian_model.py:33-40), vectors from tests/golden/make_activation_golden.py"""
+    from oracle import activation_oracle as ao
+    g = np.load(os.path.join(GOLDEN, "activations.npz"))
+    y = ao.forward(g["scaling"], g["rotation"], g["opacity"])
+    d = ao.backward(g["scaling"], g["rotation"], g["opacity"], g["g_scaling"], g["g_rotation"], g["g_opacity"])
+    for a, k in zip(y, ("y_scaling", "y_rotation", "y_opacity")):
+        assert np.abs(a - g[k]).max() <= 1e-6 * np.abs(g[k]).max()
+    for a, k in zip(d, ("d_scaling", "d_rotation", "d_opacity")):
+        assert np.abs(a - g[k]).max() <= 1e-6 * np.abs(g[k]).max()
+
+
 # ------------------------------------------------------------------------------ the C-ABI library
 def test_cabi_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "gsr.h")).read()
