@@ -293,7 +293,7 @@ rasterize_gaussians_batched(const torch::Tensor& background, const torch::Tensor
                             const torch::Tensor& scales, const torch::Tensor& rotations, const float scale_modifier,
                             const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices, const float tan_fovx,
                             const float tan_fovy, const int image_height, const int image_width, const torch::Tensor& sh,
-                            const int degree, const torch::Tensor& camposs, const bool debug)
+                            const int degree, const torch::Tensor& camposs, const bool debug, const torch::Tensor& sh_rest)
 {
     if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
@@ -312,9 +312,15 @@ rasterize_gaussians_batched(const torch::Tensor& background, const torch::Tensor
     torch::Tensor geomBuffer = torch::empty({0}, u8), binningBuffer = torch::empty({0}, u8), imgBuffer = torch::empty({0}, u8);
     int rendered = 0;
     if (P != 0 && V != 0) {
-        F32 bg(background), m3(means3D), op(opacity), sc(scales), rot(rotations), vm(viewmatrices), pm(projmatrices), shs(sh), cam(camposs);
+        F32 bg(background), m3(means3D), op(opacity), sc(scales), rot(rotations), vm(viewmatrices), pm(projmatrices), shs(sh), cam(camposs),
+            shr(sh_rest);
         GsrFwdArgs a = {};
         a.P = P; a.D = degree; a.M = (int)sh.size(1); a.W = W; a.H = H;
+        if (sh_rest.numel() != 0) {                              // split SH storage: sh = features_dc, sh_rest = features_rest
+            TORCH_CHECK(sh.size(1) == 1 && sh_rest.dim() == 3 && sh_rest.size(0) == P, "split SH: sh [P,1,3] and sh_rest [P,K,3] expected");
+            a.M = 1 + (int)sh_rest.size(1);
+            a.shs_rest = shr.ptr();
+        }
         a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr(); a.opacities = op.ptr();
         a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr();
         a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
@@ -327,9 +333,9 @@ rasterize_gaussians_batched(const torch::Tensor& background, const torch::Tensor
     return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer);
 }
 
-// returns (dL_dmeans2D [V,P,3], dL_dopacity [P,1], dL_dmeans3D [P,3], dL_dsh [P,M,3], dL_dscales [P,3], dL_drotations [P,4]),
-// all but the first summed over the views
-std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+// returns (dL_dmeans2D [V,P,3], dL_dopacity [P,1], dL_dmeans3D [P,3], dL_dsh [P,M,3], dL_dscales [P,3], dL_drotations [P,4],
+// dL_dsh_rest), all but the first summed over the views; with split SH storage dL_dsh is [P,1,3] and dL_dsh_rest [P,M-1,3]
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
 rasterize_gaussians_batched_backward(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
                                      const torch::Tensor& scales, const torch::Tensor& rotations, const float scale_modifier,
                                      const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices, const float tan_fovx,
@@ -337,7 +343,8 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
                                      const torch::Tensor& camposs, const torch::Tensor& geomBuffer, const int R,
                                      const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
                                      const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
-                                     const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate)
+                                     const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate,
+                                     const torch::Tensor& sh_rest, const torch::Tensor& into_sh_rest)
 {
     // non-empty `into_*` (all five or none): the summed gradients are written (or, with `accumulate`, added) straight into
     // these buffers - the parameters' .grad - and the corresponding returned tensors are empty
@@ -346,7 +353,10 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
     const c10::cuda::CUDAGuard guard(means3D.device());
     const int P = (int)means3D.size(0), V = (int)dL_dout_color.size(0);
     const int H = (int)dL_dout_color.size(2), W = (int)dL_dout_color.size(3);
-    const int M = (int)sh.size(1);
+    const bool split = sh_rest.numel() != 0;
+    const int Mdc = (int)sh.size(1);
+    const int M = split ? 1 + (int)sh_rest.size(1) : Mdc;
+    TORCH_CHECK(!split || (Mdc == 1 && sh_rest.dim() == 3 && sh_rest.size(0) == P), "split SH: sh [P,1,3] and sh_rest [P,K,3] expected");
     auto f32 = means3D.options().dtype(torch::kFloat32);
     const bool live = P != 0 && V != 0;
     auto alloc = [&](std::initializer_list<int64_t> shape) { return live ? torch::empty(shape, f32) : torch::zeros(shape, f32); };
@@ -355,21 +365,23 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
         auto ok = [&](const torch::Tensor& t, int64_t n) {
             return t.is_cuda() && t.scalar_type() == torch::kFloat32 && t.is_contiguous() && t.numel() == n;
         };
-        TORCH_CHECK(ok(into_means3D, (int64_t)P * 3) && ok(into_opacity, P) && ok(into_sh, (int64_t)P * M * 3) &&
-                        ok(into_scales, (int64_t)P * 3) && ok(into_rotations, (int64_t)P * 4),
+        TORCH_CHECK(ok(into_means3D, (int64_t)P * 3) && ok(into_opacity, P) && ok(into_sh, (int64_t)P * Mdc * 3) &&
+                        ok(into_scales, (int64_t)P * 3) && ok(into_rotations, (int64_t)P * 4) &&
+                        (!split || ok(into_sh_rest, (int64_t)P * (M - 1) * 3)),
                     "gradient targets must be contiguous fp32 CUDA tensors with the gradients' element counts");
     }
     auto none = [&]() { return torch::empty({0}, f32); };
     torch::Tensor dL_dmeans2D = alloc({V, P, 3});
     torch::Tensor dL_dopacity = into ? none() : alloc({P, 1}), dL_dmeans3D = into ? none() : alloc({P, 3}),
-                  dL_dsh = into ? none() : alloc({P, M, 3}), dL_dscales = into ? none() : alloc({P, 3}),
-                  dL_drotations = into ? none() : alloc({P, 4});
+                  dL_dsh = into ? none() : alloc({P, Mdc, 3}), dL_dscales = into ? none() : alloc({P, 3}),
+                  dL_drotations = into ? none() : alloc({P, 4}), dL_dsh_rest = (split && !into) ? alloc({P, M - 1, 3}) : none();
     if (live) {
         torch::Tensor accum = torch::empty({(long long)(gsr_bwd_accum_bytes(P * V) / sizeof(float))}, f32);
         F32 bg(background), m3(means3D), sc(scales), rot(rotations), vm(viewmatrices), pm(projmatrices), shs(sh), cam(camposs),
-            dpix(dL_dout_color);
+            dpix(dL_dout_color), shr(sh_rest);
         torch::Tensor radii_c = radii.contiguous();
         GsrBwdArgs a = {};
+        if (split) { a.shs_rest = shr.ptr(); a.dL_dsh_rest = (into ? into_sh_rest : dL_dsh_rest).data_ptr<float>(); }
         a.P = P; a.D = degree; a.M = M; a.R = R; a.W = W; a.H = H;
         a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr();
         a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr();
@@ -389,7 +401,7 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
         if (into && accumulate) a.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
         check(gsr_backward_batched(&a, V, current_stream()), "rasterize_gaussians_batched_backward");
     }
-    return std::make_tuple(dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_dsh, dL_dscales, dL_drotations);
+    return std::make_tuple(dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_dsh, dL_dscales, dL_drotations, dL_dsh_rest);
 }
 
 // fused L1 loss: returns (sum |image - target| as a 1-element tensor, dL/dimage for loss = mean |image - target|)

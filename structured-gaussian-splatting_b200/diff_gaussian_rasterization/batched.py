@@ -37,31 +37,37 @@ class BatchedRasterizationSettings(NamedTuple):
 
 class _RasterizeGaussiansBatched(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, means3D, means2D, sh, opacities, scales, rotations, rs):
+    def forward(ctx, means3D, means2D, sh, opacities, scales, rotations, rs, sh_rest):
         R, color, radii, geom, binning, img = _C.rasterize_gaussians_batched(
             rs.bg, means3D, opacities, scales, rotations, rs.scale_modifier, rs.viewmatrices, rs.projmatrices, rs.tanfovx,
-            rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree, rs.camposs, rs.debug)
+            rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree, rs.camposs, rs.debug, sh_rest)
         ctx.rs = rs
         ctx.R = R
+        ctx.split = sh_rest.numel() != 0
         # diff_gaussian_rasterization.set_grad_mode: write / add the summed gradients straight into the leaves' .grad
         ctx.grad_mode = _dgr._GRAD_MODE
-        targets = tuple(_grad_target(t) for t in (means3D, opacities, sh, scales, rotations)) if ctx.grad_mode else ()
+        leaves = (means3D, opacities, sh, scales, rotations) + ((sh_rest,) if ctx.split else ())
+        targets = tuple(_grad_target(t) for t in leaves) if ctx.grad_mode else ()
         ctx.grad_targets = targets if targets and all(t is not None for t in targets) else None
-        ctx.save_for_backward(means3D, scales, rotations, radii, sh, geom, binning, img)
+        ctx.save_for_backward(means3D, scales, rotations, radii, sh, geom, binning, img, sh_rest)
         ctx.mark_non_differentiable(radii)
         return color, radii
 
     @staticmethod
     def backward(ctx, grad_color, _grad_radii):
         rs = ctx.rs
-        means3D, scales, rotations, radii, sh, geom, binning, img = ctx.saved_tensors
-        g2d, gop, g3d, gsh, gsc, grot = _C.rasterize_gaussians_batched_backward(
+        means3D, scales, rotations, radii, sh, geom, binning, img, sh_rest = ctx.saved_tensors
+        e = torch.Tensor([])
+        t = ctx.grad_targets
+        into = (tuple(t[:5]) if t else (e,) * 5)
+        into_rest = t[5] if (t and ctx.split) else e
+        g2d, gop, g3d, gsh, gsc, grot, grest = _C.rasterize_gaussians_batched_backward(
             rs.bg, means3D, radii, scales, rotations, rs.scale_modifier, rs.viewmatrices, rs.projmatrices, rs.tanfovx, rs.tanfovy,
             grad_color, sh, rs.sh_degree, rs.camposs, geom, ctx.R, binning, img, rs.debug,
-            *(ctx.grad_targets if ctx.grad_targets else (torch.Tensor([]),) * 5), ctx.grad_mode == "accumulate")
-        if ctx.grad_targets:
-            return None, g2d, None, None, None, None, None
-        return g3d, g2d, gsh, gop, gsc, grot, None
+            *into, ctx.grad_mode == "accumulate", sh_rest, into_rest)
+        if t:
+            return None, g2d, None, None, None, None, None, None
+        return g3d, g2d, gsh, gop, gsc, grot, None, (grest if ctx.split else None)
 
 
 class GaussianRasterizerBatched(nn.Module):
@@ -69,11 +75,16 @@ class GaussianRasterizerBatched(nn.Module):
         super().__init__()
         self.raster_settings = raster_settings
 
-    def forward(self, means3D, means2D, opacities, shs, scales, rotations):
+    def forward(self, means3D, means2D, opacities, shs, scales, rotations, shs_rest=None):
+        """shs_rest given: split SH storage - shs is the model's features_dc [P,1,3], shs_rest its features_rest [P,15,3]
+        (read in place, see diff_gaussian_rasterization.split)."""
         rs = self.raster_settings
         V = rs.viewmatrices.shape[0]
         if shs is None or scales is None or rotations is None:
             raise Exception('The batched rasterizer takes SHs, scales and rotations (no precomputed colours / covariances)')
         if means2D.shape[0] != V:
             raise Exception('means2D must be [V,P,3]: one screen-space gradient sink per view')
-        return _RasterizeGaussiansBatched.apply(means3D, means2D, shs, opacities, scales, rotations, rs)
+        if shs_rest is not None and (shs.shape[1] != 1 or shs_rest.dim() != 3 or shs_rest.shape[1] not in (0, 15)):
+            raise Exception('split SH storage: shs [P,1,3] and shs_rest [P,15,3] (or [P,0,3]) expected')
+        rest = torch.Tensor([]) if (shs_rest is None or shs_rest.numel() == 0) else shs_rest
+        return _RasterizeGaussiansBatched.apply(means3D, means2D, shs, opacities, scales, rotations, rs, rest)
