@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--batched", action="store_true",
                     help="render each rank's views of a step in ONE batched call (GaussianRasterizerBatched, row f1)")
+    ap.add_argument("--no-train-step", action="store_true",
+                    help="skip the extra `train_step` object (a full iteration: activations, render, L1+D-SSIM, Adam; N=1 only)")
     ap.add_argument("--plain-autograd", action="store_true",
                     help="sum the views' gradients through autograd (.grad += per parameter) instead of in the backward kernels")
     return ap.parse_args()
@@ -408,6 +410,33 @@ def main():
             batched_extra["e2e"] = {"value": views_total / (ms_be * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
                                     "d2h_bytes_per_step": 4}
 
+    # ---- a whole training iteration (train.py:95-140) assembled from the fused pieces, next to the torch formulation over the
+    # same rasterizer (gsr_b200.train_step); one view per iteration like the reference trainer.  Extra information only.
+    train_extra = None
+    if world == 1 and not args.no_train_step and spec.D == 3:
+        from gsr_b200 import train_step
+        gen = torch.Generator().manual_seed(3)
+        gts = [torch.rand(3, spec.H, spec.W, generator=gen).to(dev) for _ in range(2)]
+        train_extra = {"what": "activations + render + L1/D-SSIM loss + backward + densification stats + Adam, one view per iteration"}
+        for key, is_fused, n_it in (("fused", True, 10), ("torch_formulation", False, 5)):
+            leaf = lambda t: t.to(dev).clone().contiguous().requires_grad_(True)
+            model = {"xyz": leaf(scene["means3D"]), "features_dc": leaf(scene["shs"][:, :1]), "features_rest": leaf(scene["shs"][:, 1:]),
+                     "scaling": leaf(torch.log(scene["scales"])), "rotation": leaf(scene["rotations"]),
+                     "opacity": leaf(torch.logit(scene["opacities"].clamp(1e-4, 1 - 1e-4)))}
+            st = train_step.new_stats(P, dev)
+            opt = train_step.make_optimizer(model, is_fused)
+            fn = train_step.fused_step if is_fused else train_step.reference_step
+            for k in range(3):
+                fn(model, st, opt, cams[k % V], bg, gts[k % 2], spec.D)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(); e0.record()
+            for k in range(n_it):
+                fn(model, st, opt, cams[(3 + k) % V], bg, gts[k % 2], spec.D)
+            e1.record(); torch.cuda.synchronize()
+            train_extra[key + "_ms_per_iteration"] = e0.elapsed_time(e1) / n_it
+            del model, st, opt
+            torch.cuda.empty_cache()
+
     if rank == 0:
         peaks = {}
         try:
@@ -460,7 +489,7 @@ def main():
                            "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else "GaussianRasterizer: one call per view",
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat.nbytes() + 48 * P + 20 * R) / 1e9)},
-                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "batched": batched_extra,
+                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "batched": batched_extra, "train_step": train_extra,
                 "gpu_launches": launches,
                 "clocks": clocks}
         print(json.dumps(line), flush=True)
