@@ -205,6 +205,23 @@ def test_activation_oracle_matches_torch_golden():
         assert np.abs(a - g[k]).max() <= 1e-6 * np.abs(g[k]).max()
 
 
+def test_training_step_modules_import_without_gpu_and_refuse_cpu_tensors():
+    """row f2-f4 host modules import on a CPU-only box (the binding is loaded lazily) and never fall back to the CPU"""
+    from gsr_b200 import activations, losses, optim, ply, train_step   # noqa: F401
+    for bad in (lambda: losses.l1_loss(torch.rand(4), torch.rand(4)),
+                lambda: losses.l1_ssim_loss(torch.rand(3, 4, 4), torch.rand(3, 4, 4)),
+                lambda: losses.ssim(torch.rand(3, 4, 4), torch.rand(3, 4, 4)),
+                lambda: activations.activate(torch.zeros(2, 3), torch.zeros(2, 4), torch.zeros(2, 1)),
+                lambda: ply.save_ply("/tmp/x.ply", *(torch.zeros(1, k) for k in (3, 3, 45, 1, 3, 4)))):
+        with pytest.raises(RuntimeError):
+            bad()
+    p = torch.nn.Parameter(torch.ones(3))
+    p.grad = torch.ones(3)
+    with pytest.raises(RuntimeError):
+        optim.FusedAdam([p], lr=0.1).step()
+    assert [n for n, _ in train_step.PARAM_LR] == ["xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation"]
+
+
 # ------------------------------------------------------------------------------ the C-ABI library
 def test_cabi_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "gsr.h")).read()
