@@ -163,6 +163,22 @@ int gsr_backward(const GsrBwdArgs* args, gsr_stream_t stream);
  */
 int gsr_backward_batched(const GsrBwdArgs* args, int n_views, gsr_stream_t stream);
 
+/*
+ * Several scenes per call (many small scenes, a few views each; the reference renders
+ * one view of one scene per call, train_lgm.py:111-120).  n_scenes scenes of args->P Gaussians EACH, views_per_scene cameras
+ * per scene.  Same structs with
+ *   means3D [S,P,3], opacities [S,P], scales [S,P,3], rotations [S,P,4], shs [S,P,M,3] (or split: shs [S,P,1,3], shs_rest [S,P,M-1,3])
+ *   viewmatrix / projmatrix [S,Vs,16], cam_pos [S,Vs,3];  out_color [S,Vs,3,H,W], radii [S,Vs,P]
+ * and for the backward dL_dpix [S,Vs,3,H,W], dL_dmean2D [S,Vs,P,3], parameter gradients [S,P,...] (summed over the scene's views),
+ * accum = gsr_bwd_accum_bytes(S*Vs*P).  Preprocess and the per-Gaussian backward run once per scene, depth sort, tile split
+ * and both blending kernels ONCE over all S*Vs*P (Gaussian, view) pairs; the host is blocked once.  Every view's result is
+ * identical to a single-view call on its scene.  gsr_forward_batched(args, V) == gsr_forward_scenes(args, 1, V).
+ * Blob sizes: gsr_geom_bytes(S*Vs*P), gsr_img_bytes_batched(W, H, S*Vs).  Split SH storage needs P % 4 == 0 when S > 1.
+ */
+int gsr_forward_scenes(const GsrFwdArgs* args, int n_scenes, int views_per_scene, GsrAlloc geom, GsrAlloc binning,
+                       GsrAlloc img, gsr_stream_t stream, int* num_rendered);
+int gsr_backward_scenes(const GsrBwdArgs* args, int n_scenes, int views_per_scene, gsr_stream_t stream);
+
 /* present[i] = (view-space z of means3D[i] > 0.2).  `present` is uint8 (bool). */
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, gsr_stream_t stream);

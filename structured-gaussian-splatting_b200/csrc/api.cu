@@ -159,12 +159,15 @@ size_t gsr_bwd_accum_bytes(int P) { return (size_t)(P > 0 ? P : 1) * 12 * sizeof
 // V views of ONE Gaussian set in one pass: the views are stacked into a tall image (tile row v * gy + ty), every
 // (Gaussian, view) pair is a "virtual Gaussian" v * P + g with its own record, and depth sort, tile split and blending
 // run once over all of them.  V = 1 is the reference's single-view call.
-static int forward_impl(const GsrFwdArgs* a, int V, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream_, int* num_rendered)
+// S > 1: S scenes of P Gaussians each (parameter arrays [S][P][...]) with V / S cameras per scene: preprocess runs once per scene
+// on that scene's parameters and cameras, everything after it once over all S * (V / S) * P virtual Gaussians.
+static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream_,
+                        int* num_rendered)
 {
     cudaStream_t s = (cudaStream_t)stream_;
     if (!a || !num_rendered || !geom.fn || !binning.fn || !img.fn) return GSR_EINVAL;
     *num_rendered = 0;
-    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3 || V < 1) return GSR_EINVAL;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3 || V < 1 || S < 1 || V % S != 0) return GSR_EINVAL;
     if (!a->out_color || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
     const int gx = (a->W + GSR_TILE - 1) / GSR_TILE, gy = (a->H + GSR_TILE - 1) / GSR_TILE;
     if (gx > 65535 || (long long)gy * V > 65535 || (long long)a->P * V >= (1ll << 31)) return GSR_ETOOBIG;
@@ -193,7 +196,24 @@ static int forward_impl(const GsrFwdArgs* a, int V, GsrAlloc geom, GsrAlloc binn
 
     int rc;
     stage_begin(0, s);
-    if ((rc = launch_preprocess(*a, V, g, s))) return rc;
+    {
+        const int Vs = V / S;
+        const int Mdc = (a->shs_rest && a->M > 1) ? 1 : a->M;
+        for (int sc_i = 0; sc_i < S; sc_i++) {
+            GsrFwdArgs as = *a;
+            const size_t o = (size_t)sc_i * a->P;
+            as.means3D = a->means3D + 3 * o; as.opacities = a->opacities + o;
+            if (a->shs) as.shs = a->shs + 3 * (size_t)Mdc * o;
+            if (a->shs_rest) as.shs_rest = a->shs_rest + 3 * (size_t)(a->M - 1) * o;
+            if (a->colors_precomp) as.colors_precomp = a->colors_precomp + 3 * o;
+            if (a->scales) as.scales = a->scales + 3 * o;
+            if (a->rotations) as.rotations = a->rotations + 4 * o;
+            if (a->cov3D_precomp) as.cov3D_precomp = a->cov3D_precomp + 6 * o;
+            as.viewmatrix = a->viewmatrix + 16 * (size_t)sc_i * Vs; as.projmatrix = a->projmatrix + 16 * (size_t)sc_i * Vs;
+            if (a->cam_pos) as.cam_pos = a->cam_pos + 3 * (size_t)sc_i * Vs;
+            if ((rc = launch_preprocess(as, Vs, sc_i * Vs, V, g, s))) return rc;
+        }
+    }
     stage_end(0, s);
     GSR_STAGE(a->debug, s, "preprocess");
 
@@ -244,20 +264,28 @@ static int forward_impl(const GsrFwdArgs* a, int V, GsrAlloc geom, GsrAlloc binn
 
 int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream, int* num_rendered)
 {
-    return forward_impl(a, 1, geom, binning, img, stream, num_rendered);
+    return forward_impl(a, 1, 1, geom, binning, img, stream, num_rendered);
 }
 int gsr_forward_batched(const GsrFwdArgs* a, int n_views, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream,
                         int* num_rendered)
 {
     if (n_views > 1 && a && (a->colors_precomp || a->cov3D_precomp)) return GSR_EINVAL;   // per-view accumulation of their gradients is not wired
-    return forward_impl(a, n_views, geom, binning, img, stream, num_rendered);
+    return forward_impl(a, n_views, 1, geom, binning, img, stream, num_rendered);
+}
+int gsr_forward_scenes(const GsrFwdArgs* a, int n_scenes, int views_per_scene, GsrAlloc geom, GsrAlloc binning, GsrAlloc img,
+                       gsr_stream_t stream, int* num_rendered)
+{
+    if (n_scenes < 1 || views_per_scene < 1) return GSR_EINVAL;
+    if (a && (a->colors_precomp || a->cov3D_precomp) && (long long)n_scenes * views_per_scene > 1) return GSR_EINVAL;
+    if ((long long)n_scenes * views_per_scene > 65535) return GSR_ETOOBIG;
+    return forward_impl(a, n_scenes * views_per_scene, n_scenes, geom, binning, img, stream, num_rendered);
 }
 
-static int backward_impl(const GsrBwdArgs* a, int V, gsr_stream_t stream_)
+static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_)
 {
     cudaStream_t s = (cudaStream_t)stream_;
     if (!a) return GSR_EINVAL;
-    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->R < 0 || a->D < 0 || a->D > 3 || V < 1) return GSR_EINVAL;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->R < 0 || a->D < 0 || a->D > 3 || V < 1 || S < 1 || V % S != 0) return GSR_EINVAL;
     if (a->P == 0) return GSR_OK;
     if (!a->means3D || !a->radii || !a->dL_dpix || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
     if (!a->geom_blob || !a->binning_blob || !a->img_blob || !a->accum) return GSR_EBLOB;
@@ -289,22 +317,50 @@ static int backward_impl(const GsrBwdArgs* a, int V, gsr_stream_t stream_)
     stage_end(4, s);
     GSR_STAGE(a->debug, s, "blend_backward");
     stage_begin(5, s);
-    if (V <= GSR_MAX_VIEWS) {
-        // one launch pair over all views: the per-view contributions are summed in registers (preprocess_bwd.cu)
-        if ((rc = launch_preprocess_backward(*a, V, g, accum, s))) return rc;
-    } else {
-        for (int v = 0; v < V; v++) {
-            // view by view over its slice of the virtual Gaussians; the views after the first add to what the first wrote
-            GsrBwdArgs av = *a;
-            GeomView gv = g;
-            const size_t o = (size_t)v * a->P;
-            gv.rec = g.rec + o; gv.clamped = g.clamped + o;
-            av.radii = a->radii + o;
-            av.viewmatrix = a->viewmatrix + 16 * v; av.projmatrix = a->projmatrix + 16 * v;
-            if (a->cam_pos) av.cam_pos = a->cam_pos + 3 * v;
-            av.dL_dmean2D = a->dL_dmean2D + 3 * o;
-            if (v > 0) av.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
-            if ((rc = launch_preprocess_backward(av, 1, gv, accum + 12 * o, s))) return rc;
+    // scene by scene (S = 1 for the single-scene calls): the per-Gaussian backward of scene sc_i sees its own parameters,
+    // cameras and gradient rows and the slice of the per-view arrays that belongs to its Vs views
+    const int Vs = V / S;
+    const int Mdc = (a->shs_rest && a->M > 1) ? 1 : a->M;
+    for (int sc_i = 0; sc_i < S; sc_i++) {
+        GsrBwdArgs as = *a;
+        GeomView gs = g;
+        const size_t o = (size_t)sc_i * a->P;            // first Gaussian of the scene
+        const size_t ov = o * Vs;                          // first virtual Gaussian of the scene (= sc_i * Vs views * P)
+        as.means3D = a->means3D + 3 * o;
+        if (a->shs) { as.shs = a->shs + 3 * (size_t)Mdc * o; as.dL_dsh = a->dL_dsh + 3 * (size_t)Mdc * o; }
+        if (a->shs_rest) { as.shs_rest = a->shs_rest + 3 * (size_t)(a->M - 1) * o; if (a->dL_dsh_rest) as.dL_dsh_rest = a->dL_dsh_rest + 3 * (size_t)(a->M - 1) * o; }
+        if (a->colors_precomp) as.colors_precomp = a->colors_precomp + 3 * o;
+        if (a->scales) as.scales = a->scales + 3 * o;
+        if (a->rotations) as.rotations = a->rotations + 4 * o;
+        if (a->cov3D_precomp) as.cov3D_precomp = a->cov3D_precomp + 6 * o;
+        as.viewmatrix = a->viewmatrix + 16 * (size_t)sc_i * Vs; as.projmatrix = a->projmatrix + 16 * (size_t)sc_i * Vs;
+        if (a->cam_pos) as.cam_pos = a->cam_pos + 3 * (size_t)sc_i * Vs;
+        as.radii = a->radii + ov;
+        as.dL_dmean2D = a->dL_dmean2D + 3 * ov;
+        as.dL_dopacity = a->dL_dopacity + o; as.dL_dmean3D = a->dL_dmean3D + 3 * o;
+        if (a->dL_dcolor) as.dL_dcolor = a->dL_dcolor + 3 * o;
+        if (a->dL_dcov3D) as.dL_dcov3D = a->dL_dcov3D + 6 * o;
+        if (a->dL_dscale) as.dL_dscale = a->dL_dscale + 3 * o;
+        if (a->dL_drot) as.dL_drot = a->dL_drot + 4 * o;
+        gs.rec = g.rec + ov; gs.clamped = g.clamped + ov;
+        float* accum_s = accum + 12 * ov;
+        if (Vs <= GSR_MAX_VIEWS) {
+            // one launch pair over the scene's views: the per-view contributions are summed in registers (preprocess_bwd.cu)
+            if ((rc = launch_preprocess_backward(as, Vs, gs, accum_s, s))) return rc;
+        } else {
+            for (int v = 0; v < Vs; v++) {
+                // view by view over its slice of the virtual Gaussians; the views after the first add to what the first wrote
+                GsrBwdArgs av = as;
+                GeomView gv = gs;
+                const size_t ovv = (size_t)v * a->P;
+                gv.rec = gs.rec + ovv; gv.clamped = gs.clamped + ovv;
+                av.radii = as.radii + ovv;
+                av.viewmatrix = as.viewmatrix + 16 * v; av.projmatrix = as.projmatrix + 16 * v;
+                if (as.cam_pos) av.cam_pos = as.cam_pos + 3 * v;
+                av.dL_dmean2D = as.dL_dmean2D + 3 * ovv;
+                if (v > 0) av.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
+                if ((rc = launch_preprocess_backward(av, 1, gv, accum_s + 12 * ovv, s))) return rc;
+            }
         }
     }
     stage_end(5, s);
@@ -312,11 +368,17 @@ static int backward_impl(const GsrBwdArgs* a, int V, gsr_stream_t stream_)
     return GSR_OK;
 }
 
-int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream) { return backward_impl(a, 1, stream); }
+int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream) { return backward_impl(a, 1, 1, stream); }
 int gsr_backward_batched(const GsrBwdArgs* a, int n_views, gsr_stream_t stream)
 {
     if (n_views > 1 && a && (a->colors_precomp || a->cov3D_precomp)) return GSR_EINVAL;
-    return backward_impl(a, n_views, stream);
+    return backward_impl(a, n_views, 1, stream);
+}
+int gsr_backward_scenes(const GsrBwdArgs* a, int n_scenes, int views_per_scene, gsr_stream_t stream)
+{
+    if (n_scenes < 1 || views_per_scene < 1 || (long long)n_scenes * views_per_scene > 65535) return GSR_EINVAL;
+    if (a && (a->colors_precomp || a->cov3D_precomp) && (long long)n_scenes * views_per_scene > 1) return GSR_EINVAL;
+    return backward_impl(a, n_scenes * views_per_scene, n_scenes, stream);
 }
 
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,

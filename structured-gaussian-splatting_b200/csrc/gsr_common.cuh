@@ -150,7 +150,7 @@ __device__ __forceinline__ void load_camera(Camera& cam, const CameraArgs& ca)
 #endif
 
 // preprocess.cu
-int launch_preprocess(const GsrFwdArgs& a, int V, const GeomView& g, cudaStream_t s);
+int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, const GeomView& g, cudaStream_t s);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
 int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, const float* accum, cudaStream_t s);
 

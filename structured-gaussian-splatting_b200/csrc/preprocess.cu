@@ -172,6 +172,7 @@ struct PreArgs {
     ushort4* rect;      // [P] tile rect
     uint32_t* total;    // sum of tiles touched (R)
     int* err;          // device flag: prefiltered violated
+    int view_base;     // first view of this launch inside the batched call (scene s of a multi-scene call: s * views_per_scene)
 };
 
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraArgs ca)
@@ -179,10 +180,13 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
     __shared__ Camera cam;
     // blockIdx.y = view of a batched call (gsr_forward_batched): its camera, its slice v * P + idx of the per-view
     // outputs, its band of tile rows in the stacked image
-    const int view = blockIdx.y;
-    ca.view += 16 * view;
-    if (ca.proj) ca.proj += 16 * view;
-    if (ca.cam) ca.cam += 3 * view;
+    // (the launch's camera arrays and Gaussian parameters start at its first view / its scene; outputs are indexed by the
+    // global view a.view_base + blockIdx.y)
+    const int lview = blockIdx.y;
+    const int view = a.view_base + lview;
+    ca.view += 16 * lview;
+    if (ca.proj) ca.proj += 16 * lview;
+    if (ca.cam) ca.cam += 3 * lview;
     load_camera(cam, ca);
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P) return;
@@ -281,7 +285,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
     if (tiles && (int)(threadIdx.x & 31) == __ffs(am) - 1) atomicAdd(a.total, tiles);
 }
 
-int launch_preprocess(const GsrFwdArgs& a, int V, const GeomView& g, cudaStream_t s)
+int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, const GeomView& g, cudaStream_t s)
 {
     const CameraArgs cam = make_camera_args(a.viewmatrix, a.projmatrix, a.cam_pos, a.tan_fovx, a.tan_fovy, a.W, a.H);
     PreArgs k;
@@ -289,7 +293,8 @@ int launch_preprocess(const GsrFwdArgs& a, int V, const GeomView& g, cudaStream_
     k.means = a.means3D; k.shs = a.shs; k.shs_rest = (a.shs && a.M > 1) ? a.shs_rest : nullptr; k.colors_pre = a.colors_precomp; k.opac = a.opacities;
     k.scales = a.scales; k.rots = a.rotations; k.cov_pre = a.cov3D_precomp; k.mod = a.scale_modifier;
     k.prefiltered = a.prefiltered; k.radii = a.radii; k.rec = g.rec; k.clamped = g.clamped;
-    const GeomScratch sc = carve_geom_scratch(g.scratch, a.P * V);
+    const GeomScratch sc = carve_geom_scratch(g.scratch, a.P * V_total);
+    k.view_base = view_base;
     k.depthkey = sc.depthkey; k.rect = sc.rect; k.total = sc.counters;
     k.err = reinterpret_cast<int*>(sc.counters + 8);
     GSR_LAUNCH(preprocess_fwd_kernel, dim3(cdiv(a.P, 256), V), 256, 0, s, k, cam);

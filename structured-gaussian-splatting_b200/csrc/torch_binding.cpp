@@ -295,30 +295,44 @@ rasterize_gaussians_batched(const torch::Tensor& background, const torch::Tensor
                             const float tan_fovy, const int image_height, const int image_width, const torch::Tensor& sh,
                             const int degree, const torch::Tensor& camposs, const bool debug, const torch::Tensor& sh_rest)
 {
-    if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
+    // one scene: means3D [P,3], cameras [V,4,4] / [V,3].  Several scenes: means3D [S,P,3] (and every parameter with the
+    // leading S), cameras [S,Vs,4,4] / [S,Vs,3]; outputs get the leading S as well.
+    const bool scenes = means3D.ndimension() == 3;
+    if (!scenes && (means3D.ndimension() != 2 || means3D.size(1) != 3)) AT_ERROR("means3D must have dimensions (num_points, 3)");
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
-    TORCH_CHECK(viewmatrices.ndimension() == 3 && projmatrices.sizes() == viewmatrices.sizes() && camposs.ndimension() == 2 &&
-                    camposs.size(0) == viewmatrices.size(0),
-                "viewmatrices / projmatrices must be [V,4,4] and camposs [V,3]");
+    if (scenes) {
+        TORCH_CHECK(means3D.size(2) == 3 && viewmatrices.ndimension() == 4 && viewmatrices.size(0) == means3D.size(0) &&
+                        projmatrices.sizes() == viewmatrices.sizes() && camposs.ndimension() == 3 && camposs.size(0) == means3D.size(0) &&
+                        camposs.size(1) == viewmatrices.size(1),
+                    "scenes: means3D [S,P,3], viewmatrices / projmatrices [S,Vs,4,4], camposs [S,Vs,3]");
+    } else {
+        TORCH_CHECK(viewmatrices.ndimension() == 3 && projmatrices.sizes() == viewmatrices.sizes() && camposs.ndimension() == 2 &&
+                        camposs.size(0) == viewmatrices.size(0),
+                    "viewmatrices / projmatrices must be [V,4,4] and camposs [V,3]");
+    }
     TORCH_CHECK(sh.numel() != 0 && scales.numel() != 0 && rotations.numel() != 0, "batched rasterization takes shs, scales and rotations");
     const c10::cuda::CUDAGuard guard(means3D.device());
-    const int P = (int)means3D.size(0), V = (int)viewmatrices.size(0);
+    const int S = scenes ? (int)means3D.size(0) : 1, Vs = (int)viewmatrices.size(scenes ? 1 : 0);
+    const int P = (int)means3D.size(scenes ? 1 : 0), V = S * Vs;
+    const int shdim = scenes ? 2 : 1;                     // the coefficient dimension of sh / sh_rest
     const int H = image_height, W = image_width;
     auto f32 = means3D.options().dtype(torch::kFloat32);
     auto i32 = means3D.options().dtype(torch::kInt32);
     auto u8 = means3D.options().dtype(torch::kByte);
     torch::Tensor out_color = P == 0 ? torch::zeros({V, 3, H, W}, f32) : torch::empty({V, 3, H, W}, f32);
     torch::Tensor radii = P == 0 ? torch::zeros({V, P}, i32) : torch::empty({V, P}, i32);
+    if (scenes) { out_color = out_color.view({S, Vs, 3, H, W}); radii = radii.view({S, Vs, P}); }
     torch::Tensor geomBuffer = torch::empty({0}, u8), binningBuffer = torch::empty({0}, u8), imgBuffer = torch::empty({0}, u8);
     int rendered = 0;
     if (P != 0 && V != 0) {
         F32 bg(background), m3(means3D), op(opacity), sc(scales), rot(rotations), vm(viewmatrices), pm(projmatrices), shs(sh), cam(camposs),
             shr(sh_rest);
         GsrFwdArgs a = {};
-        a.P = P; a.D = degree; a.M = (int)sh.size(1); a.W = W; a.H = H;
+        a.P = P; a.D = degree; a.M = (int)sh.size(shdim); a.W = W; a.H = H;
         if (sh_rest.numel() != 0) {                              // split SH storage: sh = features_dc, sh_rest = features_rest
-            TORCH_CHECK(sh.size(1) == 1 && sh_rest.dim() == 3 && sh_rest.size(0) == P, "split SH: sh [P,1,3] and sh_rest [P,K,3] expected");
-            a.M = 1 + (int)sh_rest.size(1);
+            TORCH_CHECK(sh.size(shdim) == 1 && sh_rest.dim() == shdim + 2 && sh_rest.size(shdim - 1) == P,
+                        "split SH: sh [P,1,3] and sh_rest [P,K,3] expected");
+            a.M = 1 + (int)sh_rest.size(shdim);
             a.shs_rest = shr.ptr();
         }
         a.background = bg.ptr(); a.means3D = m3.ptr(); a.shs = shs.ptr(); a.opacities = op.ptr();
@@ -326,8 +340,8 @@ rasterize_gaussians_batched(const torch::Tensor& background, const torch::Tensor
         a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
         a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.prefiltered = 0; a.debug = debug;
         a.out_color = out_color.data_ptr<float>(); a.radii = radii.data_ptr<int>();
-        check(gsr_forward_batched(&a, V, GsrAlloc{resize_cb, &geomBuffer}, GsrAlloc{resize_cb, &binningBuffer},
-                                  GsrAlloc{resize_cb, &imgBuffer}, current_stream(), &rendered),
+        check(gsr_forward_scenes(&a, S, Vs, GsrAlloc{resize_cb, &geomBuffer}, GsrAlloc{resize_cb, &binningBuffer},
+                                 GsrAlloc{resize_cb, &imgBuffer}, current_stream(), &rendered),
               "rasterize_gaussians_batched");
     }
     return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer);
@@ -349,14 +363,18 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
     // non-empty `into_*` (all five or none): the summed gradients are written (or, with `accumulate`, added) straight into
     // these buffers - the parameters' .grad - and the corresponding returned tensors are empty
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
-    TORCH_CHECK(dL_dout_color.ndimension() == 4, "dL_dout_color must be [V,3,H,W]");
+    const bool scenes = means3D.ndimension() == 3;
+    TORCH_CHECK(dL_dout_color.ndimension() == (scenes ? 5 : 4), "dL_dout_color must be [V,3,H,W] ([S,Vs,3,H,W] with scenes)");
     const c10::cuda::CUDAGuard guard(means3D.device());
-    const int P = (int)means3D.size(0), V = (int)dL_dout_color.size(0);
-    const int H = (int)dL_dout_color.size(2), W = (int)dL_dout_color.size(3);
+    const int S = scenes ? (int)means3D.size(0) : 1, Vs = (int)dL_dout_color.size(scenes ? 1 : 0);
+    const int P = (int)means3D.size(scenes ? 1 : 0), V = S * Vs;
+    const int H = (int)dL_dout_color.size(scenes ? 3 : 2), W = (int)dL_dout_color.size(scenes ? 4 : 3);
+    const int shdim = scenes ? 2 : 1;
     const bool split = sh_rest.numel() != 0;
-    const int Mdc = (int)sh.size(1);
-    const int M = split ? 1 + (int)sh_rest.size(1) : Mdc;
-    TORCH_CHECK(!split || (Mdc == 1 && sh_rest.dim() == 3 && sh_rest.size(0) == P), "split SH: sh [P,1,3] and sh_rest [P,K,3] expected");
+    const int Mdc = (int)sh.size(shdim);
+    const int M = split ? 1 + (int)sh_rest.size(shdim) : Mdc;
+    TORCH_CHECK(!split || (Mdc == 1 && sh_rest.dim() == shdim + 2 && sh_rest.size(shdim - 1) == P),
+                "split SH: sh [P,1,3] and sh_rest [P,K,3] expected");
     auto f32 = means3D.options().dtype(torch::kFloat32);
     const bool live = P != 0 && V != 0;
     auto alloc = [&](std::initializer_list<int64_t> shape) { return live ? torch::empty(shape, f32) : torch::zeros(shape, f32); };
@@ -365,16 +383,17 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
         auto ok = [&](const torch::Tensor& t, int64_t n) {
             return t.is_cuda() && t.scalar_type() == torch::kFloat32 && t.is_contiguous() && t.numel() == n;
         };
-        TORCH_CHECK(ok(into_means3D, (int64_t)P * 3) && ok(into_opacity, P) && ok(into_sh, (int64_t)P * Mdc * 3) &&
-                        ok(into_scales, (int64_t)P * 3) && ok(into_rotations, (int64_t)P * 4) &&
-                        (!split || ok(into_sh_rest, (int64_t)P * (M - 1) * 3)),
+        const int64_t SP = (int64_t)S * P;
+        TORCH_CHECK(ok(into_means3D, SP * 3) && ok(into_opacity, SP) && ok(into_sh, SP * Mdc * 3) &&
+                        ok(into_scales, SP * 3) && ok(into_rotations, SP * 4) && (!split || ok(into_sh_rest, SP * (M - 1) * 3)),
                     "gradient targets must be contiguous fp32 CUDA tensors with the gradients' element counts");
     }
     auto none = [&]() { return torch::empty({0}, f32); };
     torch::Tensor dL_dmeans2D = alloc({V, P, 3});
-    torch::Tensor dL_dopacity = into ? none() : alloc({P, 1}), dL_dmeans3D = into ? none() : alloc({P, 3}),
-                  dL_dsh = into ? none() : alloc({P, Mdc, 3}), dL_dscales = into ? none() : alloc({P, 3}),
-                  dL_drotations = into ? none() : alloc({P, 4}), dL_dsh_rest = (split && !into) ? alloc({P, M - 1, 3}) : none();
+    const int64_t SPn = (int64_t)S * P;                    // gradients are allocated flat over the scenes and reshaped at the end
+    torch::Tensor dL_dopacity = into ? none() : alloc({SPn, 1}), dL_dmeans3D = into ? none() : alloc({SPn, 3}),
+                  dL_dsh = into ? none() : alloc({SPn, Mdc, 3}), dL_dscales = into ? none() : alloc({SPn, 3}),
+                  dL_drotations = into ? none() : alloc({SPn, 4}), dL_dsh_rest = (split && !into) ? alloc({SPn, M - 1, 3}) : none();
     if (live) {
         torch::Tensor accum = torch::empty({(long long)(gsr_bwd_accum_bytes(P * V) / sizeof(float))}, f32);
         F32 bg(background), m3(means3D), sc(scales), rot(rotations), vm(viewmatrices), pm(projmatrices), shs(sh), cam(camposs),
@@ -399,7 +418,15 @@ rasterize_gaussians_batched_backward(const torch::Tensor& background, const torc
         a.dL_drot = (into ? into_rotations : dL_drotations).data_ptr<float>();
         a.debug = debug;
         if (into && accumulate) a.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
-        check(gsr_backward_batched(&a, V, current_stream()), "rasterize_gaussians_batched_backward");
+        check(gsr_backward_scenes(&a, S, Vs, current_stream()), "rasterize_gaussians_batched_backward");
+    }
+    if (scenes) {
+        dL_dmeans2D = dL_dmeans2D.view({S, Vs, P, 3});
+        if (!into) {
+            dL_dopacity = dL_dopacity.view({S, P, 1}); dL_dmeans3D = dL_dmeans3D.view({S, P, 3}); dL_dsh = dL_dsh.view({S, P, Mdc, 3});
+            dL_dscales = dL_dscales.view({S, P, 3}); dL_drotations = dL_drotations.view({S, P, 4});
+            if (split) dL_dsh_rest = dL_dsh_rest.view({S, P, M - 1, 3});
+        }
     }
     return std::make_tuple(dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_dsh, dL_dscales, dL_drotations, dL_dsh_rest);
 }

@@ -10,6 +10,12 @@ wait instead of V.  Every view's image, radii and gradients equal what V single-
     colors[V,3,H,W], radii[V,P] = GaussianRasterizerBatched(settings)(means3D, means2D[V,P,3], opacities, shs, scales, rotations)
 
 Parameter gradients come back summed over the views; `means2D.grad` stays per view (densification statistics).
+
+Several scenes per call (config C4: many small scenes, a few views each): give every parameter a leading scene dimension
+(means3D [S,P,3], opacities [S,P,1], shs [S,P,M,3], scales [S,P,3], rotations [S,P,4], means2D [S,Vs,P,3]) and the cameras as
+viewmatrices / projmatrices [S,Vs,4,4], camposs [S,Vs,3]: colors come back as [S,Vs,3,H,W], radii as [S,Vs,P], each scene's
+gradients summed over its own views.  Preprocess and the per-Gaussian backward run once per scene, everything in between
+once over all scenes (gsr_forward_scenes / gsr_backward_scenes).
 """
 from typing import NamedTuple
 
@@ -82,9 +88,15 @@ class GaussianRasterizerBatched(nn.Module):
         V = rs.viewmatrices.shape[0]
         if shs is None or scales is None or rotations is None:
             raise Exception('The batched rasterizer takes SHs, scales and rotations (no precomputed colours / covariances)')
-        if means2D.shape[0] != V:
+        if means3D.dim() == 3:
+            # several scenes per call: every parameter carries a leading scene dimension S, the cameras are [S,Vs,...]
+            if rs.viewmatrices.dim() != 4 or rs.viewmatrices.shape[0] != means3D.shape[0]:
+                raise Exception('scenes: means3D [S,P,3] needs viewmatrices / projmatrices [S,Vs,4,4] and camposs [S,Vs,3]')
+            if tuple(means2D.shape[:3]) != (means3D.shape[0], rs.viewmatrices.shape[1], means3D.shape[1]):
+                raise Exception('scenes: means2D must be [S,Vs,P,3]')
+        elif means2D.shape[0] != V:
             raise Exception('means2D must be [V,P,3]: one screen-space gradient sink per view')
-        if shs_rest is not None and (shs.shape[1] != 1 or shs_rest.dim() != 3 or shs_rest.shape[1] not in (0, 15)):
+        if shs_rest is not None and (shs.shape[-2] != 1 or shs_rest.dim() != shs.dim() or shs_rest.shape[-2] not in (0, 15)):
             raise Exception('split SH storage: shs [P,1,3] and shs_rest [P,15,3] (or [P,0,3]) expected')
         rest = torch.Tensor([]) if (shs_rest is None or shs_rest.numel() == 0) else shs_rest
         return _RasterizeGaussiansBatched.apply(means3D, means2D, shs, opacities, scales, rotations, rs, rest)
