@@ -1,6 +1,6 @@
 """Config C4 (BASELINE.json: latent Gaussian model, train_lgm.py): S small scenes x V views at 512x512, forward+backward.
 Three arms on the same GPU: the single-view drop-in API (one call per view, as train_lgm.py:111-120 does), the batched
-entry point (one call per scene, row f1) and - when oracle/_ref was built - the unmodified reference extension.
+entry point (one call per scene, row f1), all scenes in one call (gsr_forward_scenes) and - when oracle/_ref was built - the unmodified reference extension.
 Prints one JSON line.  usage: python scripts/bench_c4.py [--scenes 8] [--iters 5]"""
 import argparse, json, os, sys
 import torch
@@ -41,6 +41,24 @@ def batched():
         color.backward(go_b)
 
 
+# all scenes in ONE call (gsr_forward_scenes): parameters stacked [S,P,...], the same V cameras for every scene
+stacked = {k: torch.stack([p[k].detach() for p in scenes]).requires_grad_(True) for k in scenes[0]}
+S_ = args.scenes
+vm_s = vm.unsqueeze(0).expand(S_, -1, -1, -1).contiguous(); pm_s = pm.unsqueeze(0).expand(S_, -1, -1, -1).contiguous()
+cp_s = cp.unsqueeze(0).expand(S_, -1, -1).contiguous()
+go_s = go_b.unsqueeze(0).expand(S_, -1, -1, -1, -1).contiguous()
+
+
+def scenes_call():
+    rs = BatchedRasterizationSettings(spec.H, spec.W, cams[0].tanfovx, cams[0].tanfovy, bg, 1.0, vm_s, pm_s, spec.D, cp_s, False)
+    m2d = torch.zeros(S_, V, spec.P, 3, device=dev, requires_grad=True)
+    color, _ = GaussianRasterizerBatched(rs)(stacked["means3D"], m2d, stacked["opacities"], stacked["shs"], stacked["scales"],
+                                             stacked["rotations"])
+    color.backward(go_s)
+    for t in stacked.values():
+        t.grad = None
+
+
 def timeit(fn):
     for _ in range(2):
         fn()
@@ -59,6 +77,7 @@ def timeit(fn):
 out = {"config": "C4: %d scenes x %d views, P=%d SH%d, %dx%d, fwd+bwd" % (args.scenes, V, spec.P, spec.D, spec.W, spec.H), "unit": "views/s"}
 out["single_view_api"] = timeit(lambda: single(dgr))
 out["batched_api"] = timeit(batched)
+out["scenes_per_call_api"] = timeit(scenes_call)
 # raw extension calls (no autograd wrapper) for an apples-to-apples comparison with the unmodified reference extension
 raw_scenes = [{k: v.detach() for k, v in p.items()} for p in scenes]
 cams_host = cams
