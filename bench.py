@@ -466,7 +466,29 @@ def main():
         roofline = {"kernel": dom, "bound": "hbm", "achieved": stages[dom]["GBps"], "peak": peak, "peak_source": peak_src,
                     "unit": "GB/s", "frac": stages[dom]["frac_hbm"], "traffic": traffic,
                     "note": "blending stages are FP32/MUFU/atomic bound (no dense contraction, no tensor cores); "
-                            "the HBM fraction is reported as the contract asks, per-stage figures in `stages`"}
+                            "the HBM fraction is reported as the contract asks, per-stage figures in `stages`, the FP32 "
+                            "roofline of SURVEY 8(d) in `compute`"}
+        try:
+            # 16 FP32 flop per required forward pair, 60 per contributing backward pair, against
+            # SMs * 128 lanes * 2 * clock; issue-slot utilisation from the committed ncu captures
+            pairs_f, pairs_b, lanes_eval = probe_pairs(C, params, cams[my_views(0)[0]], bg, spec.D)
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            mhz = (clocks or {}).get("sm_mhz") or 1965
+            fp32_peak = sms * 128 * 2 * mhz * 1e6
+            comp = {"fp32_peak_tflops": round(fp32_peak / 1e12, 1), "pairs_f": pairs_f, "pairs_b": pairs_b,
+                    "lanes_evaluated_fwd": lanes_eval,
+                    "model": "16 flop per (pixel, entry) pair up to the last contributor (fwd), 60 per blended pair (bwd)"}
+            for name, pairs, fl in (("blend_forward", pairs_f, 16), ("blend_backward", pairs_b, 60)):
+                if name in stages:
+                    tf = pairs * fl / (stages[name]["ms"] * 1e-3)
+                    comp[name] = {"tflops": round(tf / 1e12, 2), "frac_fp32": round(tf / fp32_peak, 4)}
+            try:
+                comp["issue_active_pct"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("issue_active_pct")
+            except Exception:
+                pass
+            roofline["compute"] = comp
+        except Exception as ex:                      # the probe is extra information: never fail the bench line over it
+            roofline["compute"] = {"unavailable": str(ex)[:200]}
         cpu_baseline = None
         if world == 1 and not args.no_cpu_baseline:
             import oracle
@@ -507,6 +529,31 @@ def probe_R(C, params, cam, bg, D):
                                     cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, params["shs"], D,
                                     cam.campos, False, False)
     return int(out[0])
+
+
+def probe_pairs(C, params, cam, bg, D):
+    """(pairs_f, pairs_b) of one view, untimed: SURVEY 8(d)'s units of the blending kernels' FP32 roofline.
+    pairs_f = sum over pixels of the list entries up to the pixel's last contributor (from n_contrib);
+    pairs_b = (pixel, entry) pairs that were actually blended (counted by the debug statistics kernel)."""
+    import ctypes
+    import torch
+    e = torch.Tensor([])
+    lib = ctypes.CDLL(os.path.join(ROOT, "structured-gaussian-splatting_b200", "gsr_b200", "libgsr_b200.so"))
+    os.environ["GSR_BLEND_STATS"] = "1"
+    try:
+        lib.gsr_debug_blend_stats(None, 1)
+        with torch.no_grad():
+            out = C.rasterize_gaussians(bg, params["means3D"], e, params["opacities"], params["scales"], params["rotations"], 1.0, e,
+                                        cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, params["shs"], D,
+                                        cam.campos, False, False)
+        torch.cuda.synchronize()
+    finally:
+        os.environ["GSR_BLEND_STATS"] = "0"
+    st = (ctypes.c_ulonglong * 16)()
+    lib.gsr_debug_blend_stats(st, 1)
+    R, _color, _radii, geom, binning, img = out
+    ncontrib = C.export_binning(geom, binning, img, int(params["means3D"].shape[0]), int(R), cam.W, cam.H)[3]
+    return int(ncontrib.to(torch.int64).sum()), int(st[5]), int(st[2])
 
 
 if __name__ == "__main__":
