@@ -387,7 +387,7 @@ def main():
     # ---- e2e timing
     e2e = None
     if not args.no_e2e:
-        for i in range(min(2, args.warmup)):
+        for i in range(max(3, args.warmup)):      # untimed: allocator, pinned buffers and NCCL settle
             step_e2e(i)
         ms_e2e = timed(step_e2e, args.steps, args.warmup)
         e2e = {"value": views_total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
@@ -404,7 +404,7 @@ def main():
         batched_extra = {"api": "GaussianRasterizerBatched (gsr_forward_batched): one call per rank and step",
                          "value": views_total / (ms_b * 1e-3), "unit": UNIT, "ms_per_view": ms_b / args.steps / vps}
         if not args.no_e2e:
-            for i in range(min(2, args.warmup)):
+            for i in range(max(3, args.warmup)):      # untimed: allocator, pinned buffers and NCCL settle
                 step_e2e_batched(i)
             ms_be = timed(step_e2e_batched, args.steps, args.warmup)
             batched_extra["e2e"] = {"value": views_total / (ms_be * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
