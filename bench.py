@@ -40,7 +40,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--views-per-step", type=int, default=4)
+    ap.add_argument("--views-per-step", type=int, default=8,
+                    help="views each rank renders per step (BASELINE config C5: 64 views per step on 8 GPUs = 8 per GPU)")
     ap.add_argument("--config", default="C3")
     ap.add_argument("--gaussians", type=int, default=0, help="override P (debug only; makes the number invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
