@@ -137,11 +137,11 @@ size_t gsr_geom_bytes(int P) { return geom_fixed_bytes(P) + geom_scratch_bytes(P
 size_t gsr_img_bytes_batched(int W, int H, int n_views)
 {
     const size_t V = n_views > 0 ? n_views : 1;
-    const size_t gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (size_t)((H + GSR_TILE - 1) / GSR_TILE) * V;
+    const size_t gx = (W + GSR_TILE - 1) / GSR_TILE, gy1 = (size_t)((H + GSR_TILE - 1) / GSR_TILE), gy = gy1 * V;
     const size_t tiles = gx * gy;
     const size_t N = (size_t)W * H * V;
     return sizeof(BlobHeader) + align_up((tiles ? tiles : 1) * sizeof(uint2)) + 2 * align_up((N ? N : 1) * 4) +
-           align_up((gx + 1) * (gy + 1) * sizeof(int));
+           align_up((gx + 1) * (gy1 + 1) * V * sizeof(int));         // the difference array has one band per view
 }
 size_t gsr_img_bytes(int W, int H) { return gsr_img_bytes_batched(W, H, 1); }
 size_t gsr_binning_bytes(int P, int R, int W, int H)
@@ -170,7 +170,7 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3 || V < 1 || S < 1 || V % S != 0) return GSR_EINVAL;
     if (!a->out_color || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
     const int gx = (a->W + GSR_TILE - 1) / GSR_TILE, gy = (a->H + GSR_TILE - 1) / GSR_TILE;
-    if (gx > 65535 || (long long)gy * V > 65535 || (long long)a->P * V >= (1ll << 31)) return GSR_ETOOBIG;
+    if (gx > 65535 || (long long)gy * V > 65535 || (long long)a->P * V >= (1ll << 31) || V > 4095) return GSR_ETOOBIG;
     const int Pv = a->P * V;                    // virtual Gaussians
     const int gyT = gy * V, HT = gyT * GSR_TILE; // the tall image in whole tiles
     if (a->P == 0) {
@@ -192,7 +192,7 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     GSR_CUDA(cudaMemsetAsync(g.hdr, 0, sizeof(BlobHeader), s));
     const GeomScratch sc = carve_geom_scratch(g.scratch, Pv);
     GSR_CUDA(cudaMemsetAsync(sc.ctl, 0, sc.ctl_words * 4, s));       // counters, histograms, look-back words
-    GSR_CUDA(cudaMemsetAsync(im.tile_diff, 0, sizeof(int) * (size_t)(gx + 1) * (gyT + 1), s));
+    GSR_CUDA(cudaMemsetAsync(im.tile_diff, 0, sizeof(int) * (size_t)(gx + 1) * (gy + 1) * V, s));
 
     int rc;
     stage_begin(0, s);
@@ -227,7 +227,17 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     GSR_CUDA(cudaEventRecord(g_R_event, s));
 
     stage_begin(1, s);
-    if ((rc = launch_depth_order(Pv, a->W, HT, g, im, s))) return rc;
+    {
+        // views never share a tile, so the depth order is only needed inside a view: sort runs of whole views that fit the L2
+        // (about 12 M items) instead of all V * P items at once
+        int seg = 0;
+        if (V > 1 && (a->P & 3) == 0) {
+            const long long per = (long long)env_int("GSR_DEPTH_SEG_ITEMS", 12500000) / a->P;     // 0 items = one view per run
+            const long long views_per_seg = per < 1 ? 1 : per;
+            if (views_per_seg < V) seg = (int)(views_per_seg * a->P);
+        }
+        if ((rc = launch_depth_order(Pv, a->W, HT, g, im, s, seg, V))) return rc;
+    }
     stage_end(1, s);
     GSR_STAGE(a->debug, s, "depth_order");
 

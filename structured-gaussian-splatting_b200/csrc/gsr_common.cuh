@@ -86,7 +86,7 @@ struct ImgView {
     uint2*      ranges;        // [tiles]
     float*      final_T;       // [W*H]
     uint32_t*   n_contrib;     // [W*H]
-    int*        tile_diff;     // [(gy+1)*(gx+1)] 2-D difference array of the tile rects (zeroed before preprocess), only live inside forward
+    int*        tile_diff;     // [V][(gy+1)*(gx+1)] 2-D difference array of the tile rects, one band per view (zeroed before preprocess), only live inside forward
 };
 
 // layout of GeomView::scratch (sort.cu).  The control block [ctl, ctl + ctl_words) must be zero before preprocess runs.
@@ -96,6 +96,7 @@ struct GeomScratch {
     uint32_t* counters;        // [64]: 0 = R (sum of tiles touched, accumulated by preprocess), 1 = emit ticket, 8 = prefiltered-violated flag
     uint32_t* tile_hist;       // [4][256] digit histograms of the tile-split passes (counted by emit_instances_kernel)
     unsigned long long* emit_status;   // [ceil(P/256)] look-back words of the fused tile-count scan
+    uint32_t* view_status;     // tile_prefix_kernel: ticket + one look-back word per view of a batched call
     uint32_t* radix_ctl;       // digit histograms, tickets and look-back words of the four depth passes
     uint32_t* depthkey;        // [P] float bits of the view-space depth, 0xFFFFFFFF for culled Gaussians (written by preprocess)
     ushort4*  rect;            // [P] tile rect (x0, y0, x1, y1) of every Gaussian, all zero when culled (written by preprocess)
@@ -156,7 +157,7 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
 
 // sort.cu
 // sorts Gaussian ids by depth bits (stable) into g.order; counts instances per tile -> tile ranges, split-pass histograms
-int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im, cudaStream_t s);
+int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im, cudaStream_t s, int seg_items = 0, int V = 1);
 // emits instances in depth order, splits them stably by tile id, writes vals + tile ranges
 int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
 // comparison arm only (bench / tests): the reference's formulation, cub::DeviceRadixSort on 64-bit keys
@@ -167,7 +168,7 @@ size_t cub_sort_scratch_bytes(long long R);
 // words of control state, zeroed by the call unless ctl_zeroed
 size_t radix_ctl_words(uint32_t n);
 int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n,
-                          uint32_t* ctl, bool ctl_zeroed, cudaStream_t s);
+                          uint32_t* ctl, bool ctl_zeroed, cudaStream_t s, uint32_t val_base = 0);   // values = val_base + index
 
 // blend.cu
 size_t blend_plane_words(long long R, int W, int H);
