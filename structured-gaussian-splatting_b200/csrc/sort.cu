@@ -433,8 +433,7 @@ __global__ void __launch_bounds__(1024) tile_prefix_kernel(int gx, int gyv, int*
 }
 
 // seg_items > 0: the P items are seg_items-sized runs (whole views of a batched call) that never share a tile, so each
-// run is sorted on its own - the ping-pong buffers of a 12 M-item run stay in the 126 MB L2, those of 24 M items do not
-// (measured: 0.137 ms per view for one 12 M sort, 0.28 ms per view for one 24 M sort).
+// run may be sorted on its own (comparison arm, GSR_DEPTH_SEG_ITEMS; one sort over everything measured as fast or faster).
 int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im, cudaStream_t s, int seg_items, int V)
 {
     // P virtual Gaussians = V views x P / V; H = the stacked image height (V x whole tiles)
@@ -447,6 +446,22 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
     const TileDigits td = tile_digits((uint32_t)(gx * gy));
     // instances per tile (depends on preprocess only): ranges + histograms of the tile split
     const int cblocks = max(1, min(cdiv(Pper, 4096), max(1, 296 / V)));
+    // The two tile kernels depend on preprocess only and the radix passes do not need them: they run on a side stream next to
+    // the depth sort (both are small latency-bound launches) and are joined before this function returns.
+    static cudaStream_t side = nullptr;
+    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    const bool forked = env_int("GSR_SIDE_STREAM", 1) != 0;
+    cudaStream_t main_s = s;
+    if (forked) {
+        if (!side) {
+            GSR_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+            GSR_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+            GSR_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+        }
+        GSR_CUDA(cudaEventRecord(ev_fork, main_s));
+        GSR_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        s = side;
+    }
     if (smem <= 160 * 1024) {
         if (smem > 40 * 1024) {
             GSR_CUDA(cudaFuncSetAttribute(tile_count_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -459,18 +474,25 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
                    im.tile_diff);
         GSR_LAUNCH(tile_prefix_kernel<false>, V, 1024, 0, s, gx, gyv, im.tile_diff, im.ranges, sc.tile_hist, td, sc.view_status);
     }
-    // depth keys were written by preprocess; the control block was zeroed before it
-    if (seg_items <= 0 || seg_items >= P || (seg_items & 3) != 0 || cdiv(P, seg_items) > DEPTH_MAX_SEGMENTS)
-        return radix_sort_by_key_u32(sc.depthkey, sc.K0, sc.K1, sc.V0, g.order, (uint32_t)P, sc.radix_ctl, true, s, 0);
-    uint32_t* ctl = sc.radix_ctl;
-    for (int off = 0; off < P; off += seg_items) {
-        const int n = min(seg_items, P - off);
-        int rc = radix_sort_by_key_u32(sc.depthkey + off, sc.K0 + off, sc.K1 + off, sc.V0 + off, g.order + off, (uint32_t)n, ctl, true, s,
-                                       (uint32_t)off);
-        if (rc) return rc;
-        ctl += radix_ctl_words((uint32_t)n);
+    if (forked) {
+        GSR_CUDA(cudaEventRecord(ev_join, side));
+        s = main_s;
     }
-    return GSR_OK;
+    // depth keys were written by preprocess; the control block was zeroed before it
+    int rc = GSR_OK;
+    if (seg_items <= 0 || seg_items >= P || (seg_items & 3) != 0 || cdiv(P, seg_items) > DEPTH_MAX_SEGMENTS) {
+        rc = radix_sort_by_key_u32(sc.depthkey, sc.K0, sc.K1, sc.V0, g.order, (uint32_t)P, sc.radix_ctl, true, s, 0);
+    } else {
+        uint32_t* ctl = sc.radix_ctl;
+        for (int off = 0; off < P && rc == GSR_OK; off += seg_items) {
+            const int n = min(seg_items, P - off);
+            rc = radix_sort_by_key_u32(sc.depthkey + off, sc.K0 + off, sc.K1 + off, sc.V0 + off, g.order + off, (uint32_t)n, ctl, true, s,
+                                       (uint32_t)off);
+            ctl += radix_ctl_words((uint32_t)n);
+        }
+    }
+    if (forked) GSR_CUDA(cudaStreamWaitEvent(main_s, ev_join, 0));      // join even when a launch failed
+    return rc;
 }
 
 // ------------------------------------------------------------------ instance emission (in depth order)
