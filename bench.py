@@ -274,6 +274,12 @@ def main():
                 stats["views"] += 1
         flat.all_reduce()
 
+    def step_device_streams(step):
+        # same step through gsr_b200.dp.backward_views with the views alternating over two CUDA streams (two views in flight)
+        dp.backward_views(dgr, params, flat, cams, bg, spec.D, lambda color, k: (color * go).sum(), my_views(step), fused=True,
+                          n_streams=2)
+        flat.all_reduce()
+
     # e2e: host buffers in, host scalar out.  Per view: camera + ground-truth image copied from pinned host memory
     # (on a copy stream, one view ahead of the rendering, as a trainer's data loader does), forward, fused L1 loss
     # (gsr_b200.losses) against it, backward; the step's summed loss is read back to the host once per step (train.py:91-106).
@@ -411,6 +417,15 @@ def main():
             batched_extra["e2e"] = {"value": views_total / (ms_be * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
                                     "d2h_bytes_per_step": 4}
 
+    # ---- the same step with two views in flight (two CUDA streams through the drop-in API), reported next to the headline
+    streams_extra = None
+    if not args.batched and fused and vps > 1:
+        for i in range(args.warmup):
+            step_device_streams(i)
+        ms_s = timed(step_device_streams, args.steps, args.warmup)
+        streams_extra = {"api": "GaussianRasterizer from two CUDA streams (gsr_b200.dp.backward_views(n_streams=2))",
+                         "value": views_total / (ms_s * 1e-3), "unit": UNIT, "ms_per_view": ms_s / args.steps / vps}
+
     # ---- a whole training iteration (train.py:95-140) assembled from the fused pieces, next to the torch formulation over the
     # same rasterizer (gsr_b200.train_step); one view per iteration like the reference trainer.  Extra information only.
     train_extra = None
@@ -512,7 +527,7 @@ def main():
                            "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else "GaussianRasterizer: one call per view",
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat.nbytes() + 48 * P + 20 * R) / 1e9)},
-                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "batched": batched_extra, "train_step": train_extra,
+                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "batched": batched_extra, "two_streams": streams_extra, "train_step": train_extra,
                 "gpu_launches": launches,
                 "clocks": clocks}
         print(json.dumps(line), flush=True)

@@ -328,6 +328,12 @@ static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_
     stage_end(4, s);
     GSR_STAGE(a->debug, s, "blend_backward");
     stage_begin(5, s);
+    // Gradient fence: the per-Gaussian kernels read-modify-write the caller's gradient buffers when they accumulate.  Calls
+    // issued from different streams (a trainer keeping two views in flight, gsr_b200.dp.backward_views(n_streams=2)) are
+    // ordered here, in host call order, through one event: everything before this point (blending) still overlaps.
+    static cudaEvent_t g_grad_fence = nullptr;
+    if (!g_grad_fence) GSR_CUDA(cudaEventCreateWithFlags(&g_grad_fence, cudaEventDisableTiming));
+    else GSR_CUDA(cudaStreamWaitEvent(s, g_grad_fence, 0));
     // scene by scene (S = 1 for the single-scene calls): the per-Gaussian backward of scene sc_i sees its own parameters,
     // cameras and gradient rows and the slice of the per-view arrays that belongs to its Vs views
     const int Vs = V / S;
@@ -374,6 +380,7 @@ static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_
             }
         }
     }
+    GSR_CUDA(cudaEventRecord(g_grad_fence, s));
     stage_end(5, s);
     GSR_STAGE(a->debug, s, "preprocess_backward");
     return GSR_OK;

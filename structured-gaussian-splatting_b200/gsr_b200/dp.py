@@ -78,17 +78,51 @@ def render_view(rasterizer_mod, params, cam, bg, sh_degree: int, scale_modifier:
     return color, radii, means2D
 
 
+_STREAMS: List["torch.cuda.Stream"] = []
+
+
+def _side_streams(n: int):
+    while len(_STREAMS) < n:
+        _STREAMS.append(torch.cuda.Stream())
+    return _STREAMS[:n]
+
+
 def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
-                   loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], fused: bool = True):
+                   loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], fused: bool = True,
+                   n_streams: int = 1):
     """Renders the given views and back-propagates `loss_fn(color, view_id)` of each into the flat buffer.
     fused=True: the backward kernels write the first view's gradients straight into the buffer and ADD the following
     views' (diff_gaussian_rasterization.set_grad_mode) - no zero-fill, no per-view elementwise adds.
-    fused=False: plain autograd accumulation into the zeroed buffer (what the reference API alone offers)."""
+    fused=False: plain autograd accumulation into the zeroed buffer (what the reference API alone offers).
+    n_streams > 1 (fused only): consecutive views alternate over that many CUDA streams, so the latency-bound sort stages
+    and the HBM-bound per-Gaussian kernels of one view run next to the issue-bound blending kernels of another; the
+    gradient accumulation stays ordered (the core fences its read-modify-write kernels in call order)."""
     total = None
     views = list(view_ids)
     if not views or not fused or not hasattr(rasterizer_mod, "set_grad_mode"):
         flat.zero_()
         fused = False
+    if fused and n_streams > 1 and len(views) > 1 and params[flat.names[0]].is_cuda:
+        cur = torch.cuda.current_stream()
+        streams = _side_streams(n_streams)
+        for st in streams:
+            st.wait_stream(cur)
+        losses = []
+        for i, k in enumerate(views):
+            with torch.cuda.stream(streams[i % n_streams]):
+                prev = rasterizer_mod.set_grad_mode("overwrite" if i == 0 else "accumulate")
+                try:
+                    color, _radii, _m2d = render_view(rasterizer_mod, params, cams[k], bg, sh_degree)
+                    loss = loss_fn(color, k)
+                    loss.backward()
+                finally:
+                    rasterizer_mod.set_grad_mode(prev)
+                losses.append(loss.detach())
+        for st in streams:
+            cur.wait_stream(st)
+        for l in losses:
+            l.record_stream(cur)
+        return torch.stack(losses).sum()
     for i, k in enumerate(views):
         prev = rasterizer_mod.set_grad_mode(("overwrite" if i == 0 else "accumulate")) if fused else None
         try:
@@ -103,9 +137,10 @@ def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
 
 
 def dp_step(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
-            loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None, fused: bool = True):
+            loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None, fused: bool = True,
+            n_streams: int = 1):
     """Renders this rank's views, back-propagates `loss_fn(color, view_id)` for each into the flat
     buffer, then all-reduces it.  Returns the summed local loss (a device scalar)."""
-    total = backward_views(rasterizer_mod, params, flat, cams, bg, sh_degree, loss_fn, view_ids, fused)
+    total = backward_views(rasterizer_mod, params, flat, cams, bg, sh_degree, loss_fn, view_ids, fused, n_streams)
     flat.all_reduce(group)
     return total
