@@ -44,6 +44,14 @@ struct PreBwdArgs {
 
 // out = v, or out += v when accumulating
 __device__ __forceinline__ void put(float* p, float v, bool acc) { *p = acc ? *p + v : v; }
+// dL/dmean3D gets a share from the SH kernel and one from preprocess_bwd_kernel; when the two run concurrently
+// (launch_preprocess_backward) both add atomically onto a buffer that was zeroed (or already holds earlier views' sums)
+constexpr unsigned ACC_ATOMIC_M3 = 0x80000000u;
+__device__ __forceinline__ void put_m3(float* p, float v, bool acc, bool atomic)
+{
+    if (atomic) atomicAdd(p, v);
+    else put(p, v, acc);
+}
 
 __device__ __forceinline__ void store_sh_grads(float* __restrict__ dst, const float* g, int nfloats, int total_floats, bool acc = false)
 {
@@ -336,7 +344,9 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : (MULTI ? 3 : 4)) preprocess
     put(a.dL_dopacity + idx, s_dop, acc_o);
     {
         const bool add = acc_m || a.sh_done;       // sh_bwd_m16_kernel has already written its share
-        put(a.dL_dmean3D + 3 * idx, s_dm[0], add); put(a.dL_dmean3D + 3 * idx + 1, s_dm[1], add); put(a.dL_dmean3D + 3 * idx + 2, s_dm[2], add);
+        const bool atom = a.acc & ACC_ATOMIC_M3;   // ... or is writing it right now
+        put_m3(a.dL_dmean3D + 3 * idx, s_dm[0], add, atom); put_m3(a.dL_dmean3D + 3 * idx + 1, s_dm[1], add, atom);
+        put_m3(a.dL_dmean3D + 3 * idx + 2, s_dm[2], add, atom);
     }
 
     // ---- cov3D -> scale / rotation (backward.cu:278-341; no quaternion-normalisation Jacobian)
@@ -575,11 +585,12 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D
             sh_chunk_apply<3>(row, D, x, y, z, dR, dG, dB, ddx, ddy, ddz);
         }
         const float inv = rl * rl * rl;          // 1 / |o|^3
-        put(dL_dmean3D + 3 * (size_t)gid, ((sq - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * inv, acc_m);
-        put(dL_dmean3D + 3 * (size_t)gid + 1, (-ox * oy * ddx + (sq - oy * oy) * ddy - oz * oy * ddz) * inv, acc_m);
-        put(dL_dmean3D + 3 * (size_t)gid + 2, (-ox * oz * ddx - oy * oz * ddy + (sq - oz * oz) * ddz) * inv, acc_m);
+        const bool atom = acc & ACC_ATOMIC_M3;
+        put_m3(dL_dmean3D + 3 * (size_t)gid, ((sq - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * inv, acc_m, atom);
+        put_m3(dL_dmean3D + 3 * (size_t)gid + 1, (-ox * oy * ddx + (sq - oy * oy) * ddy - oz * oy * ddz) * inv, acc_m, atom);
+        put_m3(dL_dmean3D + 3 * (size_t)gid + 2, (-ox * oz * ddx - oy * oz * ddy + (sq - oz * oz) * ddz) * inv, acc_m, atom);
     } else if (lane < nrow) {
-        if (!acc_m) { dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f; }
+        if (!acc_m && !(acc & ACC_ATOMIC_M3)) { dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f; }
         if (SPLIT) flat_zero_row(frow);
     }
     __syncwarp();
@@ -707,11 +718,12 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P,
             sh_chunk_views<2>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
             sh_chunk_views<3>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
         }
-        put(dL_dmean3D + 3 * (size_t)gid, dm[0], acc_m);
-        put(dL_dmean3D + 3 * (size_t)gid + 1, dm[1], acc_m);
-        put(dL_dmean3D + 3 * (size_t)gid + 2, dm[2], acc_m);
+        const bool atom = acc & ACC_ATOMIC_M3;
+        put_m3(dL_dmean3D + 3 * (size_t)gid, dm[0], acc_m, atom);
+        put_m3(dL_dmean3D + 3 * (size_t)gid + 1, dm[1], acc_m, atom);
+        put_m3(dL_dmean3D + 3 * (size_t)gid + 2, dm[2], acc_m, atom);
     } else if (lane < nrow) {
-        if (!acc_m) { dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f; }
+        if (!acc_m && !(acc & ACC_ATOMIC_M3)) { dL_dmean3D[3 * (size_t)gid] = 0.f; dL_dmean3D[3 * (size_t)gid + 1] = 0.f; dL_dmean3D[3 * (size_t)gid + 2] = 0.f; }
         if (SPLIT) flat_zero_row(frow);
     }
     __syncwarp();
@@ -761,23 +773,49 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
     k.acc = a.accumulate;
     k.sh_done = 0;
     const bool split = a.shs && a.shs_rest && a.M > 1;      // DC and the other coefficients in two arrays (M == 16, checked by the API)
+    const bool sh_fast = split || (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && env_int("GSR_SH_SPLIT", 1));
+    // The SH kernel and preprocess_bwd_kernel are both HBM-bound and share one output only (dL/dmean3D): with that output
+    // turned into atomic adds they run side by side on two streams (the pair reaches a higher fraction of the HBM peak than
+    // either alone) and are joined before this function returns.
+    static cudaStream_t side = nullptr;
+    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    const bool forked = sh_fast && env_int("GSR_BWD_SIDE", 1) != 0;
+    cudaStream_t main_s = s;
+    unsigned acc_flags = a.accumulate;
+    if (forked) {
+        if (!side) {
+            GSR_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+            GSR_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+            GSR_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+        }
+        if (!(a.accumulate & GSR_ACC_MEAN3D)) GSR_CUDA(cudaMemsetAsync(a.dL_dmean3D, 0, sizeof(float) * 3 * (size_t)a.P, main_s));
+        acc_flags |= ACC_ATOMIC_M3;
+        k.acc = acc_flags;
+        GSR_CUDA(cudaEventRecord(ev_fork, main_s));
+        GSR_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        s = side;
+    }
     if (split) {
         if (((((size_t)a.shs) | ((size_t)a.dL_dsh) | ((size_t)a.shs_rest) | ((size_t)a.dL_dsh_rest)) & 15) != 0) return GSR_EINVAL;
         if (V == 1)
             GSR_LAUNCH(sh_bwd_m16_kernel<true>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs,
-                       g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate, a.shs_rest, a.dL_dsh_rest);
+                       g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, a.shs_rest, a.dL_dsh_rest);
         else
             GSR_LAUNCH(sh_bwd_m16_views_kernel<true>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii,
-                       a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate, a.shs_rest, a.dL_dsh_rest);
+                       a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, a.shs_rest, a.dL_dsh_rest);
         k.sh_done = 1;
     } else if (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && env_int("GSR_SH_SPLIT", 1)) {
         if (V == 1)
             GSR_LAUNCH(sh_bwd_m16_kernel<false>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs,
-                       g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate, (const float*)nullptr, (float*)nullptr);
+                       g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, (const float*)nullptr, (float*)nullptr);
         else
             GSR_LAUNCH(sh_bwd_m16_views_kernel<false>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii,
-                       a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, a.accumulate, (const float*)nullptr, (float*)nullptr);
+                       a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, (const float*)nullptr, (float*)nullptr);
         k.sh_done = 1;
+    }
+    if (forked) {
+        GSR_CUDA(cudaEventRecord(ev_join, side));
+        s = main_s;
     }
     const bool with_sh = !(k.sh_done || !a.shs);
     if (V == 1) {
@@ -787,6 +825,7 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
         if (!with_sh) GSR_LAUNCH((preprocess_bwd_kernel<false, true>), cdiv(a.P, 256), 256, 0, s, k, cam);
         else GSR_LAUNCH((preprocess_bwd_kernel<true, true>), cdiv(a.P, 256), 256, 0, s, k, cam);
     }
+    if (forked) GSR_CUDA(cudaStreamWaitEvent(main_s, ev_join, 0));
     return GSR_OK;
 }
 
