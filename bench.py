@@ -417,6 +417,20 @@ def main():
             batched_extra["e2e"] = {"value": views_total / (ms_be * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
                                     "d2h_bytes_per_step": 4}
 
+    # ---- config C2: forward only under torch.no_grad(), same scene and cameras
+    def step_forward_only(step):
+        with torch.no_grad():
+            for k in my_views(step):
+                dp.render_view(dgr, params, cams[k], bg, spec.D)
+
+    forward_extra = None
+    if not args.batched:
+        for i in range(2):
+            step_forward_only(i)
+        ms_f = timed(step_forward_only, args.steps, args.warmup)
+        forward_extra = {"config": "C2: forward only, torch.no_grad()", "ms_per_view": ms_f / args.steps / vps,
+                         "value": views_total / (ms_f * 1e-3), "unit": UNIT}
+
     # ---- the same step with two views in flight (two CUDA streams through the drop-in API), reported next to the headline
     streams_extra = None
     if not args.batched and fused and vps > 1:
@@ -527,7 +541,7 @@ def main():
                            "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else "GaussianRasterizer: one call per view",
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat.nbytes() + 48 * P + 20 * R) / 1e9)},
-                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "batched": batched_extra, "two_streams": streams_extra, "train_step": train_extra,
+                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "batched": batched_extra, "two_streams": streams_extra, "forward_only": forward_extra, "train_step": train_extra,
                 "gpu_launches": launches,
                 "clocks": clocks}
         print(json.dumps(line), flush=True)
