@@ -102,7 +102,8 @@ ImgView img_view(void* blob, int W, int H, int V)
     v.ranges = (uint2*)p; p += align_up((tiles ? tiles : 1) * sizeof(uint2));
     v.final_T = (float*)p; p += align_up((N ? N : 1) * 4);
     v.n_contrib = (uint32_t*)p; p += align_up((N ? N : 1) * 4);
-    v.tile_diff = (int*)p;
+    v.tile_diff = (int*)p; p += align_up((gx + 1) * (gy / (V > 0 ? V : 1) + 1) * (V > 0 ? V : 1) * sizeof(int));
+    v.tile_order = (uint32_t*)p;
     return v;
 }
 
@@ -141,7 +142,8 @@ size_t gsr_img_bytes_batched(int W, int H, int n_views)
     const size_t tiles = gx * gy;
     const size_t N = (size_t)W * H * V;
     return sizeof(BlobHeader) + align_up((tiles ? tiles : 1) * sizeof(uint2)) + 2 * align_up((N ? N : 1) * 4) +
-           align_up((gx + 1) * (gy1 + 1) * V * sizeof(int));         // the difference array has one band per view
+           align_up((gx + 1) * (gy1 + 1) * V * sizeof(int)) +        // the difference array has one band per view
+           align_up((tiles ? tiles : 1) * sizeof(uint32_t));         // tile launch order
 }
 size_t gsr_img_bytes(int W, int H) { return gsr_img_bytes_batched(W, H, 1); }
 size_t gsr_binning_bytes(int P, int R, int W, int H)

@@ -233,21 +233,25 @@ template <int UMAX, int MINB>
 __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                    float* __restrict__ out, uint32_t* __restrict__ planes, uint32_t plane_words, int gyv)
+                    float* __restrict__ out, uint32_t* __restrict__ planes, uint32_t plane_words, int gyv,
+                    const uint32_t* __restrict__ tile_order)
 {
     __shared__ BlendStage stage[2];
     __shared__ uint32_t bits[2][8][8];     // [buffer][consumer warp][chunk of 32 entries]
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    // batched calls stack the views' tile rows: tile row blockIdx.y = view * gyv + by; pixel coordinates stay per view
-    const uint32_t view = blockIdx.y / (uint32_t)gyv, by = blockIdx.y - view * (uint32_t)gyv;
-    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(by * GSR_TILE);
-    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    // the CTA's tile: the launch order (longest lists first) when given, else the grid position
+    const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const uint32_t tile = tile_order ? tile_order[lin] : lin;
+    const uint32_t trow = tile / gridDim.x, bx = tile - trow * gridDim.x;
+    // batched calls stack the views' tile rows: tile row trow = view * gyv + by; pixel coordinates stay per view
+    const uint32_t view = trow / (uint32_t)gyv, by = trow - view * (uint32_t)gyv;
+    const float X0 = (float)(bx * GSR_TILE), Y0 = (float)(by * GSR_TILE);
+    const uint32_t px = bx * GSR_TILE + (wid & 1) * 8 + (lane & 7);
     const uint32_t py = by * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const float pxf = (float)px, pyf = (float)py;
     bool done = !inside;
 
-    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
     // classification words are kept for the backward: plane k (sub-tile k), word (range.x >> 5) + 16 tile + chunk
@@ -446,16 +450,17 @@ int launch_blend_forward(long long R, int W, int H, int V, const float* bg, cons
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, gyv * V);
     const uint32_t pw = (uint32_t)blend_plane_words(R, W, gyv * V * GSR_TILE);
     if (V > 1 && (env_int("GSR_BLEND", 0) != 0 || env_int("GSR_BLEND_STATS", 0) != 0)) return GSR_EINVAL;   // comparison arms are single-view
+    const uint32_t* lpt = env_int("GSR_LPT", 1) ? im.tile_order : nullptr;
     if (env_int("GSR_BLEND_STATS", 0) == 1)
         GSR_LAUNCH(blend_stats_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H);
     if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
     else if (env_int("GSR_FWD_MINB", 4) == 3)
         GSR_LAUNCH((blend_fwd_v3_kernel<4, 3>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   out_color, b.scratch, pw, gyv);
+                   out_color, b.scratch, pw, gyv, lpt);
     else
         GSR_LAUNCH((blend_fwd_v3_kernel<4, 4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   out_color, b.scratch, pw, gyv);
+                   out_color, b.scratch, pw, gyv, lpt);
     return GSR_OK;
 }
 
@@ -1100,7 +1105,7 @@ __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     const uint32_t* __restrict__ planes, uint32_t plane_words, int W, int H, const float* __restrict__ bg,
                     const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
-                    float* __restrict__ accum, int gyv)
+                    float* __restrict__ accum, int gyv, const uint32_t* __restrict__ tile_order)
 {
     constexpr int D = NS - 1;          // gather distance in steps
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1108,16 +1113,18 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpRed& R = S.red[wid];
     WarpRing<NS>& Q = S.ring[wid];
-    const uint32_t view = blockIdx.y / (uint32_t)gyv, by = blockIdx.y - view * (uint32_t)gyv;     // see blend_fwd_v3_kernel
-    const float X0s = (float)(blockIdx.x * GSR_TILE + (wid & 1) * 8), Y0s = (float)(by * GSR_TILE + (wid >> 1) * 4);
-    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;                                  // see blend_fwd_v3_kernel
+    const uint32_t tile = tile_order ? tile_order[lin] : lin;
+    const uint32_t trow = tile / gridDim.x, bx = tile - trow * gridDim.x;
+    const uint32_t view = trow / (uint32_t)gyv, by = trow - view * (uint32_t)gyv;
+    const float X0s = (float)(bx * GSR_TILE + (wid & 1) * 8), Y0s = (float)(by * GSR_TILE + (wid >> 1) * 4);
+    const uint32_t px = bx * GSR_TILE + (wid & 1) * 8 + (lane & 7);
     const uint32_t py = by * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const float pxf = (float)px, pyf = (float)py;
     const size_t HW = (size_t)H * W;
     const size_t pix = view * HW + (size_t)W * py + px;
     dL_dpix += 2 * view * HW;                   // [V][3][H][W]: channel c of this pixel is dL_dpix[c * HW + pix]
-    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
     const uint2 range = ranges[tile];
 
     const float T_final = inside ? final_T[pix] : 0.f;
@@ -1264,6 +1271,7 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
     const uint32_t pw = (uint32_t)blend_plane_words(R, W, gyv * V * GSR_TILE);
     if (V > 1 && env_int("GSR_BLEND", 0) != 0) return GSR_EINVAL;        // comparison arms are single-view
     const int variant = env_int("GSR_BLEND", 0);       // 0: v5 (needs the planes of blend_fwd_v3), 1 / 3 / 4: comparison arms
+    const uint32_t* lpt = env_int("GSR_LPT", 1) ? im.tile_order : nullptr;
     if (env_int("GSR_BLEND", 0) == 1)
         GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
                    accum);
@@ -1281,13 +1289,13 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
         const int ns = env_int("GSR_BWD_NS", 2), minb = env_int("GSR_BWD_MINB", 4);
         if (ns == 4)
             GSR_LAUNCH((blend_bwd_v5_kernel<4, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<4>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv);
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
         else if (minb == 3)
             GSR_LAUNCH((blend_bwd_v5_kernel<2, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv);
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
         else
             GSR_LAUNCH((blend_bwd_v5_kernel<2, 4>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv);
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
     } else {
         static bool attr_set = false;
         if (!attr_set) {

@@ -87,6 +87,7 @@ struct ImgView {
     float*      final_T;       // [W*H]
     uint32_t*   n_contrib;     // [W*H]
     int*        tile_diff;     // [V][(gy+1)*(gx+1)] 2-D difference array of the tile rects, one band per view (zeroed before preprocess), only live inside forward
+    uint32_t*   tile_order;    // [tiles] the tiles of every view by decreasing list length (blending launch order), written by tile_prefix_kernel
 };
 
 // layout of GeomView::scratch (sort.cu).  The control block [ctl, ctl + ctl_words) must be zero before preprocess runs.

@@ -367,12 +367,13 @@ __global__ void __launch_bounds__(1024) tile_count_kernel(int Pper, int gyv, con
 template <bool SMEM>
 __global__ void __launch_bounds__(1024) tile_prefix_kernel(int gx, int gyv, int* __restrict__ diff, uint2* __restrict__ ranges,
                                                            uint32_t* __restrict__ tile_hist, TileDigits td,
-                                                           uint32_t* __restrict__ vstatus)
+                                                           uint32_t* __restrict__ vstatus, uint32_t* __restrict__ tile_order)
 {
     extern __shared__ int sd[];
     __shared__ uint32_t warp_sum[32];
     __shared__ uint32_t sh[4 * RS_NB];
-    __shared__ uint32_t s_view, s_base;
+    __shared__ uint32_t s_view, s_base, s_max;
+    __shared__ uint32_t bucket[64];
     const int gx1 = gx + 1, band = gx1 * (gyv + 1), t = threadIdx.x;
     if (t == 0) s_view = atomicAdd(vstatus, 1u);
     for (int i = t; i < 4 * RS_NB; i += 1024) sh[i] = 0;
@@ -430,6 +431,39 @@ __global__ void __launch_bounds__(1024) tile_prefix_kernel(int gx, int gyv, int*
     __syncthreads();
     for (int i = t; i < 4 * RS_NB; i += 1024)
         if (sh[i]) atomicAdd(&tile_hist[i], sh[i]);          // tile_hist lies in the zeroed control block
+
+    // launch order of the view's tiles for the blending kernels: longest lists first (64 buckets of list length, counting
+    // sort), so the last CTAs of a view are short ones and the tail of the grid stays busy
+    if (t == 0) s_max = 0;
+    if (t < 64) bucket[t] = 0;
+    __syncthreads();
+    uint32_t mx = 0;
+    for (int i = i0; i < i1; i++) mx = max(mx, (uint32_t)d[(i / gx) * gx1 + (i % gx)]);
+    if (mx) atomicMax(&s_max, mx);
+    __syncthreads();
+    const uint32_t scale = s_max + 1;
+    for (int i = i0; i < i1; i++) {
+        const uint32_t c = (uint32_t)d[(i / gx) * gx1 + (i % gx)];
+        atomicAdd(&bucket[63u - min(63u, (c * 64u) / scale)], 1u);
+    }
+    __syncthreads();
+    if (t < 32) {                                            // exclusive scan of the 64 bucket sizes
+        const uint32_t a = bucket[2 * t], b = bucket[2 * t + 1];
+        uint32_t inc = a + b;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (t >= o) inc += u;
+        }
+        bucket[2 * t] = inc - a - b;
+        bucket[2 * t + 1] = inc - b;
+    }
+    __syncthreads();
+    for (int i = i0; i < i1; i++) {
+        const uint32_t c = (uint32_t)d[(i / gx) * gx1 + (i % gx)];
+        const uint32_t pos = atomicAdd(&bucket[63u - min(63u, (c * 64u) / scale)], 1u);
+        tile_order[tile0 + pos] = tile0 + (uint32_t)i;
+    }
 }
 
 // seg_items > 0: the P items are seg_items-sized runs (whole views of a batched call) that never share a tile, so each
@@ -468,11 +502,11 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
             GSR_CUDA(cudaFuncSetAttribute(tile_prefix_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         }
         GSR_LAUNCH(tile_count_kernel<true>, dim3(cblocks, V), 1024, smem, s, Pper, gyv, sc.rect, gx + 1, band, im.tile_diff);
-        GSR_LAUNCH(tile_prefix_kernel<true>, V, 1024, smem, s, gx, gyv, im.tile_diff, im.ranges, sc.tile_hist, td, sc.view_status);
+        GSR_LAUNCH(tile_prefix_kernel<true>, V, 1024, smem, s, gx, gyv, im.tile_diff, im.ranges, sc.tile_hist, td, sc.view_status, im.tile_order);
     } else {
         GSR_LAUNCH(tile_count_kernel<false>, dim3(max(cblocks, min(cdiv(Pper, 4096), 592)), V), 1024, 0, s, Pper, gyv, sc.rect, gx + 1, band,
                    im.tile_diff);
-        GSR_LAUNCH(tile_prefix_kernel<false>, V, 1024, 0, s, gx, gyv, im.tile_diff, im.ranges, sc.tile_hist, td, sc.view_status);
+        GSR_LAUNCH(tile_prefix_kernel<false>, V, 1024, 0, s, gx, gyv, im.tile_diff, im.ranges, sc.tile_hist, td, sc.view_status, im.tile_order);
     }
     if (forked) {
         GSR_CUDA(cudaEventRecord(ev_join, side));
