@@ -11,7 +11,17 @@
  *
  * Return value: 0 on success, a negative GSR_E* code otherwise (never throws).
  * gsr_strerror() maps a code to text; gsr_last_cuda_error() gives the CUDA
- * error string behind GSR_ECUDA.
+ * error string behind GSR_ECUDA (kept per host thread).
+ *
+ * Threads and devices: like the reference core (static methods without state,
+ * rasterizer.h:24-84) every entry point may be called from several host threads
+ * at once, on the same or on different CUDA devices; a call works on the device
+ * that is current in the calling thread (the pointers must belong to it).  The
+ * library keeps only reusable CUDA resources between calls (side streams, events,
+ * pinned read-back slots), one set per device, created on first use.  Gradient
+ * accumulation into caller-owned buffers (GsrBwdArgs.accumulate) from concurrent
+ * calls on one device is ordered in host call order.  No environment variable is
+ * read after the first call into the library.
  *
  * reference interface replaced (file:line, relative to /root/reference/submodules):
  *   gsr_forward        <- CudaRasterizer::Rasterizer::forward      diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:31-57,  rasterizer_impl.cu:198-336
@@ -30,7 +40,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 2
+#define GSR_ABI_VERSION 3
 
 /* error codes */
 #define GSR_OK          0
@@ -40,7 +50,7 @@ extern "C" {
 #define GSR_ECHANNELS  -4   /* neither shs nor colors_precomp given (reference: "For non-RGB, provide precomputed Gaussian colors!") */
 #define GSR_ECOV       -5   /* neither (scales, rotations) nor cov3D_precomp given */
 #define GSR_EBLOB      -6   /* a state blob handed to backward does not carry our magic / sizes */
-#define GSR_ETOOBIG    -7   /* image has more than 65535 tiles per axis or R >= 2^30 */
+#define GSR_ETOOBIG    -7   /* image has more than 65535 tiles per axis, P * n_views >= 2^30 or R >= 2^30 */
 
 /* CUDA stream handle (== cudaStream_t) without dragging in cuda headers. */
 typedef struct CUstream_st* gsr_stream_t;
@@ -85,8 +95,9 @@ typedef struct GsrFwdArgs {
 } GsrFwdArgs;
 
 /*
- * Forward.  Blocks the host once (like rasterizer_impl.cu:280-281) to learn
- * num_rendered, because the binning blob is sized from it.
+ * Forward.  Blocks the calling host thread once (like rasterizer_impl.cu:280-281) to learn
+ * num_rendered, because the binning blob is sized from it (the wait is placed after the
+ * depth sort has been queued; other host threads are not blocked).
  * *num_rendered (host) receives R = sum of tiles touched.
  */
 int gsr_forward(const GsrFwdArgs* args, GsrAlloc geom, GsrAlloc binning, GsrAlloc img,
@@ -155,6 +166,17 @@ typedef struct GsrBwdArgs {
 #define GSR_ACC_ROT     16u
 
 int gsr_backward(const GsrBwdArgs* args, gsr_stream_t stream);
+
+/*
+ * gsr_backward in separately callable pieces (ABI 3).  `stages` bit 0: the blending backward (fills args->accum for all
+ * Gaussians); bit 1: the per-Gaussian backward (cov2D / cov3D / SH / projection, rasterizer_impl.cu:404-433) restricted to
+ * the Gaussians [g_begin, g_end) - g_begin a multiple of 128, g_end = -1 for P.  Every output row inside the range is written
+ * exactly as gsr_backward writes it, rows outside are not touched; gsr_backward(args) ==
+ * gsr_backward_staged(args, 3, 0, -1).  A view-sharded data-parallel trainer calls bit 0 once and bit 1 range by range for
+ * the last view of its step, starting the all-reduce of a range's gradients while the next range is computed
+ * (gsr_b200/dp.py; the reference has no multi-GPU path).
+ */
+int gsr_backward_staged(const GsrBwdArgs* args, int stages, int g_begin, int g_end, gsr_stream_t stream);
 
 /*
  * Backward of gsr_forward_batched: radii [n_views,P], dL_dpix [n_views,3,H,W], camera arrays as in the forward,

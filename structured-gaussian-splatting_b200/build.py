@@ -19,14 +19,18 @@ PKG = os.path.join(HERE, "gsr_b200")
 OBJ = os.path.join(HERE, "build")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-CU_SOURCES = ["api.cu", "preprocess.cu", "preprocess_bwd.cu", "sort.cu", "sort_cub.cu", "blend.cu", "knn.cu", "loss.cu", "ssim.cu", "optim.cu", "io.cu", "activate.cu"]
-HEADERS = ["gsr_common.cuh", "math3.cuh", os.path.join(INCLUDE, "gsr.h")]
+CU_SOURCES = ["api.cu", "context.cu", "preprocess.cu", "preprocess_bwd.cu", "sort.cu", "blend.cu", "knn.cu", "loss.cu", "ssim.cu", "optim.cu", "io.cu", "activate.cu"]
+# test-only comparison arms (plain blending kernels, statistics kernel, cp.async.bulk staging arm, CUB sort): a library of
+# their own, loaded only by tests / benchmarks (gsr_b200.load_arms()); nothing of it is linked into libgsr_b200.so
+ARM_SOURCES = [os.path.join("arms", "blend_arms.cu"), os.path.join("arms", "sort_cub.cu")]
+HEADERS = ["gsr_common.cuh", "blend_common.cuh", "math3.cuh", os.path.join(INCLUDE, "gsr.h")]
 # nvcc defaults on purpose (-fmad=true, IEEE div/sqrt, no fast-math): the bit-exact integer contract
 # depends on the same fp32 rounding as the reference build (torch's BuildExtension adds no fast-math).
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
               "-Xcompiler", "-fPIC"]
 
 LIB = os.path.join(PKG, "libgsr_b200.so")
+ARMS_LIB = os.path.join(PKG, "libgsr_b200_arms.so")
 
 
 def _nvcc():
@@ -76,6 +80,25 @@ def build_core(force=False, verbose=False):
     return LIB
 
 
+def build_arms(force=False, verbose=False):
+    """libgsr_b200_arms.so: links against libgsr_b200.so (launch counter, device contexts, hook registration)."""
+    os.makedirs(os.path.join(OBJ, "arms"), exist_ok=True)
+    hdrs = [h if os.path.isabs(h) else os.path.join(CSRC, h) for h in HEADERS]
+    jobs, objs = [], []
+    for src in ARM_SOURCES:
+        s = os.path.join(CSRC, src)
+        o = os.path.join(OBJ, src.replace(".cu", ".o"))
+        objs.append(o)
+        if force or _stale(o, [s] + hdrs):
+            jobs.append([_nvcc()] + NVCC_FLAGS + ["-c", s, "-o", o])
+    with ThreadPoolExecutor(max_workers=min(4, max(1, len(jobs)))) as ex:
+        list(ex.map(lambda c: _run(c, verbose), jobs))
+    if force or jobs or _stale(ARMS_LIB, objs + [LIB]):
+        _run([_nvcc(), "-shared", "-o", ARMS_LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static",
+              "-L", PKG, "-lgsr_b200", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN"], verbose)
+    return ARMS_LIB
+
+
 def build_binding(force=False, verbose=False):
     out = binding_path()
     src = os.path.join(CSRC, "torch_binding.cpp")
@@ -97,9 +120,10 @@ def build_binding(force=False, verbose=False):
 
 def build(force=False, verbose=False):
     build_core(force, verbose)
+    build_arms(force, verbose)
     build_binding(force, verbose)
 
 
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose="--verbose" in sys.argv or "-v" in sys.argv)
-    print("built", LIB, "and", binding_path())
+    print("built", LIB, ARMS_LIB, "and", binding_path())

@@ -13,51 +13,50 @@
 
 namespace gsr {
 
-unsigned long long g_launches = 0;
-char g_last_cuda_error[256] = "";
+std::atomic<unsigned long long> g_launches{0};
+static thread_local char t_last_cuda_error[256] = "";
 
 int record_cuda_error(cudaError_t e, const char* where)
 {
-    snprintf(g_last_cuda_error, sizeof g_last_cuda_error, "%s: %s", where, cudaGetErrorString(e));
+    snprintf(t_last_cuda_error, sizeof t_last_cuda_error, "%s: %s", where, cudaGetErrorString(e));
     cudaGetLastError();   // clear the sticky flag of non-fatal errors
     return GSR_ECUDA;
 }
 
-int env_int(const char* name, int dflt)
-{
-    const char* v = getenv(name);
-    return v && *v ? atoi(v) : dflt;
-}
-
 // ------------------------------------------------------------------ per-stage event timing
-static uint32_t* g_R_host = nullptr;        // pinned landing slot of the R read-back
-static cudaEvent_t g_R_event = nullptr;
-static bool g_timing = false;
+// A measurement facility for bench.py (off by default): one global table guarded by a mutex; the events belong to the
+// device that was current when the stage was opened, and a stage is open on one stream at a time per host thread.
+static std::atomic<bool> g_timing{false};
 struct Pending { int stage; cudaEvent_t a, b; };
+static std::mutex g_timing_mu;
 static std::vector<Pending> g_pending;
 static std::vector<cudaEvent_t> g_pool;
 static double g_stage_ms[GSR_NUM_STAGES];
 static unsigned long long g_stage_calls[GSR_NUM_STAGES];
-static cudaEvent_t g_open[GSR_NUM_STAGES];
+static thread_local cudaEvent_t t_open[GSR_NUM_STAGES];
 
 static cudaEvent_t get_event()
 {
-    if (!g_pool.empty()) { cudaEvent_t e = g_pool.back(); g_pool.pop_back(); return e; }
+    {
+        std::lock_guard<std::mutex> lk(g_timing_mu);
+        if (!g_pool.empty()) { cudaEvent_t e = g_pool.back(); g_pool.pop_back(); return e; }
+    }
     cudaEvent_t e; cudaEventCreate(&e); return e;
 }
 void stage_begin(int stage, cudaStream_t s)
 {
-    if (!g_timing) return;
-    g_open[stage] = get_event();
-    cudaEventRecord(g_open[stage], s);
+    if (!g_timing.load(std::memory_order_relaxed)) return;
+    t_open[stage] = get_event();
+    cudaEventRecord(t_open[stage], s);
 }
 void stage_end(int stage, cudaStream_t s)
 {
-    if (!g_timing || !g_open[stage]) return;
+    if (!g_timing.load(std::memory_order_relaxed) || !t_open[stage]) return;
     cudaEvent_t b = get_event();
     cudaEventRecord(b, s);
-    g_pending.push_back(Pending{stage, g_open[stage], b});
-    g_open[stage] = nullptr;
+    std::lock_guard<std::mutex> lk(g_timing_mu);
+    g_pending.push_back(Pending{stage, t_open[stage], b});
+    t_open[stage] = nullptr;
 }
 
 // ------------------------------------------------------------------ blob layouts
@@ -151,7 +150,7 @@ size_t gsr_binning_bytes(int P, int R, int W, int H)
     (void)P;
     const size_t Rp = (size_t)(R > 0 ? R : 1);
     size_t scratch = bin_scratch_bytes(R);
-    if (env_int("GSR_SORT", 0) == 1) { size_t c = cub_sort_scratch_bytes(R); if (c > scratch) scratch = c; }
+    if (options().sort_cub == 1 && g_arms.cub_sort_scratch_bytes) { size_t c = g_arms.cub_sort_scratch_bytes(R); if (c > scratch) scratch = c; }
     const size_t planes = 8 * 4 * blend_plane_words(R, W, H);      // written by the forward blending into the dead sort scratch
     if (planes > scratch) scratch = planes;
     return sizeof(BlobHeader) + align_up(Rp * 4) + scratch;
@@ -172,7 +171,8 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3 || V < 1 || S < 1 || V % S != 0) return GSR_EINVAL;
     if (!a->out_color || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
     const int gx = (a->W + GSR_TILE - 1) / GSR_TILE, gy = (a->H + GSR_TILE - 1) / GSR_TILE;
-    if (gx > 65535 || (long long)gy * V > 65535 || (long long)a->P * V >= (1ll << 31) || V > 4095) return GSR_ETOOBIG;
+    // P * V < 2^30: the look-back status words of the depth sort keep 30 value bits (sort.cu ST_VAL)
+    if (gx > 65535 || (long long)gy * V > 65535 || (long long)a->P * V >= (1ll << 30) || V > 4095) return GSR_ETOOBIG;
     const int Pv = a->P * V;                    // virtual Gaussians
     const int gyT = gy * V, HT = gyT * GSR_TILE; // the tall image in whole tiles
     if (a->P == 0) {
@@ -221,12 +221,14 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
 
     // R (sum of tiles touched) is accumulated by preprocess: start its read-back now and wait for it only after
     // the depth sort has been queued, so the host's launch work overlaps the device
-    if (!g_R_host) {
-        GSR_CUDA(cudaHostAlloc((void**)&g_R_host, 64, cudaHostAllocDefault));
-        GSR_CUDA(cudaEventCreateWithFlags(&g_R_event, cudaEventDisableTiming));
-    }
-    GSR_CUDA(cudaMemcpyAsync(g_R_host, sc.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-    GSR_CUDA(cudaEventRecord(g_R_event, s));
+    // (every call in flight has a pinned slot and an event of its own, taken from the device context)
+    DeviceCtx* ctx = nullptr;
+    if ((rc = device_ctx(&ctx))) return rc;
+    RSlot* slot = nullptr;
+    if ((rc = ctx_acquire_rslot(ctx, &slot))) return rc;
+    struct SlotGuard { DeviceCtx* c; RSlot* r; ~SlotGuard() { ctx_release_rslot(c, r); } } slot_guard{ctx, slot};
+    GSR_CUDA(cudaMemcpyAsync(slot->host, sc.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    GSR_CUDA(cudaEventRecord(slot->ev, s));
 
     stage_begin(1, s);
     {
@@ -234,8 +236,8 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
         // whole views of at most n items instead of all V * P items at once.  Off by default: measured at C3 with 8 views
         // (24 M items) one sort takes 0.119 ms per view, two runs of 12 M 0.122, eight runs of 3 M 0.151.
         int seg = 0;
-        if (V > 1 && (a->P & 3) == 0 && env_int("GSR_DEPTH_SEG_ITEMS", -1) >= 0) {
-            const long long per = (long long)env_int("GSR_DEPTH_SEG_ITEMS", 0) / a->P;     // 0 items = one view per run
+        if (V > 1 && (a->P & 3) == 0 && options().depth_seg_items >= 0) {
+            const long long per = (long long)options().depth_seg_items / a->P;     // 0 items = one view per run
             const long long views_per_seg = per < 1 ? 1 : per;
             if (views_per_seg < V) seg = (int)(views_per_seg * a->P);
         }
@@ -245,8 +247,8 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     GSR_STAGE(a->debug, s, "depth_order");
 
     // the binning blob is sized from R: the one blocking wait of the forward, like rasterizer_impl.cu:280-281
-    GSR_CUDA(cudaEventSynchronize(g_R_event));
-    const uint32_t R_host = *g_R_host;
+    GSR_CUDA(cudaEventSynchronize(slot->ev));
+    const uint32_t R_host = *slot->host;
     if (R_host >= 0x40000000u) return GSR_ETOOBIG;
     const int R = (int)R_host;
     *num_rendered = R;
@@ -257,7 +259,7 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     GSR_LAUNCH(init_headers_kernel, 1, 32, 0, s, g.hdr, b.hdr, im.hdr, Pv, R, a->W, a->H);
 
     stage_begin(2, s);
-    if (env_int("GSR_SORT", 0) == 1) rc = launch_tile_split_cub(Pv, R, a->W, HT, g, b, im, s);
+    if (options().sort_cub == 1) rc = g_arms.tile_split_cub ? g_arms.tile_split_cub(Pv, R, a->W, HT, g, b, im, s) : GSR_EINVAL;
     else rc = launch_tile_split(Pv, R, a->W, HT, g, b, im, s);
     if (rc) return rc;
     stage_end(2, s);
@@ -294,7 +296,11 @@ int gsr_forward_scenes(const GsrFwdArgs* a, int n_scenes, int views_per_scene, G
     return forward_impl(a, n_scenes * views_per_scene, n_scenes, geom, binning, img, stream, num_rendered);
 }
 
-static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_)
+// stages: bit 0 = blending backward (fills the accumulator rows of all Gaussians), bit 1 = per-Gaussian backward.
+// [g_begin, g_end) restricts the per-Gaussian backward to a range of Gaussians (single-view, single-scene calls only): a
+// data-parallel trainer runs the last view's per-Gaussian backward range by range and starts the all-reduce of each range's
+// gradients while the next range is still being computed (gsr_backward_staged).
+static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_, int stages = 3, int g_begin = 0, int g_end = -1)
 {
     cudaStream_t s = (cudaStream_t)stream_;
     if (!a) return GSR_EINVAL;
@@ -307,6 +313,10 @@ static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_
     if (a->shs && a->shs_rest && a->M > 1 && (a->M != 16 || !a->dL_dsh_rest)) return GSR_EINVAL;
     if (!a->cov3D_precomp && (!a->scales || !a->rotations || !a->dL_dscale || !a->dL_drot)) return GSR_ECOV;
 
+    if (g_end < 0) g_end = a->P;
+    if (g_begin < 0 || g_end > a->P || g_begin > g_end || (stages & ~3) != 0) return GSR_EINVAL;
+    const bool ranged = g_begin != 0 || g_end != a->P;
+    if (ranged && (V != 1 || S != 1 || (g_begin & 127) != 0)) return GSR_EINVAL;   // ranges start on multiples of 128 (alignment of the SH rows)
     const int Pv = a->P * V;
     GeomView g = geom_view(const_cast<void*>(a->geom_blob), Pv);
     BinView b = bin_view(const_cast<void*>(a->binning_blob), a->R);
@@ -324,18 +334,24 @@ static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_
     }
     float* accum = (float*)a->accum;
     int rc;
-    stage_begin(4, s);
-    GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(Pv), s));
-    if ((rc = launch_blend_backward(a->R, a->W, a->H, V, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
-    stage_end(4, s);
-    GSR_STAGE(a->debug, s, "blend_backward");
+    if (stages & 1) {
+        stage_begin(4, s);
+        GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(Pv), s));
+        if ((rc = launch_blend_backward(a->R, a->W, a->H, V, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
+        stage_end(4, s);
+        GSR_STAGE(a->debug, s, "blend_backward");
+    }
+    if (!(stages & 2) || g_begin == g_end) return GSR_OK;
     stage_begin(5, s);
     // Gradient fence: the per-Gaussian kernels read-modify-write the caller's gradient buffers when they accumulate.  Calls
     // issued from different streams (a trainer keeping two views in flight, gsr_b200.dp.backward_views(n_streams=2)) are
     // ordered here, in host call order, through one event: everything before this point (blending) still overlaps.
-    static cudaEvent_t g_grad_fence = nullptr;
-    if (!g_grad_fence) GSR_CUDA(cudaEventCreateWithFlags(&g_grad_fence, cudaEventDisableTiming));
-    else GSR_CUDA(cudaStreamWaitEvent(s, g_grad_fence, 0));
+    // The fence belongs to the device; its mutex keeps wait -> launches -> record of one call together when several host
+    // threads drive the same device.
+    DeviceCtx* ctx = nullptr;
+    if ((rc = device_ctx(&ctx))) return rc;
+    std::lock_guard<std::mutex> fence_lock(ctx->fence_mu);
+    if (ctx->fence_recorded) GSR_CUDA(cudaStreamWaitEvent(s, ctx->grad_fence, 0));
     // scene by scene (S = 1 for the single-scene calls): the per-Gaussian backward of scene sc_i sees its own parameters,
     // cameras and gradient rows and the slice of the per-view arrays that belongs to its Vs views
     const int Vs = V / S;
@@ -343,7 +359,8 @@ static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_
     for (int sc_i = 0; sc_i < S; sc_i++) {
         GsrBwdArgs as = *a;
         GeomView gs = g;
-        const size_t o = (size_t)sc_i * a->P;            // first Gaussian of the scene
+        as.P = g_end - g_begin;                            // (== a->P unless a range was asked for)
+        const size_t o = (size_t)sc_i * a->P + (size_t)g_begin;     // first Gaussian of the scene (of the range)
         const size_t ov = o * Vs;                          // first virtual Gaussian of the scene (= sc_i * Vs views * P)
         as.means3D = a->means3D + 3 * o;
         if (a->shs) { as.shs = a->shs + 3 * (size_t)Mdc * o; as.dL_dsh = a->dL_dsh + 3 * (size_t)Mdc * o; }
@@ -382,13 +399,18 @@ static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_
             }
         }
     }
-    GSR_CUDA(cudaEventRecord(g_grad_fence, s));
+    GSR_CUDA(cudaEventRecord(ctx->grad_fence, s));
+    ctx->fence_recorded = true;
     stage_end(5, s);
     GSR_STAGE(a->debug, s, "preprocess_backward");
     return GSR_OK;
 }
 
 int gsr_backward(const GsrBwdArgs* a, gsr_stream_t stream) { return backward_impl(a, 1, 1, stream); }
+int gsr_backward_staged(const GsrBwdArgs* a, int stages, int g_begin, int g_end, gsr_stream_t stream)
+{
+    return backward_impl(a, 1, 1, stream, stages, g_begin, g_end);
+}
 int gsr_backward_batched(const GsrBwdArgs* a, int n_views, gsr_stream_t stream)
 {
     if (n_views > 1 && a && (a->colors_precomp || a->cov3D_precomp)) return GSR_EINVAL;
@@ -453,29 +475,36 @@ const char* gsr_strerror(int code)
     default: return "unknown error";
     }
 }
-const char* gsr_last_cuda_error(void) { return g_last_cuda_error; }
+const char* gsr_last_cuda_error(void) { return t_last_cuda_error; }
 int gsr_abi_version(void) { return GSR_ABI_VERSION; }
 
-void gsr_timing_enable(int on) { g_timing = on != 0; }
+void gsr_timing_enable(int on) { g_timing.store(on != 0); }
 void gsr_timing_reset(void)
 {
+    std::lock_guard<std::mutex> lk(g_timing_mu);
     for (int i = 0; i < GSR_NUM_STAGES; i++) { g_stage_ms[i] = 0; g_stage_calls[i] = 0; }
 }
 int gsr_timing_collect(void)
 {
-    for (auto& p : g_pending) {
+    std::vector<Pending> todo;
+    {
+        std::lock_guard<std::mutex> lk(g_timing_mu);
+        todo.swap(g_pending);
+    }
+    for (auto& p : todo) {
         GSR_CUDA(cudaEventSynchronize(p.b));
         float ms = 0.f;
         GSR_CUDA(cudaEventElapsedTime(&ms, p.a, p.b));
+        std::lock_guard<std::mutex> lk(g_timing_mu);
         g_stage_ms[p.stage] += ms; g_stage_calls[p.stage]++;
         g_pool.push_back(p.a); g_pool.push_back(p.b);
     }
-    g_pending.clear();
     return GSR_OK;
 }
 int gsr_timing_read(int stage, double* ms_total, unsigned long long* calls)
 {
     if (stage < 0 || stage >= GSR_NUM_STAGES) return GSR_EINVAL;
+    std::lock_guard<std::mutex> lk(g_timing_mu);
     if (ms_total) *ms_total = g_stage_ms[stage];
     if (calls) *calls = g_stage_calls[stage];
     return GSR_OK;
@@ -486,7 +515,7 @@ const char* gsr_stage_name(int stage)
                                             "preprocess_backward", "dist2"};
     return stage >= 0 && stage < GSR_NUM_STAGES ? n[stage] : "?";
 }
-void gsr_reset_launch_count(void) { g_launches = 0; }
-unsigned long long gsr_launch_count(void) { return g_launches; }
+void gsr_reset_launch_count(void) { g_launches.store(0); }
+unsigned long long gsr_launch_count(void) { return g_launches.load(); }
 
 }  // extern "C"

@@ -1,10 +1,10 @@
-// sort_cub.cu - COMPARISON ARM ONLY (GSR_SORT=1): the reference's binning formulation on the same
+// arms/sort_cub.cu - TEST-ONLY COMPARISON ARM (option sort_cub = 1, libgsr_b200_arms.so): the reference's binning formulation on the same
 // inputs - id-major emission of 64-bit tile|depth keys, cub::DeviceRadixSort::SortPairs over
 // 32 + tile_bits bits (CUB 2.8 picks its sm_100 tuning), identifyTileRanges
 // (rasterizer_impl.cu:70-138,277,300-318).  It exists so tests can assert that our trimmed-key sort
 // yields the identical sequence and so bench.py can time "the bar to beat" on the same GPU.
 // It is never the default path.
-#include "gsr_common.cuh"
+#include "../gsr_common.cuh"
 #include <cub/cub.cuh>
 
 namespace gsr {
@@ -61,14 +61,14 @@ static size_t cub_temp_bytes(long long R, int P)
     return align_up(a > b ? a : b);
 }
 
-size_t cub_sort_scratch_bytes(long long R)
+size_t arm_cub_sort_scratch_bytes(long long R)
 {
     const size_t Rp = (size_t)(R > 0 ? R : 1);
     // keys_unsorted, keys_sorted (u64), vals_unsorted (u32), temp (sized for the worst case of P <= 2^27 scan)
     return 2 * align_up(Rp * 8) + align_up(Rp * 4) + cub_temp_bytes(R > 0 ? R : 1, 1 << 27);
 }
 
-int launch_tile_split_cub(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s)
+int arm_tile_split_cub(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s)
 {
     const int gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
     GSR_CUDA(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)gx * gy, s));

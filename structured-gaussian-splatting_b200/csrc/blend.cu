@@ -1,233 +1,18 @@
-// blend.cu - per-tile alpha blending, forward and backward.
+// blend.cu - per-tile alpha blending, forward and backward (product kernels).
 //
 // Replaces (reference: submodules/diff-gaussian-rasterization/cuda_rasterizer):
-//   blend_fwd_kernel  <- renderCUDA<3> (forward)   forward.cu:261-374
-//   blend_bwd_kernel  <- renderCUDA<3> (backward)  backward.cu:399-557
+//   blend_fwd_v3_kernel          <- renderCUDA<3> (forward)   forward.cu:261-374
+//   blend_bwd_v6_kernel (/ v5)   <- renderCUDA<3> (backward)  backward.cu:399-557
 //
-// One CTA per 16x16 tile, one thread per pixel.  Tile-list entries are staged in shared memory as
-// packed records gathered with 16-byte cp.async copies (position+conic+opacity+colour: everything
-// the inner loop touches, so the loop never goes to global memory), double buffered so the gather
-// of batch b+1 overlaps the blending of batch b with a single barrier per batch.
-// The per-pixel arithmetic keeps the reference's expression order: skip decisions (power > 0,
-// alpha < 1/255, T < 1e-4) must be identical or a pixel can differ by up to 1/255.
-//
-// Backward: every lane computes its pixel's contribution to the 9 per-Gaussian gradient terms, a
-// transposing warp butterfly (9 + 5 shuffles instead of 45) reduces them, and 9 lanes issue one
-// red.global.add each into a packed 48-byte accumulator row (one or two L2 sectors per warp-entry
-// instead of the reference's 9 atomics per pixel-entry into four arrays).
-#include "gsr_common.cuh"
+// One CTA per 16x16 tile, eight warps, each warp owns an 8x4 pixel sub-tile.  Tile-list entries are staged in shared
+// memory as packed records gathered with 16-byte cp.async copies (position + conic + opacity + colour: everything the
+// inner loop touches), double buffered.  The per-pixel arithmetic keeps the reference's expression order: the skip
+// decisions (power > 0, alpha < 1/255, T < 1e-4) must be identical or a pixel can differ by up to 1/255.
+// The plain kernels without sub-tile culling, the statistics kernel and the cp.async.bulk staging arm live in
+// arms/blend_arms.cu (test-only library).
+#include "blend_common.cuh"
 
 namespace gsr {
-
-constexpr int BL_THREADS = GSR_TILE * GSR_TILE;   // 256
-
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
-{
-    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async4(void* smem, const void* gmem)
-{
-    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
-
-struct BlendStage {
-    float4 q0[BL_THREADS];   // pix.x pix.y conic.x conic.y
-    float4 q1[BL_THREADS];   // conic.z opacity r g
-    float  b[BL_THREADS];    // b
-};
-
-// issue the gather of one batch: entry `pos` of the sorted list (if in range) into slot threadIdx
-__device__ __forceinline__ void stage_gather(BlendStage& st, const SplatRec* __restrict__ rec, uint32_t id, bool valid)
-{
-    if (valid) {
-        const SplatRec* r = rec + id;
-        cp_async16(&st.q0[threadIdx.x], &r->q0);
-        cp_async16(&st.q1[threadIdx.x], &r->q1);
-        cp_async4(&st.b[threadIdx.x], &r->q2);
-    }
-    cp_async_commit();
-}
-
-__global__ void __launch_bounds__(BL_THREADS)
-blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
-                 int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                 float* __restrict__ out)
-{
-    __shared__ BlendStage stage[2];
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    const uint32_t px = blockIdx.x * GSR_TILE + tx, py = blockIdx.y * GSR_TILE + ty;
-    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    const float pxf = (float)px, pyf = (float)py;
-    bool done = !inside;
-
-    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
-    const int total = (int)(range.y - range.x);
-    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
-
-    float T = 1.0f;
-    uint32_t contributor = 0, last_contributor = 0;
-    float C0 = 0.f, C1 = 0.f, C2 = 0.f;
-
-    // prologue: ids of batches 0 and 1, gather of batch 0
-    uint32_t id_next = 0;
-    {
-        const bool v0 = (int)threadIdx.x < total;
-        const uint32_t id0 = v0 ? vals[range.x + threadIdx.x] : 0;
-        stage_gather(stage[0], rec, id0, v0);
-        const int p1 = BL_THREADS + threadIdx.x;
-        if (p1 < total) id_next = vals[range.x + p1];
-    }
-    int todo = total;
-    for (int i = 0; i < rounds; i++, todo -= BL_THREADS) {
-        cp_async_wait<0>();
-        // barrier: batch i is visible to everyone, everyone has left batch i-1 (its buffer is reused below)
-        const int num_done = __syncthreads_count(done);
-        if (num_done == BL_THREADS) break;
-        // gather batch i+1 into the other buffer, fetch the ids of batch i+2
-        {
-            const int p1 = (i + 1) * BL_THREADS + threadIdx.x;
-            stage_gather(stage[(i + 1) & 1], rec, id_next, p1 < total);
-            const int p2 = p1 + BL_THREADS;
-            if (p2 < total) id_next = vals[range.x + p2];
-        }
-        const BlendStage& st = stage[i & 1];
-        const int n = min(BL_THREADS, todo);
-        for (int j = 0; !done && j < n; j++) {
-            contributor++;
-            const float4 a = st.q0[j];
-            const float4 c = st.q1[j];
-            const float dx = a.x - pxf, dy = a.y - pyf;
-            const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
-            if (power > 0.0f) continue;
-            const float alpha = fminf(0.99f, c.y * expf(power));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) { done = true; continue; }
-            const float at = alpha * T;     // colour weight; (c * alpha) * T in the reference, same value to 1 ulp
-            C0 = fmaf(c.z, at, C0);
-            C1 = fmaf(c.w, at, C1);
-            C2 = fmaf(st.b[j], at, C2);
-            T = test_T;
-            last_contributor = contributor;
-        }
-    }
-    cp_async_wait<0>();
-    if (inside) {
-        const size_t pix = (size_t)W * py + px;
-        final_T[pix] = T;
-        n_contrib[pix] = last_contributor;
-        const size_t HW = (size_t)H * W;
-        out[pix] = C0 + T * bg[0];
-        out[HW + pix] = C1 + T * bg[1];
-        out[2 * HW + pix] = C2 + T * bg[2];
-    }
-}
-
-// ------------------------------------------------------------------------------------------ sub-tile culling
-// Each warp owns an 8x4 pixel sub-tile (2 x 4 sub-tiles per 16x16 tile).  Before a batch is blended, the
-// thread that gathered entry t decides for which of the 8 sub-tiles the entry can possibly be blended:
-// alpha >= 1/255 needs  q(d) = 0.5*(A dx^2 + C dy^2) + B dx dy <= ln(255*opacity) =: tau.  The test is exact up
-// to rounding: q is a convex quadratic, so its minimum over the sub-tile's pixel-centre rectangle is attained
-// either on the vertical edge nearest the centre (u = cu) at the clamped 1-D minimiser v* = -B cu / C, or on the
-// nearest horizontal edge (v = cv) at u* = -B cv / A (both candidates are points of the rectangle, so taking
-// the smaller never under-estimates; when the centre is inside both are 0).  A sub-tile whose minimum exceeds
-// tau cannot contain a pixel the reference would blend, so dropping the entry for that warp leaves every
-// result bit-identical.  tau is inflated for the rounding of the per-pixel fp32 power (error <= ~1e-6 * q *
-// AC/det), of the approximate log / reciprocals and of this evaluation; the rectangle grows by 1e-3 px;
-// ill-conditioned conics (AC/det > 1e4) are never culled.
-__device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-
-__device__ __forceinline__ uint32_t subtile_mask(const float4 a, const float4 c, float X0, float Y0)
-{
-    const float o = c.y;
-    if (o < 1.0f / 255.0f) return 0u;                 // alpha = min(0.99, o*exp(p<=0)) <= o < 1/255 everywhere
-    const float A = a.z, B = a.w, C = c.x;
-    const float det = A * C - B * B;
-    const float kappa = A * C * rcp_fast(det);
-    if (!(kappa <= 1.0e4f) || !(det > 0.f) || !(A > 0.f) || !(C > 0.f)) return 0xFFu;
-    const float tau = (__logf(255.0f * o) + 1.0e-3f) * (1.0f + 6.0e-6f * kappa) * 1.0004f;
-    const float nBC = -B * rcp_fast(C), nBA = -B * rcp_fast(A);
-    const float hA = 0.5f * A, hC = 0.5f * C;
-    float u0[2], u1[2], vst[2], qa[2], bu[2];
-#pragma unroll
-    for (int sx = 0; sx < 2; sx++) {
-        u0[sx] = (X0 + 8.0f * sx - 1.0e-3f) - a.x; u1[sx] = u0[sx] + 7.002f;
-        const float cu = fminf(fmaxf(0.0f, u0[sx]), u1[sx]);
-        vst[sx] = nBC * cu; qa[sx] = hA * cu * cu; bu[sx] = B * cu;
-    }
-    uint32_t m = 0;
-#pragma unroll
-    for (int sy = 0; sy < 4; sy++) {
-        const float v0 = (Y0 + 4.0f * sy - 1.0e-3f) - a.y, v1 = v0 + 3.002f;
-        const float cv = fminf(fmaxf(0.0f, v0), v1);
-        const float ust = nBA * cv, qc = hC * cv * cv, bv = B * cv;
-#pragma unroll
-        for (int sx = 0; sx < 2; sx++) {
-            const float vs = fminf(fmaxf(vst[sx], v0), v1);
-            const float q1 = fmaf(vs, fmaf(hC, vs, bu[sx]), qa[sx]);
-            const float us = fminf(fmaxf(ust, u0[sx]), u1[sx]);
-            const float q2 = fmaf(us, fmaf(hA, us, bv), qc);
-            if (fminf(q1, q2) <= tau) m |= 1u << (sy * 2 + sx);       // warp w: sx = w & 1, sy = w >> 1
-        }
-    }
-    return m;
-}
-
-// ------------------------------------------------------------------------------------------ forward with sub-tile culling
-// Staging as in blend_fwd_kernel plus the sub-tile masks; the per-warp entry loop takes up to UMAX surviving entries per trip:
-// their alphas (independent of the pixel's running state) are evaluated side by side, which doubles the
-// instruction-level parallelism of the latency chain LDS -> power -> expf, halves the loop overhead, and the
-// sequential part (T test, colour accumulation) is predicated instead of branched.  Arithmetic per pixel is
-// unchanged (same expressions, same order), so every output is bit-identical to variants 1 and 2.
-__device__ __forceinline__ float entry_alpha(const float4 a, const float4 c, float pxf, float pyf, bool& ok)
-{
-    const float dx = a.x - pxf, dy = a.y - pyf;
-    const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
-    const float alpha = fminf(0.99f, c.y * expf(power));
-    ok = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-    return alpha;
-}
-
-__device__ __forceinline__ void blend_step(float alpha, bool ok, float r, float g, float b, uint32_t pos, bool& done, float& T,
-                                           float& C0, float& C1, float& C2, uint32_t& last)
-{
-    const float test_T = T * (1 - alpha);
-    const bool v = ok && !done;
-    const bool stop = v && (test_T < 0.0001f);
-    done = done || stop;
-    if (v && !stop) {
-        const float at = alpha * T;         // colour weight; (c * alpha) * T in the reference, same value to 1 ulp
-        C0 = fmaf(r, at, C0);
-        C1 = fmaf(g, at, C1);
-        C2 = fmaf(b, at, C2);
-        T = test_T;
-        last = pos;
-    }
-}
-
-// U surviving entries of chunk `jb` (taken from the low set bits of m) in one trip
-template <int U>
-__device__ __forceinline__ void blend_trip(const BlendStage& st, uint32_t& m, int jb, uint32_t pos_base, float pxf, float pyf,
-                                           bool& done, float& T, float& C0, float& C1, float& C2, uint32_t& last)
-{
-    int j[U];
-    float4 a[U], c[U];
-    float b[U], al[U];
-    bool ok[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) { j[u] = jb + __ffs(m) - 1; m &= m - 1; }
-#pragma unroll
-    for (int u = 0; u < U; u++) { a[u] = st.q0[j[u]]; c[u] = st.q1[j[u]]; b[u] = st.b[j[u]]; }
-#pragma unroll
-    for (int u = 0; u < U; u++) al[u] = entry_alpha(a[u], c[u], pxf, pyf, ok[u]);
-#pragma unroll
-    for (int u = 0; u < U; u++) blend_step(al[u], ok[u], c[u].z, c[u].w, b[u], pos_base + j[u], done, T, C0, C1, C2, last);
-}
 
 template <int UMAX, int MINB>
 __global__ void __launch_bounds__(BL_THREADS, MINB)
@@ -321,120 +106,6 @@ blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     }
 }
 
-// ------------------------------------------------------------------------------------------ statistics (debug hook)
-// Counts what the culled forward does, to size the kernels' work (scripts/exp_blend.py): not on the product path.
-//  0 entries staged (until the tile is done)   1 (warp, entry) pairs evaluated   2 lanes not done at evaluation
-//  3 lanes with power <= 0   4 lanes with alpha >= 1/255   5 lanes blended   6 (warp, entry) pairs with >= 1 lane passing alpha
-//  7 (half-warp 8x2, entry) pairs with >= 1 lane passing alpha   8 (quarter 4x2.. lanes 8-groups) likewise   9 batches
-__device__ unsigned long long g_blend_stats[16];
-
-__global__ void __launch_bounds__(BL_THREADS)
-blend_stats_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec, int W, int H)
-{
-    __shared__ BlendStage stage;
-    __shared__ uint32_t bits[8][8];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(blockIdx.y * GSR_TILE);
-    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
-    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
-    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    const float pxf = (float)px, pyf = (float)py;
-    bool done = !inside;
-    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
-    const int total = (int)(range.y - range.x);
-    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
-    float T = 1.0f;
-    unsigned long long c[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    __shared__ uint32_t wcnt[8];
-    uint32_t tile_cnt = 0;
-    for (int i = 0; i < rounds; i++) {
-        uint32_t n44[2] = {0, 0}, n82[2] = {0, 0}, n42[4] = {0, 0, 0, 0}, nw = 0;
-        const int num_done = __syncthreads_count(done);
-        if (num_done == BL_THREADS) break;
-        const int p = i * BL_THREADS + (int)threadIdx.x;
-        uint32_t m = 0;
-        if (p < total) {
-            const SplatRec r = rec[vals[range.x + p]];
-            stage.q0[threadIdx.x] = r.q0; stage.q1[threadIdx.x] = r.q1; stage.b[threadIdx.x] = r.q2.x;
-            m = subtile_mask(r.q0, r.q1, X0, Y0);
-            c[0]++;
-        }
-        if (threadIdx.x == 0) c[9]++;
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-            const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
-            if (lane == k) bits[k][wid] = bk;
-        }
-        __syncthreads();
-        for (int cch = 0; cch < 8; cch++) {
-            uint32_t mm = bits[wid][cch];
-            if (__all_sync(0xffffffffu, done)) mm = 0;
-            while (mm) {
-                const int j = cch * 32 + __ffs(mm) - 1;
-                mm &= mm - 1;
-                if (__all_sync(0xffffffffu, done)) break;
-                if (lane == 0) c[1]++;
-                nw++;
-                bool pass = false;
-                if (!done) {
-                    c[2]++;
-                    const float4 a = stage.q0[j];
-                    const float4 q = stage.q1[j];
-                    const float dx = a.x - pxf, dy = a.y - pyf;
-                    const float power = -0.5f * (a.z * dx * dx + q.x * dy * dy) - a.w * dx * dy;
-                    if (!(power > 0.0f)) {
-                        c[3]++;
-                        const float alpha = fminf(0.99f, q.y * expf(power));
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            c[4]++;
-                            pass = true;
-                            const float test_T = T * (1 - alpha);
-                            if (test_T < 0.0001f) done = true;
-                            else { c[5]++; T = test_T; }
-                        }
-                    }
-                }
-                const uint32_t pb = __ballot_sync(0xffffffffu, pass);
-                if (lane == 0) {
-                    c[6] += pb != 0;
-                    c[7] += ((pb & 0xFFFFu) != 0) + ((pb >> 16) != 0);
-                    c[8] += ((pb & 0xFFu) != 0) + (((pb >> 8) & 0xFFu) != 0) + (((pb >> 16) & 0xFFu) != 0) + ((pb >> 24) != 0);
-                }
-                n44[0] += (pb & 0x0F0F0F0Fu) != 0; n44[1] += (pb & 0xF0F0F0F0u) != 0;
-                n82[0] += (pb & 0x0000FFFFu) != 0; n82[1] += (pb & 0xFFFF0000u) != 0;
-                n42[0] += (pb & 0x00000F0Fu) != 0; n42[1] += (pb & 0x0000F0F0u) != 0;
-                n42[2] += (pb & 0x0F0F0000u) != 0; n42[3] += (pb & 0xF0F00000u) != 0;
-            }
-        }
-        if (lane == 0) {
-            c[10] += max(n44[0], n44[1]); c[11] += max(n82[0], n82[1]);
-            c[12] += max(max(n42[0], n42[1]), max(n42[2], n42[3]));
-            c[13] += n44[0] + n44[1];
-            wcnt[wid] = nw;
-        }
-        tile_cnt += nw;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            uint32_t mx = 0;
-            for (int k = 0; k < 8; k++) mx = max(mx, wcnt[k]);
-            c[14] += mx;                      // per-batch critical path (slowest warp)
-        }
-    }
-    if (lane == 0) wcnt[wid] = tile_cnt;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t mx = 0;
-        for (int k = 0; k < 8; k++) mx = max(mx, wcnt[k]);
-        c[15] += mx;                          // per-tile critical path if warps never waited for each other
-    }
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        unsigned long long v = c[k];
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0 && v) atomicAdd(&g_blend_stats[k], v);
-    }
-}
-
 // classification words kept for the backward (in the binning blob's sort scratch, dead once the tile split is done):
 // 8 planes (one per sub-tile of a tile) of (R >> 5) + 16 tiles + 16 words
 size_t blend_plane_words(long long R, int W, int H)
@@ -443,179 +114,6 @@ size_t blend_plane_words(long long R, int W, int H)
     return (size_t)((R > 0 ? R : 0) >> 5) + 16 * tiles + 16;
 }
 
-int launch_blend_forward(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
-                         float* out_color, cudaStream_t s)
-{
-    const int gyv = (H + GSR_TILE - 1) / GSR_TILE;
-    const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, gyv * V);
-    const uint32_t pw = (uint32_t)blend_plane_words(R, W, gyv * V * GSR_TILE);
-    if (V > 1 && (env_int("GSR_BLEND", 0) != 0 || env_int("GSR_BLEND_STATS", 0) != 0)) return GSR_EINVAL;   // comparison arms are single-view
-    const uint32_t* lpt = env_int("GSR_LPT", 1) ? im.tile_order : nullptr;
-    if (env_int("GSR_BLEND_STATS", 0) == 1)
-        GSR_LAUNCH(blend_stats_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H);
-    if (env_int("GSR_BLEND", 0) == 1)
-        GSR_LAUNCH(blend_fwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, out_color);
-    else if (env_int("GSR_FWD_MINB", 4) == 3)
-        GSR_LAUNCH((blend_fwd_v3_kernel<4, 3>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   out_color, b.scratch, pw, gyv, lpt);
-    else
-        GSR_LAUNCH((blend_fwd_v3_kernel<4, 4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   out_color, b.scratch, pw, gyv, lpt);
-    return GSR_OK;
-}
-
-// ------------------------------------------------------------------------------------------ backward
-
-// Per-pixel contribution of one blended entry to the per-Gaussian sums (restates backward.cu:494-556).
-// Instead of the reference's nine final gradient terms the lanes produce MOMENTS of w = dL/dG * G:
-//   g0..g2 = alpha*T*dL/dpix (colour), gmx = w dx, gmy = w dy, gcx = w dx^2, gcy = w dx dy, gcw = w dy^2, gop = w
-// The conic / opacity factors are constant per Gaussian, so they are applied once per Gaussian in
-// preprocess_bwd (dL/dmean2D.x = -W/2 (A gmx + B gmy), dL/dconic = -1/2 (gcx, gcy, gcw), dL/dopacity = gop / o).
-// 1/(1-alpha) is one MUFU.RCP (alpha <= 0.99) instead of two IEEE divisions: gradients carry a 1e-3 tolerance.
-__device__ __forceinline__ void bwd_live_math(float alpha, float araw, float dx, float dy, float c0, float c1, float c2,
-                                              float dp0, float dp1, float dp2, float tfb, float& T, float& last_alpha,
-                                              float& acc0, float& acc1, float& acc2, float& lc0, float& lc1, float& lc2,
-                                              float& g0, float& g1, float& g2, float& gmx, float& gmy, float& gcx, float& gcy,
-                                              float& gcw, float& gop)
-{
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f - alpha));
-    T *= r;
-    const float at = alpha * T;
-    acc0 = fmaf(last_alpha, lc0 - acc0, acc0); lc0 = c0;
-    acc1 = fmaf(last_alpha, lc1 - acc1, acc1); lc1 = c1;
-    acc2 = fmaf(last_alpha, lc2 - acc2, acc2); lc2 = c2;
-    float dL_dalpha = (c0 - acc0) * dp0 + (c1 - acc1) * dp1 + (c2 - acc2) * dp2;
-    g0 = at * dp0; g1 = at * dp1; g2 = at * dp2;
-    last_alpha = alpha;
-    dL_dalpha = fmaf(dL_dalpha, T, -tfb * r);
-    const float w = araw * dL_dalpha;          // dL/dG * G = opacity * dL/dalpha * G  (no zeroing when alpha was clamped)
-    gmx = w * dx; gmy = w * dy;
-    gcx = gmx * dx; gcy = gmx * dy; gcw = gmy * dy;
-    gop = w;
-}
-
-// reduces 8 per-lane values over the warp with a transposing butterfly: afterwards lane L holds the
-// warp total of value ((L>>4)&1)*4 + ((L>>3)&1)*2 + ((L>>2)&1)  (replicated over the low two lane bits)
-__device__ __forceinline__ float butterfly8(float v0, float v1, float v2, float v3, float v4, float v5, float v6, float v7,
-                                            int lane)
-{
-    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
-    // offset 16: 8 -> 4
-    float a0 = (b4 ? v4 : v0) + __shfl_xor_sync(0xffffffffu, b4 ? v0 : v4, 16);
-    float a1 = (b4 ? v5 : v1) + __shfl_xor_sync(0xffffffffu, b4 ? v1 : v5, 16);
-    float a2 = (b4 ? v6 : v2) + __shfl_xor_sync(0xffffffffu, b4 ? v2 : v6, 16);
-    float a3 = (b4 ? v7 : v3) + __shfl_xor_sync(0xffffffffu, b4 ? v3 : v7, 16);
-    // offset 8: 4 -> 2
-    float c0 = (b3 ? a2 : a0) + __shfl_xor_sync(0xffffffffu, b3 ? a0 : a2, 8);
-    float c1 = (b3 ? a3 : a1) + __shfl_xor_sync(0xffffffffu, b3 ? a1 : a3, 8);
-    // offset 4: 2 -> 1
-    float e = (b2 ? c1 : c0) + __shfl_xor_sync(0xffffffffu, b2 ? c0 : c1, 4);
-    e += __shfl_xor_sync(0xffffffffu, e, 2);
-    e += __shfl_xor_sync(0xffffffffu, e, 1);
-    return e;
-}
-
-struct BlendStageBwd {
-    float4 q0[BL_THREADS];
-    float4 q1[BL_THREADS];
-    float  b[BL_THREADS];
-    uint32_t id[BL_THREADS];
-};
-
-// accumulator row layout (12 floats per Gaussian): 0-2 dL/dcolour, 3-4 sum w*(dx,dy), 5-7 sum w*(dx^2, dx dy, dy^2), 8 sum w
-__global__ void __launch_bounds__(BL_THREADS)
-blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
-                 int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
-                 const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, float* __restrict__ accum)
-{
-    __shared__ BlendStageBwd stage[2];
-    const int lane = threadIdx.x & 31;
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    const uint32_t px = blockIdx.x * GSR_TILE + tx, py = blockIdx.y * GSR_TILE + ty;
-    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    const float pxf = (float)px, pyf = (float)py;
-    const size_t pix = (size_t)W * py + px;
-    const size_t HW = (size_t)H * W;
-
-    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
-    const int total = (int)(range.y - range.x);
-    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
-
-    const float T_final = inside ? final_T[pix] : 0.f;
-    float T = T_final;
-    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
-    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
-    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
-    const float tfb = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;       // accum_rec
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-
-    // the warp only has work in list positions below the largest n_contrib of its lanes
-    int warp_last = last_contributor;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
-
-    // which accumulator column this lane commits after the butterfly
-    const int col8 = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-
-    // entries are walked back to front: batch i covers list positions total-1-i*256 .. (descending)
-    auto gather = [&](BlendStageBwd& st, int batch) {
-        const int p = batch * BL_THREADS + threadIdx.x;
-        if (p < total) {
-            const uint32_t id = vals[range.y - 1 - p];
-            st.id[threadIdx.x] = id;
-            const SplatRec* r = rec + id;
-            cp_async16(&st.q0[threadIdx.x], &r->q0);
-            cp_async16(&st.q1[threadIdx.x], &r->q1);
-            cp_async4(&st.b[threadIdx.x], &r->q2);
-        }
-        cp_async_commit();
-    };
-    gather(stage[0], 0);
-    int contributor = total;
-    for (int i = 0; i < rounds; i++) {
-        cp_async_wait<0>();
-        __syncthreads();
-        if (i + 1 < rounds) gather(stage[(i + 1) & 1], i + 1);
-        const BlendStageBwd& st = stage[i & 1];
-        const int n = min(BL_THREADS, total - i * BL_THREADS);
-        for (int j = 0; j < n; j++) {
-            contributor--;
-            if (contributor >= warp_last) continue;      // warp-uniform
-            const float4 a = st.q0[j];
-            const float4 c = st.q1[j];
-            const float dx = a.x - pxf, dy = a.y - pyf;
-            const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
-            const float araw = c.y * expf(power);
-            const float alpha = fminf(0.99f, araw);
-            const bool live = contributor < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-            if (!__any_sync(0xffffffffu, live)) continue;
-
-            float g0 = 0.f, g1 = 0.f, g2 = 0.f, gmx = 0.f, gmy = 0.f, gcx = 0.f, gcy = 0.f, gcw = 0.f, gop = 0.f;
-            if (live) {
-                bwd_live_math(alpha, araw, dx, dy, c.z, c.w, st.b[j], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
-                              lc0, lc1, lc2, g0, g1, g2, gmx, gmy, gcx, gcy, gcw, gop);
-            }
-            const float r8 = butterfly8(g0, g1, g2, gmx, gmy, gcx, gcy, gcw, lane);
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) gop += __shfl_xor_sync(0xffffffffu, gop, o);
-            float* row = accum + (size_t)st.id[j] * 12;
-            if ((lane & 3) == 0) atomicAdd(row + col8, r8);
-            else if (lane == 1) atomicAdd(row + 8, gop);
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------ backward with sub-tile culling
-// Same tiles / sub-tiles / culling as the forward; the list is truncated to the largest n_contrib of the tile, a warp
-// additionally ignores entries at or beyond its own largest n_contrib.
-// Two surviving entries per trip: both alphas are evaluated side by side (instruction-level parallelism on the
-// LDS -> power -> expf chain), the per-pixel state update stays sequential, and the two entries' 8 + 8 values
-// go through ONE 16-value transposing butterfly (16 + 5 shuffles for two entries instead of 2 x 14).
-struct PixState {
-    float T, last_alpha, acc0, acc1, acc2, lc0, lc1, lc2;
-};
 struct EntryHead {
     float dx, dy, araw, alpha;
     bool live;
@@ -631,189 +129,12 @@ __device__ __forceinline__ EntryHead bwd_head(const float4 a, const float4 c, fl
     return h;
 }
 
-// lane L ends up with the warp total of v[((L>>4)&1)*8 + ((L>>3)&1)*4 + ((L>>2)&1)*2 + ((L>>1)&1)]
-__device__ __forceinline__ float butterfly16(const float* v, int lane)
-{
-    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
-    float a[8], c[4], d[2];
-#pragma unroll
-    for (int k = 0; k < 8; k++) a[k] = (b4 ? v[k + 8] : v[k]) + __shfl_xor_sync(0xffffffffu, b4 ? v[k] : v[k + 8], 16);
-#pragma unroll
-    for (int k = 0; k < 4; k++) c[k] = (b3 ? a[k + 4] : a[k]) + __shfl_xor_sync(0xffffffffu, b3 ? a[k] : a[k + 4], 8);
-#pragma unroll
-    for (int k = 0; k < 2; k++) d[k] = (b2 ? c[k + 2] : c[k]) + __shfl_xor_sync(0xffffffffu, b2 ? c[k] : c[k + 2], 4);
-    float e = (b1 ? d[1] : d[0]) + __shfl_xor_sync(0xffffffffu, b1 ? d[0] : d[1], 2);
-    e += __shfl_xor_sync(0xffffffffu, e, 1);
-    return e;
-}
-
-template <int MINB>
-__global__ void __launch_bounds__(BL_THREADS, MINB)
-blend_bwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
-                    int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
-                    const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, float* __restrict__ accum)
-{
-    __shared__ BlendStageBwd stage[2];
-    __shared__ uint32_t bits[2][8][8];
-    __shared__ int s_warp_last[8];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(blockIdx.y * GSR_TILE);
-    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
-    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
-    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    const float pxf = (float)px, pyf = (float)py;
-    const size_t pix = (size_t)W * py + px;
-    const size_t HW = (size_t)H * W;
-
-    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
-
-    const float T_final = inside ? final_T[pix] : 0.f;
-    float T = T_final;
-    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
-    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
-    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
-    const float tfb = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-
-    int warp_last = last_contributor;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
-    if (lane == 0) s_warp_last[wid] = warp_last;
-    __syncthreads();
-    int total = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) total = max(total, s_warp_last[k]);
-    total = min(total, (int)(range.y - range.x));
-    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
-    const uint32_t list_end = range.x + total;
-
-    const int col8 = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-    const int col16 = (lane >> 1) & 7, ent16 = lane >> 4;
-
-    auto gather = [&](BlendStageBwd& st, int batch) {
-        const int p = batch * BL_THREADS + threadIdx.x;
-        if (p < total) {
-            const uint32_t id = vals[list_end - 1 - p];
-            st.id[threadIdx.x] = id;
-            const SplatRec* r = rec + id;
-            cp_async16(&st.q0[threadIdx.x], &r->q0);
-            cp_async16(&st.q1[threadIdx.x], &r->q1);
-            cp_async4(&st.b[threadIdx.x], &r->q2);
-        }
-        cp_async_commit();
-    };
-    gather(stage[0], 0);
-    for (int i = 0; i < rounds; i++) {
-        const int buf = i & 1;
-        cp_async_wait<0>();
-        {
-            uint32_t m = 0;
-            const int p = i * BL_THREADS + (int)threadIdx.x;
-            if (p < total) {
-                m = subtile_mask(stage[buf].q0[threadIdx.x], stage[buf].q1[threadIdx.x], X0, Y0);
-                const int pos = total - 1 - p;
-#pragma unroll
-                for (int k = 0; k < 8; k++)
-                    if (pos >= s_warp_last[k]) m &= ~(1u << k);
-            }
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
-                if (lane == k) bits[buf][k][wid] = bk;
-            }
-        }
-        __syncthreads();
-        if (i + 1 < rounds) gather(stage[buf ^ 1], i + 1);
-        const BlendStageBwd& st = stage[buf];
-        const int pos_top = total - 1 - i * BL_THREADS;
-#pragma unroll 1
-        for (int cch = 0; cch < 8; cch++) {
-            uint32_t m = bits[buf][wid][cch];
-            const int jb = cch * 32;
-            while (m) {
-                const int j0 = jb + __ffs(m) - 1;
-                m &= m - 1;
-                if (m) {
-                    const int j1 = jb + __ffs(m) - 1;
-                    m &= m - 1;
-                    const float4 a0 = st.q0[j0], c0 = st.q1[j0], a1 = st.q0[j1], c1 = st.q1[j1];
-                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
-                    const EntryHead h1 = bwd_head(a1, c1, pxf, pyf, pos_top - j1, last_contributor);
-                    const bool any0 = __any_sync(0xffffffffu, h0.live), any1 = __any_sync(0xffffffffu, h1.live);
-                    if (!any0 && !any1) continue;
-                    float v[16], gop0 = 0.f, gop1 = 0.f;
-#pragma unroll
-                    for (int k = 0; k < 16; k++) v[k] = 0.f;
-                    if (h0.live)
-                        bwd_live_math(h0.alpha, h0.araw, h0.dx, h0.dy, c0.z, c0.w, st.b[j0], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1,
-                                      acc2, lc0, lc1, lc2, v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], gop0);
-                    if (h1.live)
-                        bwd_live_math(h1.alpha, h1.araw, h1.dx, h1.dy, c1.z, c1.w, st.b[j1], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1,
-                                      acc2, lc0, lc1, lc2, v[8], v[9], v[10], v[11], v[12], v[13], v[14], v[15], gop1);
-                    const float e = butterfly16(v, lane);
-                    float g = (ent16 ? gop1 : gop0) + __shfl_xor_sync(0xffffffffu, ent16 ? gop0 : gop1, 16);
-#pragma unroll
-                    for (int o = 8; o > 0; o >>= 1) g += __shfl_xor_sync(0xffffffffu, g, o);
-                    const bool mine = ent16 ? any1 : any0;
-                    float* row = accum + (size_t)st.id[ent16 ? j1 : j0] * 12;
-                    if (mine) {
-                        if ((lane & 1) == 0) atomicAdd(row + col16, e);
-                        else if ((lane & 15) == 1) atomicAdd(row + 8, g);
-                    }
-                } else {
-                    const float4 a0 = st.q0[j0], c0 = st.q1[j0];
-                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
-                    if (!__any_sync(0xffffffffu, h0.live)) continue;
-                    float g0 = 0.f, g1 = 0.f, g2 = 0.f, gmx = 0.f, gmy = 0.f, gcx = 0.f, gcy = 0.f, gcw = 0.f, gop = 0.f;
-                    if (h0.live)
-                        bwd_live_math(h0.alpha, h0.araw, h0.dx, h0.dy, c0.z, c0.w, st.b[j0], dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1,
-                                      acc2, lc0, lc1, lc2, g0, g1, g2, gmx, gmy, gcx, gcy, gcw, gop);
-                    const float r8 = butterfly8(g0, g1, g2, gmx, gmy, gcx, gcy, gcw, lane);
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) gop += __shfl_xor_sync(0xffffffffu, gop, o);
-                    float* row = accum + (size_t)st.id[j0] * 12;
-                    if ((lane & 3) == 0) atomicAdd(row + col8, r8);
-                    else if (lane == 1) atomicAdd(row + 8, gop);
-                }
-            }
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------ backward, tensor-core reduction
-// The per-Gaussian sums of blend_bwd_v3 cost a 16-value butterfly (21 shuffles, 30 selects, 21 adds) per pair of
-// entries: 40 % of the kernel's instructions.  They are linear in two per-lane scalars of the entry,
-//   w  = dL/dG * G   and   at = alpha * T,
-// with coefficients that do not depend on the entry: the pixel's offset inside the warp's 8x4 sub-tile
-// (lx, ly in 0..7 x 0..3) for the six moments of w, and the pixel's dL/dpixel for the three colour sums.  So a warp
-// parks (w, at) of each surviving entry in a shared-memory slot (two STS) and, every 8 entries, reduces all of them
-// over the 32 lanes with the tensor cores (mma.sync m16n8k8 tf32, fp32 accumulate, K = the 32 lanes in 4 steps):
-//   A[16 x 32]  rows 0-7 = w of slots 0-7, rows 8-15 = at of slots 0-7          (split hi + lo: two MMAs)
-//   B1[32 x 8]  columns (1, lx, lx', ...) = the moment matrix (small integers: exact in tf32)   -> D1 rows 0-7
-//   B2[32 x 8]  columns (hi, lo) of dL/dpixel r, g, b                                           -> D2 rows 8-15
-// The hi/lo splits keep ~21 mantissa bits (error < 1e-6; the gradients carry a 1e-3 tolerance).  The slot array is
-// stored in A-fragment order, so one LDS.128 per k-step is the whole A operand.  The moments about the sub-tile origin
-// are shifted to the Gaussian's centre (dx = u - lx, u = mean.x - origin.x) and committed with the same RED.ADDs
-// into the same accumulator rows as before (two of them as 8-byte vector REDs).
 constexpr int RED_SLOTS = 8;
 constexpr int RED_KSTRIDE = 144;      // floats per k-step of the slot array: 8 slots x 16 + 16 (STS of one slot: 2-way conflicts only)
 struct __align__(16) WarpRed {
     float a[4 * RED_KSTRIDE];         // [k-step s][slot][t][b][w | at]   (lane = 8t + 2s + b)
     float2 b2[4][32];                 // B2 fragments: [k-step][lane (g, t)] = column g of dL/dpixel at lanes 8t+2s, 8t+2s+1
     float4 meta[RED_SLOTS];           // mean.x, mean.y, Gaussian id (bits)
-};
-struct BlendStageBwd4 {
-    float4 q0[BL_THREADS];
-    float4 q1[BL_THREADS];
-    float2 bi[BL_THREADS];            // colour b, Gaussian id (bits): one LDS.64 at the top of a trip
-};
-struct __align__(16) BwdSmemV4 {
-    BlendStageBwd4 stage[2];
-    WarpRed red[8];
-    float2 b1[4][32];                 // B1 fragments (moment matrix), same for all warps
-    uint32_t bits[2][8][8];
-    int warp_last[8];
 };
 
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
@@ -882,181 +203,6 @@ __device__ __forceinline__ void red_flush(WarpRed& R, const float2 (*b1)[32], in
         atomicAdd(row + t, col);
     }
     __syncwarp();
-}
-
-// per-pixel state update of one blended entry (restates backward.cu:494-556); returns w = dL/dG * G and at = alpha * T
-__device__ __forceinline__ void bwd_live_wa(float alpha, float araw, float c0, float c1, float c2, float dp0, float dp1, float dp2,
-                                            float tfb, float& T, float& last_alpha, float& acc0, float& acc1, float& acc2,
-                                            float& lc0, float& lc1, float& lc2, float& w, float& at)
-{
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f - alpha));
-    T *= r;
-    at = alpha * T;
-    acc0 = fmaf(last_alpha, lc0 - acc0, acc0); lc0 = c0;
-    acc1 = fmaf(last_alpha, lc1 - acc1, acc1); lc1 = c1;
-    acc2 = fmaf(last_alpha, lc2 - acc2, acc2); lc2 = c2;
-    float dL_dalpha = (c0 - acc0) * dp0 + (c1 - acc1) * dp1 + (c2 - acc2) * dp2;
-    last_alpha = alpha;
-    dL_dalpha = fmaf(dL_dalpha, T, -tfb * r);
-    w = araw * dL_dalpha;
-}
-
-template <int MINB>
-__global__ void __launch_bounds__(BL_THREADS, MINB)
-blend_bwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
-                    int W, int H, const float* __restrict__ bg, const float* __restrict__ final_T,
-                    const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, float* __restrict__ accum)
-{
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    BwdSmemV4& S = *reinterpret_cast<BwdSmemV4*>(smem_raw);
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    WarpRed& R = S.red[wid];
-    const float X0 = (float)(blockIdx.x * GSR_TILE), Y0 = (float)(blockIdx.y * GSR_TILE);
-    const float X0s = X0 + (float)((wid & 1) * 8), Y0s = Y0 + (float)((wid >> 1) * 4);
-    const uint32_t px = blockIdx.x * GSR_TILE + (wid & 1) * 8 + (lane & 7);
-    const uint32_t py = blockIdx.y * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
-    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    const float pxf = (float)px, pyf = (float)py;
-    const size_t pix = (size_t)W * py + px;
-    const size_t HW = (size_t)H * W;
-
-    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
-
-    const float T_final = inside ? final_T[pix] : 0.f;
-    float T = T_final;
-    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
-    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
-    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
-    const float tfb = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-
-    // constant operands of the reduction in B-fragment order: the moment matrix (whole block) and this warp's
-    // dL/dpixel columns (r_hi, r_lo, g_hi, g_lo, b_hi, b_lo, 0, 0)
-    if (threadIdx.x < 128) {
-        const int s = threadIdx.x >> 5, l = threadIdx.x & 31, n = l >> 2;
-        const float ly = (float)(l & 3), lx0 = (float)(2 * s), lx1 = lx0 + 1.f;
-        float2 m;
-        m.x = n == 0 ? 1.f : n == 1 ? lx0 : n == 2 ? ly : n == 3 ? lx0 * lx0 : n == 4 ? lx0 * ly : n == 5 ? ly * ly : 0.f;
-        m.y = n == 0 ? 1.f : n == 1 ? lx1 : n == 2 ? ly : n == 3 ? lx1 * lx1 : n == 4 ? lx1 * ly : n == 5 ? ly * ly : 0.f;
-        S.b1[s][l] = m;
-    }
-    const int tL = lane >> 3, sL = (lane >> 1) & 3, bL = lane & 1;      // this pixel is k index tL + 4 bL of k-step sL
-    {
-        const float d[3] = {dp0, dp1, dp2};
-        float* col = reinterpret_cast<float*>(&R.b2[sL][tL]) + bL;
-#pragma unroll
-        for (int c = 0; c < 3; c++) {
-            const float hi = __uint_as_float(__float_as_uint(d[c]) & 0xffffe000u);
-            col[(2 * c) * 8] = hi;                 // column n lives at lane index 4n + tL: 8 floats apart
-            col[(2 * c + 1) * 8] = d[c] - hi;
-        }
-        col[6 * 8] = 0.f;
-        col[7 * 8] = 0.f;
-    }
-    float2* const slot0 = reinterpret_cast<float2*>(&R.a[sL * RED_KSTRIDE + tL * 4 + bL * 2]);   // slot c: slot0 + 8 c
-
-    int warp_last = last_contributor;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
-    if (lane == 0) S.warp_last[wid] = warp_last;
-    __syncthreads();
-    int total = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) total = max(total, S.warp_last[k]);
-    total = min(total, (int)(range.y - range.x));
-    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
-    const uint32_t list_end = range.x + total;
-
-    auto gather = [&](BlendStageBwd4& st, int batch) {
-        const int p = batch * BL_THREADS + threadIdx.x;
-        if (p < total) {
-            const uint32_t id = vals[list_end - 1 - p];
-            st.bi[threadIdx.x].y = __uint_as_float(id);
-            const SplatRec* r = rec + id;
-            cp_async16(&st.q0[threadIdx.x], &r->q0);
-            cp_async16(&st.q1[threadIdx.x], &r->q1);
-            cp_async4(&st.bi[threadIdx.x].x, &r->q2);
-        }
-        cp_async_commit();
-    };
-    gather(S.stage[0], 0);
-    int cnt = 0;                  // filled reduction slots of this warp (warp-uniform)
-    for (int i = 0; i < rounds; i++) {
-        const int buf = i & 1;
-        cp_async_wait<0>();
-        {
-            uint32_t m = 0;
-            const int p = i * BL_THREADS + (int)threadIdx.x;
-            if (p < total) {
-                m = subtile_mask(S.stage[buf].q0[threadIdx.x], S.stage[buf].q1[threadIdx.x], X0, Y0);
-                const int pos = total - 1 - p;
-#pragma unroll
-                for (int k = 0; k < 8; k++)
-                    if (pos >= S.warp_last[k]) m &= ~(1u << k);
-            }
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
-                if (lane == k) S.bits[buf][k][wid] = bk;
-            }
-        }
-        __syncthreads();
-        if (i + 1 < rounds) gather(S.stage[buf ^ 1], i + 1);
-        const BlendStageBwd4& st = S.stage[buf];
-        const int pos_top = total - 1 - i * BL_THREADS;
-#pragma unroll 1
-        for (int cch = 0; cch < 8; cch++) {
-            uint32_t m = S.bits[buf][wid][cch];
-            const int jb = cch * 32;
-            while (m) {
-                if (cnt >= RED_SLOTS - 1) { red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum); cnt = 0; }
-                const int j0 = jb + __ffs(m) - 1;
-                m &= m - 1;
-                if (m) {
-                    const int j1 = jb + __ffs(m) - 1;
-                    m &= m - 1;
-                    const float4 a0 = st.q0[j0], c0 = st.q1[j0], a1 = st.q0[j1], c1 = st.q1[j1];
-                    const float2 e0 = st.bi[j0], e1 = st.bi[j1];
-                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
-                    const EntryHead h1 = bwd_head(a1, c1, pxf, pyf, pos_top - j1, last_contributor);
-                    const bool any0 = __any_sync(0xffffffffu, h0.live), any1 = __any_sync(0xffffffffu, h1.live);
-                    if (any0) {
-                        float wv = 0.f, atv = 0.f;
-                        if (h0.live)
-                            bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
-                                        lc0, lc1, lc2, wv, atv);
-                        slot0[8 * cnt] = make_float2(wv, atv);
-                        if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, e0.y, 0.f);
-                        cnt++;
-                    }
-                    if (any1) {
-                        float wv = 0.f, atv = 0.f;
-                        if (h1.live)
-                            bwd_live_wa(h1.alpha, h1.araw, c1.z, c1.w, e1.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
-                                        lc0, lc1, lc2, wv, atv);
-                        slot0[8 * cnt] = make_float2(wv, atv);
-                        if (lane == 0) R.meta[cnt] = make_float4(a1.x, a1.y, e1.y, 0.f);
-                        cnt++;
-                    }
-                } else {
-                    const float4 a0 = st.q0[j0], c0 = st.q1[j0];
-                    const float2 e0 = st.bi[j0];
-                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, pos_top - j0, last_contributor);
-                    if (!__any_sync(0xffffffffu, h0.live)) continue;
-                    float wv = 0.f, atv = 0.f;
-                    if (h0.live)
-                        bwd_live_wa(h0.alpha, h0.araw, c0.z, c0.w, e0.x, dp0, dp1, dp2, tfb, T, last_alpha, acc0, acc1, acc2,
-                                    lc0, lc1, lc2, wv, atv);
-                    slot0[8 * cnt] = make_float2(wv, atv);
-                    if (lane == 0) R.meta[cnt] = make_float4(a0.x, a0.y, e0.y, 0.f);
-                    cnt++;
-                }
-            }
-        }
-    }
-    if (cnt) red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum);
 }
 
 // ------------------------------------------------------------------------------------------ backward, warp-autonomous
@@ -1263,65 +409,349 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     if (cnt) red_flush(R, S.b1, cnt, lane, X0s, Y0s, accum);
 }
 
-int launch_blend_backward(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
-                          const float* dL_dpix, float* accum, cudaStream_t s)
+// ------------------------------------------------------------------------------------------ backward, compacted work queue (v6)
+// blend_bwd_v5 walks the tile list 32 entries per step and finds ~7 of them set in its classification word: the step
+// overhead (mask bookkeeping, id loads, gather issue: ~70 instructions) is paid per ~7 entries, every entry costs a
+// find-highest-bit sequence and a warp vote, and the tensor-core reduction runs with half of its rows idle (8 entries x
+// (w | at) share one 16-row A operand).  v6 keeps the arithmetic and changes the bookkeeping:
+//  * work queue: the warp compacts the set bits of its classification words into a queue of list positions in shared
+//    memory (one STS per set bit, ~14 instructions per 32-entry word) and then works on DENSE groups of 32 queued entries:
+//    every lane gathers one record per group (ids one group ahead, records one group ahead through cp.async into a
+//    two-buffer ring), and the blending loop is a plain counted loop over the ring - no bit scans, no votes;
+//  * 16-row reduction: w and at of an entry go to two separate A operands (16 entries x 32 lanes each), so each of the
+//    16 HMMAs of a flush does useful work in all rows: one flush per 16 entries instead of one per 8, the entry's
+//    centre and id are read from the ring at flush time (no per-entry meta store);
+//  * entries none of whose lanes is live simply contribute zero sums, which the epilogue does not commit (a RED of 0 is
+//    a no-op, so skipping it is exact): no warp vote per entry.
+// Shared-memory layout of the A operands (floats): [k-step s][row g = entry & 7][t][pair slot p][w | at], pair slot
+// p = 2 b + (hi ^ (s & 1)), hi = entry >> 3, rows padded to 36 floats.  A pixel lane L is K index (t, b) of k-step s with
+// s = L >> 3, t = (L >> 1) & 3, b = L & 1: its STS.64 of (w, at) is bank-conflict free (the 16 lanes of a store phase
+// have s in {0,1} or {2,3}; the parity swap spreads them over all 32 banks) and so is the reader's LDS.128 (row stride
+// 36 = 4 mod 32).  The k-step loop is unrolled, so the parity swap costs no instruction on the reading side.
+constexpr int V6_GS = 36;               // floats per row g of a k-step
+constexpr int V6_KS = 8 * V6_GS;        // floats per k-step
+constexpr int V6_QCAP = 128;            // queue capacity (power of two; <= 95 live entries, see the fill loop)
+struct __align__(16) WarpV6 {
+    float4 q0[2][32];                   // ring: pix.x pix.y conic.x conic.y
+    float4 q1[2][32];                   //       conic.z opacity r g
+    float4 e[2][32];                    //       Gaussian id (bits), list position (bits), colour b, unused
+    float  a[4 * V6_KS];
+    float2 b2[4][32];                   // B2 fragments of this warp's dL/dpixel (hi, lo per channel)
+    uint32_t queue[V6_QCAP];
+};
+struct __align__(16) BwdSmemV6 {
+    WarpV6 w[8];
+    float2 b1[4][32];                   // B1 fragments (moment matrix), same for all warps
+};
+
+// Reduces rows [0, cnt) of the warp's A operands (entries jbase .. jbase + cnt - 1 of ring buffer kq) over the 32 lanes and
+// commits them.  Fragments of m16n8k8 (g = lane >> 2, t = lane & 3): A rows g / g+8 at k = t / t+4, B column g at
+// k = t / t+4, D rows g / g+8, columns 2t, 2t+1.  Columns of D1: S0 Sx | Sy Sxx | Sxy Syy | - -  (moments of w about the
+// sub-tile origin), of D2: r_hi r_lo | g_hi g_lo | b_hi b_lo | - -.
+__device__ __forceinline__ void v6_flush(const WarpV6& S, const float2 (*b1)[32], int kq, int jbase, int cnt, int lane, float X0s,
+                                         float Y0s, float* __restrict__ accum)
 {
+    __syncwarp();
+    const int g = lane >> 2, t = lane & 3;
+    float d1[4] = {0.f, 0.f, 0.f, 0.f}, d2[4] = {0.f, 0.f, 0.f, 0.f};
+    const float* ab = S.a + g * V6_GS + t * 8;
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        const float4 Q1 = *reinterpret_cast<const float4*>(ab + s * V6_KS);          // k = t:   (w, at) of the two rows
+        const float4 Q2 = *reinterpret_cast<const float4*>(ab + s * V6_KS + 4);      // k = t+4
+        const float2 m = b1[s][lane];
+        const float2 q = S.b2[s][lane];
+        float xw[4], xa[4];
+        if ((s & 1) == 0) {
+            xw[0] = Q1.x; xw[1] = Q1.z; xw[2] = Q2.x; xw[3] = Q2.z;
+            xa[0] = Q1.y; xa[1] = Q1.w; xa[2] = Q2.y; xa[3] = Q2.w;
+        } else {
+            xw[0] = Q1.z; xw[1] = Q1.x; xw[2] = Q2.z; xw[3] = Q2.x;
+            xa[0] = Q1.w; xa[1] = Q1.y; xa[2] = Q2.w; xa[3] = Q2.y;
+        }
+        uint32_t whi[4], wlo[4], ahi[4], alo[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {      // x = hi + lo, hi exact in tf32 (the tensor core ignores the 13 low mantissa bits)
+            whi[k] = __float_as_uint(xw[k]) & 0xffffe000u;
+            wlo[k] = __float_as_uint(xw[k] - __uint_as_float(whi[k]));
+            ahi[k] = __float_as_uint(xa[k]) & 0xffffe000u;
+            alo[k] = __float_as_uint(xa[k] - __uint_as_float(ahi[k]));
+        }
+        mma_tf32(d1, whi, __float_as_uint(m.x), __float_as_uint(m.y));
+        mma_tf32(d1, wlo, __float_as_uint(m.x), __float_as_uint(m.y));
+        mma_tf32(d2, ahi, __float_as_uint(q.x), __float_as_uint(q.y));
+        mma_tf32(d2, alo, __float_as_uint(q.x), __float_as_uint(q.y));
+    }
+    const int q0l = lane & ~3;
+#pragma unroll
+    for (int hi = 0; hi < 2; hi++) {
+        const float m0 = d1[2 * hi], m1 = d1[2 * hi + 1];
+        const float col = d2[2 * hi] + d2[2 * hi + 1];
+        const float S0 = __shfl_sync(0xffffffffu, m0, q0l);
+        const float Sx = __shfl_sync(0xffffffffu, m1, q0l);
+        const float Sy = __shfl_sync(0xffffffffu, m0, q0l + 1);
+        const int row = g + 8 * hi;
+        if (row < cnt && t < 3) {
+            const int j = jbase + row;
+            const float2 xy = *reinterpret_cast<const float2*>(&S.q0[kq][j]);
+            const uint32_t id = __float_as_uint(S.e[kq][j].x);
+            const float u = xy.x - X0s, v = xy.y - Y0s;         // dx = u - lx, dy = v - ly
+            const float a1 = fmaf(u, S0, -Sx);                   // sum w dx
+            const float a2 = fmaf(v, S0, -Sy);                   // sum w dy
+            const float o3 = fmaf(u, a1 - Sx, m1);               // sum w dx^2  = Sxx - 2u Sx + u^2 S0      (lane t = 1)
+            const float o4 = fmaf(-v, Sx, fmaf(u, a2, m0));      // sum w dx dy = Sxy - u Sy - v Sx + uv S0 (lane t = 2)
+            const float o5 = fmaf(v, a2 - Sy, m1);               // sum w dy^2  = Syy - 2v Sy + v^2 S0      (lane t = 2)
+            const float out0 = fsel(t == 0, m0, fsel(t == 1, a2, o4));
+            const float out1 = fsel(t == 0, a1, fsel(t == 1, o3, o5));
+            float* rowp = accum + (size_t)id * 12;
+            // an entry without a live lane has exactly zero sums: adding them is a no-op, so they are not sent
+            if (out0 != 0.f || out1 != 0.f) {
+                if (t == 0) { atomicAdd(rowp + 8, out0); atomicAdd(rowp + 3, out1); }
+                else red_add_v2(rowp + 2 + 2 * t, out0, out1);   // t = 1: columns 4, 5   t = 2: columns 6, 7
+            }
+            if (col != 0.f) atomicAdd(rowp + t, col);
+        }
+    }
+    __syncwarp();
+}
+
+template <int MINB>
+__global__ void __launch_bounds__(BL_THREADS, MINB)
+blend_bwd_v6_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                    const uint32_t* __restrict__ planes, uint32_t plane_words, int W, int H, const float* __restrict__ bg,
+                    const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
+                    float* __restrict__ accum, int gyv, const uint32_t* __restrict__ tile_order)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BwdSmemV6& SM = *reinterpret_cast<BwdSmemV6*>(smem_raw);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    WarpV6& S = SM.w[wid];
+    const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;                                  // see blend_fwd_v3_kernel
+    const uint32_t tile = tile_order ? tile_order[lin] : lin;
+    const uint32_t trow = tile / gridDim.x, bx = tile - trow * gridDim.x;
+    const uint32_t view = trow / (uint32_t)gyv, by = trow - view * (uint32_t)gyv;
+    const float X0s = (float)(bx * GSR_TILE + (wid & 1) * 8), Y0s = (float)(by * GSR_TILE + (wid >> 1) * 4);
+    const uint32_t px = bx * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t py = by * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t HW = (size_t)H * W;
+    const size_t pix = view * HW + (size_t)W * py + px;
+    dL_dpix += 2 * view * HW;                   // [V][3][H][W]: channel c of this pixel is dL_dpix[c * HW + pix]
+    const uint2 range = ranges[tile];
+
+    const float T_final = inside ? final_T[pix] : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
+    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
+    float Sd = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);     // see bwd_live_sd
+
+    // this pixel lane as a K index of the reduction: k-step sK, index tK + 4 bK
+    const int sK = lane >> 3, tK = (lane >> 1) & 3, bK = lane & 1;
+    // B1: the moment matrix (1, lx, ly, lx^2, lx ly, ly^2, 0, 0) in B-fragment order; reading lane l = (n = l >> 2, t = l & 3)
+    // of k-step s takes column n at the pixels (lx, ly) = (2t, s) and (2t + 1, s)
+    if (threadIdx.x < 128) {
+        const int s = threadIdx.x >> 5, l = threadIdx.x & 31, n = l >> 2;
+        const float ly = (float)s, lx0 = (float)(2 * (l & 3)), lx1 = lx0 + 1.f;
+        float2 m;
+        m.x = n == 0 ? 1.f : n == 1 ? lx0 : n == 2 ? ly : n == 3 ? lx0 * lx0 : n == 4 ? lx0 * ly : n == 5 ? ly * ly : 0.f;
+        m.y = n == 0 ? 1.f : n == 1 ? lx1 : n == 2 ? ly : n == 3 ? lx1 * lx1 : n == 4 ? lx1 * ly : n == 5 ? ly * ly : 0.f;
+        SM.b1[s][l] = m;
+    }
+    {
+        // B2: columns (r_hi, r_lo, g_hi, g_lo, b_hi, b_lo, 0, 0) of this warp's dL/dpixel; column n of this pixel lives at
+        // reading lane 4 n + tK, component bK
+        const float d[3] = {dp0, dp1, dp2};
+        float* col = reinterpret_cast<float*>(&S.b2[sK][tK]) + bK;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const float hi = __uint_as_float(__float_as_uint(d[c]) & 0xffffe000u);
+            col[(2 * c) * 8] = hi;
+            col[(2 * c + 1) * 8] = d[c] - hi;
+        }
+        col[6 * 8] = 0.f;
+        col[7 * 8] = 0.f;
+    }
+    // this lane's (w, at) slot of A row g, half hi: a_lo / a_hi + g * V6_GS  (see the layout above)
+    float* const a_lo = S.a + sK * V6_KS + tK * 8 + 4 * bK + 2 * (sK & 1);
+    float* const a_hi = S.a + sK * V6_KS + tK * 8 + 4 * bK + 2 - 2 * (sK & 1);
+
+    int warp_last = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+    warp_last = min(warp_last, (int)(range.y - range.x));
+    __syncthreads();                       // b1 is visible; the only block barrier
+    const int nch = (warp_last + 31) >> 5; // chunks of 32 list entries this warp has work in
+    if (nch == 0) return;
+    const uint32_t* plane = planes + (size_t)wid * plane_words + (range.x >> 5) + 16u * tile;
+    const uint32_t* tvals = vals + range.x;
+
+    // ---- work queue: step st = 0 .. nch-1 handles chunk nch-1-st (back to front); the words of 32 consecutive steps sit in
+    // one register per lane (wA: block blkA, wB: the block after it)
+    auto load_words = [&](int blk) -> uint32_t {
+        const int s = blk * 32 + lane;
+        return s < nch ? plane[nch - 1 - s] : 0u;
+    };
+    uint32_t wA = load_words(0), wB = load_words(1);
+    int blkA = 0, st_next = 0;
+    uint32_t qtail = 0;                                    // entries queued so far (warp-uniform)
+    const uint32_t above = ~(0xffffffffu >> lane);         // the bits lane `lane` ranks behind: it owns bit 31 - lane
+    {
+        // the top chunk may reach beyond the warp's last contributor
+        const int rem = warp_last - (nch - 1) * 32;        // 1 .. 32
+        if (lane == 0 && rem < 32) wA &= (1u << rem) - 1u;
+    }
+    auto fill = [&](uint32_t want) {                       // queue entries until `want` are there or the list is exhausted
+        while (qtail < want && st_next < nch) {
+            const uint32_t m = __shfl_sync(0xffffffffu, wA, st_next & 31);
+            const uint32_t base = (uint32_t)(nch - 1 - st_next) * 32u;
+            if ((m >> (31 - lane)) & 1u) S.queue[(qtail + __popc(m & above)) & (V6_QCAP - 1)] = base + 31u - (uint32_t)lane;
+            qtail += __popc(m);
+            st_next++;
+            if ((st_next & 31) == 0) { wA = wB; blkA++; wB = load_words(blkA + 1); }
+        }
+        __syncwarp();
+    };
+    // group k = queue entries [32k, 32k + 32); its size is final once `fill(32 (k + 1))` has returned
+    auto group_size = [&](uint32_t k) -> int { return (int)min(32u, qtail - min(qtail, 32u * k)); };
+    auto load_pos = [&](uint32_t k, uint32_t& pos, uint32_t& id) {      // lane's entry of group k: list position and Gaussian id
+        const bool v = lane < group_size(k);
+        pos = v ? S.queue[(32u * k + (uint32_t)lane) & (V6_QCAP - 1)] : 0u;
+        id = v ? tvals[pos] : 0u;
+    };
+    auto issue = [&](uint32_t k, uint32_t pos, uint32_t id) {           // gather group k into ring buffer k & 1
+        if (lane < group_size(k)) {
+            const int kb = k & 1;
+            const SplatRec* r = rec + id;
+            cp_async16(&S.q0[kb][lane], &r->q0);
+            cp_async16(&S.q1[kb][lane], &r->q1);
+            cp_async4(&S.e[kb][lane].z, &r->q2);
+            *reinterpret_cast<uint2*>(&S.e[kb][lane]) = make_uint2(id, pos);
+        }
+        cp_async_commit();
+    };
+
+    uint32_t posc, idc;
+    fill(64);
+    load_pos(0, posc, idc);
+    issue(0, posc, idc);
+    load_pos(1, posc, idc);
+#pragma unroll 1
+    for (uint32_t k = 0;; k++) {
+        const int n = group_size(k);
+        if (n == 0) break;                                  // (one empty cp.async group may still be pending: harmless)
+        fill(32u * (k + 3));
+        uint32_t posn, idn;
+        load_pos(k + 2, posn, idn);                         // ids two groups ahead
+        issue(k + 1, posc, idc);                            // records one group ahead
+        posc = posn; idc = idn;
+        cp_async_wait<1>();                                 // my records of group k have landed
+        __syncwarp();
+        const int kq = k & 1;
+        const float4* rq0 = S.q0[kq];
+        const float4* rq1 = S.q1[kq];
+        const float4* re = S.e[kq];
+#pragma unroll 1
+        for (int h = 0; h < 2; h++) {
+            const int cnt = min(16, n - 16 * h);            // entries of this half (warp-uniform)
+            if (cnt <= 0) break;
+            const int jb = 16 * h;
+#pragma unroll
+            for (int c = 0; c < 16; c += 2) {
+                if (c < cnt) {
+                    const int j0 = jb + c, j1 = j0 + 1;
+                    const float4 a0 = rq0[j0], c0 = rq1[j0], e0 = re[j0], a1 = rq0[j1], c1 = rq1[j1], e1 = re[j1];
+                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, __float_as_int(e0.y), last_contributor);
+                    EntryHead h1 = bwd_head(a1, c1, pxf, pyf, __float_as_int(e1.y), last_contributor);
+                    h1.live = h1.live && (c + 1 < cnt);     // odd count: the ring slot behind the last entry holds stale data
+                    float w0 = 0.f, at0 = 0.f, w1 = 0.f, at1 = 0.f;
+                    if (h0.live) bwd_live_sd(h0.alpha, h0.araw, c0.z, c0.w, e0.z, dp0, dp1, dp2, T, Sd, w0, at0);
+                    if (h1.live) bwd_live_sd(h1.alpha, h1.araw, c1.z, c1.w, e1.z, dp0, dp1, dp2, T, Sd, w1, at1);
+                    float* const s0 = ((c >> 3) ? a_hi : a_lo) + (c & 7) * V6_GS;
+                    float* const s1 = (((c + 1) >> 3) ? a_hi : a_lo) + ((c + 1) & 7) * V6_GS;
+                    *reinterpret_cast<float2*>(s0) = make_float2(w0, at0);
+                    *reinterpret_cast<float2*>(s1) = make_float2(w1, at1);
+                }
+            }
+            v6_flush(S, SM.b1, kq, jb, cnt, lane, X0s, Y0s, accum);
+        }
+        __syncwarp();                  // everyone has left ring buffer kq before the gather of group k + 2 overwrites it
+    }
+    cp_async_wait<0>();
+}
+
+// ------------------------------------------------------------------------------------------ launchers
+int launch_blend_forward(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+                         float* out_color, cudaStream_t s)
+{
+    const Options& o = options();
     const int gyv = (H + GSR_TILE - 1) / GSR_TILE;
     const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, gyv * V);
     const uint32_t pw = (uint32_t)blend_plane_words(R, W, gyv * V * GSR_TILE);
-    if (V > 1 && env_int("GSR_BLEND", 0) != 0) return GSR_EINVAL;        // comparison arms are single-view
-    const int variant = env_int("GSR_BLEND", 0);       // 0: v5 (needs the planes of blend_fwd_v3), 1 / 3 / 4: comparison arms
-    const uint32_t* lpt = env_int("GSR_LPT", 1) ? im.tile_order : nullptr;
-    if (env_int("GSR_BLEND", 0) == 1)
-        GSR_LAUNCH(blend_bwd_kernel, grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, dL_dpix,
-                   accum);
-    else if (env_int("GSR_BLEND", 0) == 3)
-        GSR_LAUNCH((blend_bwd_v3_kernel<4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   dL_dpix, accum);
-    else if (variant == 0) {
-        static bool attr5_set = false;
-        if (!attr5_set) {
-            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
-            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
-            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<4>)));
-            attr5_set = true;
-        }
-        const int ns = env_int("GSR_BWD_NS", 2), minb = env_int("GSR_BWD_MINB", 4);
-        if (ns == 4)
-            GSR_LAUNCH((blend_bwd_v5_kernel<4, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<4>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
-        else if (minb == 3)
+    const uint32_t* lpt = o.lpt ? im.tile_order : nullptr;
+    // comparison arms (test-only library): never taken unless a test or benchmark asked for them
+    if (o.blend_stats == 1) {
+        if (V > 1 || !g_arms.blend_stats) return GSR_EINVAL;
+        int rc = g_arms.blend_stats(R, W, H, g, b, im, s);
+        if (rc) return rc;
+    }
+    if (o.blend_arm == 1) {
+        if (V > 1 || !g_arms.blend_forward_plain) return GSR_EINVAL;
+        return g_arms.blend_forward_plain(R, W, H, bg, g, b, im, out_color, s);
+    }
+    if (o.blend_arm == 2) {
+        if (!g_arms.blend_forward_bulk) return GSR_EINVAL;
+        return g_arms.blend_forward_bulk(R, W, H, V, bg, g, b, im, out_color, s);
+    }
+    if (o.fwd_minb == 3)
+        GSR_LAUNCH((blend_fwd_v3_kernel<4, 3>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+                   out_color, b.scratch, pw, gyv, lpt);
+    else
+        GSR_LAUNCH((blend_fwd_v3_kernel<4, 4>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+                   out_color, b.scratch, pw, gyv, lpt);
+    return GSR_OK;
+}
+
+int launch_blend_backward(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+                          const float* dL_dpix, float* accum, cudaStream_t s)
+{
+    const Options& o = options();
+    const int gyv = (H + GSR_TILE - 1) / GSR_TILE;
+    const dim3 grid((W + GSR_TILE - 1) / GSR_TILE, gyv * V);
+    const uint32_t pw = (uint32_t)blend_plane_words(R, W, gyv * V * GSR_TILE);
+    const uint32_t* lpt = o.lpt ? im.tile_order : nullptr;
+    if (o.blend_arm == 1) {        // plain kernel of the test-only library (does not need the forward's classification words)
+        if (V > 1 || !g_arms.blend_backward_plain) return GSR_EINVAL;
+        return g_arms.blend_backward_plain(R, W, H, bg, g, b, im, dL_dpix, accum, s);
+    }
+    DeviceCtx* ctx = nullptr;
+    int rc;
+    if ((rc = device_ctx(&ctx))) return rc;
+    rc = ctx_once(ctx, 2u, [] {    // per device: opt in to the kernels' dynamic shared memory
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6)));
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6)));
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
+        return (int)GSR_OK;
+    });
+    if (rc) return rc;
+    if (o.bwd_variant == 5) {
+        if (o.bwd_minb == 3)
             GSR_LAUNCH((blend_bwd_v5_kernel<2, 3>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
                        bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
         else
             GSR_LAUNCH((blend_bwd_v5_kernel<2, 4>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
                        bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
     } else {
-        static bool attr_set = false;
-        if (!attr_set) {
-            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v4_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV4)));
-            GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v4_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV4)));
-            attr_set = true;
-        }
-        if (env_int("GSR_BWD_MINB", 4) == 3)
-            GSR_LAUNCH((blend_bwd_v4_kernel<3>), grid, BL_THREADS, sizeof(BwdSmemV4), s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T,
-                       im.n_contrib, dL_dpix, accum);
+        if (o.bwd_minb == 2)
+            GSR_LAUNCH((blend_bwd_v6_kernel<2>), grid, BL_THREADS, sizeof(BwdSmemV6), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
         else
-            GSR_LAUNCH((blend_bwd_v4_kernel<4>), grid, BL_THREADS, sizeof(BwdSmemV4), s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T,
-                       im.n_contrib, dL_dpix, accum);
+            GSR_LAUNCH((blend_bwd_v6_kernel<3>), grid, BL_THREADS, sizeof(BwdSmemV6), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
+                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
     }
     return GSR_OK;
 }
 
 }  // namespace gsr
-
-// debug hook (not declared in include/gsr.h): reads and optionally clears the counters of blend_stats_kernel
-extern "C" int gsr_debug_blend_stats(unsigned long long* out16, int reset)
-{
-    if (out16 && cudaMemcpyFromSymbol(out16, gsr::g_blend_stats, sizeof(unsigned long long) * 16) != cudaSuccess) return GSR_ECUDA;
-    if (reset) {
-        unsigned long long z[16] = {0};
-        if (cudaMemcpyToSymbol(gsr::g_blend_stats, z, sizeof z) != cudaSuccess) return GSR_ECUDA;
-    }
-    return GSR_OK;
-}

@@ -6,6 +6,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <atomic>
+#include <mutex>
+#include <vector>
 #include "../../include/gsr.h"
 
 #define GSR_TILE 16                 // reference config.h:16-17 (BLOCK_X = BLOCK_Y = 16), part of the bit-exact contract
@@ -15,9 +18,8 @@
 namespace gsr {
 
 // ---------------------------------------------------------------- error / launch bookkeeping
-extern unsigned long long g_launches;          // api.cu
-extern char g_last_cuda_error[256];            // api.cu
-int record_cuda_error(cudaError_t e, const char* where);
+extern std::atomic<unsigned long long> g_launches;      // api.cu
+int record_cuda_error(cudaError_t e, const char* where);    // the message is kept per host thread
 
 #define GSR_CUDA(call)                                                           \
     do {                                                                         \
@@ -161,9 +163,6 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
 int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im, cudaStream_t s, int seg_items = 0, int V = 1);
 // emits instances in depth order, splits them stably by tile id, writes vals + tile ranges
 int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
-// comparison arm only (bench / tests): the reference's formulation, cub::DeviceRadixSort on 64-bit keys
-int launch_tile_split_cub(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
-size_t cub_sort_scratch_bytes(long long R);
 
 // generic stable radix sort of (u32 key, identity value) pairs on all 32 key bits (sort.cu); ctl = radix_ctl_words(n)
 // words of control state, zeroed by the call unless ctl_zeroed
@@ -181,6 +180,78 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
 // knn.cu
 int launch_dist2(int P, const float* points, float* out, GsrAlloc scratch, cudaStream_t s);
 
-int env_int(const char* name, int dflt);
+// ---------------------------------------------------------------- tuning options (context.cu)
+// Read from the environment ONCE, at the first call into the library (GSR_<NAME>); tests and benchmarks change them through
+// gsr_debug_set_option().  The product defaults are the values below; nothing calls getenv on the hot path.
+struct Options {
+    int bwd_variant = 6;        // blending backward kernel: 6 = blend_bwd_v6_kernel, 5 = blend_bwd_v5_kernel (round 1)
+    int lpt = 1;                // blending kernels take their tiles longest list first
+    int fwd_minb = 4;           // __launch_bounds__ min blocks of the forward blending kernel (3 or 4)
+    int bwd_minb = 3;           // same for the backward (v5: 3 or 4; v6: 3)
+    int side_stream = 1;        // tile-count kernels on a side stream next to the depth sort
+    int bwd_side = 1;           // SH backward on a side stream next to the cov/projection backward
+    int sh_split = 1;           // dedicated M = 16 SH backward kernel
+    int depth_seg_items = -1;   // >= 0: batched calls sort the depth keys in runs of whole views (comparison arm)
+    // comparison arms: honoured only when the test-only library libgsr_b200_arms.so is loaded (else GSR_EINVAL)
+    int blend_arm = 0;          // 1: plain blending kernels (no culling)   2: forward staging through cp.async.bulk + mbarrier
+    int sort_cub = 0;           // 1: cub::DeviceRadixSort on the reference's 64-bit keys
+    int blend_stats = 0;        // 1: run the statistics kernel next to the forward
+};
+Options& options();
+
+// entry points of the test-only comparison arms (arms/*.cu -> libgsr_b200_arms.so); all null in the product library
+struct ArmHooks {
+    int (*blend_forward_plain)(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+                               float* out_color, cudaStream_t s);
+    int (*blend_backward_plain)(long long R, int W, int H, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+                                const float* dL_dpix, float* accum, cudaStream_t s);
+    int (*blend_forward_bulk)(long long R, int W, int H, int V, const float* bg, const GeomView& g, const BinView& b, const ImgView& im,
+                              float* out_color, cudaStream_t s);
+    int (*blend_stats)(long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
+    int (*tile_split_cub)(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
+    size_t (*cub_sort_scratch_bytes)(long long R);
+};
+extern ArmHooks g_arms;
+void register_arms(const ArmHooks& h);
+
+// ---------------------------------------------------------------- per-device state (context.cu)
+// Everything the library keeps between calls lives here, one instance per CUDA device, created on first use under a
+// mutex: side streams with their fork / join events (one set per caller stream, so calls issued from different streams
+// do not serialise on a shared side stream), pinned landing slots of the R read-back (one per forward call in flight),
+// the gradient fence, and the per-device "function attributes set" flags.  Host threads may call into the library
+// concurrently, on the same or on different devices.
+struct SideStream {
+    cudaStream_t user = nullptr, side = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+struct RSlot {
+    uint32_t* host = nullptr;       // 64 pinned bytes
+    cudaEvent_t ev = nullptr;
+    bool busy = false;
+};
+struct DeviceCtx {
+    int device = -1;
+    std::mutex mu;                  // guards the vectors and flags below
+    std::vector<SideStream> sides[2];   // 0: forward (tile kernels), 1: backward (SH kernel)
+    std::vector<RSlot*> rslots;
+    unsigned attrs_set = 0;         // bit per kernel family whose cudaFuncSetAttribute calls were made on this device
+    std::mutex fence_mu;            // serialises stage 5 (read-modify-write of the caller's gradient buffers) in host call order
+    cudaEvent_t grad_fence = nullptr;
+    bool fence_recorded = false;
+};
+int device_ctx(DeviceCtx** out);                                                   // of the current device
+int ctx_side_stream(DeviceCtx* c, int which, cudaStream_t user, SideStream* out);  // created on first use
+int ctx_acquire_rslot(DeviceCtx* c, RSlot** out);
+void ctx_release_rslot(DeviceCtx* c, RSlot* r);
+// runs fn() once per device and kernel family (cudaFuncSetAttribute is per device)
+template <class F>
+static inline int ctx_once(DeviceCtx* c, unsigned bit, F fn)
+{
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (c->attrs_set & bit) return GSR_OK;
+    const int rc = fn();
+    if (rc == GSR_OK) c->attrs_set |= bit;
+    return rc;
+}
 
 }  // namespace gsr

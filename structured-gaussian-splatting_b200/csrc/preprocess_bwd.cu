@@ -773,27 +773,27 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
     k.acc = a.accumulate;
     k.sh_done = 0;
     const bool split = a.shs && a.shs_rest && a.M > 1;      // DC and the other coefficients in two arrays (M == 16, checked by the API)
-    const bool sh_fast = split || (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && env_int("GSR_SH_SPLIT", 1));
+    const bool sh_fast = split || (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && options().sh_split);
     // The SH kernel and preprocess_bwd_kernel are both HBM-bound and share one output only (dL/dmean3D): with that output
     // turned into atomic adds they run side by side on two streams (the pair reaches a higher fraction of the HBM peak than
     // either alone) and are joined before this function returns.
-    static cudaStream_t side = nullptr;
-    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    const bool forked = sh_fast && env_int("GSR_BWD_SIDE", 1) != 0;
+    // (the side stream and its events belong to the device context, one set per caller stream)
+    const bool forked = sh_fast && options().bwd_side != 0;
     cudaStream_t main_s = s;
     unsigned acc_flags = a.accumulate;
+    SideStream ss;
     if (forked) {
-        if (!side) {
-            GSR_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
-            GSR_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-            GSR_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
-        }
+        DeviceCtx* ctx = nullptr;
+        int rc0;
+        if ((rc0 = device_ctx(&ctx)) || (rc0 = ctx_side_stream(ctx, 1, main_s, &ss))) return rc0;
+    }
+    if (forked) {
         if (!(a.accumulate & GSR_ACC_MEAN3D)) GSR_CUDA(cudaMemsetAsync(a.dL_dmean3D, 0, sizeof(float) * 3 * (size_t)a.P, main_s));
         acc_flags |= ACC_ATOMIC_M3;
         k.acc = acc_flags;
-        GSR_CUDA(cudaEventRecord(ev_fork, main_s));
-        GSR_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
-        s = side;
+        GSR_CUDA(cudaEventRecord(ss.fork, main_s));
+        GSR_CUDA(cudaStreamWaitEvent(ss.side, ss.fork, 0));
+        s = ss.side;
     }
     if (split) {
         if (((((size_t)a.shs) | ((size_t)a.dL_dsh) | ((size_t)a.shs_rest) | ((size_t)a.dL_dsh_rest)) & 15) != 0) return GSR_EINVAL;
@@ -804,7 +804,7 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
             GSR_LAUNCH(sh_bwd_m16_views_kernel<true>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii,
                        a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, a.shs_rest, a.dL_dsh_rest);
         k.sh_done = 1;
-    } else if (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && env_int("GSR_SH_SPLIT", 1)) {
+    } else if (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && options().sh_split) {
         if (V == 1)
             GSR_LAUNCH(sh_bwd_m16_kernel<false>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs,
                        g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, (const float*)nullptr, (float*)nullptr);
@@ -814,7 +814,7 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
         k.sh_done = 1;
     }
     if (forked) {
-        GSR_CUDA(cudaEventRecord(ev_join, side));
+        GSR_CUDA(cudaEventRecord(ss.join, ss.side));
         s = main_s;
     }
     const bool with_sh = !(k.sh_done || !a.shs);
@@ -825,7 +825,7 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
         if (!with_sh) GSR_LAUNCH((preprocess_bwd_kernel<false, true>), cdiv(a.P, 256), 256, 0, s, k, cam);
         else GSR_LAUNCH((preprocess_bwd_kernel<true, true>), cdiv(a.P, 256), 256, 0, s, k, cam);
     }
-    if (forked) GSR_CUDA(cudaStreamWaitEvent(main_s, ev_join, 0));
+    if (forked) GSR_CUDA(cudaStreamWaitEvent(main_s, ss.join, 0));
     return GSR_OK;
 }
 

@@ -482,24 +482,30 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
     const int cblocks = max(1, min(cdiv(Pper, 4096), max(1, 296 / V)));
     // The two tile kernels depend on preprocess only and the radix passes do not need them: they run on a side stream next to
     // the depth sort (both are small latency-bound launches) and are joined before this function returns.
-    static cudaStream_t side = nullptr;
-    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    const bool forked = env_int("GSR_SIDE_STREAM", 1) != 0;
+    // (the side stream and its fork / join events belong to the device context, one set per caller stream)
+    const bool forked = options().side_stream != 0;
     cudaStream_t main_s = s;
+    DeviceCtx* ctx = nullptr;
+    SideStream ss;
+    {
+        int rc0;
+        if ((rc0 = device_ctx(&ctx))) return rc0;
+        if (forked && (rc0 = ctx_side_stream(ctx, 0, main_s, &ss))) return rc0;
+    }
     if (forked) {
-        if (!side) {
-            GSR_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
-            GSR_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-            GSR_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
-        }
-        GSR_CUDA(cudaEventRecord(ev_fork, main_s));
-        GSR_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
-        s = side;
+        GSR_CUDA(cudaEventRecord(ss.fork, main_s));
+        GSR_CUDA(cudaStreamWaitEvent(ss.side, ss.fork, 0));
+        s = ss.side;
     }
     if (smem <= 160 * 1024) {
         if (smem > 40 * 1024) {
-            GSR_CUDA(cudaFuncSetAttribute(tile_count_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            GSR_CUDA(cudaFuncSetAttribute(tile_prefix_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            // once per device: the largest band these launches accept
+            int rc0 = ctx_once(ctx, 1u, [] {
+                GSR_CUDA(cudaFuncSetAttribute(tile_count_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+                GSR_CUDA(cudaFuncSetAttribute(tile_prefix_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+                return (int)GSR_OK;
+            });
+            if (rc0) return rc0;
         }
         GSR_LAUNCH(tile_count_kernel<true>, dim3(cblocks, V), 1024, smem, s, Pper, gyv, sc.rect, gx + 1, band, im.tile_diff);
         GSR_LAUNCH(tile_prefix_kernel<true>, V, 1024, smem, s, gx, gyv, im.tile_diff, im.ranges, sc.tile_hist, td, sc.view_status, im.tile_order);
@@ -509,7 +515,7 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
         GSR_LAUNCH(tile_prefix_kernel<false>, V, 1024, 0, s, gx, gyv, im.tile_diff, im.ranges, sc.tile_hist, td, sc.view_status, im.tile_order);
     }
     if (forked) {
-        GSR_CUDA(cudaEventRecord(ev_join, side));
+        GSR_CUDA(cudaEventRecord(ss.join, ss.side));
         s = main_s;
     }
     // depth keys were written by preprocess; the control block was zeroed before it
@@ -525,7 +531,7 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
             ctl += radix_ctl_words((uint32_t)n);
         }
     }
-    if (forked) GSR_CUDA(cudaStreamWaitEvent(main_s, ev_join, 0));      // join even when a launch failed
+    if (forked) GSR_CUDA(cudaStreamWaitEvent(main_s, ss.join, 0));      // join even when a launch failed
     return rc;
 }
 

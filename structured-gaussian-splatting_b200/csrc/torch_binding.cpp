@@ -12,10 +12,16 @@
 #include <torch/extension.h>
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
+#include <functional>
 #include <tuple>
 #include <string>
 #include <vector>
 #include "../../include/gsr.h"
+
+// debug hooks of the core library (csrc/context.cu; not part of the public C ABI): tuning options and the comparison arms
+extern "C" int gsr_debug_set_option(const char* name, int value);
+extern "C" int gsr_debug_get_option(const char* name, int* value);
+extern "C" int gsr_debug_arms_loaded(void);
 
 namespace {
 
@@ -107,9 +113,13 @@ rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3
 }
 
 // returns the reference's eight gradients plus dL_dsh_rest (empty unless sh_rest is given)
-std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
-           torch::Tensor>
-rasterize_gaussians_backward_split(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+using BwdResult = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+                             torch::Tensor, torch::Tensor>;
+
+// n_chunks > 0: the per-Gaussian backward runs in n_chunks ranges of Gaussians (gsr_backward_staged) and `after_chunk(g0, g1)`
+// is called on the host after each range has been queued (the data-parallel step starts that range's all-reduce there)
+static BwdResult
+backward_core(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
                                   const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
                                   const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
                                   const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
@@ -118,7 +128,8 @@ rasterize_gaussians_backward_split(const torch::Tensor& background, const torch:
                                   const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
                                   const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
                                   const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate,
-                                  const torch::Tensor& sh_rest, const torch::Tensor& into_sh_rest)
+                                  const torch::Tensor& sh_rest, const torch::Tensor& into_sh_rest, int n_chunks,
+                                  const std::function<void(int, int)>& after_chunk)
 {
     // Extension of the reference entry point: a non-empty `into_*` tensor (contiguous fp32 CUDA, same element count as
     // the gradient) receives that gradient directly - overwritten, or added to when `accumulate` - and the
@@ -195,9 +206,60 @@ rasterize_gaussians_backward_split(const torch::Tensor& background, const torch:
         a.dL_drot = has_sr ? (t_rt ? t_rt : dL_drotations.data_ptr<float>()) : nullptr;
         a.debug = debug;
         a.accumulate = acc_bits;
-        check(gsr_backward(&a, current_stream()), "rasterize_gaussians_backward");
+        if (n_chunks <= 0) {
+            check(gsr_backward(&a, current_stream()), "rasterize_gaussians_backward");
+        } else {
+            check(gsr_backward_staged(&a, 1, 0, 0, current_stream()), "rasterize_gaussians_backward (blending)");
+            const int rows = (((P + n_chunks - 1) / n_chunks) + 127) / 128 * 128;      // ranges start on multiples of 128
+            for (int g0 = 0; g0 < P; g0 += rows) {
+                const int g1 = std::min(P, g0 + rows);
+                check(gsr_backward_staged(&a, 2, g0, g1, current_stream()), "rasterize_gaussians_backward (per-Gaussian range)");
+                if (after_chunk) after_chunk(g0, g1);
+            }
+        }
     }
     return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, dL_dsh_rest);
+}
+
+BwdResult
+rasterize_gaussians_backward_split(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                                  const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
+                                  const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                                  const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                                  const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                                  const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
+                                  const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
+                                  const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
+                                  const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate,
+                                  const torch::Tensor& sh_rest, const torch::Tensor& into_sh_rest)
+{
+    return backward_core(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                         tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug,
+                         into_means3D, into_opacity, into_sh, into_scales, into_rotations, accumulate, sh_rest, into_sh_rest, 0, nullptr);
+}
+
+// rasterize_gaussians_backward_into with the per-Gaussian backward in `n_chunks` ranges; `after_chunk(g0, g1)` (a Python
+// callable) runs after each range has been queued on the current stream.  Holds the GIL (it calls back into Python).
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_backward_chunked(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                                     const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
+                                     const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                                     const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                                     const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                                     const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
+                                     const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
+                                     const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
+                                     const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate,
+                                     const int n_chunks, py::object after_chunk)
+{
+    const torch::Tensor e = torch::empty({0});
+    std::function<void(int, int)> cb;
+    if (!after_chunk.is_none()) cb = [&after_chunk](int g0, int g1) { after_chunk(g0, g1); };
+    auto r = backward_core(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                           tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug,
+                           into_means3D, into_opacity, into_sh, into_scales, into_rotations, accumulate, e, e, n_chunks < 1 ? 1 : n_chunks, cb);
+    return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r), std::get<3>(r), std::get<4>(r), std::get<5>(r),
+                           std::get<6>(r), std::get<7>(r));
 }
 
 std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
@@ -595,13 +657,30 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
     m.def("densify_stats", &densify_stats);
     m.def("l1_ssim_loss", &l1_ssim_loss);
     m.def("l1_loss", &l1_loss);
-    m.def("rasterize_gaussians_batched", &rasterize_gaussians_batched);
-    m.def("rasterize_gaussians_batched_backward", &rasterize_gaussians_batched_backward);
-    m.def("rasterize_gaussians", &rasterize_gaussians);
-    m.def("rasterize_gaussians_split", &rasterize_gaussians_split);
-    m.def("rasterize_gaussians_backward_split", &rasterize_gaussians_backward_split);
-    m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
-    m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into);
+    // The rasterizer entry points release the GIL (they touch no Python object): the forward blocks the host once for
+    // num_rendered, and a trainer driving two CUDA streams from two Python threads must not serialise on that wait.
+    // (The reference binding holds the GIL throughout: SURVEY 8(b).)
+    using nogil = py::call_guard<py::gil_scoped_release>;
+    m.def("rasterize_gaussians_batched", &rasterize_gaussians_batched, nogil());
+    m.def("rasterize_gaussians_batched_backward", &rasterize_gaussians_batched_backward, nogil());
+    m.def("rasterize_gaussians", &rasterize_gaussians, nogil());
+    m.def("rasterize_gaussians_split", &rasterize_gaussians_split, nogil());
+    m.def("rasterize_gaussians_backward_split", &rasterize_gaussians_backward_split, nogil());
+    m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward, nogil());
+    m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into, nogil());
+    m.def("rasterize_gaussians_backward_chunked", &rasterize_gaussians_backward_chunked);
+    m.def("set_option", [](const std::string& name, int value) {
+        int prev = 0;
+        if (gsr_debug_get_option(name.c_str(), &prev) != GSR_OK || gsr_debug_set_option(name.c_str(), value) != GSR_OK)
+            throw std::runtime_error("unknown gsr option: " + name);
+        return prev;
+    });
+    m.def("get_option", [](const std::string& name) {
+        int v = 0;
+        if (gsr_debug_get_option(name.c_str(), &v) != GSR_OK) throw std::runtime_error("unknown gsr option: " + name);
+        return v;
+    });
+    m.def("arms_loaded", []() { return gsr_debug_arms_loaded() != 0; });
     m.def("mark_visible", &mark_visible);
     m.def("distCUDA2", &distCUDA2);
     m.def("export_binning", &export_binning);

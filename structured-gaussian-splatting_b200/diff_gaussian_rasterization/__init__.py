@@ -8,6 +8,7 @@ Public surface mirrors the reference package
   _RasterizeGaussians            (:44-155)   autograd.Function, same argument / gradient order
 so gaussian_renderer/__init__.py, train.py, train_lgm.py and render.py call it unchanged.
 """
+import weakref
 from typing import NamedTuple
 
 import torch
@@ -41,7 +42,22 @@ def _call_with_snapshot(fn, args, debug, dump_name, stage):
 # its gradient written (mode "overwrite") or added (mode "accumulate") by the backward kernels themselves, and
 # autograd receives None for it.  Inputs that are not such leaves (the reference trainer passes activations)
 # are unaffected, as is everything when the mode is None.
+#
+# Contract (checked in backward; a violated check falls back to handing the gradient to autograd, which is always right):
+#   * the target is the leaf's .grad AS IT IS WHEN BACKWARD RUNS: if .grad was rebound or set to None between forward and
+#     backward (optimizer.zero_grad(set_to_none=True)), nothing is written in place for that leaf;
+#   * "overwrite" replaces what the buffer holds, so at most ONE render of a leaf may be pending in that mode: a second
+#     forward of the same leaf before the first one's backward raises (it would silently drop the first view's gradient);
+#     use "accumulate" for the other views of a step, as gsr_b200.dp.backward_views does;
+#   * in "accumulate" mode dL/dmean3D is added with float atomics from two concurrently running kernels: sums are exact
+#     to rounding but not bit-reproducible from run to run (like the reference's atomicAdd gradients).
 _GRAD_MODE = None
+_PENDING_OVERWRITE = {}          # data_ptr of a .grad buffer -> weak reference to the token of the pending "overwrite" render
+
+
+class _Token:
+    """lives as long as the autograd node of a pending render (dropped graphs release their claim automatically)"""
+    __slots__ = ("__weakref__",)
 
 
 def set_grad_mode(mode):
@@ -59,6 +75,19 @@ def _grad_target(t):
             and g.is_contiguous() and g.numel() == t.numel()):
         return g
     return None
+
+
+# ---- extension (off by default): the per-Gaussian backward of a view in ranges of Gaussians, with a host callback after
+# each range (gsr_backward_staged): gsr_b200.dp starts the all-reduce of a range's gradients from it.  Only honoured
+# together with a grad mode (the gradients must land in caller-owned buffers for the callback to see them).
+_CHUNK_HOOK = None               # (n_chunks, callable(g_begin, g_end)) or None
+
+
+def set_chunk_hook(hook):
+    """hook = (n_chunks, callback) or None; returns the previous hook."""
+    global _CHUNK_HOOK
+    prev, _CHUNK_HOOK = _CHUNK_HOOK, hook
+    return prev
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -90,7 +119,17 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.num_rendered = num_rendered
         ctx.grad_mode = _GRAD_MODE
         if _GRAD_MODE is not None:
-            ctx.grad_targets = tuple(_grad_target(t) for t in (means3D, opacities, sh, scales, rotations))
+            ctx.grad_leaves = (means3D, opacities, sh, scales, rotations)
+            ctx.grad_targets = tuple(_grad_target(t) for t in ctx.grad_leaves)
+            if _GRAD_MODE == "overwrite" and torch.is_grad_enabled():
+                ctx.overwrite_token = _Token()
+                for g in ctx.grad_targets:
+                    if g is not None:
+                        other = _PENDING_OVERWRITE.get(g.data_ptr())
+                        if other is not None and other() is not None:
+                            raise RuntimeError("set_grad_mode('overwrite'): this parameter already has a pending render whose "
+                                               "backward will overwrite its .grad; use 'accumulate' for further views")
+                        _PENDING_OVERWRITE[g.data_ptr()] = weakref.ref(ctx.overwrite_token)
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
                               binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
@@ -110,12 +149,26 @@ class _RasterizeGaussians(torch.autograd.Function):
              grad_rotations) = _call_with_snapshot(_C.rasterize_gaussians_backward, args, rs.debug, "snapshot_bw.dump", "backward")
         else:
             empty = torch.Tensor([])
-            into = tuple(empty if t is None else t for t in ctx.grad_targets)
-            (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
-             grad_rotations) = _call_with_snapshot(_C.rasterize_gaussians_backward_into,
-                                                   args + into + (ctx.grad_mode == "accumulate",), rs.debug, "snapshot_bw.dump",
-                                                   "backward")
-            t_m3, t_op, t_sh, t_sc, t_rt = ctx.grad_targets
+            if ctx.grad_mode == "overwrite":
+                for g in ctx.grad_targets:
+                    if g is not None:
+                        _PENDING_OVERWRITE.pop(g.data_ptr(), None)
+            # the target must still be the leaf's .grad: a buffer rebound or dropped since the forward gets nothing in place
+            targets = tuple(g if (g is not None and getattr(leaf, "grad", None) is g) else None
+                            for g, leaf in zip(ctx.grad_targets, ctx.grad_leaves))
+            into = tuple(empty if t is None else t for t in targets)
+            hook = _CHUNK_HOOK
+            if hook is not None and all(t is not None for t in targets):
+                (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+                 grad_rotations) = _call_with_snapshot(_C.rasterize_gaussians_backward_chunked,
+                                                       args + into + (ctx.grad_mode == "accumulate", int(hook[0]), hook[1]),
+                                                       rs.debug, "snapshot_bw.dump", "backward")
+            else:
+                (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+                 grad_rotations) = _call_with_snapshot(_C.rasterize_gaussians_backward_into,
+                                                       args + into + (ctx.grad_mode == "accumulate",), rs.debug,
+                                                       "snapshot_bw.dump", "backward")
+            t_m3, t_op, t_sh, t_sc, t_rt = targets
             # written in place by the kernels: autograd gets None for these inputs
             grad_means3D = None if t_m3 is not None else grad_means3D
             grad_opacities = None if t_op is not None else grad_opacities

@@ -6,6 +6,7 @@ import ctypes
 import math
 import os
 import re
+import subprocess
 import sys
 
 import numpy as np
@@ -233,7 +234,7 @@ def test_cabi_exports_every_declared_symbol():
     for s in sorted(declared):
         assert hasattr(lib, s), "libgsr_b200.so does not export %s" % s
     lib.gsr_abi_version.restype = ctypes.c_int
-    assert lib.gsr_abi_version() == 2
+    assert lib.gsr_abi_version() == 3
     lib.gsr_strerror.restype = ctypes.c_char_p
     assert b"precomputed" in lib.gsr_strerror(-4)
     lib.gsr_geom_bytes.restype = ctypes.c_size_t
@@ -242,6 +243,19 @@ def test_cabi_exports_every_declared_symbol():
     # argument validation happens before any CUDA call
     assert lib.gsr_forward(None, None, None, None, None, None) == -1
     assert lib.gsr_backward(None, None) == -1
+    assert lib.gsr_backward_staged(None, 3, 0, -1, None) == -1
+    # the product library carries no comparison arms (they live in the test-only libgsr_b200_arms.so) ...
+    assert lib.gsr_debug_arms_loaded() == 0
+    assert lib.gsr_debug_set_option(b"blend_arm", 1) == 0 and lib.gsr_debug_set_option(b"no_such_option", 1) == -1
+    assert lib.gsr_debug_set_option(b"blend_arm", 0) == 0
+    syms = subprocess.run(["nm", "-D", "--defined-only", os.path.join(util.ROOT, "structured-gaussian-splatting_b200", "gsr_b200",
+                                                                      "libgsr_b200.so")], stdout=subprocess.PIPE, text=True).stdout
+    assert "blend_fwd_v3_kernel" in syms and "blend_bwd_v6_kernel" in syms
+    for retired in ("blend_stats_kernel", "blend_bwd_v4_kernel", "blend_bwd_v3_kernel", "cub_emit_kernel", "DeviceRadixSort"):
+        assert retired not in syms, retired
+    # ... and reads no environment variable on the hot path: getenv is referenced from context.cu's one-time reader only
+    arms = ctypes.CDLL(os.path.join(util.ROOT, "structured-gaussian-splatting_b200", "gsr_b200", "libgsr_b200_arms.so"), mode=ctypes.RTLD_GLOBAL)
+    assert hasattr(arms, "gsr_debug_blend_stats")
 
 
 def test_python_api_surface_and_argument_checks():
