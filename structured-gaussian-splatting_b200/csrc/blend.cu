@@ -428,104 +428,161 @@ blend_bwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
 // s = L >> 3, t = (L >> 1) & 3, b = L & 1: its STS.64 of (w, at) is bank-conflict free (the 16 lanes of a store phase
 // have s in {0,1} or {2,3}; the parity swap spreads them over all 32 banks) and so is the reader's LDS.128 (row stride
 // 36 = 4 mod 32).  The k-step loop is unrolled, so the parity swap costs no instruction on the reading side.
-constexpr int V6_GS = 36;               // floats per row g of a k-step
-constexpr int V6_KS = 8 * V6_GS;        // floats per k-step
 constexpr int V6_QCAP = 128;            // queue capacity (power of two; <= 95 live entries, see the fill loop)
+// SLOTS = 16: w and at in two A operands of 16 entries each (rows padded to 36 floats, 288 per k-step);
+// SLOTS = 8:  one A operand, rows 0-7 = w, rows 8-15 = at of 8 entries ([k-step][entry][t][b][w | at], 16 floats per
+//             entry, 144 per k-step): half the shared memory (4 CTAs per SM instead of 3) for twice the HMMAs per entry
+template <int SLOTS> struct V6Layout;
+template <> struct V6Layout<16> { static constexpr int GS = 36, KS = 8 * 36; };
+template <> struct V6Layout<8>  { static constexpr int GS = 16, KS = 144; };
+template <int SLOTS>
 struct __align__(16) WarpV6 {
     float4 q0[2][32];                   // ring: pix.x pix.y conic.x conic.y
     float4 q1[2][32];                   //       conic.z opacity r g
     float4 e[2][32];                    //       Gaussian id (bits), list position (bits), colour b, unused
-    float  a[4 * V6_KS];
+    float  a[4 * V6Layout<SLOTS>::KS];
     float2 b2[4][32];                   // B2 fragments of this warp's dL/dpixel (hi, lo per channel)
     uint32_t queue[V6_QCAP];
 };
+template <int SLOTS>
 struct __align__(16) BwdSmemV6 {
-    WarpV6 w[8];
+    WarpV6<SLOTS> w[8];
     float2 b1[4][32];                   // B1 fragments (moment matrix), same for all warps
 };
 
-// Reduces rows [0, cnt) of the warp's A operands (entries jbase .. jbase + cnt - 1 of ring buffer kq) over the 32 lanes and
-// commits them.  Fragments of m16n8k8 (g = lane >> 2, t = lane & 3): A rows g / g+8 at k = t / t+4, B column g at
-// k = t / t+4, D rows g / g+8, columns 2t, 2t+1.  Columns of D1: S0 Sx | Sy Sxx | Sxy Syy | - -  (moments of w about the
-// sub-tile origin), of D2: r_hi r_lo | g_hi g_lo | b_hi b_lo | - -.
-__device__ __forceinline__ void v6_flush(const WarpV6& S, const float2 (*b1)[32], int kq, int jbase, int cnt, int lane, float X0s,
-                                         float Y0s, float* __restrict__ accum)
+// x = hi + lo with hi exact in tf32 (the tensor core ignores the 13 low mantissa bits)
+__device__ __forceinline__ void split_tf32(const float (&x)[4], uint32_t (&hi)[4], uint32_t (&lo)[4])
 {
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        hi[k] = __float_as_uint(x[k]) & 0xffffe000u;
+        lo[k] = __float_as_uint(x[k] - __uint_as_float(hi[k]));
+    }
+}
+
+// one reduced row (entry j of ring buffer kq): moments m0, m1 = columns 2t, 2t+1 of D1 (S0 Sx | Sy Sxx | Sxy Syy | - -,
+// about the sub-tile origin), col = colour sum t; shifted to the Gaussian's centre and committed
+template <int SLOTS>
+__device__ __forceinline__ void v6_commit(const WarpV6<SLOTS>& S, int kq, int j, bool valid, int lane, float m0, float m1, float col,
+                                          float X0s, float Y0s, float* __restrict__ accum)
+{
+    const int t = lane & 3, q0l = lane & ~3;
+    const float S0 = __shfl_sync(0xffffffffu, m0, q0l);
+    const float Sx = __shfl_sync(0xffffffffu, m1, q0l);
+    const float Sy = __shfl_sync(0xffffffffu, m0, q0l + 1);
+    if (valid && t < 3) {
+        const float2 xy = *reinterpret_cast<const float2*>(&S.q0[kq][j]);
+        const uint32_t id = __float_as_uint(S.e[kq][j].x);
+        const float u = xy.x - X0s, v = xy.y - Y0s;         // dx = u - lx, dy = v - ly
+        const float a1 = fmaf(u, S0, -Sx);                   // sum w dx
+        const float a2 = fmaf(v, S0, -Sy);                   // sum w dy
+        const float o3 = fmaf(u, a1 - Sx, m1);               // sum w dx^2  = Sxx - 2u Sx + u^2 S0      (lane t = 1)
+        const float o4 = fmaf(-v, Sx, fmaf(u, a2, m0));      // sum w dx dy = Sxy - u Sy - v Sx + uv S0 (lane t = 2)
+        const float o5 = fmaf(v, a2 - Sy, m1);               // sum w dy^2  = Syy - 2v Sy + v^2 S0      (lane t = 2)
+        const float out0 = fsel(t == 0, m0, fsel(t == 1, a2, o4));
+        const float out1 = fsel(t == 0, a1, fsel(t == 1, o3, o5));
+        float* rowp = accum + (size_t)id * 12;
+        // an entry without a live lane has exactly zero sums: adding them is a no-op, so they are not sent
+        if (out0 != 0.f || out1 != 0.f) {
+            if (t == 0) { atomicAdd(rowp + 8, out0); atomicAdd(rowp + 3, out1); }
+            else red_add_v2(rowp + 2 + 2 * t, out0, out1);   // t = 1: columns 4, 5   t = 2: columns 6, 7
+        }
+        if (col != 0.f) atomicAdd(rowp + t, col);
+    }
+}
+
+// Reduces rows [0, cnt) of the warp's A operand(s) (entries jbase .. jbase + cnt - 1 of ring buffer kq) over the 32 lanes
+// and commits them.  Fragments of m16n8k8 (g = lane >> 2, t = lane & 3): A rows g / g+8 at k = t / t+4, B column g at
+// k = t / t+4, D rows g / g+8, columns 2t, 2t+1.  Columns of D2: r_hi r_lo | g_hi g_lo | b_hi b_lo | - -.
+template <int SLOTS>
+__device__ __forceinline__ void v6_flush(const WarpV6<SLOTS>& S, const float2 (*b1)[32], int kq, int jbase, int cnt, int lane,
+                                         float X0s, float Y0s, float* __restrict__ accum)
+{
+    constexpr int GS = V6Layout<SLOTS>::GS, KS = V6Layout<SLOTS>::KS;
     __syncwarp();
     const int g = lane >> 2, t = lane & 3;
     float d1[4] = {0.f, 0.f, 0.f, 0.f}, d2[4] = {0.f, 0.f, 0.f, 0.f};
-    const float* ab = S.a + g * V6_GS + t * 8;
+    if (SLOTS == 16) {
+        const float* ab = S.a + g * GS + t * 8;
 #pragma unroll
-    for (int s = 0; s < 4; s++) {
-        const float4 Q1 = *reinterpret_cast<const float4*>(ab + s * V6_KS);          // k = t:   (w, at) of the two rows
-        const float4 Q2 = *reinterpret_cast<const float4*>(ab + s * V6_KS + 4);      // k = t+4
-        const float2 m = b1[s][lane];
-        const float2 q = S.b2[s][lane];
-        float xw[4], xa[4];
-        if ((s & 1) == 0) {
-            xw[0] = Q1.x; xw[1] = Q1.z; xw[2] = Q2.x; xw[3] = Q2.z;
-            xa[0] = Q1.y; xa[1] = Q1.w; xa[2] = Q2.y; xa[3] = Q2.w;
-        } else {
-            xw[0] = Q1.z; xw[1] = Q1.x; xw[2] = Q2.z; xw[3] = Q2.x;
-            xa[0] = Q1.w; xa[1] = Q1.y; xa[2] = Q2.w; xa[3] = Q2.y;
-        }
-        uint32_t whi[4], wlo[4], ahi[4], alo[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {      // x = hi + lo, hi exact in tf32 (the tensor core ignores the 13 low mantissa bits)
-            whi[k] = __float_as_uint(xw[k]) & 0xffffe000u;
-            wlo[k] = __float_as_uint(xw[k] - __uint_as_float(whi[k]));
-            ahi[k] = __float_as_uint(xa[k]) & 0xffffe000u;
-            alo[k] = __float_as_uint(xa[k] - __uint_as_float(ahi[k]));
-        }
-        mma_tf32(d1, whi, __float_as_uint(m.x), __float_as_uint(m.y));
-        mma_tf32(d1, wlo, __float_as_uint(m.x), __float_as_uint(m.y));
-        mma_tf32(d2, ahi, __float_as_uint(q.x), __float_as_uint(q.y));
-        mma_tf32(d2, alo, __float_as_uint(q.x), __float_as_uint(q.y));
-    }
-    const int q0l = lane & ~3;
-#pragma unroll
-    for (int hi = 0; hi < 2; hi++) {
-        const float m0 = d1[2 * hi], m1 = d1[2 * hi + 1];
-        const float col = d2[2 * hi] + d2[2 * hi + 1];
-        const float S0 = __shfl_sync(0xffffffffu, m0, q0l);
-        const float Sx = __shfl_sync(0xffffffffu, m1, q0l);
-        const float Sy = __shfl_sync(0xffffffffu, m0, q0l + 1);
-        const int row = g + 8 * hi;
-        if (row < cnt && t < 3) {
-            const int j = jbase + row;
-            const float2 xy = *reinterpret_cast<const float2*>(&S.q0[kq][j]);
-            const uint32_t id = __float_as_uint(S.e[kq][j].x);
-            const float u = xy.x - X0s, v = xy.y - Y0s;         // dx = u - lx, dy = v - ly
-            const float a1 = fmaf(u, S0, -Sx);                   // sum w dx
-            const float a2 = fmaf(v, S0, -Sy);                   // sum w dy
-            const float o3 = fmaf(u, a1 - Sx, m1);               // sum w dx^2  = Sxx - 2u Sx + u^2 S0      (lane t = 1)
-            const float o4 = fmaf(-v, Sx, fmaf(u, a2, m0));      // sum w dx dy = Sxy - u Sy - v Sx + uv S0 (lane t = 2)
-            const float o5 = fmaf(v, a2 - Sy, m1);               // sum w dy^2  = Syy - 2v Sy + v^2 S0      (lane t = 2)
-            const float out0 = fsel(t == 0, m0, fsel(t == 1, a2, o4));
-            const float out1 = fsel(t == 0, a1, fsel(t == 1, o3, o5));
-            float* rowp = accum + (size_t)id * 12;
-            // an entry without a live lane has exactly zero sums: adding them is a no-op, so they are not sent
-            if (out0 != 0.f || out1 != 0.f) {
-                if (t == 0) { atomicAdd(rowp + 8, out0); atomicAdd(rowp + 3, out1); }
-                else red_add_v2(rowp + 2 + 2 * t, out0, out1);   // t = 1: columns 4, 5   t = 2: columns 6, 7
+        for (int s = 0; s < 4; s++) {
+            const float4 Q1 = *reinterpret_cast<const float4*>(ab + s * KS);          // k = t:   (w, at) of the two rows
+            const float4 Q2 = *reinterpret_cast<const float4*>(ab + s * KS + 4);      // k = t+4
+            const float2 m = b1[s][lane];
+            const float2 q = S.b2[s][lane];
+            float xw[4], xa[4];
+            if ((s & 1) == 0) {
+                xw[0] = Q1.x; xw[1] = Q1.z; xw[2] = Q2.x; xw[3] = Q2.z;
+                xa[0] = Q1.y; xa[1] = Q1.w; xa[2] = Q2.y; xa[3] = Q2.w;
+            } else {
+                xw[0] = Q1.z; xw[1] = Q1.x; xw[2] = Q2.z; xw[3] = Q2.x;
+                xa[0] = Q1.w; xa[1] = Q1.y; xa[2] = Q2.w; xa[3] = Q2.y;
             }
-            if (col != 0.f) atomicAdd(rowp + t, col);
+            uint32_t whi[4], wlo[4], ahi[4], alo[4];
+            split_tf32(xw, whi, wlo);
+            split_tf32(xa, ahi, alo);
+            mma_tf32(d1, whi, __float_as_uint(m.x), __float_as_uint(m.y));
+            mma_tf32(d1, wlo, __float_as_uint(m.x), __float_as_uint(m.y));
+            mma_tf32(d2, ahi, __float_as_uint(q.x), __float_as_uint(q.y));
+            mma_tf32(d2, alo, __float_as_uint(q.x), __float_as_uint(q.y));
         }
+#pragma unroll
+        for (int hi = 0; hi < 2; hi++)
+            v6_commit<SLOTS>(S, kq, jbase + g + 8 * hi, g + 8 * hi < cnt, lane, d1[2 * hi], d1[2 * hi + 1], d2[2 * hi] + d2[2 * hi + 1],
+                             X0s, Y0s, accum);
+    } else {
+        const float* ab = S.a + g * GS + t * 4;
+#pragma unroll
+        for (int s = 0; s < 4; s++) {
+            const float4 av = *reinterpret_cast<const float4*>(ab + s * KS);           // w, at at k = t | w, at at k = t+4
+            const float2 m = b1[s][lane];
+            const float2 q = S.b2[s][lane];
+            const float x[4] = {av.x, av.y, av.z, av.w};      // rows g (w) / g+8 (at) at k = t, then at k = t+4
+            uint32_t hi[4], lo[4];
+            split_tf32(x, hi, lo);
+            mma_tf32(d1, hi, __float_as_uint(m.x), __float_as_uint(m.y));
+            mma_tf32(d1, lo, __float_as_uint(m.x), __float_as_uint(m.y));
+            mma_tf32(d2, hi, __float_as_uint(q.x), __float_as_uint(q.y));
+            mma_tf32(d2, lo, __float_as_uint(q.x), __float_as_uint(q.y));
+        }
+        v6_commit<SLOTS>(S, kq, jbase + g, g < cnt, lane, d1[0], d1[1], d2[2] + d2[3], X0s, Y0s, accum);
     }
     __syncwarp();
 }
 
-template <int MINB>
+// head of one entry for this lane's pixel, and the branch-free state update: a lane that does not blend the entry (dead)
+// runs the same instructions with alpha = 0, which leaves T and Sd unchanged and yields w = at = 0
+__device__ __forceinline__ void v6_entry(const float4 a, const float4 c, const float4 e, float pxf, float pyf, int last_contributor,
+                                         bool slot_valid, float dp0, float dp1, float dp2, float& T, float& Sd, float& w, float& at)
+{
+    const float dx = a.x - pxf, dy = a.y - pyf;
+    const float power = -0.5f * (a.z * dx * dx + c.x * dy * dy) - a.w * dx * dy;
+    const float araw = c.y * expf(power);
+    const float alpha = fminf(0.99f, araw);
+    const bool live = slot_valid && __float_as_int(e.y) < last_contributor && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+    const float araw_s = live ? araw : 0.f, alpha_s = live ? alpha : 0.f;
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f - alpha_s));        // rcp(1) == 1 exactly
+    T *= r;
+    const float ec = fmaf(e.z, dp2, fmaf(c.w, dp1, c.z * dp0));
+    at = alpha_s * T;
+    const float dL_dalpha = fmaf(T, ec, -(Sd * r));
+    Sd = fmaf(ec, at, Sd);
+    w = araw_s * dL_dalpha;
+}
+
+template <int SLOTS, int TRIP, int MINB>
 __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_bwd_v6_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     const uint32_t* __restrict__ planes, uint32_t plane_words, int W, int H, const float* __restrict__ bg,
                     const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
                     float* __restrict__ accum, int gyv, const uint32_t* __restrict__ tile_order)
 {
+    constexpr int GS = V6Layout<SLOTS>::GS, KS = V6Layout<SLOTS>::KS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    BwdSmemV6& SM = *reinterpret_cast<BwdSmemV6*>(smem_raw);
+    BwdSmemV6<SLOTS>& SM = *reinterpret_cast<BwdSmemV6<SLOTS>*>(smem_raw);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    WarpV6& S = SM.w[wid];
+    WarpV6<SLOTS>& S = SM.w[wid];
     const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;                                  // see blend_fwd_v3_kernel
     const uint32_t tile = tile_order ? tile_order[lin] : lin;
     const uint32_t trow = tile / gridDim.x, bx = tile - trow * gridDim.x;
@@ -573,9 +630,10 @@ blend_bwd_v6_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
         col[6 * 8] = 0.f;
         col[7 * 8] = 0.f;
     }
-    // this lane's (w, at) slot of A row g, half hi: a_lo / a_hi + g * V6_GS  (see the layout above)
-    float* const a_lo = S.a + sK * V6_KS + tK * 8 + 4 * bK + 2 * (sK & 1);
-    float* const a_hi = S.a + sK * V6_KS + tK * 8 + 4 * bK + 2 - 2 * (sK & 1);
+    // this lane's (w, at) slot of entry c of a flush group (see the layouts above):
+    //   SLOTS 16: (c < 8 ? a_lo : a_hi) + (c & 7) * GS       SLOTS 8: a_lo + c * GS
+    float* const a_lo = SLOTS == 16 ? S.a + sK * KS + tK * 8 + 4 * bK + 2 * (sK & 1) : S.a + sK * KS + tK * 4 + 2 * bK;
+    float* const a_hi = S.a + sK * KS + tK * 8 + 4 * bK + 2 - 2 * (sK & 1);
 
     int warp_last = last_contributor;
 #pragma unroll
@@ -621,13 +679,18 @@ blend_bwd_v6_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
         id = v ? tvals[pos] : 0u;
     };
     auto issue = [&](uint32_t k, uint32_t pos, uint32_t id) {           // gather group k into ring buffer k & 1
-        if (lane < group_size(k)) {
-            const int kb = k & 1;
+        const int kb = k & 1, gs = group_size(k);
+        if (lane < gs) {
             const SplatRec* r = rec + id;
             cp_async16(&S.q0[kb][lane], &r->q0);
             cp_async16(&S.q1[kb][lane], &r->q1);
             cp_async4(&S.e[kb][lane].z, &r->q2);
             *reinterpret_cast<uint2*>(&S.e[kb][lane]) = make_uint2(id, pos);
+        } else if (lane < gs + TRIP - 1) {
+            // the slots a trip may read behind the last entry get a record that blends nothing and holds no NaN
+            S.q0[kb][lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+            S.q1[kb][lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+            S.e[kb][lane] = make_float4(0.f, __int_as_float(0x7fffffff), 0.f, 0.f);
         }
         cp_async_commit();
     };
@@ -653,28 +716,27 @@ blend_bwd_v6_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
         const float4* rq1 = S.q1[kq];
         const float4* re = S.e[kq];
 #pragma unroll 1
-        for (int h = 0; h < 2; h++) {
-            const int cnt = min(16, n - 16 * h);            // entries of this half (warp-uniform)
-            if (cnt <= 0) break;
-            const int jb = 16 * h;
+        for (int jb = 0; jb < n; jb += SLOTS) {
+            const int cnt = min(SLOTS, n - jb);             // entries of this flush group (warp-uniform)
 #pragma unroll
-            for (int c = 0; c < 16; c += 2) {
+            for (int c = 0; c < SLOTS; c += TRIP) {
                 if (c < cnt) {
-                    const int j0 = jb + c, j1 = j0 + 1;
-                    const float4 a0 = rq0[j0], c0 = rq1[j0], e0 = re[j0], a1 = rq0[j1], c1 = rq1[j1], e1 = re[j1];
-                    const EntryHead h0 = bwd_head(a0, c0, pxf, pyf, __float_as_int(e0.y), last_contributor);
-                    EntryHead h1 = bwd_head(a1, c1, pxf, pyf, __float_as_int(e1.y), last_contributor);
-                    h1.live = h1.live && (c + 1 < cnt);     // odd count: the ring slot behind the last entry holds stale data
-                    float w0 = 0.f, at0 = 0.f, w1 = 0.f, at1 = 0.f;
-                    if (h0.live) bwd_live_sd(h0.alpha, h0.araw, c0.z, c0.w, e0.z, dp0, dp1, dp2, T, Sd, w0, at0);
-                    if (h1.live) bwd_live_sd(h1.alpha, h1.araw, c1.z, c1.w, e1.z, dp0, dp1, dp2, T, Sd, w1, at1);
-                    float* const s0 = ((c >> 3) ? a_hi : a_lo) + (c & 7) * V6_GS;
-                    float* const s1 = (((c + 1) >> 3) ? a_hi : a_lo) + ((c + 1) & 7) * V6_GS;
-                    *reinterpret_cast<float2*>(s0) = make_float2(w0, at0);
-                    *reinterpret_cast<float2*>(s1) = make_float2(w1, at1);
+                    float4 a[TRIP], q[TRIP], e[TRIP];
+                    float w[TRIP], at[TRIP];
+#pragma unroll
+                    for (int u = 0; u < TRIP; u++) { a[u] = rq0[jb + c + u]; q[u] = rq1[jb + c + u]; e[u] = re[jb + c + u]; }
+#pragma unroll
+                    for (int u = 0; u < TRIP; u++)
+                        v6_entry(a[u], q[u], e[u], pxf, pyf, last_contributor, u == 0 || c + u < cnt, dp0, dp1, dp2, T, Sd, w[u], at[u]);
+#pragma unroll
+                    for (int u = 0; u < TRIP; u++) {
+                        const int cc = c + u;
+                        float* const sp = SLOTS == 16 ? ((cc >> 3) ? a_hi : a_lo) + (cc & 7) * GS : a_lo + cc * GS;
+                        *reinterpret_cast<float2*>(sp) = make_float2(w[u], at[u]);
+                    }
                 }
             }
-            v6_flush(S, SM.b1, kq, jb, cnt, lane, X0s, Y0s, accum);
+            v6_flush<SLOTS>(S, SM.b1, kq, jb, cnt, lane, X0s, Y0s, accum);
         }
         __syncwarp();                  // everyone has left ring buffer kq before the gather of group k + 2 overwrites it
     }
@@ -729,8 +791,11 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
     int rc;
     if ((rc = device_ctx(&ctx))) return rc;
     rc = ctx_once(ctx, 2u, [] {    // per device: opt in to the kernels' dynamic shared memory
-        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6)));
-        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6)));
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
         return (int)GSR_OK;
@@ -744,12 +809,17 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
             GSR_LAUNCH((blend_bwd_v5_kernel<2, 4>), grid, BL_THREADS, sizeof(BwdSmemV5<2>), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
                        bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
     } else {
-        if (o.bwd_minb == 2)
-            GSR_LAUNCH((blend_bwd_v6_kernel<2>), grid, BL_THREADS, sizeof(BwdSmemV6), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
-        else
-            GSR_LAUNCH((blend_bwd_v6_kernel<3>), grid, BL_THREADS, sizeof(BwdSmemV6), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H,
-                       bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
+#define GSR_V6(SLOTS, TRIP, MINB)                                                                                                  \
+    GSR_LAUNCH((blend_bwd_v6_kernel<SLOTS, TRIP, MINB>), grid, BL_THREADS, sizeof(BwdSmemV6<SLOTS>), s, im.ranges, b.vals, g.rec,   \
+               b.scratch, pw, W, H, bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt)
+        // bwd_variant 6: 16 reduction rows, 3 CTAs per SM;  68 / 84 / 83: 8 rows (4 / 4 / 3 CTAs per SM), trips of 2 / 4 / 4 entries;
+        // 64: 16 rows, trips of 4
+        if (o.bwd_variant == 68) GSR_V6(8, 2, 4);
+        else if (o.bwd_variant == 84) GSR_V6(8, 4, 4);
+        else if (o.bwd_variant == 83) GSR_V6(8, 4, 3);
+        else if (o.bwd_variant == 64) GSR_V6(16, 4, 3);
+        else GSR_V6(16, 2, 3);
+#undef GSR_V6
     }
     return GSR_OK;
 }

@@ -10,6 +10,14 @@ Flat layout (floats per Gaussian: 3 + 3 + 4 + 1 + 3*M):
     means3D P*3 | scales P*3 | rotations P*4 | opacities P*1 | shs P*M*3
 Each parameter's .grad is a view into the buffer, so autograd accumulates in place and no
 flatten / unflatten copy happens before the collective.
+
+The collective ("bucketed ... issued from the K10 epilogue of the last local view on a side stream"):
+no gradient is final before the rank's last view has gone through its per-Gaussian backward, so that stage of the
+LAST view runs in ranges of Gaussians (gsr_backward_staged) and the all-reduce of a range - one coalesced NCCL call
+over the range's rows of every parameter - is issued as soon as the range has been queued; NCCL's stream waits for
+exactly that point of the compute stream, so range k travels over NVLink while range k+1 is computed.  The buffer can
+be allocated from NCCL's own allocator and registered with the communicator (ncclMemAlloc / ncclCommRegister through
+torch.cuda.MemPool), which lets NCCL run its NVLS (in-switch reduction) path without staging copies.
 """
 from __future__ import annotations
 
@@ -29,12 +37,29 @@ def shard_views(n_views: int, rank: int, world: int) -> List[int]:
 class FlatGrads:
     """Owns the flat gradient buffer and binds each parameter's .grad to its slice."""
 
-    def __init__(self, params: Dict[str, torch.Tensor]):
+    def __init__(self, params: Dict[str, torch.Tensor], nccl_registered: bool = False, group=None):
         self.params = params
         self.names = [n for n in PARAM_ORDER if n in params]
         total = sum(params[n].numel() for n in self.names)
         ref = params[self.names[0]]
-        self.flat = torch.zeros(total, dtype=torch.float32, device=ref.device)
+        self.P = int(ref.shape[0])
+        self.registered = False
+        self.flat = None
+        if nccl_registered and ref.is_cuda and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            # buffer from NCCL's allocator, registered with the communicator: zero-copy NVLS all-reduce
+            try:
+                pg = group if group is not None else dist.distributed_c10d._get_default_group()
+                backend = pg._get_backend(ref.device)
+                self._pool = torch.cuda.MemPool(backend.mem_allocator)
+                with torch.cuda.use_mem_pool(self._pool):
+                    self.flat = torch.zeros(total, dtype=torch.float32, device=ref.device)
+                backend.register_mem_pool(self._pool)
+                self.registered = True
+            except Exception as ex:      # older NCCL / no NVLS: a plain buffer works everywhere
+                self.flat = None
+                self.register_error = str(ex)[:200]
+        if self.flat is None:
+            self.flat = torch.zeros(total, dtype=torch.float32, device=ref.device)
         self.slices = {}
         o = 0
         for n in self.names:
@@ -58,6 +83,26 @@ class FlatGrads:
         if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
             return None
         return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+    def row_slices(self, g0: int, g1: int) -> List[torch.Tensor]:
+        """The rows [g0, g1) of every parameter's gradient, as views into the flat buffer."""
+        out = []
+        for n in self.names:
+            a, b = self.slices[n]
+            k = (b - a) // self.P
+            out.append(self.flat[a + g0 * k:a + g1 * k])
+        return out
+
+    def all_reduce_rows(self, g0: int, g1: int, group=None):
+        """One coalesced all-reduce (a single NCCL group call) over the rows [g0, g1) of every parameter; asynchronous:
+        NCCL's stream waits for the current stream as of this call.  Returns an object with .wait(), or None."""
+        if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+            return None
+        ts = self.row_slices(g0, g1)
+        with dist._coalescing_manager(group=group, device=self.flat.device, async_ops=True) as cm:
+            for t in ts:
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        return cm
 
 
 def make_leaf_params(scene: Dict[str, torch.Tensor], device) -> Dict[str, torch.Tensor]:
@@ -138,9 +183,36 @@ def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
 
 def dp_step(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
             loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None, fused: bool = True,
-            n_streams: int = 1):
+            n_streams: int = 1, overlap_chunks: int = 0):
     """Renders this rank's views, back-propagates `loss_fn(color, view_id)` for each into the flat
-    buffer, then all-reduces it.  Returns the summed local loss (a device scalar)."""
-    total = backward_views(rasterizer_mod, params, flat, cams, bg, sh_degree, loss_fn, view_ids, fused, n_streams)
-    flat.all_reduce(group)
+    buffer, then all-reduces it.  Returns the summed local loss (a device scalar).
+    overlap_chunks = K > 0 (fused, one stream): the per-Gaussian backward of the LAST view runs in K ranges of Gaussians and
+    each range's all-reduce is issued right behind it (see the module docstring); the result is the same sum."""
+    views = list(view_ids)
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    if (overlap_chunks <= 0 or not multi or not fused or n_streams > 1 or not views
+            or not hasattr(rasterizer_mod, "set_chunk_hook")):
+        total = backward_views(rasterizer_mod, params, flat, cams, bg, sh_degree, loss_fn, views, fused, n_streams)
+        flat.all_reduce(group)
+        return total
+    total = None
+    if len(views) > 1:
+        total = backward_views(rasterizer_mod, params, flat, cams, bg, sh_degree, loss_fn, views[:-1], True, 1)
+    works = []
+    prev_hook = rasterizer_mod.set_chunk_hook((overlap_chunks, lambda g0, g1: works.append(flat.all_reduce_rows(g0, g1, group))))
+    prev_mode = rasterizer_mod.set_grad_mode("accumulate" if len(views) > 1 else "overwrite")
+    try:
+        k = views[-1]
+        color, _radii, _m2d = render_view(rasterizer_mod, params, cams[k], bg, sh_degree)
+        loss = loss_fn(color, k)
+        loss.backward()
+    finally:
+        rasterizer_mod.set_grad_mode(prev_mode)
+        rasterizer_mod.set_chunk_hook(prev_hook)
+    if not works:                       # the hook was not honoured (a parameter without an in-place gradient target)
+        flat.all_reduce(group)
+    for w in works:
+        if w is not None:
+            w.wait()
+    total = loss.detach() if total is None else total + loss.detach()
     return total
