@@ -663,6 +663,15 @@ void orc_knn_morton(int P, const float* pts, float* out, uint32_t* morton_out /*
     free(kk); free(idx); free(bmin); free(bmax);
 }
 
+void orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int orc_num_threads(void)
 {
 #ifdef _OPENMP

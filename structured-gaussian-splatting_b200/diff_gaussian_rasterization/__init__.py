@@ -8,6 +8,7 @@ Public surface mirrors the reference package
   _RasterizeGaussians            (:44-155)   autograd.Function, same argument / gradient order
 so gaussian_renderer/__init__.py, train.py, train_lgm.py and render.py call it unchanged.
 """
+import threading
 import weakref
 from typing import NamedTuple
 
@@ -53,6 +54,9 @@ def _call_with_snapshot(fn, args, debug, dump_name, stage):
 #     to rounding but not bit-reproducible from run to run (like the reference's atomicAdd gradients).
 _GRAD_MODE = None
 _PENDING_OVERWRITE = {}          # data_ptr of a .grad buffer -> weak reference to the token of the pending "overwrite" render
+
+
+_TLS = threading.local()
 
 
 class _Token:
@@ -121,7 +125,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         if _GRAD_MODE is not None:
             ctx.grad_leaves = (means3D, opacities, sh, scales, rotations)
             ctx.grad_targets = tuple(_grad_target(t) for t in ctx.grad_leaves)
-            if _GRAD_MODE == "overwrite" and torch.is_grad_enabled():
+            # (autograd runs forward() with grad mode off: the caller's mode was noted by rasterize_gaussians())
+            if _GRAD_MODE == "overwrite" and getattr(_TLS, "grad_enabled", False):
                 ctx.overwrite_token = _Token()
                 for g in ctx.grad_targets:
                     if g is not None:
@@ -186,6 +191,7 @@ class _RasterizeGaussians(torch.autograd.Function):
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
+    _TLS.grad_enabled = torch.is_grad_enabled()
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                                      raster_settings)
 
