@@ -797,6 +797,7 @@ def main():
     if extras and not args.no_c5 and not args.batched and spec.name in ("C3", "C2") and not args.gaussians:
         spec5 = synth.CONFIGS["C5"]
         n_flat = flat.nbytes()
+        flat.release()
         del params, flat, scene
         torch.cuda.empty_cache()
         scene5 = synth.spec_scene(spec5)
@@ -831,10 +832,12 @@ def main():
             c5["allreduce_ms_alone"] = round(float(t5.item()), 4)
             c5["busbw_GBps"] = round(2.0 * (world - 1) / world * flat5.nbytes() / (float(t5.item()) * 1e-3) / 1e9, 1)
         flat_nbytes = n_flat
+        flat5.release()
         del params5, flat5
         torch.cuda.empty_cache()
     else:
         flat_nbytes = flat.nbytes()
+        flat.release()                               # (a NCCL-registered buffer must go before the process group does)
 
     if rank == 0:
         peaks = {}

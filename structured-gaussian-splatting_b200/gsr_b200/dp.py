@@ -50,6 +50,7 @@ class FlatGrads:
             try:
                 pg = group if group is not None else dist.distributed_c10d._get_default_group()
                 backend = pg._get_backend(ref.device)
+                self._backend = backend
                 self._pool = torch.cuda.MemPool(backend.mem_allocator)
                 with torch.cuda.use_mem_pool(self._pool):
                     self.flat = torch.zeros(total, dtype=torch.float32, device=ref.device)
@@ -70,6 +71,21 @@ class FlatGrads:
 
     def zero_(self):
         self.flat.zero_()
+
+    def release(self):
+        """Drops the buffer (the parameters' .grad become None).  A buffer registered with NCCL MUST be released before the
+        process group is destroyed: its memory pool deregisters from the communicator when it is freed."""
+        for n in self.names:
+            self.params[n].grad = None
+        self.flat = None
+        if self.registered:
+            try:
+                self._backend.deregister_mem_pool(self._pool)
+            except Exception:
+                pass
+            self._pool = None
+            self._backend = None
+            self.registered = False
 
     def grad(self, name: str) -> torch.Tensor:
         a, b = self.slices[name]

@@ -37,6 +37,7 @@ def _worker(rank, world, port, q):
             total = dp.dp_step(dgr, params, flat, cams, bg, D, loss_fn, dp.shard_views(V, rank, world), **kw)
             torch.cuda.synchronize()
             res[name] = (flat.flat.clone().cpu().numpy(), float(total), bool(flat.registered))
+            flat.release()
         ref = None
         if rank == 0:
             params = dp.make_leaf_params(sc, dev)
