@@ -54,12 +54,9 @@ def main():
                 C.set_option(k, v)
 
     variants = {
-        "v6_s16_t2_b3": dict(bwd_variant=6),
-        "v6_s16_t4_b3": dict(bwd_variant=64),
-        "v6_s8_t2_b4": dict(bwd_variant=68),
-        "v6_s8_t4_b4": dict(bwd_variant=84),
-        "v6_s8_t4_b3": dict(bwd_variant=83),
-        "v5_minb4": dict(bwd_variant=5, bwd_minb=4),
+        "default": dict(),
+        "pre_stage0": dict(pre_stage=0),
+        "default_again": dict(),
     }
     ref_g = None
     for name, kw in variants.items():

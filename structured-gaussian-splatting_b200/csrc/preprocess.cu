@@ -175,21 +175,50 @@ struct PreArgs {
     int view_base;     // first view of this launch inside the batched call (scene s of a multi-scene call: s * views_per_scene)
 };
 
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraArgs ca)
+constexpr int PRE_THREADS = 128;
+constexpr int PRE_ROW4 = 13;        // float4 per staged SH row: 12 + 1 padding (odd: conflict-free LDS.128 by row)
+
+// STAGE (SH degree 3 on [P,16,3] storage, 16-byte aligned): the 192-byte SH rows are 60 % of this kernel's traffic.  Read
+// per thread (12 x LDG.128 at a 192-byte lane stride) every load instruction touches 32 different lines and the kernel is
+// bound by the L1's line rate, not by HBM (measured 4.3 TB/s).  Instead the warp copies the 6 KB its 32 Gaussians occupy
+// with fully coalesced 16-byte cp.async into shared memory at the top of the kernel - the copy overlaps the cull /
+// covariance / rect arithmetic and costs no registers - and every visible lane then reads its own row from there.
+// Rows of Gaussians that turn out culled are fetched for nothing (15 % at C3).
+template <bool STAGE>
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreArgs a, CameraArgs ca)
 {
     __shared__ Camera cam;
+    __shared__ float4 stage[STAGE ? (PRE_THREADS / 32) * 32 * PRE_ROW4 : 1];
     // blockIdx.y = view of a batched call (gsr_forward_batched): its camera, its slice v * P + idx of the per-view
     // outputs, its band of tile rows in the stacked image
     // (the launch's camera arrays and Gaussian parameters start at its first view / its scene; outputs are indexed by the
     // global view a.view_base + blockIdx.y)
     const int lview = blockIdx.y;
     const int view = a.view_base + lview;
+    const int lane = threadIdx.x & 31;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    float4* const st = stage + (STAGE ? (threadIdx.x >> 5) * 32 * PRE_ROW4 : 0);
+    if (STAGE) {
+        const int wbase = idx - lane;                                   // first Gaussian of this warp
+        const int n4 = max(0, min(32, a.P - wbase)) * 12;               // float4s of the warp's rows
+        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)wbase * 12;
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane;
+            if (e < n4) {
+                const int r = e / 12, c = e - r * 12;
+                const uint32_t dst = (uint32_t)__cvta_generic_to_shared(st + r * PRE_ROW4 + c);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(src + e) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
     ca.view += 16 * lview;
     if (ca.proj) ca.proj += 16 * lview;
     if (ca.cam) ca.cam += 3 * lview;
     load_camera(cam, ca);
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.P) return;
+    const bool inb = idx < a.P;
+    if (!STAGE && !inb) return;
     const size_t oidx = (size_t)view * a.P + idx;
 
     SplatRec out;
@@ -199,8 +228,11 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
     int radius_out = 0;
     uint32_t clamp_bits = 0;
     ushort4 rect_out = make_ushort4(0, 0, 0, 0);
+    bool vis = false;                           // survives every cull: gets a colour
+    float3 p = {0.f, 0.f, 0.f};
 
-    const float3 p = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
+    if (inb) {
+    p = make_float3(a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]);
     const float3 p_view = xform4x3(p, cam.view);
     if (!(p_view.z <= 0.2f)) {   // near cull only (auxiliary.h:154); NaN passes like the reference
         const float4 p_hom = xform4x4(p, cam.proj);
@@ -230,41 +262,11 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
             tile_rect(px, py, (int)my_radius, cam.gx, cam.gy, x0, y0, x1, y1);
             const uint32_t area = (uint32_t)(x1 - x0) * (uint32_t)(y1 - y0);
             if (area != 0) {
-                float rgb[3];
-                if (a.colors_pre != nullptr) {
-                    rgb[0] = a.colors_pre[3 * (size_t)idx];
-                    rgb[1] = a.colors_pre[3 * (size_t)idx + 1];
-                    rgb[2] = a.colors_pre[3 * (size_t)idx + 2];
-                } else {
-                    // view direction (forward.cu:26-28): dir / length(dir), IEEE divide per component
-                    float dx = p.x - cam.cam[0], dy = p.y - cam.cam[1], dz = p.z - cam.cam[2];
-                    const float len = sqrtf(dx * dx + dy * dy + dz * dz);
-                    dx = dx / len; dy = dy / len; dz = dz / len;
-                    float f[48];
-                    if (a.shs_rest != nullptr) {
-                        // M == 16 here (the API rejects other split layouts): rows of 45 floats
-                        const float* dc = a.shs + (size_t)3 * idx;
-                        const bool vec = (((size_t)a.shs_rest) & 15) == 0;
-                        switch (a.D) {
-                        case 0: load_sh_split<0>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        case 1: load_sh_split<9>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        case 2: load_sh_split<24>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        default: load_sh_split<45>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        }
-                    } else {
-                        const float* shp = a.shs + (size_t)3 * a.M * idx;
-                        const bool vec = (((size_t)shp) & 15) == 0;
-                        switch (a.D) {
-                        case 0: load_sh<3>(shp, false, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        case 1: load_sh<12>(shp, vec, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        case 2: load_sh<27>(shp, vec, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        default: load_sh<48>(shp, vec, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
-                        }
-                    }
-                }
+                vis = true;
+                // (the colour is filled in below)
                 out.q0 = make_float4(px, py, conic.x, conic.y);
-                out.q1 = make_float4(conic.z, a.opac[idx], rgb[0], rgb[1]);
-                out.q2 = make_float4(rgb[2], p_view.z, __int_as_float((int)my_radius), __uint_as_float(area));
+                out.q1 = make_float4(conic.z, a.opac[idx], 0.f, 0.f);
+                out.q2 = make_float4(0.f, p_view.z, __int_as_float((int)my_radius), __uint_as_float(area));
                 radius_out = (int)my_radius;
                 const int yoff = view * cam.gy;
                 rect_out = make_ushort4((unsigned short)x0, (unsigned short)(y0 + yoff), (unsigned short)x1, (unsigned short)(y1 + yoff));
@@ -273,6 +275,56 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreArgs a, CameraAr
     } else if (a.prefiltered) {
         *a.err = 1;   // reference: printf + __trap (auxiliary.h:156-160); we flag it and report GSR_EINVAL in debug mode
     }
+    }
+
+    if (STAGE) {
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncwarp();                           // the rows were copied by all lanes of the warp
+    }
+    if (vis) {
+        float rgb[3];
+        if (a.colors_pre != nullptr) {
+            rgb[0] = a.colors_pre[3 * (size_t)idx];
+            rgb[1] = a.colors_pre[3 * (size_t)idx + 1];
+            rgb[2] = a.colors_pre[3 * (size_t)idx + 2];
+        } else {
+            // view direction (forward.cu:26-28): dir / length(dir), IEEE divide per component
+            float dx = p.x - cam.cam[0], dy = p.y - cam.cam[1], dz = p.z - cam.cam[2];
+            const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+            dx = dx / len; dy = dy / len; dz = dz / len;
+            float f[48];
+            if (STAGE) {
+                const float4* row = st + lane * PRE_ROW4;
+#pragma unroll
+                for (int i = 0; i < 12; i++) {
+                    const float4 v = row[i];
+                    f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w;
+                }
+                sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits);
+            } else if (a.shs_rest != nullptr) {
+                // M == 16 here (the API rejects other split layouts): rows of 45 floats
+                const float* dc = a.shs + (size_t)3 * idx;
+                const bool vec = (((size_t)a.shs_rest) & 15) == 0;
+                switch (a.D) {
+                case 0: load_sh_split<0>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
+                case 1: load_sh_split<9>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
+                case 2: load_sh_split<24>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
+                default: load_sh_split<45>(dc, a.shs_rest, idx, a.P, vec, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
+                }
+            } else {
+                const float* shp = a.shs + (size_t)3 * a.M * idx;
+                const bool vec = (((size_t)shp) & 15) == 0;
+                switch (a.D) {
+                case 0: load_sh<3>(shp, false, f); sh_to_rgb<0>(f, dx, dy, dz, rgb, clamp_bits); break;
+                case 1: load_sh<12>(shp, vec, f); sh_to_rgb<1>(f, dx, dy, dz, rgb, clamp_bits); break;
+                case 2: load_sh<27>(shp, vec, f); sh_to_rgb<2>(f, dx, dy, dz, rgb, clamp_bits); break;
+                default: load_sh<48>(shp, vec, f); sh_to_rgb<3>(f, dx, dy, dz, rgb, clamp_bits); break;
+                }
+            }
+        }
+        out.q1.z = rgb[0]; out.q1.w = rgb[1]; out.q2.x = rgb[2];
+    }
+    if (!inb) return;
     a.radii[oidx] = radius_out;
     a.rec[oidx] = out;
     a.clamped[oidx] = (uint8_t)clamp_bits;
@@ -297,7 +349,9 @@ int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, co
     k.view_base = view_base;
     k.depthkey = sc.depthkey; k.rect = sc.rect; k.total = sc.counters;
     k.err = reinterpret_cast<int*>(sc.counters + 8);
-    GSR_LAUNCH(preprocess_fwd_kernel, dim3(cdiv(a.P, 256), V), 256, 0, s, k, cam);
+    const bool stage = options().pre_stage && a.shs && !a.colors_precomp && !k.shs_rest && a.M == 16 && a.D == 3 && (((size_t)a.shs) & 15) == 0;
+    if (stage) GSR_LAUNCH(preprocess_fwd_kernel<true>, dim3(cdiv(a.P, PRE_THREADS), V), PRE_THREADS, 0, s, k, cam);
+    else GSR_LAUNCH(preprocess_fwd_kernel<false>, dim3(cdiv(a.P, PRE_THREADS), V), PRE_THREADS, 0, s, k, cam);
     return GSR_OK;
 }
 
