@@ -41,6 +41,14 @@ def main():
                 a, f = util.raw_forward(C, sc, cam, bg, spec.D)
                 g = util.raw_backward(C, a, f, go)
             torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                a, f = util.raw_forward(C, sc, cam, bg, spec.D)
+                g = util.raw_backward(C, a, f, go)
+            e1.record()
+            torch.cuda.synchronize()
+            total = e0.elapsed_time(e1) / n
             C.timing_reset(); C.timing_enable(True)
             for _ in range(n):
                 a, f = util.raw_forward(C, sc, cam, bg, spec.D)
@@ -48,6 +56,7 @@ def main():
             torch.cuda.synchronize()
             C.timing_enable(False)
             rows = {name: round(ms / max(1, calls), 4) for name, ms, calls in C.timing_collect() if calls}
+            rows["TOTAL_fwd_bwd"] = round(total, 4)
             return rows, f, g
         finally:
             for k, v in prev.items():
@@ -55,7 +64,8 @@ def main():
 
     variants = {
         "default": dict(),
-        "pre_stage0": dict(pre_stage=0),
+        "split_512x8": dict(radix_split=0),
+        "depth_256x16": dict(radix_depth=1),
         "default_again": dict(),
     }
     ref_g = None

@@ -192,6 +192,8 @@ struct Options {
     int bwd_side = 1;           // SH backward on a side stream next to the cov/projection backward
     int sh_split = 1;           // dedicated M = 16 SH backward kernel
     int pre_stage = 1;          // preprocess moves the SH rows of a warp's 32 Gaussians through shared memory (coalesced cp.async)
+    int radix_split = 1;        // block shape of the tile-split radix passes: 0 = 512 threads x 8 items, 1 = 256 x 16
+    int radix_depth = 0;        // same for the depth-sort passes
     int depth_seg_items = -1;   // >= 0: batched calls sort the depth keys in runs of whole views (comparison arm)
     // comparison arms: honoured only when the test-only library libgsr_b200_arms.so is loaded (else GSR_EINVAL)
     int blend_arm = 0;          // 1: plain blending kernels (no culling)   2: forward staging through cp.async.bulk + mbarrier

@@ -106,8 +106,8 @@ __global__ void __launch_bounds__(RS_THREADS) radix_hist4_kernel(const uint32_t*
 //           blocks' status words for the exclusive prefix, publish the inclusive one
 //  phase 3  items are placed in digit order in shared memory, phase 4 writes them out so that consecutive
 //           threads write consecutive addresses inside each digit run (full sectors, not 4-byte scatters)
-template <int BITS>
-__global__ void __launch_bounds__(RS_THREADS) radix_onesweep_kernel(const uint32_t* __restrict__ keys_in,
+template <int BITS, int THREADS, int IPT>
+__global__ void __launch_bounds__(THREADS) radix_onesweep_kernel(const uint32_t* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                                     uint32_t n, int shift, const uint32_t* __restrict__ ghist,
@@ -115,6 +115,8 @@ __global__ void __launch_bounds__(RS_THREADS) radix_onesweep_kernel(const uint32
                                                                     uint32_t val_base)
 {
     constexpr uint32_t NB = 1u << BITS, MASK = NB - 1;
+    constexpr int RS_THREADS = THREADS, RS_IPT = IPT, RS_WARPS = THREADS / 32, RS_TILE = THREADS * IPT;     // (shadow the defaults)
+    static_assert(NB <= (uint32_t)THREADS, "one thread per digit in phase 2");
     __shared__ uint32_t skey[RS_TILE];
     __shared__ uint32_t sval[RS_TILE];
     uint32_t (*wcount)[NB] = reinterpret_cast<uint32_t (*)[NB]>(sval);     // [RS_WARPS][NB], dead before sval is written
@@ -228,12 +230,28 @@ __global__ void __launch_bounds__(RS_THREADS) radix_onesweep_kernel(const uint32
 // one pass; bits in 1..8
 static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t n,
                       int shift, int bits, const uint32_t* ghist, uint32_t* status, uint32_t* ticket, cudaStream_t s,
-                      uint32_t val_base = 0)
+                      uint32_t val_base = 0, int shape = 0)
 {
+    // Block shape (both 4096 items per block): 0 = 512 threads x 8 items, 1 = 256 threads x 16 items.  Measured at C3: the
+    // R-sized tile-split passes gain from four independent blocks per SM instead of two (0.299 -> 0.260 ms for the stage:
+    // a block stalled in its look-back or at a barrier leaves three others issuing), the P-sized depth passes do not
+    // (0.148 vs 0.151 ms: they are bound by the look-back chain itself).
     const int nblocks = cdiv(n, RS_TILE);
+    if (shape == 1) {
+#define GSR_PASS_B(B)                                                                                                    \
+    case B:                                                                                                              \
+        GSR_LAUNCH((radix_onesweep_kernel<B, 256, 16>), nblocks, 256, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, ghist, \
+                   status, ticket, val_base);                                                                            \
+        return GSR_OK;
+        switch (bits) {
+            GSR_PASS_B(1) GSR_PASS_B(2) GSR_PASS_B(3) GSR_PASS_B(4) GSR_PASS_B(5) GSR_PASS_B(6) GSR_PASS_B(7) GSR_PASS_B(8)
+        default: return GSR_EINVAL;
+        }
+#undef GSR_PASS_B
+    }
 #define GSR_PASS(B)                                                                                                      \
     case B:                                                                                                              \
-        GSR_LAUNCH(radix_onesweep_kernel<B>, nblocks, RS_THREADS, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, ghist, \
+        GSR_LAUNCH((radix_onesweep_kernel<B, RS_THREADS, RS_IPT>), nblocks, RS_THREADS, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, ghist, \
                    status, ticket, val_base);                                                                            \
         break;
     switch (bits) {
@@ -264,7 +282,7 @@ int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint
     for (int p = 0; p < 4; p++) {
         const bool last = p == 3;
         int rc = radix_pass(kin, vin, last ? nullptr : Kb[p & 1], Vb[p & 1], n, 8 * p, 8, ghist + p * RS_NB,
-                            status + (size_t)p * RS_NB * nblocks, tickets + p, s, val_base);
+                            status + (size_t)p * RS_NB * nblocks, tickets + p, s, val_base, options().radix_depth);
         if (rc) return rc;
         kin = Kb[p & 1]; vin = Vb[p & 1];
     }
@@ -622,7 +640,18 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, int gx, cons
                 const uint32_t og = __shfl_sync(0xffffffffu, g[r], lo);
                 if (t < total) {
                     const uint32_t j = t - orel;
-                    const uint32_t row = j / (uint32_t)ow, col = j - row * (uint32_t)ow;
+                    // row = j / ow: a float quotient with a +-1 fix-up instead of the ~20-instruction integer division
+                    // (exact while j < 2^22; larger rects take the integer path)
+                    uint32_t row, col;
+                    if (j < (1u << 22)) {
+                        row = __float2uint_rz(__fdividef((float)j, (float)ow));
+                        int c = (int)j - (int)(row * (uint32_t)ow);
+                        if (c < 0) { row--; c += ow; }
+                        else if (c >= ow) { row++; c -= ow; }
+                        col = (uint32_t)c;
+                    } else {
+                        row = j / (uint32_t)ow; col = j - row * (uint32_t)ow;
+                    }
                     tile_ids[off0 + t] = (uint32_t)((oy0 + (int)row) * gx + ox0 + (int)col);
                     gauss_ids[off0 + t] = og;
                 }
@@ -667,7 +696,7 @@ int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const
     for (int p = 0; p < td.npass; p++) {
         const bool last = p == td.npass - 1;
         int rc = radix_pass(T[cur], G[cur], last ? nullptr : T[cur ^ 1], last ? b.vals : G[cur ^ 1], (uint32_t)R, td.shift[p], td.bits[p],
-                            sc.tile_hist + p * RS_NB, st, tickets + p, s);
+                            sc.tile_hist + p * RS_NB, st, tickets + p, s, 0, options().radix_split);
         if (rc) return rc;
         st += (size_t)nblk << td.bits[p];
         cur ^= 1;
