@@ -64,8 +64,6 @@ def main():
 
     variants = {
         "default": dict(),
-        "split_512x8": dict(radix_split=0),
-        "depth_256x16": dict(radix_depth=1),
         "default_again": dict(),
     }
     ref_g = None

@@ -564,15 +564,17 @@ constexpr unsigned long long ES_AGG = 1ull << 62, ES_INC = 2ull << 62, ES_VAL = 
 
 constexpr int EM_SUB = 4;                       // sub-rounds of 256 Gaussians per chunk (one look-back per chunk)
 constexpr int EM_CHUNK = 256 * EM_SUB;
+constexpr int EM_WIN = 256;                     // instance slots of a warp's window in shared memory (2 KB per warp)
 
 __global__ void __launch_bounds__(256) emit_instances_kernel(int P, int gx, const uint32_t* __restrict__ order,
                                                              const ushort4* __restrict__ rect, uint32_t* __restrict__ tile_ids,
                                                              uint32_t* __restrict__ gauss_ids,
                                                              unsigned long long* __restrict__ estatus, uint32_t* __restrict__ ticket)
 {
-    __shared__ uint32_t warp_sum[8];
     __shared__ uint32_t s_chunk, s_base;
-    const int lane = threadIdx.x & 31;
+    __shared__ uint2 em_win[8][EM_WIN];
+    __shared__ uint32_t em_ws[EM_SUB][8];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int nchunks = (P + EM_CHUNK - 1) / EM_CHUNK;
     while (true) {
         __syncthreads();
@@ -594,28 +596,56 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, int gx, cons
             wdt[r] = max(1, (int)q.z - (int)q.x);
             cnt[r] = ((int)q.z - (int)q.x) * ((int)q.w - (int)q.y);
         }
-        // exclusive offsets inside the chunk (sub-round major = depth order), chunk total
+        // exclusive offsets inside the chunk (sub-round major = depth order), chunk total: warp scans of all sub-rounds, ONE
+        // barrier, then every thread adds the warp sums in front of it (the kernel was bound by its block barriers: 11 per
+        // chunk with one block scan per sub-round and a single-thread look-back)
         uint32_t excl[EM_SUB], run = 0;
+        {
+            uint32_t inc[EM_SUB];
 #pragma unroll
-        for (int r = 0; r < EM_SUB; r++) {
-            uint32_t tot;
-            excl[r] = run + block_excl_scan<8>((uint32_t)cnt[r], warp_sum, &tot);
-            run += tot;
-        }
-        if (threadIdx.x == 0) {
-            unsigned long long base = 0;
-            if (c == 0) st_volatile64(estatus, ES_INC | run);
-            else {
-                st_volatile64(estatus + c, ES_AGG | run);
-                for (int j = c - 1;; j--) {
-                    unsigned long long v;
-                    do { v = ld_volatile64(estatus + j); } while ((v >> 62) == 0);
-                    base += v & ES_VAL;
-                    if (v & ES_INC) break;
+            for (int r = 0; r < EM_SUB; r++) {
+                inc[r] = (uint32_t)cnt[r];
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t u = __shfl_up_sync(0xffffffffu, inc[r], o);
+                    if (lane >= o) inc[r] += u;
                 }
-                st_volatile64(estatus + c, ES_INC | (base + run));
+                if (lane == 31) em_ws[r][w] = inc[r];
             }
-            s_base = (uint32_t)base;
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < EM_SUB; r++) {
+                uint32_t wb = 0, all = 0;
+#pragma unroll
+                for (int i = 0; i < 8; i++) { const uint32_t v = em_ws[r][i]; if (i < w) wb += v; all += v; }
+                excl[r] = run + wb + inc[r] - (uint32_t)cnt[r];
+                run += all;
+            }
+        }
+        // look-back over the preceding chunks' status words, 32 at a time, by the first warp
+        if (w == 0) {
+            unsigned long long base = 0;
+            if (c == 0) {
+                if (lane == 0) st_volatile64(estatus, ES_INC | run);
+            } else {
+                if (lane == 0) st_volatile64(estatus + c, ES_AGG | run);
+                for (int j = c - 1;; j -= 32) {
+                    const int idx = j - lane;
+                    unsigned long long v = ES_INC;                    // before chunk 0: an inclusive prefix of 0
+                    if (idx >= 0) {
+                        do { v = ld_volatile64(estatus + idx); } while ((v >> 62) == 0);
+                    }
+                    const unsigned m = __ballot_sync(0xffffffffu, (v & ES_INC) != 0);
+                    const int first = m ? __ffs(m) - 1 : 32;          // nearest chunk with an inclusive prefix
+                    unsigned long long val = lane <= first ? (v & ES_VAL) : 0ull;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+                    base += val;
+                    if (m) break;
+                }
+                if (lane == 0) st_volatile64(estatus + c, ES_INC | (base + run));
+            }
+            if (lane == 0) s_base = (uint32_t)base;
         }
         __syncthreads();
         const uint32_t chunk_base = s_base;
@@ -626,35 +656,35 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, int gx, cons
             const uint32_t rel = off - off0;
             // total instances of this warp = end offset of the last lane
             const uint32_t total = __shfl_sync(0xffffffffu, rel + (uint32_t)cnt[r], 31);
-            for (uint32_t base = 0; base < total; base += 32) {
-                const uint32_t t = base + lane;
-                int lo = 0;
-#pragma unroll
-                for (int s = 16; s > 0; s >>= 1) {
-                    const uint32_t v = __shfl_sync(0xffffffffu, rel, lo + s);     // lo + s <= 31 always
-                    if (v <= t) lo += s;
-                }
-                const uint32_t orel = __shfl_sync(0xffffffffu, rel, lo);
-                const int ox0 = __shfl_sync(0xffffffffu, x0[r], lo), oy0 = __shfl_sync(0xffffffffu, y0[r], lo);
-                const int ow = __shfl_sync(0xffffffffu, wdt[r], lo);
-                const uint32_t og = __shfl_sync(0xffffffffu, g[r], lo);
-                if (t < total) {
-                    const uint32_t j = t - orel;
-                    // row = j / ow: a float quotient with a +-1 fix-up instead of the ~20-instruction integer division
-                    // (exact while j < 2^22; larger rects take the integer path)
-                    uint32_t row, col;
-                    if (j < (1u << 22)) {
-                        row = __float2uint_rz(__fdividef((float)j, (float)ow));
-                        int c = (int)j - (int)(row * (uint32_t)ow);
-                        if (c < 0) { row--; c += ow; }
-                        else if (c >= ow) { row++; c -= ow; }
-                        col = (uint32_t)c;
-                    } else {
-                        row = j / (uint32_t)ow; col = j - row * (uint32_t)ow;
+            // Push form: every lane writes the instances of ITS Gaussian (row-major over the rect, one running (row, col)
+            // pair: no search, no division) into a window of EM_WIN slots of the warp's run in shared memory; the warp then
+            // copies the window out with consecutive lanes on consecutive slots.  The push loop runs as long as the largest
+            // rect of the 32 Gaussians (mean 5 tiles at C3), against 5 shuffle-search steps + 5 fetch shuffles + a division
+            // per 32 instances of the pull form it replaces.
+            uint2* const win = em_win[threadIdx.x >> 5];
+            for (uint32_t base = 0; base < total; base += EM_WIN) {
+                // this lane's instances inside [base, base + EM_WIN): k in [k0, k1)
+                const uint32_t k0 = rel < base ? min(base - rel, (uint32_t)cnt[r]) : 0u;
+                const uint32_t k1 = rel + (uint32_t)cnt[r] > base + EM_WIN ? (base + EM_WIN > rel ? base + EM_WIN - rel : 0u) : (uint32_t)cnt[r];
+                if (k0 < k1) {
+                    uint32_t row = 0, col = k0;
+                    if (k0 >= (uint32_t)wdt[r]) { row = k0 / (uint32_t)wdt[r]; col = k0 - row * (uint32_t)wdt[r]; }    // only when a rect straddles windows
+                    uint32_t tile = (uint32_t)((y0[r] + (int)row) * gx + x0[r] + (int)col);
+                    uint2* dst = win + (rel + k0 - base);
+                    for (uint32_t k = k0; k < k1; k++) {
+                        *dst++ = make_uint2(tile, g[r]);
+                        tile++; col++;
+                        if (col == (uint32_t)wdt[r]) { col = 0; tile += (uint32_t)(gx - wdt[r]); }
                     }
-                    tile_ids[off0 + t] = (uint32_t)((oy0 + (int)row) * gx + ox0 + (int)col);
-                    gauss_ids[off0 + t] = og;
                 }
+                __syncwarp();
+                const uint32_t nwin = min((uint32_t)EM_WIN, total - base);
+                for (uint32_t t = lane; t < nwin; t += 32) {
+                    const uint2 v = win[t];
+                    tile_ids[off0 + base + t] = v.x;
+                    gauss_ids[off0 + base + t] = v.y;
+                }
+                __syncwarp();
             }
         }
     }
