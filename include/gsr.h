@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 3
+#define GSR_ABI_VERSION 4
 
 /* error codes */
 #define GSR_OK          0
@@ -177,6 +177,28 @@ int gsr_backward(const GsrBwdArgs* args, gsr_stream_t stream);
  * (gsr_b200/dp.py; the reference has no multi-GPU path).
  */
 int gsr_backward_staged(const GsrBwdArgs* args, int stages, int g_begin, int g_end, gsr_stream_t stream);
+
+/*
+ * Deferred per-Gaussian backward (ABI 4): a step that renders several views of ONE Gaussian set through single-view calls
+ * runs, per view, only the blending backward (gsr_backward_staged(args_v, 1, 0, 0, stream) into that view's accum scratch) and,
+ * once per step, the per-Gaussian backward of all n_views <= 16 views together: the parameters are read once and every
+ * gradient row is written once (summed over the views) instead of once per view.  `common` carries what the views share
+ * (P, D, M, W, H, tan_fov*, scale_modifier, means3D, shs / shs_rest, scales, rotations, the summed outputs dL_dopacity,
+ * dL_dmean3D, dL_dsh / dL_dsh_rest, dL_dscale, dL_drot and `accumulate`); colors_precomp / cov3D_precomp must be NULL.
+ * [g_begin, g_end) restricts the call to a range of Gaussians as in gsr_backward_staged (g_end = -1: P).
+ * The result equals n_views gsr_backward calls of which the first overwrites and the others accumulate.
+ */
+typedef struct GsrViewState {
+    const float* viewmatrix;     /* [16] */
+    const float* projmatrix;     /* [16] */
+    const float* cam_pos;        /* [3]  */
+    const int*   radii;          /* [P] of this view's forward */
+    const void*  geom_blob;      /* of this view's forward */
+    const void*  accum;          /* gsr_bwd_accum_bytes(P) bytes filled by this view's blending backward */
+    float*       dL_dmean2D;     /* [P,3], written for this view */
+} GsrViewState;
+int gsr_backward_views(const GsrBwdArgs* common, int n_views, const GsrViewState* views, int g_begin, int g_end,
+                       gsr_stream_t stream);
 
 /*
  * Backward of gsr_forward_batched: radii [n_views,P], dL_dpix [n_views,3,H,W], camera arrays as in the forward,

@@ -308,10 +308,12 @@ static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_
     if (a->P == 0) return GSR_OK;
     if (!a->means3D || !a->radii || !a->dL_dpix || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
     if (!a->geom_blob || !a->binning_blob || !a->img_blob || !a->accum) return GSR_EBLOB;
-    if (!a->dL_dmean2D || !a->dL_dopacity || !a->dL_dmean3D) return GSR_EINVAL;
-    if (a->shs && (!a->dL_dsh || !a->cam_pos)) return GSR_EINVAL;
-    if (a->shs && a->shs_rest && a->M > 1 && (a->M != 16 || !a->dL_dsh_rest)) return GSR_EINVAL;
-    if (!a->cov3D_precomp && (!a->scales || !a->rotations || !a->dL_dscale || !a->dL_drot)) return GSR_ECOV;
+    if (stages & 2) {          // the gradient outputs belong to the per-Gaussian backward
+        if (!a->dL_dmean2D || !a->dL_dopacity || !a->dL_dmean3D) return GSR_EINVAL;
+        if (a->shs && (!a->dL_dsh || !a->cam_pos)) return GSR_EINVAL;
+        if (a->shs && a->shs_rest && a->M > 1 && (a->M != 16 || !a->dL_dsh_rest)) return GSR_EINVAL;
+        if (!a->cov3D_precomp && (!a->scales || !a->rotations || !a->dL_dscale || !a->dL_drot)) return GSR_ECOV;
+    }
 
     if (g_end < 0) g_end = a->P;
     if (g_begin < 0 || g_end > a->P || g_begin > g_end || (stages & ~3) != 0) return GSR_EINVAL;
@@ -411,6 +413,60 @@ int gsr_backward_staged(const GsrBwdArgs* a, int stages, int g_begin, int g_end,
 {
     return backward_impl(a, 1, 1, stream, stages, g_begin, g_end);
 }
+// Per-Gaussian backward of n_views single-view calls at once (the deferred form of a multi-view step): every view brings
+// the blobs of its own forward and the accumulator rows its blending backward filled (gsr_backward_staged, stages = 1); the
+// parameters are read once and every gradient row is written once for all views, instead of once per view.
+int gsr_backward_views(const GsrBwdArgs* a, int n_views, const GsrViewState* views, int g_begin, int g_end, gsr_stream_t stream_)
+{
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (!a || !views || n_views < 1 || n_views > GSR_MAX_VIEWS) return GSR_EINVAL;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3) return GSR_EINVAL;
+    if (a->P == 0) return GSR_OK;
+    if (a->colors_precomp || a->cov3D_precomp) return GSR_EINVAL;           // like the batched entry points
+    if (!a->means3D || !a->shs || !a->scales || !a->rotations) return GSR_EINVAL;
+    if (!a->dL_dopacity || !a->dL_dmean3D || !a->dL_dsh || !a->dL_dscale || !a->dL_drot) return GSR_EINVAL;
+    if (a->shs_rest && a->M > 1 && (a->M != 16 || !a->dL_dsh_rest)) return GSR_EINVAL;
+    if (g_end < 0) g_end = a->P;
+    if (g_begin < 0 || g_end > a->P || g_begin > g_end || (g_begin & 127) != 0) return GSR_EINVAL;
+    if (g_begin == g_end) return GSR_OK;
+    const size_t o = (size_t)g_begin;
+    const int Mdc = (a->shs_rest && a->M > 1) ? 1 : a->M;
+    ViewTab vt = {};
+    for (int v = 0; v < n_views; v++) {
+        const GsrViewState& w = views[v];
+        if (!w.viewmatrix || !w.projmatrix || !w.cam_pos || !w.radii || !w.geom_blob || !w.accum || !w.dL_dmean2D) return GSR_EINVAL;
+        const GeomView gv = geom_view(const_cast<void*>(w.geom_blob), a->P);
+        vt.radii[v] = w.radii + o; vt.rec[v] = gv.rec + o; vt.clamped[v] = gv.clamped + o;
+        vt.accum[v] = (const float*)w.accum + 12 * o; vt.m2d[v] = w.dL_dmean2D + 3 * o;
+        vt.view[v] = w.viewmatrix; vt.proj[v] = w.projmatrix; vt.cam[v] = w.cam_pos;
+    }
+    GsrBwdArgs as = *a;
+    as.P = g_end - g_begin;
+    as.means3D = a->means3D + 3 * o;
+    as.shs = a->shs + 3 * (size_t)Mdc * o; as.dL_dsh = a->dL_dsh + 3 * (size_t)Mdc * o;
+    if (a->shs_rest) { as.shs_rest = a->shs_rest + 3 * (size_t)(a->M - 1) * o; if (a->dL_dsh_rest) as.dL_dsh_rest = a->dL_dsh_rest + 3 * (size_t)(a->M - 1) * o; }
+    as.scales = a->scales + 3 * o; as.rotations = a->rotations + 4 * o;
+    as.dL_dopacity = a->dL_dopacity + o; as.dL_dmean3D = a->dL_dmean3D + 3 * o;
+    as.dL_dscale = a->dL_dscale + 3 * o; as.dL_drot = a->dL_drot + 4 * o;
+    as.dL_dcolor = nullptr; as.dL_dcov3D = nullptr;
+    as.viewmatrix = views[0].viewmatrix; as.projmatrix = views[0].projmatrix; as.cam_pos = views[0].cam_pos;
+    as.radii = vt.radii[0]; as.dL_dmean2D = vt.m2d[0];
+    GeomView g0v = {};
+    g0v.rec = const_cast<SplatRec*>(vt.rec[0]); g0v.clamped = const_cast<uint8_t*>(vt.clamped[0]);
+    int rc;
+    DeviceCtx* ctx = nullptr;
+    if ((rc = device_ctx(&ctx))) return rc;
+    stage_begin(5, s);
+    std::lock_guard<std::mutex> fence_lock(ctx->fence_mu);
+    if (ctx->fence_recorded) GSR_CUDA(cudaStreamWaitEvent(s, ctx->grad_fence, 0));
+    if ((rc = launch_preprocess_backward(as, n_views, g0v, vt.accum[0], s, n_views > 1 ? &vt : nullptr))) return rc;
+    GSR_CUDA(cudaEventRecord(ctx->grad_fence, s));
+    ctx->fence_recorded = true;
+    stage_end(5, s);
+    GSR_STAGE(a->debug, s, "preprocess_backward (views)");
+    return GSR_OK;
+}
+
 int gsr_backward_batched(const GsrBwdArgs* a, int n_views, gsr_stream_t stream)
 {
     if (n_views > 1 && a && (a->colors_precomp || a->cov3D_precomp)) return GSR_EINVAL;

@@ -156,7 +156,19 @@ __device__ __forceinline__ void load_camera(Camera& cam, const CameraArgs& ca)
 // preprocess.cu
 int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, const GeomView& g, cudaStream_t s);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
-int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, const float* accum, cudaStream_t s);
+// per-view base pointers of a multi-view per-Gaussian backward (kernel parameter; <= GSR_MAX_VIEWS views)
+struct ViewTab {
+    const int*      radii[GSR_MAX_VIEWS];
+    const SplatRec* rec[GSR_MAX_VIEWS];
+    const uint8_t*  clamped[GSR_MAX_VIEWS];
+    const float*    accum[GSR_MAX_VIEWS];
+    float*          m2d[GSR_MAX_VIEWS];
+    const float*    view[GSR_MAX_VIEWS];
+    const float*    proj[GSR_MAX_VIEWS];
+    const float*    cam[GSR_MAX_VIEWS];
+};
+int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, const float* accum, cudaStream_t s,
+                               const ViewTab* tab = nullptr);
 
 // sort.cu
 // sorts Gaussian ids by depth bits (stable) into g.order; counts instances per tile -> tile ranges, split-pass histograms

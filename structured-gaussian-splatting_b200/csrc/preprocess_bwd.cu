@@ -84,18 +84,18 @@ __device__ __forceinline__ void store_sh_grads(float* __restrict__ dst, const fl
 }
 
 template <bool WITH_SH, bool MULTI>
-__global__ void __launch_bounds__(256, WITH_SH ? 1 : (MULTI ? 3 : 4)) preprocess_bwd_kernel(PreBwdArgs a, CameraArgs ca)
+__global__ void __launch_bounds__(256, WITH_SH ? 1 : (MULTI ? 3 : 4)) preprocess_bwd_kernel(PreBwdArgs a, CameraArgs ca,
+                                                                                            const __grid_constant__ ViewTab vt)
 {
     const int NV = MULTI ? a.V : 1;            // compile-time 1 for the single-view call: the view loops fold away
-    // a.V views of a batched call (1 for the reference's single-view call): view v owns slice v * P + idx of the per-view
-    // arrays (radii, records, clamp flags, accumulator rows, dL/dmean2D); the parameter gradients are summed over the
+    // a.V views (1 for the reference's single-view call): view v's per-view arrays (radii, records, clamp flags, accumulator
+    // rows, dL/dmean2D, camera) are reached through the pointer table vt - slices v * P of one allocation for a batched call,
+    // separate allocations for the deferred backward of single-view calls; the parameter gradients are summed over the
     // views in registers and written once.
     __shared__ Camera cams[MULTI ? GSR_MAX_VIEWS : 1];
     for (int v = 0; v < NV; v++) {
         CameraArgs cv = ca;
-        cv.view += 16 * v;
-        if (cv.proj) cv.proj += 16 * v;
-        if (cv.cam) cv.cam += 3 * v;
+        if (MULTI) { cv.view = vt.view[v]; cv.proj = vt.proj[v]; cv.cam = vt.cam[v]; }
         load_camera(cams[v], cv);
     }
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -105,11 +105,11 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : (MULTI ? 3 : 4)) preprocess
     const bool acc_m = a.acc & GSR_ACC_MEAN3D, acc_o = a.acc & GSR_ACC_OPACITY, acc_sh = a.acc & GSR_ACC_SH,
                acc_s = a.acc & GSR_ACC_SCALE, acc_r = a.acc & GSR_ACC_ROT;
     bool any_visible = false;
-    for (int v = 0; v < NV; v++) any_visible = any_visible || a.radii[(size_t)v * a.P + idx] > 0;
+    for (int v = 0; v < NV; v++) any_visible = any_visible || (MULTI ? vt.radii[v][idx] : a.radii[idx]) > 0;
     if (!any_visible) {
         // culled in every view: every owned gradient row is zero (left untouched when accumulating)
         for (int v = 0; v < NV; v++) {
-            float* m2 = a.dL_dmean2D + 3 * ((size_t)v * a.P + idx);
+            float* m2 = (MULTI ? vt.m2d[v] : a.dL_dmean2D) + 3 * (size_t)idx;
             m2[0] = 0.f; m2[1] = 0.f; m2[2] = 0.f;
         }
         if (!acc_o) a.dL_dopacity[idx] = 0.f;
@@ -162,22 +162,28 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : (MULTI ? 3 : 4)) preprocess
     (void)sh_written;
     for (int v = 0; v < NV; v++) {
     const Camera& cam = cams[v];
-    const size_t vi = (size_t)v * a.P + idx;
-    if (!(a.radii[vi] > 0)) {
-        a.dL_dmean2D[3 * vi] = 0.f; a.dL_dmean2D[3 * vi + 1] = 0.f; a.dL_dmean2D[3 * vi + 2] = 0.f;
+    const int* v_radii = MULTI ? vt.radii[v] : a.radii;
+    float* v_m2d = MULTI ? vt.m2d[v] : a.dL_dmean2D;
+    const float* v_accum = MULTI ? vt.accum[v] : a.accum;
+    const SplatRec* v_rec = MULTI ? vt.rec[v] : a.rec;
+    const uint8_t* v_clamped = MULTI ? vt.clamped[v] : a.clamped;
+    (void)v_clamped;
+    const size_t vi = (size_t)idx;            // index inside view v's arrays
+    if (!(v_radii[vi] > 0)) {
+        v_m2d[3 * vi] = 0.f; v_m2d[3 * vi + 1] = 0.f; v_m2d[3 * vi + 2] = 0.f;
         continue;
     }
     // accumulator row: three 16-byte loads
-    const float4* ar = reinterpret_cast<const float4*>(a.accum + (size_t)12 * vi);
+    const float4* ar = reinterpret_cast<const float4*>(v_accum + (size_t)12 * vi);
     const float4 A0 = ar[0], A1 = ar[1], A2 = ar[2];
     const float dcol[3] = {A0.x, A0.y, A0.z};
     // moments -> gradients (backward.cu:536-551 with the per-Gaussian constants factored out of the pixel sums)
-    const float4 r0 = a.rec[vi].q0, r1 = a.rec[vi].q1;
+    const float4 r0 = v_rec[vi].q0, r1 = v_rec[vi].q1;
     const float cA = r0.z, cB = r0.w, cC = r1.x, opac = r1.y;
     const float g2x = -0.5f * cam.W * (cA * A0.w + cB * A1.x);
     const float g2y = -0.5f * cam.H * (cC * A1.x + cB * A0.w);
     const float dcon_x = -0.5f * A1.y, dcon_y = -0.5f * A1.z, dcon_w = -0.5f * A1.w;
-    a.dL_dmean2D[3 * vi] = g2x; a.dL_dmean2D[3 * vi + 1] = g2y; a.dL_dmean2D[3 * vi + 2] = 0.f;
+    v_m2d[3 * vi] = g2x; v_m2d[3 * vi + 1] = g2y; v_m2d[3 * vi + 2] = 0.f;
     s_dop += opac > 0.f ? A2.x / opac : 0.f;
     if (a.dL_dcolor) { a.dL_dcolor[3 * idx] = dcol[0]; a.dL_dcolor[3 * idx + 1] = dcol[1]; a.dL_dcolor[3 * idx + 2] = dcol[2]; }
 
@@ -262,7 +268,7 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : (MULTI ? 3 : 4)) preprocess
         const float s2 = ox * ox + oy * oy + oz * oz;
         const float len = sqrtf(s2);
         const float x = ox / len, y = oy / len, z = oz / len;
-        const uint32_t cl = a.clamped[vi];
+        const uint32_t cl = v_clamped[vi];
         const float dRGB[3] = {(cl & 1) ? 0.f : dcol[0], (cl & 2) ? 0.f : dcol[1], (cl & 4) ? 0.f : dcol[2]};
         const float* shp = a.shs + (size_t)M3f * idx;
         const bool vec = (((size_t)shp) & 15) == 0 && (M3f % 4 == 0);
@@ -632,9 +638,8 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D
 // the direction gradient of that chunk to dL/dmean3D straight away (dnormvdv is linear in it), so no per-view state
 // survives the inner loop.  Replaces V read-modify-write passes over the 192-byte gradient rows.
 template <int J, class Row>
-__device__ __forceinline__ void sh_chunk_views(const Row& row, int P, int V, int D, int gid, float px, float py, float pz,
-                                               const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
-                                               const float* __restrict__ accum, const float* __restrict__ campos, float* dm)
+__device__ __forceinline__ void sh_chunk_views(const Row& row, int V, int D, int gid, float px, float py, float pz, const ViewTab& vt,
+                                               float* dm)
 {
     float f[12];
     row.template load<J>(f);
@@ -642,12 +647,12 @@ __device__ __forceinline__ void sh_chunk_views(const Row& row, int P, int V, int
 #pragma unroll
     for (int k = 0; k < 12; k++) g[k] = 0.f;
     for (int v = 0; v < V; v++) {
-        const size_t vi = (size_t)v * P + gid;
-        if (!(radii[vi] > 0)) continue;
-        const float4 A0 = *reinterpret_cast<const float4*>(accum + (size_t)12 * vi);
-        const uint32_t cl = clamped[vi];
+        if (!(vt.radii[v][gid] > 0)) continue;
+        const float4 A0 = *reinterpret_cast<const float4*>(vt.accum[v] + (size_t)12 * gid);
+        const uint32_t cl = vt.clamped[v][gid];
         const float dR = (cl & 1) ? 0.f : A0.x, dG = (cl & 2) ? 0.f : A0.y, dB = (cl & 4) ? 0.f : A0.z;
-        const float ox = px - campos[3 * v], oy = py - campos[3 * v + 1], oz = pz - campos[3 * v + 2];
+        const float* campos = vt.cam[v];
+        const float ox = px - campos[0], oy = py - campos[1], oz = pz - campos[2];
         const float sq = ox * ox + oy * oy + oz * oz;
         const float rl = rsqrtf(sq);
         float w[4], bx[4], by[4], bz[4];
@@ -669,13 +674,11 @@ __device__ __forceinline__ void sh_chunk_views(const Row& row, int P, int V, int
 
 template <bool SPLIT>
 __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P, int V, int D, const float* __restrict__ means,
-                                                                          const int* __restrict__ radii, const float* __restrict__ shs,
-                                                                          const uint8_t* __restrict__ clamped,
-                                                                          const float* __restrict__ accum,
-                                                                          const float* __restrict__ campos, float* __restrict__ dL_dsh,
+                                                                          const float* __restrict__ shs, float* __restrict__ dL_dsh,
                                                                           float* __restrict__ dL_dmean3D, unsigned acc,
                                                                           const float* __restrict__ shs_rest,
-                                                                          float* __restrict__ dL_dsh_rest)
+                                                                          float* __restrict__ dL_dsh_rest,
+                                                                          const __grid_constant__ ViewTab vt)
 {
     __shared__ float4 rows[SHB_WARPS][32 * SHB_ROW4];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -687,7 +690,7 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P,
     const int gid = g0 + lane;
     bool visible = false;
     if (lane < nrow)
-        for (int v = 0; v < V; v++) visible = visible || radii[(size_t)v * P + gid] > 0;
+        for (int v = 0; v < V; v++) visible = visible || vt.radii[v][gid] > 0;
     const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
     float* const flat = reinterpret_cast<float*>(my);
     const RowFlat frow{flat + lane * 3, flat + SHB_FLAT_DC + lane * 45};
@@ -707,16 +710,16 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P,
         const float px = means[3 * (size_t)gid], py = means[3 * (size_t)gid + 1], pz = means[3 * (size_t)gid + 2];
         float dm[3] = {0.f, 0.f, 0.f};
         if (SPLIT) {
-            sh_chunk_views<0>(frow, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-            sh_chunk_views<1>(frow, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-            sh_chunk_views<2>(frow, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-            sh_chunk_views<3>(frow, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+            sh_chunk_views<0>(frow, V, D, gid, px, py, pz, vt, dm);
+            sh_chunk_views<1>(frow, V, D, gid, px, py, pz, vt, dm);
+            sh_chunk_views<2>(frow, V, D, gid, px, py, pz, vt, dm);
+            sh_chunk_views<3>(frow, V, D, gid, px, py, pz, vt, dm);
         } else {
             const RowPadded row{my + lane * SHB_ROW4};
-            sh_chunk_views<0>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-            sh_chunk_views<1>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-            sh_chunk_views<2>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
-            sh_chunk_views<3>(row, P, V, D, gid, px, py, pz, radii, clamped, accum, campos, dm);
+            sh_chunk_views<0>(row, V, D, gid, px, py, pz, vt, dm);
+            sh_chunk_views<1>(row, V, D, gid, px, py, pz, vt, dm);
+            sh_chunk_views<2>(row, V, D, gid, px, py, pz, vt, dm);
+            sh_chunk_views<3>(row, V, D, gid, px, py, pz, vt, dm);
         }
         const bool atom = acc & ACC_ATOMIC_M3;
         put_m3(dL_dmean3D + 3 * (size_t)gid, dm[0], acc_m, atom);
@@ -757,9 +760,22 @@ __global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P,
     }
 }
 
-int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, const float* accum, cudaStream_t s)
+int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, const float* accum, cudaStream_t s, const ViewTab* tab)
 {
-    // a: the batched call's arguments (per-view arrays [V][...], cameras [V][16] / [V][3]); V <= GSR_MAX_VIEWS
+    // a: the batched call's arguments (per-view arrays [V][...], cameras [V][16] / [V][3]); V <= GSR_MAX_VIEWS.
+    // tab != nullptr: the views' arrays are reached through this pointer table instead (deferred backward of single-view
+    // calls: every view has blobs of its own); a.radii / a.dL_dmean2D / g / accum are then ignored for V > 1.
+    ViewTab vt = {};
+    if (tab) vt = *tab;
+    else if (V > 1) {
+        for (int v = 0; v < V; v++) {
+            const size_t o = (size_t)v * a.P;
+            vt.radii[v] = a.radii + o; vt.rec[v] = g.rec + o; vt.clamped[v] = g.clamped + o; vt.accum[v] = accum + 12 * o;
+            vt.m2d[v] = a.dL_dmean2D + 3 * o;
+            vt.view[v] = a.viewmatrix + 16 * v; vt.proj[v] = a.projmatrix ? a.projmatrix + 16 * v : nullptr;
+            vt.cam[v] = a.cam_pos ? a.cam_pos + 3 * v : nullptr;
+        }
+    }
     const CameraArgs cam = make_camera_args(a.viewmatrix, a.projmatrix, a.cam_pos, a.tan_fovx, a.tan_fovy, a.W, a.H);
     PreBwdArgs k;
     k.P = a.P; k.D = a.D; k.M = a.M; k.V = V;
@@ -801,16 +817,16 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
             GSR_LAUNCH(sh_bwd_m16_kernel<true>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs,
                        g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, a.shs_rest, a.dL_dsh_rest);
         else
-            GSR_LAUNCH(sh_bwd_m16_views_kernel<true>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii,
-                       a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, a.shs_rest, a.dL_dsh_rest);
+            GSR_LAUNCH(sh_bwd_m16_views_kernel<true>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D,
+                       a.shs, a.dL_dsh, a.dL_dmean3D, acc_flags, a.shs_rest, a.dL_dsh_rest, vt);
         k.sh_done = 1;
     } else if (a.shs && a.M == 16 && ((((size_t)a.shs) | ((size_t)a.dL_dsh)) & 15) == 0 && options().sh_split) {
         if (V == 1)
             GSR_LAUNCH(sh_bwd_m16_kernel<false>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, a.D, a.means3D, a.radii, a.shs,
                        g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, (const float*)nullptr, (float*)nullptr);
         else
-            GSR_LAUNCH(sh_bwd_m16_views_kernel<false>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D, a.radii,
-                       a.shs, g.clamped, accum, a.cam_pos, a.dL_dsh, a.dL_dmean3D, acc_flags, (const float*)nullptr, (float*)nullptr);
+            GSR_LAUNCH(sh_bwd_m16_views_kernel<false>, cdiv(a.P, 32 * SHB_WARPS), 32 * SHB_WARPS, 0, s, a.P, V, a.D, a.means3D,
+                       a.shs, a.dL_dsh, a.dL_dmean3D, acc_flags, (const float*)nullptr, (float*)nullptr, vt);
         k.sh_done = 1;
     }
     if (forked) {
@@ -819,11 +835,11 @@ int launch_preprocess_backward(const GsrBwdArgs& a, int V, const GeomView& g, co
     }
     const bool with_sh = !(k.sh_done || !a.shs);
     if (V == 1) {
-        if (!with_sh) GSR_LAUNCH((preprocess_bwd_kernel<false, false>), cdiv(a.P, 256), 256, 0, s, k, cam);
-        else GSR_LAUNCH((preprocess_bwd_kernel<true, false>), cdiv(a.P, 256), 256, 0, s, k, cam);
+        if (!with_sh) GSR_LAUNCH((preprocess_bwd_kernel<false, false>), cdiv(a.P, 256), 256, 0, s, k, cam, vt);
+        else GSR_LAUNCH((preprocess_bwd_kernel<true, false>), cdiv(a.P, 256), 256, 0, s, k, cam, vt);
     } else {
-        if (!with_sh) GSR_LAUNCH((preprocess_bwd_kernel<false, true>), cdiv(a.P, 256), 256, 0, s, k, cam);
-        else GSR_LAUNCH((preprocess_bwd_kernel<true, true>), cdiv(a.P, 256), 256, 0, s, k, cam);
+        if (!with_sh) GSR_LAUNCH((preprocess_bwd_kernel<false, true>), cdiv(a.P, 256), 256, 0, s, k, cam, vt);
+        else GSR_LAUNCH((preprocess_bwd_kernel<true, true>), cdiv(a.P, 256), 256, 0, s, k, cam, vt);
     }
     if (forked) GSR_CUDA(cudaStreamWaitEvent(main_s, ss.join, 0));
     return GSR_OK;

@@ -298,6 +298,102 @@ rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tenso
                                              R, binningBuffer, imageBuffer, debug, e, e, e, e, e, false);
 }
 
+// Deferred backward, step 1 (per view): the blending backward alone.  Returns the view's accumulator rows [P,12]; the
+// per-Gaussian backward of all pending views follows in rasterize_gaussians_backward_views.
+torch::Tensor rasterize_gaussians_backward_blend(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                                                 const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix, const float tan_fovx,
+                                                 const float tan_fovy, const torch::Tensor& dL_dout_color, const int M, const int degree,
+                                                 const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
+                                                 const torch::Tensor& imageBuffer, const bool debug)
+{
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = (int)means3D.size(0);
+    const int H = (int)dL_dout_color.size(1), W = (int)dL_dout_color.size(2);
+    auto f32 = means3D.options().dtype(torch::kFloat32);
+    torch::Tensor accum = torch::empty({(long long)P, 12}, f32);
+    if (P != 0) {
+        F32 bg(background), m3(means3D), vm(viewmatrix), pm(projmatrix), dpix(dL_dout_color);
+        torch::Tensor radii_c = radii.contiguous();
+        GsrBwdArgs a = {};
+        a.P = P; a.D = degree; a.M = M; a.R = R; a.W = W; a.H = H;
+        a.background = bg.ptr(); a.means3D = m3.ptr(); a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr();
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+        a.radii = radii_c.data_ptr<int>();
+        a.geom_blob = geomBuffer.data_ptr(); a.binning_blob = binningBuffer.data_ptr(); a.img_blob = imageBuffer.data_ptr();
+        a.dL_dpix = dpix.ptr();
+        a.accum = accum.data_ptr();
+        a.debug = debug;
+        check(gsr_backward_staged(&a, 1, 0, 0, current_stream()), "rasterize_gaussians_backward_blend");
+    }
+    return accum;
+}
+
+// Deferred backward, step 2 (once per step): the per-Gaussian backward of all pending views (<= 16) of ONE parameter set,
+// gradients written (or, with `accumulate`, added) into the given buffers; returns dL_dmeans2D [P,3] per view.
+// n_chunks > 0: in ranges of Gaussians with `after_chunk(g0, g1)` called after each range has been queued.
+std::vector<torch::Tensor>
+rasterize_gaussians_backward_views(const torch::Tensor& means3D, const torch::Tensor& scales, const torch::Tensor& rotations,
+                                   const float scale_modifier, const torch::Tensor& sh, const int degree, const float tan_fovx,
+                                   const float tan_fovy, const int image_height, const int image_width,
+                                   std::vector<torch::Tensor> viewmatrices, std::vector<torch::Tensor> projmatrices,
+                                   std::vector<torch::Tensor> camposs, std::vector<torch::Tensor> radii,
+                                   std::vector<torch::Tensor> geomBuffers, std::vector<torch::Tensor> accums,
+                                   const torch::Tensor& into_means3D, const torch::Tensor& into_opacity, const torch::Tensor& into_sh,
+                                   const torch::Tensor& into_scales, const torch::Tensor& into_rotations, const bool accumulate,
+                                   const int n_chunks, py::object after_chunk)
+{
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = (int)means3D.size(0);
+    const size_t V = viewmatrices.size();
+    TORCH_CHECK(V >= 1 && V <= 16 && projmatrices.size() == V && camposs.size() == V && radii.size() == V && geomBuffers.size() == V &&
+                accums.size() == V, "rasterize_gaussians_backward_views: 1..16 views, lists of equal length");
+    TORCH_CHECK(sh.dim() == 3 && sh.size(0) == P && scales.numel() == (int64_t)P * 3 && rotations.numel() == (int64_t)P * 4,
+                "rasterize_gaussians_backward_views takes shs [P,M,3], scales and rotations");
+    const int M = (int)sh.size(1);
+    auto ok = [&](const torch::Tensor& t, int64_t n) {
+        return t.is_cuda() && t.scalar_type() == torch::kFloat32 && t.is_contiguous() && t.numel() == n;
+    };
+    TORCH_CHECK(ok(into_means3D, (int64_t)P * 3) && ok(into_opacity, P) && ok(into_sh, (int64_t)P * M * 3) && ok(into_scales, (int64_t)P * 3) &&
+                ok(into_rotations, (int64_t)P * 4), "gradient targets must be contiguous fp32 CUDA tensors with the gradients' element counts");
+    auto f32 = means3D.options().dtype(torch::kFloat32);
+    std::vector<torch::Tensor> m2d;
+    for (size_t v = 0; v < V; v++) m2d.push_back(P == 0 ? torch::zeros({P, 3}, f32) : torch::empty({P, 3}, f32));
+    if (P == 0) return m2d;
+    F32 m3(means3D), sc(scales), rot(rotations), shs(sh);
+    std::vector<torch::Tensor> keep;
+    std::vector<GsrViewState> vs(V);
+    for (size_t v = 0; v < V; v++) {
+        torch::Tensor vm = viewmatrices[v].contiguous(), pm = projmatrices[v].contiguous(), cp = camposs[v].contiguous(),
+                      rd = radii[v].contiguous();
+        TORCH_CHECK(accums[v].is_cuda() && accums[v].is_contiguous() && accums[v].numel() == (int64_t)P * 12 && rd.numel() == P,
+                    "rasterize_gaussians_backward_views: bad per-view state");
+        keep.insert(keep.end(), {vm, pm, cp, rd});
+        vs[v].viewmatrix = vm.data_ptr<float>(); vs[v].projmatrix = pm.data_ptr<float>(); vs[v].cam_pos = cp.data_ptr<float>();
+        vs[v].radii = rd.data_ptr<int>(); vs[v].geom_blob = geomBuffers[v].data_ptr(); vs[v].accum = accums[v].data_ptr();
+        vs[v].dL_dmean2D = m2d[v].data_ptr<float>();
+    }
+    GsrBwdArgs a = {};
+    a.P = P; a.D = degree; a.M = M; a.W = image_width; a.H = image_height;
+    a.means3D = m3.ptr(); a.shs = shs.ptr(); a.scales = sc.ptr(); a.scale_modifier = scale_modifier; a.rotations = rot.ptr();
+    a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+    a.dL_dopacity = into_opacity.data_ptr<float>(); a.dL_dmean3D = into_means3D.data_ptr<float>(); a.dL_dsh = into_sh.data_ptr<float>();
+    a.dL_dscale = into_scales.data_ptr<float>(); a.dL_drot = into_rotations.data_ptr<float>();
+    if (accumulate) a.accumulate = GSR_ACC_MEAN3D | GSR_ACC_OPACITY | GSR_ACC_SH | GSR_ACC_SCALE | GSR_ACC_ROT;
+    if (n_chunks <= 0) {
+        check(gsr_backward_views(&a, (int)V, vs.data(), 0, -1, current_stream()), "rasterize_gaussians_backward_views");
+    } else {
+        const int rows = (((P + n_chunks - 1) / n_chunks) + 127) / 128 * 128;
+        for (int g0 = 0; g0 < P; g0 += rows) {
+            const int g1 = std::min(P, g0 + rows);
+            check(gsr_backward_views(&a, (int)V, vs.data(), g0, g1, current_stream()), "rasterize_gaussians_backward_views (range)");
+            if (!after_chunk.is_none()) after_chunk(g0, g1);
+        }
+    }
+    return m2d;
+}
+
 torch::Tensor mark_visible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix)
 {
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
@@ -669,6 +765,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
     m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward, nogil());
     m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into, nogil());
     m.def("rasterize_gaussians_backward_chunked", &rasterize_gaussians_backward_chunked);
+    m.def("rasterize_gaussians_backward_blend", &rasterize_gaussians_backward_blend, nogil());
+    m.def("rasterize_gaussians_backward_views", &rasterize_gaussians_backward_views);
     m.def("set_option", [](const std::string& name, int value) {
         int prev = 0;
         if (gsr_debug_get_option(name.c_str(), &prev) != GSR_OK || gsr_debug_set_option(name.c_str(), value) != GSR_OK)

@@ -65,12 +65,58 @@ class _Token:
 
 
 def set_grad_mode(mode):
-    """None (reference behaviour), "overwrite" or "accumulate"; returns the previous mode."""
+    """None (reference behaviour), "overwrite", "accumulate" or "deferred"; returns the previous mode.
+    "deferred": a step that renders several views of the same leaves runs, per view, only the blending backward; the
+    per-Gaussian backward of all pending views (cov2D / cov3D / SH / projection: bandwidth-bound, 0.4 ms per view at C3) runs
+    ONCE in flush_deferred(), reading the parameters once and writing every gradient row once (0.2 ms per view).  Until the
+    flush the leaves' .grad do not contain the pending views; means2D.grad of every view is set by the flush."""
     global _GRAD_MODE
-    if mode not in (None, "overwrite", "accumulate"):
-        raise ValueError("grad mode must be None, 'overwrite' or 'accumulate'")
+    if mode not in (None, "overwrite", "accumulate", "deferred"):
+        raise ValueError("grad mode must be None, 'overwrite', 'accumulate' or 'deferred'")
     prev, _GRAD_MODE = _GRAD_MODE, mode
     return prev
+
+
+_DEFERRED = []                   # pending views of the "deferred" mode (one record per backward)
+
+
+def pending_deferred():
+    return len(_DEFERRED)
+
+
+def flush_deferred(accumulate=False, n_chunks=0, after_chunk=None):
+    """Per-Gaussian backward of all pending "deferred" views, summed into the leaves' .grad buffers (replacing their contents
+    unless `accumulate`).  n_chunks > 0: in ranges of Gaussians, `after_chunk(g_begin, g_end)` being called on the host after
+    each range has been queued (gsr_b200.dp starts that range's all-reduce from it).  Returns the number of views flushed."""
+    n = len(_DEFERRED)
+    if n == 0:
+        return 0
+    recs, first = list(_DEFERRED), _DEFERRED[0]
+    del _DEFERRED[:]
+    for r in recs:
+        if any(a is not b for a, b in zip(r["leaves"], first["leaves"])) or r["key"] != first["key"]:
+            raise RuntimeError("flush_deferred: the pending views do not share parameters / raster settings")
+    means3D, opacities, sh, scales, rotations = first["leaves"]
+    targets = []
+    for leaf in first["leaves"]:
+        g = _grad_target(leaf)
+        if g is None:
+            raise RuntimeError("flush_deferred: a parameter lost its preallocated .grad buffer since the views were rendered")
+        targets.append(g)
+    H, W, tanfovx, tanfovy, degree, scale_modifier = first["key"]
+    for base in range(0, n, 16):
+        part = recs[base:base + 16]
+        with torch.no_grad():
+            m2d = _C.rasterize_gaussians_backward_views(
+                means3D, scales, rotations, scale_modifier, sh, degree, tanfovx, tanfovy, H, W,
+                [r["viewmatrix"] for r in part], [r["projmatrix"] for r in part], [r["campos"] for r in part],
+                [r["radii"] for r in part], [r["geom"] for r in part], [r["accum"] for r in part],
+                targets[0], targets[1], targets[2], targets[3], targets[4], bool(accumulate or base > 0), int(n_chunks), after_chunk)
+        for r, g2 in zip(part, m2d):
+            m = r["means2D"]
+            if m is not None and m.requires_grad and m.is_leaf:
+                m.grad = g2 if m.grad is None else m.grad + g2
+    return n
 
 
 def _grad_target(t):
@@ -125,6 +171,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         if _GRAD_MODE is not None:
             ctx.grad_leaves = (means3D, opacities, sh, scales, rotations)
             ctx.grad_targets = tuple(_grad_target(t) for t in ctx.grad_leaves)
+            ctx.means2D_ref = means2D if _GRAD_MODE == "deferred" else None
             # (autograd runs forward() with grad mode off: the caller's mode was noted by rasterize_gaussians())
             if _GRAD_MODE == "overwrite" and getattr(_TLS, "grad_enabled", False):
                 ctx.overwrite_token = _Token()
@@ -149,7 +196,18 @@ class _RasterizeGaussians(torch.autograd.Function):
         args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix,
                 rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, sh, rs.sh_degree, rs.campos, geomBuffer,
                 ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
-        if ctx.grad_mode is None:
+        deferred = (ctx.grad_mode == "deferred" and colors_precomp.numel() == 0 and cov3Ds_precomp.numel() == 0 and sh.dim() == 3
+                    and all(g is not None and getattr(leaf, "grad", None) is g for g, leaf in zip(ctx.grad_targets, ctx.grad_leaves)))
+        if deferred:
+            # the blending backward now, the per-Gaussian backward with the other pending views in flush_deferred()
+            accum = _C.rasterize_gaussians_backward_blend(rs.bg, means3D, radii, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                                                          grad_out_color, int(sh.shape[1]), rs.sh_degree, geomBuffer, ctx.num_rendered,
+                                                          binningBuffer, imgBuffer, rs.debug)
+            _DEFERRED.append(dict(accum=accum, geom=geomBuffer, radii=radii, viewmatrix=rs.viewmatrix, projmatrix=rs.projmatrix,
+                                  campos=rs.campos, means2D=ctx.means2D_ref, leaves=ctx.grad_leaves,
+                                  key=(rs.image_height, rs.image_width, rs.tanfovx, rs.tanfovy, rs.sh_degree, rs.scale_modifier)))
+            return (None,) * 9
+        if ctx.grad_mode is None or ctx.grad_mode == "deferred":
             (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
              grad_rotations) = _call_with_snapshot(_C.rasterize_gaussians_backward, args, rs.debug, "snapshot_bw.dump", "backward")
         else:

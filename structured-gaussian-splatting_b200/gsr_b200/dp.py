@@ -197,6 +197,38 @@ def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
     return total
 
 
+def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
+                   loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None,
+                   overlap_chunks: int = 0, all_reduce: bool = True):
+    """The step in DEFERRED form (diff_gaussian_rasterization.set_grad_mode("deferred")): every view runs its forward and its
+    blending backward; the per-Gaussian backward of all the rank's views then runs once (parameters read once, every gradient
+    row written once: 0.2 instead of 0.4 ms per view at C3), in `overlap_chunks` ranges of Gaussians when > 0, the all-reduce
+    of a range being issued right behind it - the whole per-Gaussian stage of the step (not just the last view's) is the
+    window the collective hides in.  Returns the summed local loss."""
+    total = None
+    prev = rasterizer_mod.set_grad_mode("deferred")
+    try:
+        for k in view_ids:
+            color, _radii, _m2d = render_view(rasterizer_mod, params, cams[k], bg, sh_degree)
+            loss = loss_fn(color, k)
+            loss.backward()
+            total = loss.detach() if total is None else total + loss.detach()
+    finally:
+        rasterizer_mod.set_grad_mode(prev)
+    multi = all_reduce and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    works = []
+    if multi and overlap_chunks > 0:
+        rasterizer_mod.flush_deferred(False, overlap_chunks, lambda g0, g1: works.append(flat.all_reduce_rows(g0, g1, group)))
+        for w in works:
+            if w is not None:
+                w.wait()
+    else:
+        rasterizer_mod.flush_deferred(False)
+        if multi:
+            flat.all_reduce(group)
+    return total
+
+
 def dp_step(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
             loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None, fused: bool = True,
             n_streams: int = 1, overlap_chunks: int = 0):

@@ -30,11 +30,13 @@ def _worker(rank, world, port, q):
         go = [synth.grad_image(W, H, seed=50 + k).to(dev) for k in range(V)]
         loss_fn = lambda color, k: (color * go[k]).sum()
         res = {}
-        for name, kw in (("plain", dict()), ("overlap3", dict(overlap_chunks=3)), ("overlap5_registered", dict(overlap_chunks=5))):
+        for name, kw in (("plain", dict()), ("overlap3", dict(overlap_chunks=3)), ("overlap5_registered", dict(overlap_chunks=5)),
+                         ("deferred", dict()), ("deferred_overlap4_registered", dict(overlap_chunks=4))):
             params = dp.make_leaf_params(sc, dev)
             flat = dp.FlatGrads(params, nccl_registered=name.endswith("registered"))
             flat.flat.fill_(float("nan"))
-            total = dp.dp_step(dgr, params, flat, cams, bg, D, loss_fn, dp.shard_views(V, rank, world), **kw)
+            step = dp.deferred_views if name.startswith("deferred") else dp.dp_step
+            total = step(dgr, params, flat, cams, bg, D, loss_fn, dp.shard_views(V, rank, world), **kw)
             torch.cuda.synchronize()
             res[name] = (flat.flat.clone().cpu().numpy(), float(total), bool(flat.registered))
             flat.release()
@@ -68,7 +70,7 @@ def test_dp_step_nccl_world2_equals_single_gpu():
         assert err is None, "rank %d failed:\n%s" % (rank, err)
     ref_flat, ref_total = out[0][2]
     assert np.isfinite(ref_flat).all()
-    for name in ("plain", "overlap3", "overlap5_registered"):
+    for name in ("plain", "overlap3", "overlap5_registered", "deferred", "deferred_overlap4_registered"):
         f0, t0, _ = out[0][1][name]
         f1, t1, _ = out[1][1][name]
         assert np.array_equal(f0, f1), name + ": replicas must hold identical sums"
