@@ -58,6 +58,10 @@ def parse_args():
                     help="skip the extra `train_step` object (a full iteration: activations, render, L1+D-SSIM, Adam; N=1 only)")
     ap.add_argument("--plain-autograd", action="store_true",
                     help="sum the views' gradients through autograd (.grad += per parameter) instead of in the backward kernels")
+    ap.add_argument("--grad-sum", default="deferred", choices=["deferred", "kernels", "autograd"],
+                    help="how a step's views are summed: deferred = blending backward per view, ONE per-Gaussian backward per step "
+                         "(set_grad_mode('deferred') + flush_deferred); kernels = every view's backward adds into the buffer "
+                         "(set_grad_mode overwrite / accumulate); autograd = plain .grad += (same as --plain-autograd)")
     ap.add_argument("--no-extras", action="store_true",
                     help="headline + stages only: skip batched / two-stream / forward-only / plain-api / dist2 / reference-cuda / c5 legs")
     ap.add_argument("--no-c5", action="store_true", help="skip the config C5 leg (6 M Gaussians)")
@@ -400,7 +404,10 @@ def main():
         return [(step * vps * world + j * world + rank) % V for j in range(vps)]
 
     stats = {"R": 0, "Pv": 0, "views": 0}
-    fused = not args.plain_autograd
+    if args.plain_autograd:
+        args.grad_sum = "autograd"
+    fused = args.grad_sum != "autograd"
+    deferred = args.grad_sum == "deferred" and not args.batched
     overlap = args.overlap_chunks if (world > 1 and fused and not args.batched) else 0
 
     def grad_mode(i):
@@ -428,10 +435,34 @@ def main():
             stats["views"] += len(ks)
         flat.all_reduce()
 
+    use_deferred = [True]            # (switched off for the `grad_sum_in_kernels` comparison leg)
+
     def run_views(prm, flt, views, loss_of, chunks, collect=False):
         """One rank's share of a step through the drop-in API: the views' gradients are summed in the backward kernels; with
         chunks > 0 the LAST view's per-Gaussian backward runs in ranges and each range's all-reduce starts behind it."""
         works = []
+        if deferred and use_deferred[0]:
+            # per view: forward + blending backward; once per step: the per-Gaussian backward of all views (in `chunks` ranges
+            # with each range's all-reduce issued behind it when N > 1)
+            prev = dgr.set_grad_mode("deferred")
+            try:
+                for k in views:
+                    color, radii, _ = dp.render_view(dgr, prm, cams[k], bg, spec.D)
+                    loss_of(color, k).backward() if loss_of is not None else color.backward(go)
+                    if collect:
+                        stats["Pv"] += int((radii > 0).sum())
+                        stats["views"] += 1
+            finally:
+                dgr.set_grad_mode(prev)
+            if chunks > 0:
+                dgr.flush_deferred(False, chunks, lambda g0, g1: works.append(flt.all_reduce_rows(g0, g1)))
+                for w in works:
+                    if w is not None:
+                        w.wait()
+            else:
+                dgr.flush_deferred(False)
+                flt.all_reduce()
+            return
         for i, k in enumerate(views):
             prev = grad_mode(i)
             hook = None
@@ -547,6 +578,31 @@ def main():
         views = my_views(step)
         total = None
         works = []
+        if deferred:
+            prev = dgr.set_grad_mode("deferred")
+            try:
+                for i, k in enumerate(views):
+                    tgt, cm, slot = take(k)
+                    nxt = views[i + 1] if i + 1 < len(views) else my_views(step + 1)[0]
+                    prefetch(nxt)                              # next view's inputs travel while this one renders
+                    cam = synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cm[:16].view(4, 4), cm[16:32].view(4, 4), cm[32:35])
+                    color, radii, _ = dp.render_view(dgr, params, cam, bg, spec.D)
+                    loss = losses.l1_loss(color, tgt)
+                    loss.backward()
+                    release(slot)
+                    total = loss.detach() if total is None else total + loss.detach()
+            finally:
+                dgr.set_grad_mode(prev)
+            if overlap > 0:
+                dgr.flush_deferred(False, overlap, lambda g0, g1: works.append(flat.all_reduce_rows(g0, g1)))
+                for w in works:
+                    if w is not None:
+                        w.wait()
+            else:
+                dgr.flush_deferred(False)
+                flat.all_reduce()
+            _ = float(total.item())
+            return
         for i, k in enumerate(views):
             prev = grad_mode(i)
             last = overlap > 0 and i == len(views) - 1
@@ -681,6 +737,17 @@ def main():
         ms_s = timed(step_device_streams, args.steps, args.warmup)
         streams_extra = {"api": "GaussianRasterizer from two CUDA streams (gsr_b200.dp.backward_views(n_streams=2))",
                          "value": views_total / (ms_s * 1e-3), "unit": UNIT, "ms_per_view": ms_s / args.steps / vps}
+
+    # ---- the same step with every view's backward adding into the buffer itself (round 1's headline form), next to the deferred one
+    kernels_extra = None
+    if extras and deferred:
+        use_deferred[0] = False
+        for i in range(args.warmup):
+            step_device(i)
+        ms_k = timed(step_device, args.steps, args.warmup)
+        use_deferred[0] = True
+        kernels_extra = {"api": "GaussianRasterizer, set_grad_mode overwrite / accumulate: the per-Gaussian backward runs per view",
+                         "value": views_total / (ms_k * 1e-3), "unit": UNIT, "ms_per_view": ms_k / args.steps / vps}
 
     # ---- what an UNCHANGED train.py sees (gaussian_renderer/__init__.py:53-80): raw parameters, torch activations,
     # torch.cat of the two SH parameters, plain autograd (no set_grad_mode, no split storage): every view pays the
@@ -847,13 +914,21 @@ def main():
             pass
         peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
         Pv = stats["Pv"] / max(1, stats["views"])
-        sb = stage_bytes(P, Pv, R, N, tiles, M, accumulate_frac=(vps - 1) / vps if fused else 0.0)
+        sb = stage_bytes(P, Pv, R, N, tiles, M, accumulate_frac=(vps - 1) / vps if (fused and not deferred) else 0.0)
+        if deferred:
+            # per view: record, accumulator row, radii, clamp byte in, dL/dmean2D out (113 B per Gaussian); per step: parameters
+            # in and gradients out once (44 + 12 M and 4 (11 + 3 M) B per Gaussian)
+            sb["preprocess_backward"] = 113 * P + (44 + 12 * M + 4 * (11 + 3 * M)) * P / vps
         stages = {}
         dom, dom_ms = None, -1.0
         for name, ms, calls in stage_rows:
             if calls == 0 or name not in sb:
                 continue
-            avg = ms / calls / (vps if args.batched else 1)       # per view
+            # per view (a batched call covers vps views; so does the deferred per-Gaussian backward, once per step)
+            if deferred and name == "preprocess_backward":
+                avg = ms / args.steps / vps                   # (calls = steps x ranges when the flush runs in ranges)
+            else:
+                avg = ms / calls / (vps if args.batched else 1)
             gbs = sb[name] / (avg * 1e-3) / 1e9
             stages[name] = {"ms": round(avg, 4), "algo_bytes": int(sb[name]), "GBps": round(gbs, 1), "frac_hbm": round(gbs / peak, 4)}
             if avg > dom_ms:
@@ -909,13 +984,15 @@ def main():
                            "views_per_gpu_per_step": vps, "R_per_view": R, "visible_per_view": int(Pv),
                            "parallelism": "view-sharded dp%d, NCCL all-reduce of %d MB per step%s" % (
                                world, flat_nbytes >> 20, (", issued in %d ranges behind the last view's per-Gaussian backward" % overlap) if overlap else ""),
-                           "grad_sum": "in the backward kernels (set_grad_mode)" if fused else "autograd .grad +=",
+                           "grad_sum": ("deferred: blending backward per view, one per-Gaussian backward over the step's views "
+                                        "(set_grad_mode('deferred') + flush_deferred)" if deferred else
+                                        "in the backward kernels (set_grad_mode)" if fused else "autograd .grad +="),
                            "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else "GaussianRasterizer: one call per view",
                            "c5": "config C5 (6M Gaussians, %d views per step) measured by the same step at this N: see the `c5` object" % (vps * world),
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat_nbytes + 48 * P + 20 * R) / 1e9)},
                 "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "allreduce": allreduce, "c5": c5,
-                "reference_cuda": ref_extra, "plain_api": plain_extra, "dist2": dist2_extra,
+                "reference_cuda": ref_extra, "plain_api": plain_extra, "grad_sum_in_kernels": kernels_extra, "dist2": dist2_extra,
                 "batched": batched_extra, "two_streams": streams_extra, "forward_only": forward_extra, "train_step": train_extra,
                 "gpu_launches": launches,
                 "clocks": clocks}
