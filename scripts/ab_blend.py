@@ -64,9 +64,6 @@ def main():
 
     variants = {
         "default": dict(),
-        "lb2": dict(radix_lb=2),
-        "lb8": dict(radix_lb=8),
-        "lb16": dict(radix_lb=16),
         "default_again": dict(),
     }
     ref_g = None

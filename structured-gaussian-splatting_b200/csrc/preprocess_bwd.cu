@@ -84,7 +84,7 @@ __device__ __forceinline__ void store_sh_grads(float* __restrict__ dst, const fl
 }
 
 template <bool WITH_SH, bool MULTI>
-__global__ void __launch_bounds__(256, WITH_SH ? 1 : (MULTI ? 3 : 4)) preprocess_bwd_kernel(PreBwdArgs a, CameraArgs ca,
+__global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(PreBwdArgs a, CameraArgs ca,
                                                                                             const __grid_constant__ ViewTab vt)
 {
     const int NV = MULTI ? a.V : 1;            // compile-time 1 for the single-view call: the view loops fold away
@@ -536,7 +536,7 @@ __device__ __forceinline__ void flat_zero_row(const RowFlat& r)
 }
 
 template <bool SPLIT>
-__global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_kernel(int P, int D, const float* __restrict__ means,
+__global__ void __launch_bounds__(32 * SHB_WARPS, 7) sh_bwd_m16_kernel(int P, int D, const float* __restrict__ means,
                                                                     const int* __restrict__ radii, const float* __restrict__ shs,
                                                                     const uint8_t* __restrict__ clamped, const float* __restrict__ accum,
                                                                     const float* __restrict__ campos, float* __restrict__ dL_dsh,
@@ -673,7 +673,7 @@ __device__ __forceinline__ void sh_chunk_views(const Row& row, int V, int D, int
 }
 
 template <bool SPLIT>
-__global__ void __launch_bounds__(32 * SHB_WARPS) sh_bwd_m16_views_kernel(int P, int V, int D, const float* __restrict__ means,
+__global__ void __launch_bounds__(32 * SHB_WARPS, 7) sh_bwd_m16_views_kernel(int P, int V, int D, const float* __restrict__ means,
                                                                           const float* __restrict__ shs, float* __restrict__ dL_dsh,
                                                                           float* __restrict__ dL_dmean3D, unsigned acc,
                                                                           const float* __restrict__ shs_rest,
