@@ -64,6 +64,8 @@ def main():
 
     variants = {
         "default": dict(),
+        "fwd_u4_b5": dict(fwd_minb=5),
+        "fwd_u2_b5": dict(fwd_minb=52),
         "default_again": dict(),
     }
     ref_g = None

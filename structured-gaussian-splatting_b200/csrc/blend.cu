@@ -766,7 +766,13 @@ int launch_blend_forward(long long R, int W, int H, int V, const float* bg, cons
         if (!g_arms.blend_forward_bulk) return GSR_EINVAL;
         return g_arms.blend_forward_bulk(R, W, H, V, bg, g, b, im, out_color, s);
     }
-    if (o.fwd_minb == 3)
+    if (o.fwd_minb == 5)
+        GSR_LAUNCH((blend_fwd_v3_kernel<4, 5>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+                   out_color, b.scratch, pw, gyv, lpt);
+    else if (o.fwd_minb == 52)
+        GSR_LAUNCH((blend_fwd_v3_kernel<2, 5>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
+                   out_color, b.scratch, pw, gyv, lpt);
+    else if (o.fwd_minb == 3)
         GSR_LAUNCH((blend_fwd_v3_kernel<4, 3>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
                    out_color, b.scratch, pw, gyv, lpt);
     else

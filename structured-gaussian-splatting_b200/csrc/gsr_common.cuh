@@ -198,7 +198,7 @@ int launch_dist2(int P, const float* points, float* out, GsrAlloc scratch, cudaS
 struct Options {
     int bwd_variant = 6;        // blending backward kernel: 6 = blend_bwd_v6_kernel, 5 = blend_bwd_v5_kernel (round 1)
     int lpt = 1;                // blending kernels take their tiles longest list first
-    int fwd_minb = 4;           // __launch_bounds__ min blocks of the forward blending kernel (3 or 4)
+    int fwd_minb = 5;           // __launch_bounds__ min blocks of the forward blending kernel (3, 4 or 5; 52 = trips of 2 at 5)
     int bwd_minb = 3;           // same for the backward (v5: 3 or 4; v6: 3)
     int side_stream = 1;        // tile-count kernels on a side stream next to the depth sort
     int bwd_side = 1;           // SH backward on a side stream next to the cov/projection backward
