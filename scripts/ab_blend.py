@@ -64,8 +64,9 @@ def main():
 
     variants = {
         "default": dict(),
-        "fwd_u4_b5": dict(fwd_minb=5),
-        "fwd_u2_b5": dict(fwd_minb=52),
+        "fwd3_bwd6": dict(fwd_variant=3, bwd_variant=6),
+        "fwd4_bwd6": dict(fwd_variant=4, bwd_variant=6),
+        "fwd3_bwd7": dict(fwd_variant=3, bwd_variant=7),
         "default_again": dict(),
     }
     ref_g = None

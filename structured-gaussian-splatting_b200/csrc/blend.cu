@@ -106,6 +106,129 @@ blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     }
 }
 
+// ------------------------------------------------------------------------------------------ forward, packed pairs
+// Same staging, classification and exported planes as blend_fwd_v3_kernel.  A warp no longer walks the set bits of its
+// classification words entry by entry (seven index instructions per entry): it queues the batch's surviving entries (one
+// byte each), then 32 at a time one lane per entry copies them into a warp-private array of pair records (PairRec; about
+// two instructions per entry all told), and the blending loop is a counted loop over pairs whose pixel-independent
+// arithmetic runs as FADD2 / FMUL2 / FFMA2 (blend_common.cuh).  The sequential part (blend_step) is the scalar code of v3.
+struct __align__(16) FwdPairs { PairRec p[16]; };
+
+template <int MINB>
+__global__ void __launch_bounds__(BL_THREADS, MINB)
+blend_fwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                    int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                    float* __restrict__ out, uint32_t* __restrict__ planes, uint32_t plane_words, int gyv,
+                    const uint32_t* __restrict__ tile_order)
+{
+    __shared__ BlendStage stage[2];
+    __shared__ uint32_t bits[2][8][8];     // [buffer][consumer warp][chunk of 32 entries]
+    __shared__ FwdPairs pairs[8];
+    __shared__ uint8_t queue[8][BL_THREADS];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;                  // see blend_fwd_v3_kernel
+    const uint32_t tile = tile_order ? tile_order[lin] : lin;
+    const uint32_t trow = tile / gridDim.x, bx = tile - trow * gridDim.x;
+    const uint32_t view = trow / (uint32_t)gyv, by = trow - view * (uint32_t)gyv;
+    const float X0 = (float)(bx * GSR_TILE), Y0 = (float)(by * GSR_TILE);
+    const uint32_t px = bx * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t py = by * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    bool done = !inside;
+
+    const uint2 range = ranges[tile];
+    const int total = (int)(range.y - range.x);
+    uint32_t* const plane = planes + (size_t)lane * plane_words + (range.x >> 5) + 16u * tile + wid;
+    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
+    const uint32_t below = (1u << lane) - 1u;
+    float* const pw = reinterpret_cast<float*>(pairs[wid].p);                 // this warp's pair records, as words
+    const PairRec* const pr = pairs[wid].p;
+    uint8_t* const qu = queue[wid];
+
+    float T = 1.0f;
+    uint32_t last_contributor = 0;
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+
+    uint32_t id_next = 0;
+    {
+        const bool v0 = (int)threadIdx.x < total;
+        const uint32_t id0 = v0 ? vals[range.x + threadIdx.x] : 0;
+        stage_gather(stage[0], rec, id0, v0);
+        const int p1 = BL_THREADS + threadIdx.x;
+        if (p1 < total) id_next = vals[range.x + p1];
+    }
+    for (int i = 0; i < rounds; i++) {
+        const int buf = i & 1;
+        cp_async_wait<0>();       // my own entry of batch i has landed: classify it
+        {
+            uint32_t m = 0;
+            if (i * BL_THREADS + (int)threadIdx.x < total) m = subtile_mask(stage[buf].q0[threadIdx.x], stage[buf].q1[threadIdx.x], X0, Y0);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
+                if (lane == k) { bits[buf][k][wid] = bk; plane[i * 8] = bk; }
+            }
+        }
+        const int num_done = __syncthreads_count(done);
+        if (num_done == BL_THREADS) break;
+        {
+            const int p1 = (i + 1) * BL_THREADS + threadIdx.x;
+            stage_gather(stage[buf ^ 1], rec, id_next, p1 < total);
+            const int p2 = p1 + BL_THREADS;
+            if (p2 < total) id_next = vals[range.x + p2];
+        }
+        if (__all_sync(0xffffffffu, done)) continue;
+        const BlendStage& st = stage[buf];
+        const uint32_t pos_base = (uint32_t)(i * BL_THREADS) + 1u;
+        // the warp's surviving entries of this batch, in list order: one byte per entry
+        int cnt = 0;
+#pragma unroll
+        for (int cch = 0; cch < 8; cch++) {
+            const uint32_t m = bits[buf][wid][cch];
+            if ((m >> lane) & 1u) qu[cnt + __popc(m & below)] = (uint8_t)(cch * 32 + lane);
+            cnt += __popc(m);
+        }
+        __syncwarp();
+#pragma unroll 1
+        for (int g = 0; g < cnt; g += 32) {
+            const int n = min(32, cnt - g);
+            if (lane < n) {                             // entry g + lane becomes slot lane & 1 of pair lane >> 1
+                const int j = qu[g + lane];
+                const float4 a = st.q0[j], c = st.q1[j];
+                const float b = st.b[j];
+                float* w = pw + (lane >> 1) * (int)(sizeof(PairRec) / 4) + (lane & 1);
+                w[0] = a.x; w[2] = a.y; w[4] = a.z; w[6] = a.w; w[8] = c.x; w[10] = c.y; w[12] = c.z; w[14] = c.w;
+                w[16] = b; w[18] = __uint_as_float(pos_base + (uint32_t)j);
+            }
+            __syncwarp();
+#pragma unroll 1
+            for (int q = 0; 2 * q < n; q++) {
+                const PairRec r = pr[q];
+                float2 dx, dy, power, araw;
+                pair_head(r, pxf, pyf, dx, dy, power, araw);
+                const float al0 = fminf(0.99f, araw.x), al1 = fminf(0.99f, araw.y);
+                const bool ok0 = !(power.x > 0.0f) && !(al0 < 1.0f / 255.0f);
+                const bool ok1 = !(power.y > 0.0f) && !(al1 < 1.0f / 255.0f) && 2 * q + 1 < n;    // the odd tail: a stale slot
+                blend_step(al0, ok0, r.rg.x, r.rg.z, r.bp.x, __float_as_uint(r.bp.z), done, T, C0, C1, C2, last_contributor);
+                blend_step(al1, ok1, r.rg.y, r.rg.w, r.bp.y, __float_as_uint(r.bp.w), done, T, C0, C1, C2, last_contributor);
+            }
+            if (__all_sync(0xffffffffu, done)) break;    // (also orders this group's reads before the next group's writes)
+        }
+    }
+    cp_async_wait<0>();
+    if (inside) {
+        const size_t HW = (size_t)H * W;
+        const size_t pix = (size_t)W * py + px;
+        final_T[view * HW + pix] = T;
+        n_contrib[view * HW + pix] = last_contributor;
+        float* o = out + 3 * view * HW + pix;
+        o[0] = C0 + T * bg[0];
+        o[HW] = C1 + T * bg[1];
+        o[2 * HW] = C2 + T * bg[2];
+    }
+}
+
 // classification words kept for the backward (in the binning blob's sort scratch, dead once the tile split is done):
 // 8 planes (one per sub-tile of a tile) of (R >> 5) + 16 tiles + 16 words
 size_t blend_plane_words(long long R, int W, int H)
@@ -462,8 +585,8 @@ __device__ __forceinline__ void split_tf32(const float (&x)[4], uint32_t (&hi)[4
 
 // one reduced row (entry j of ring buffer kq): moments m0, m1 = columns 2t, 2t+1 of D1 (S0 Sx | Sy Sxx | Sxy Syy | - -,
 // about the sub-tile origin), col = colour sum t; shifted to the Gaussian's centre and committed
-template <int SLOTS>
-__device__ __forceinline__ void v6_commit(const WarpV6<SLOTS>& S, int kq, int j, bool valid, int lane, float m0, float m1, float col,
+template <class Fetch>
+__device__ __forceinline__ void v6_commit(const Fetch& fetch, int j, bool valid, int lane, float m0, float m1, float col,
                                           float X0s, float Y0s, float* __restrict__ accum)
 {
     const int t = lane & 3, q0l = lane & ~3;
@@ -471,8 +594,9 @@ __device__ __forceinline__ void v6_commit(const WarpV6<SLOTS>& S, int kq, int j,
     const float Sx = __shfl_sync(0xffffffffu, m1, q0l);
     const float Sy = __shfl_sync(0xffffffffu, m0, q0l + 1);
     if (valid && t < 3) {
-        const float2 xy = *reinterpret_cast<const float2*>(&S.q0[kq][j]);
-        const uint32_t id = __float_as_uint(S.e[kq][j].x);
+        float2 xy;
+        uint32_t id;
+        fetch(j, xy, id);                                    // the entry's centre and Gaussian id
         const float u = xy.x - X0s, v = xy.y - Y0s;         // dx = u - lx, dy = v - ly
         const float a1 = fmaf(u, S0, -Sx);                   // sum w dx
         const float a2 = fmaf(v, S0, -Sy);                   // sum w dy
@@ -494,22 +618,22 @@ __device__ __forceinline__ void v6_commit(const WarpV6<SLOTS>& S, int kq, int j,
 // Reduces rows [0, cnt) of the warp's A operand(s) (entries jbase .. jbase + cnt - 1 of ring buffer kq) over the 32 lanes
 // and commits them.  Fragments of m16n8k8 (g = lane >> 2, t = lane & 3): A rows g / g+8 at k = t / t+4, B column g at
 // k = t / t+4, D rows g / g+8, columns 2t, 2t+1.  Columns of D2: r_hi r_lo | g_hi g_lo | b_hi b_lo | - -.
-template <int SLOTS>
-__device__ __forceinline__ void v6_flush(const WarpV6<SLOTS>& S, const float2 (*b1)[32], int kq, int jbase, int cnt, int lane,
-                                         float X0s, float Y0s, float* __restrict__ accum)
+template <int SLOTS, class Fetch>
+__device__ __forceinline__ void v6_flush(const float* __restrict__ Sa, const float2 (*Sb2)[32], const float2 (*b1)[32], const Fetch& fetch,
+                                         int jbase, int cnt, int lane, float X0s, float Y0s, float* __restrict__ accum)
 {
     constexpr int GS = V6Layout<SLOTS>::GS, KS = V6Layout<SLOTS>::KS;
     __syncwarp();
     const int g = lane >> 2, t = lane & 3;
     float d1[4] = {0.f, 0.f, 0.f, 0.f}, d2[4] = {0.f, 0.f, 0.f, 0.f};
     if (SLOTS == 16) {
-        const float* ab = S.a + g * GS + t * 8;
+        const float* ab = Sa + g * GS + t * 8;
 #pragma unroll
         for (int s = 0; s < 4; s++) {
             const float4 Q1 = *reinterpret_cast<const float4*>(ab + s * KS);          // k = t:   (w, at) of the two rows
             const float4 Q2 = *reinterpret_cast<const float4*>(ab + s * KS + 4);      // k = t+4
             const float2 m = b1[s][lane];
-            const float2 q = S.b2[s][lane];
+            const float2 q = Sb2[s][lane];
             float xw[4], xa[4];
             if ((s & 1) == 0) {
                 xw[0] = Q1.x; xw[1] = Q1.z; xw[2] = Q2.x; xw[3] = Q2.z;
@@ -528,15 +652,15 @@ __device__ __forceinline__ void v6_flush(const WarpV6<SLOTS>& S, const float2 (*
         }
 #pragma unroll
         for (int hi = 0; hi < 2; hi++)
-            v6_commit<SLOTS>(S, kq, jbase + g + 8 * hi, g + 8 * hi < cnt, lane, d1[2 * hi], d1[2 * hi + 1], d2[2 * hi] + d2[2 * hi + 1],
-                             X0s, Y0s, accum);
+            v6_commit(fetch, jbase + g + 8 * hi, g + 8 * hi < cnt, lane, d1[2 * hi], d1[2 * hi + 1], d2[2 * hi] + d2[2 * hi + 1],
+                      X0s, Y0s, accum);
     } else {
-        const float* ab = S.a + g * GS + t * 4;
+        const float* ab = Sa + g * GS + t * 4;
 #pragma unroll
         for (int s = 0; s < 4; s++) {
             const float4 av = *reinterpret_cast<const float4*>(ab + s * KS);           // w, at at k = t | w, at at k = t+4
             const float2 m = b1[s][lane];
-            const float2 q = S.b2[s][lane];
+            const float2 q = Sb2[s][lane];
             const float x[4] = {av.x, av.y, av.z, av.w};      // rows g (w) / g+8 (at) at k = t, then at k = t+4
             uint32_t hi[4], lo[4];
             split_tf32(x, hi, lo);
@@ -545,7 +669,7 @@ __device__ __forceinline__ void v6_flush(const WarpV6<SLOTS>& S, const float2 (*
             mma_tf32(d2, hi, __float_as_uint(q.x), __float_as_uint(q.y));
             mma_tf32(d2, lo, __float_as_uint(q.x), __float_as_uint(q.y));
         }
-        v6_commit<SLOTS>(S, kq, jbase + g, g < cnt, lane, d1[0], d1[1], d2[2] + d2[3], X0s, Y0s, accum);
+        v6_commit(fetch, jbase + g, g < cnt, lane, d1[0], d1[1], d2[2] + d2[3], X0s, Y0s, accum);
     }
     __syncwarp();
 }
@@ -736,9 +860,231 @@ blend_bwd_v6_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                     }
                 }
             }
-            v6_flush<SLOTS>(S, SM.b1, kq, jb, cnt, lane, X0s, Y0s, accum);
+            v6_flush<SLOTS>(S.a, S.b2, SM.b1, [&](int j, float2& xy, uint32_t& id) {
+                xy = *reinterpret_cast<const float2*>(&rq0[j]);
+                id = __float_as_uint(re[j].x);
+            }, jb, cnt, lane, X0s, Y0s, accum);
         }
         __syncwarp();                  // everyone has left ring buffer kq before the gather of group k + 2 overwrites it
+    }
+    cp_async_wait<0>();
+}
+
+// ------------------------------------------------------------------------------------------ backward, packed pairs
+// blend_bwd_v6_kernel<16, 2> with the pixel-independent arithmetic of the two entries of a trip on register pairs
+// (FADD2 / FMUL2 / FFMA2, blend_common.cuh): the gathered group is rewritten in place as pair records, the per-entry
+// state chain (T, Sd) stays scalar.  Same operations in the same order as v6_entry: results are bit-identical to v6.
+struct __align__(16) WarpV7 {
+    float4 ring[2][96];                 // as gathered: [0, 32) q0 of entry = lane, [32, 64) q1, [64, 96) (id, pos, b, -)
+                                        // as blended:  PairRec[16] in [0, 80), the 32 Gaussian ids in [80, 88)
+    float  a[4 * V6Layout<16>::KS];
+    float2 b2[4][32];
+    uint32_t queue[V6_QCAP];
+};
+struct __align__(16) BwdSmemV7 {
+    WarpV7 w[8];
+    float2 b1[4][32];
+};
+
+__device__ __forceinline__ void v7_pair(const PairRec r, float pxf, float pyf, int last_contributor, float dp0, float dp1, float dp2,
+                                        float& T, float& Sd, float& w0, float& at0, float& w1, float& at1)
+{
+    float2 dx, dy, power, araw;
+    pair_head(r, pxf, pyf, dx, dy, power, araw);
+    const float al0 = fminf(0.99f, araw.x), al1 = fminf(0.99f, araw.y);
+    const bool live0 = __float_as_int(r.bp.z) < last_contributor && !(power.x > 0.0f) && !(al0 < 1.0f / 255.0f);
+    const bool live1 = __float_as_int(r.bp.w) < last_contributor && !(power.y > 0.0f) && !(al1 < 1.0f / 255.0f);
+    const float2 araw_s = make_float2(live0 ? araw.x : 0.f, live1 ? araw.y : 0.f);
+    const float2 alpha_s = make_float2(live0 ? al0 : 0.f, live1 ? al1 : 0.f);
+    const float2 om = __fadd2_rn(bc2(1.f), neg2(alpha_s));
+    float r0, r1;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(om.x));              // rcp(1) == 1 exactly
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(om.y));
+    const float2 ec = __ffma2_rn(make_float2(r.bp.x, r.bp.y), bc2(dp2),
+                                 __ffma2_rn(make_float2(r.rg.z, r.rg.w), bc2(dp1), __fmul2_rn(make_float2(r.rg.x, r.rg.y), bc2(dp0))));
+    T *= r0;
+    at0 = alpha_s.x * T;
+    const float dL0 = fmaf(T, ec.x, -(Sd * r0));
+    Sd = fmaf(ec.x, at0, Sd);
+    w0 = araw_s.x * dL0;
+    T *= r1;
+    at1 = alpha_s.y * T;
+    const float dL1 = fmaf(T, ec.y, -(Sd * r1));
+    Sd = fmaf(ec.y, at1, Sd);
+    w1 = araw_s.y * dL1;
+}
+
+template <int MINB>
+__global__ void __launch_bounds__(BL_THREADS, MINB)
+blend_bwd_v7_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
+                    const uint32_t* __restrict__ planes, uint32_t plane_words, int W, int H, const float* __restrict__ bg,
+                    const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
+                    float* __restrict__ accum, int gyv, const uint32_t* __restrict__ tile_order)
+{
+    constexpr int SLOTS = 16, GS = V6Layout<16>::GS, KS = V6Layout<16>::KS;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BwdSmemV7& SM = *reinterpret_cast<BwdSmemV7*>(smem_raw);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    WarpV7& S = SM.w[wid];
+    const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;                                  // see blend_fwd_v3_kernel
+    const uint32_t tile = tile_order ? tile_order[lin] : lin;
+    const uint32_t trow = tile / gridDim.x, bx = tile - trow * gridDim.x;
+    const uint32_t view = trow / (uint32_t)gyv, by = trow - view * (uint32_t)gyv;
+    const float X0s = (float)(bx * GSR_TILE + (wid & 1) * 8), Y0s = (float)(by * GSR_TILE + (wid >> 1) * 4);
+    const uint32_t px = bx * GSR_TILE + (wid & 1) * 8 + (lane & 7);
+    const uint32_t py = by * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t HW = (size_t)H * W;
+    const size_t pix = view * HW + (size_t)W * py + px;
+    dL_dpix += 2 * view * HW;                   // [V][3][H][W]: channel c of this pixel is dL_dpix[c * HW + pix]
+    const uint2 range = ranges[tile];
+
+    const float T_final = inside ? final_T[pix] : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+    float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
+    if (inside) { dp0 = dL_dpix[pix]; dp1 = dL_dpix[HW + pix]; dp2 = dL_dpix[2 * HW + pix]; }
+    float Sd = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);     // see bwd_live_sd
+
+    // this pixel lane as a K index of the reduction: k-step sK, index tK + 4 bK
+    const int sK = lane >> 3, tK = (lane >> 1) & 3, bK = lane & 1;
+    // B1: the moment matrix (1, lx, ly, lx^2, lx ly, ly^2, 0, 0) in B-fragment order; reading lane l = (n = l >> 2, t = l & 3)
+    // of k-step s takes column n at the pixels (lx, ly) = (2t, s) and (2t + 1, s)
+    if (threadIdx.x < 128) {
+        const int s = threadIdx.x >> 5, l = threadIdx.x & 31, n = l >> 2;
+        const float ly = (float)s, lx0 = (float)(2 * (l & 3)), lx1 = lx0 + 1.f;
+        float2 m;
+        m.x = n == 0 ? 1.f : n == 1 ? lx0 : n == 2 ? ly : n == 3 ? lx0 * lx0 : n == 4 ? lx0 * ly : n == 5 ? ly * ly : 0.f;
+        m.y = n == 0 ? 1.f : n == 1 ? lx1 : n == 2 ? ly : n == 3 ? lx1 * lx1 : n == 4 ? lx1 * ly : n == 5 ? ly * ly : 0.f;
+        SM.b1[s][l] = m;
+    }
+    {
+        // B2: columns (r_hi, r_lo, g_hi, g_lo, b_hi, b_lo, 0, 0) of this warp's dL/dpixel; column n of this pixel lives at
+        // reading lane 4 n + tK, component bK
+        const float d[3] = {dp0, dp1, dp2};
+        float* col = reinterpret_cast<float*>(&S.b2[sK][tK]) + bK;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const float hi = __uint_as_float(__float_as_uint(d[c]) & 0xffffe000u);
+            col[(2 * c) * 8] = hi;
+            col[(2 * c + 1) * 8] = d[c] - hi;
+        }
+        col[6 * 8] = 0.f;
+        col[7 * 8] = 0.f;
+    }
+    // this lane's (w, at) slot of entry c of a flush group (see the layouts above):
+    //   (c < 8 ? a_lo : a_hi) + (c & 7) * GS
+    float* const a_lo = S.a + sK * KS + tK * 8 + 4 * bK + 2 * (sK & 1);
+    float* const a_hi = S.a + sK * KS + tK * 8 + 4 * bK + 2 - 2 * (sK & 1);
+
+    int warp_last = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
+    warp_last = min(warp_last, (int)(range.y - range.x));
+    __syncthreads();                       // b1 is visible; the only block barrier
+    const int nch = (warp_last + 31) >> 5; // chunks of 32 list entries this warp has work in
+    if (nch == 0) return;
+    const uint32_t* plane = planes + (size_t)wid * plane_words + (range.x >> 5) + 16u * tile;
+    const uint32_t* tvals = vals + range.x;
+
+    // ---- work queue: step st = 0 .. nch-1 handles chunk nch-1-st (back to front); the words of 32 consecutive steps sit in
+    // one register per lane (wA: block blkA, wB: the block after it)
+    auto load_words = [&](int blk) -> uint32_t {
+        const int s = blk * 32 + lane;
+        return s < nch ? plane[nch - 1 - s] : 0u;
+    };
+    uint32_t wA = load_words(0), wB = load_words(1);
+    int blkA = 0, st_next = 0;
+    uint32_t qtail = 0;                                    // entries queued so far (warp-uniform)
+    const uint32_t above = ~(0xffffffffu >> lane);         // the bits lane `lane` ranks behind: it owns bit 31 - lane
+    {
+        // the top chunk may reach beyond the warp's last contributor
+        const int rem = warp_last - (nch - 1) * 32;        // 1 .. 32
+        if (lane == 0 && rem < 32) wA &= (1u << rem) - 1u;
+    }
+    auto fill = [&](uint32_t want) {                       // queue entries until `want` are there or the list is exhausted
+        while (qtail < want && st_next < nch) {
+            const uint32_t m = __shfl_sync(0xffffffffu, wA, st_next & 31);
+            const uint32_t base = (uint32_t)(nch - 1 - st_next) * 32u;
+            if ((m >> (31 - lane)) & 1u) S.queue[(qtail + __popc(m & above)) & (V6_QCAP - 1)] = base + 31u - (uint32_t)lane;
+            qtail += __popc(m);
+            st_next++;
+            if ((st_next & 31) == 0) { wA = wB; blkA++; wB = load_words(blkA + 1); }
+        }
+        __syncwarp();
+    };
+    // group k = queue entries [32k, 32k + 32); its size is final once `fill(32 (k + 1))` has returned
+    auto group_size = [&](uint32_t k) -> int { return (int)min(32u, qtail - min(qtail, 32u * k)); };
+    auto load_pos = [&](uint32_t k, uint32_t& pos, uint32_t& id) {      // lane's entry of group k: list position and Gaussian id
+        const bool v = lane < group_size(k);
+        pos = v ? S.queue[(32u * k + (uint32_t)lane) & (V6_QCAP - 1)] : 0u;
+        id = v ? tvals[pos] : 0u;
+    };
+    auto issue = [&](uint32_t k, uint32_t pos, uint32_t id) {           // gather group k into ring buffer k & 1 (lane-indexed form)
+        float4* R = S.ring[k & 1];
+        if (lane < group_size(k)) {
+            const SplatRec* r = rec + id;
+            cp_async16(&R[lane], &r->q0);
+            cp_async16(&R[32 + lane], &r->q1);
+            cp_async4(&R[64 + lane].z, &r->q2);
+            *reinterpret_cast<uint2*>(&R[64 + lane]) = make_uint2(id, pos);
+        }
+        cp_async_commit();
+    };
+
+    uint32_t posc, idc;
+    fill(64);
+    load_pos(0, posc, idc);
+    issue(0, posc, idc);
+    load_pos(1, posc, idc);
+#pragma unroll 1
+    for (uint32_t k = 0;; k++) {
+        const int n = group_size(k);
+        if (n == 0) break;                                  // (one empty cp.async group may still be pending: harmless)
+        fill(32u * (k + 3));
+        uint32_t posn, idn;
+        load_pos(k + 2, posn, idn);                         // ids two groups ahead
+        issue(k + 1, posc, idc);                            // records one group ahead
+        posc = posn; idc = idn;
+        cp_async_wait<1>();                                 // my records of group k have landed
+        __syncwarp();
+        float4* const R = S.ring[k & 1];
+        {
+            // lane-indexed -> pair records, in place: every lane takes its entry into registers, then writes it back
+            // interleaved with its neighbour's.  Slots behind the group's last entry get a record that blends nothing
+            // and holds no NaN (an odd group reads one of them).
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a, e = make_float4(0.f, __int_as_float(0x7fffffff), 0.f, 0.f);
+            if (lane < n) { a = R[lane]; c = R[32 + lane]; e = R[64 + lane]; }
+            __syncwarp();
+            float* w = reinterpret_cast<float*>(R) + (lane >> 1) * (int)(sizeof(PairRec) / 4) + (lane & 1);
+            w[0] = a.x; w[2] = a.y; w[4] = a.z; w[6] = a.w; w[8] = c.x; w[10] = c.y; w[12] = c.z; w[14] = c.w;
+            w[16] = e.z; w[18] = e.y;
+            reinterpret_cast<float*>(R + 80)[lane] = e.x;
+            __syncwarp();
+        }
+        const PairRec* const P = reinterpret_cast<const PairRec*>(R);
+        const float* const Pw = reinterpret_cast<const float*>(R);
+#pragma unroll 1
+        for (int jb = 0; jb < n; jb += SLOTS) {
+            const int cnt = min(SLOTS, n - jb);             // entries of this flush group (warp-uniform)
+#pragma unroll
+            for (int c = 0; c < SLOTS; c += 2) {
+                if (c < cnt) {
+                    float w0, at0, w1, at1;
+                    v7_pair(P[(jb + c) >> 1], pxf, pyf, last_contributor, dp0, dp1, dp2, T, Sd, w0, at0, w1, at1);
+                    float* const sp = ((c >> 3) ? a_hi : a_lo) + (c & 7) * GS;
+                    *reinterpret_cast<float2*>(sp) = make_float2(w0, at0);
+                    *reinterpret_cast<float2*>(sp + GS) = make_float2(w1, at1);
+                }
+            }
+            v6_flush<SLOTS>(S.a, S.b2, SM.b1, [&](int j, float2& xy, uint32_t& id) {
+                const float* q = Pw + (j >> 1) * (int)(sizeof(PairRec) / 4) + (j & 1);
+                xy = make_float2(q[0], q[2]);
+                id = __float_as_uint(Pw[320 + j]);
+            }, jb, cnt, lane, X0s, Y0s, accum);
+        }
+        __syncwarp();                  // everyone has left ring buffer k & 1 before the gather of group k + 2 overwrites it
     }
     cp_async_wait<0>();
 }
@@ -765,6 +1111,16 @@ int launch_blend_forward(long long R, int W, int H, int V, const float* bg, cons
     if (o.blend_arm == 2) {
         if (!g_arms.blend_forward_bulk) return GSR_EINVAL;
         return g_arms.blend_forward_bulk(R, W, H, V, bg, g, b, im, out_color, s);
+    }
+    if (o.fwd_variant == 4) {
+#define GSR_F4(MINB)                                                                                                        \
+    GSR_LAUNCH((blend_fwd_v4_kernel<MINB>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, \
+               out_color, b.scratch, pw, gyv, lpt)
+        if (o.fwd_minb == 6) GSR_F4(6);
+        else if (o.fwd_minb == 4) GSR_F4(4);
+        else GSR_F4(5);
+#undef GSR_F4
+        return GSR_OK;
     }
     if (o.fwd_minb == 5)
         GSR_LAUNCH((blend_fwd_v3_kernel<4, 5>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
@@ -797,6 +1153,7 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
     int rc;
     if ((rc = device_ctx(&ctx))) return rc;
     rc = ctx_once(ctx, 2u, [] {    // per device: opt in to the kernels' dynamic shared memory
+        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v7_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV7)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
@@ -820,7 +1177,10 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
                b.scratch, pw, W, H, bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt)
         // bwd_variant 6: 16 reduction rows, 3 CTAs per SM;  68 / 84 / 83: 8 rows (4 / 4 / 3 CTAs per SM), trips of 2 / 4 / 4 entries;
         // 64: 16 rows, trips of 4
-        if (o.bwd_variant == 68) GSR_V6(8, 2, 4);
+        if (o.bwd_variant == 7) {
+            GSR_LAUNCH((blend_bwd_v7_kernel<3>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
+                       im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
+        } else if (o.bwd_variant == 68) GSR_V6(8, 2, 4);
         else if (o.bwd_variant == 84) GSR_V6(8, 4, 4);
         else if (o.bwd_variant == 83) GSR_V6(8, 4, 3);
         else if (o.bwd_variant == 64) GSR_V6(16, 4, 3);

@@ -16,7 +16,7 @@ static int env_int(const char* name, int dflt)
 
 struct OptionName { const char* name; int Options::*field; };
 static const OptionName kOptionNames[] = {
-    {"BWD_VARIANT", &Options::bwd_variant}, {"LPT", &Options::lpt}, {"FWD_MINB", &Options::fwd_minb},
+    {"BWD_VARIANT", &Options::bwd_variant}, {"FWD_VARIANT", &Options::fwd_variant}, {"LPT", &Options::lpt}, {"FWD_MINB", &Options::fwd_minb},
     {"BWD_MINB", &Options::bwd_minb}, {"SIDE_STREAM", &Options::side_stream}, {"BWD_SIDE", &Options::bwd_side},
     {"SH_SPLIT", &Options::sh_split}, {"PRE_STAGE", &Options::pre_stage}, {"DEPTH_SEG_ITEMS", &Options::depth_seg_items}, {"RADIX_SPLIT", &Options::radix_split}, {"RADIX_DEPTH", &Options::radix_depth}, {"BLEND_ARM", &Options::blend_arm},
     {"SORT_CUB", &Options::sort_cub}, {"BLEND_STATS", &Options::blend_stats},
