@@ -236,6 +236,20 @@ int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const
 int gsr_dist2(int P, const float* points, float* out, GsrAlloc scratch, gsr_stream_t stream);
 
 /*
+ * distCUDA2 for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc): the same kernels and the same result as gsr_dist2, but the scratch lives in a file-scope __device__ array
+ * of the library (about 10 MB, held by every GPU that loads the library until exit) instead of coming from an
+ * allocator callback.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).
+ * This entry point has no counterpart in the reference.
+ *   P <= GSR_DIST2_STATIC_MAX_POINTS, else GSR_ETOOBIG (gsr_last_cuda_error() holds the text); use gsr_dist2 beyond it.
+ * All calls on one device share the array, which keeps the last call's contents (the call clears what must start at
+ * zero): calls that overlap on the GPU - two streams, two host threads on one device - race; order them on one stream.
+ * Additive: GSR_ABI_VERSION is unchanged.
+ */
+#define GSR_DIST2_STATIC_MAX_POINTS 262144
+int gsr_dist2_static(int P, const float* points, float* out, gsr_stream_t stream);
+
+/*
  * Fused L1 image loss (forward + gradient in one pass): replaces utils/loss_utils.py:17-18
  * `torch.abs(network_output - gt).mean()` and its autograd backward.
  *   *loss_sum = sum_i |image[i] - target[i]|         (device scalar, zeroed by the call)

@@ -23,6 +23,12 @@ int record_cuda_error(cudaError_t e, const char* where)
     return GSR_ECUDA;
 }
 
+int record_error_text(int code, const char* text)
+{
+    snprintf(t_last_cuda_error, sizeof t_last_cuda_error, "%s", text);
+    return code;
+}
+
 // ------------------------------------------------------------------ per-stage event timing
 // A measurement facility for bench.py (off by default): one global table guarded by a mutex; the events belong to the
 // device that was current when the stage was opened, and a stage is open on one stream at a time per host thread.

@@ -20,6 +20,7 @@ namespace gsr {
 // ---------------------------------------------------------------- error / launch bookkeeping
 extern std::atomic<unsigned long long> g_launches;      // api.cu
 int record_cuda_error(cudaError_t e, const char* where);    // the message is kept per host thread
+int record_error_text(int code, const char* text);           // same slot (gsr_last_cuda_error()); returns `code`
 
 #define GSR_CUDA(call)                                                           \
     do {                                                                         \

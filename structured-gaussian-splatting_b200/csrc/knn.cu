@@ -17,6 +17,7 @@
 // computed with the same monotone fp32 expression), so the output equals brute force.
 #include "gsr_common.cuh"
 #include <cfloat>
+#include <mutex>
 
 namespace gsr {
 
@@ -232,3 +233,55 @@ int launch_dist2(int P, const float* points, float* out, GsrAlloc scratch, cudaS
 }
 
 }  // namespace gsr
+
+// ------------------------------------------------------------------------------------------ distCUDA2 without an allocator
+// gsr_dist2_static (include/gsr.h): same kernels as gsr_dist2, scratch in the file-scope device array below instead of
+// an allocator callback, for callers that may not allocate (CUDA graph capture, serving loops).  No counterpart in the
+// reference.  Every GPU that loads the library holds the array until exit.
+// All calls on a device share it: it keeps the last call's contents (launch_dist2 clears what it needs zeroed: the
+// bounding-box words and the sort's control block), and calls that overlap on the GPU race.
+namespace {
+
+constexpr size_t kDist2StaticWords = 64 + 5 * (size_t)GSR_DIST2_STATIC_MAX_POINTS + 4 * (size_t)GSR_DIST2_STATIC_MAX_POINTS
+                                   + 8 * ((size_t)GSR_DIST2_STATIC_MAX_POINTS / gsr::KB) + 64
+                                   + 128 * 1024 /* control block of the sort: radix_ctl_words(max points), checked at run time */;
+static __device__ __align__(256) uint32_t g_dist2_static_scratch[kDist2StaticWords];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_dist2_static_mu;
+void* g_dist2_static_ptr[kMaxDevices];          // device address of the array on each device, looked up once per device
+
+struct StaticArena { void* base; size_t bytes; };
+void* static_arena_alloc(void* ctx, size_t bytes)      // a GsrAlloc over the array: hands it out if the request fits
+{
+    const StaticArena* a = static_cast<const StaticArena*>(ctx);
+    return bytes <= a->bytes ? a->base : nullptr;
+}
+
+}  // namespace
+
+extern "C" int gsr_dist2_static(int P, const float* points, float* out, gsr_stream_t stream)
+{
+    if (P < 0 || (P > 0 && (!points || !out))) return GSR_EINVAL;
+    if (P > GSR_DIST2_STATIC_MAX_POINTS)
+        return gsr::record_error_text(GSR_ETOOBIG, "gsr_dist2_static: P exceeds GSR_DIST2_STATIC_MAX_POINTS (262144); use gsr_dist2");
+    if (P == 0) return GSR_OK;
+    int dev = -1;
+    GSR_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return gsr::record_error_text(GSR_EINVAL, "gsr_dist2_static: device ordinal out of range");
+    void* base = nullptr;
+    {
+        // the array's name is a host-side stand-in here, not a device address: ask the runtime, with the device current
+        std::lock_guard<std::mutex> lk(g_dist2_static_mu);
+        if (!g_dist2_static_ptr[dev]) {
+            void* p = nullptr;
+            GSR_CUDA(cudaGetSymbolAddress(&p, g_dist2_static_scratch));
+            g_dist2_static_ptr[dev] = p;
+        }
+        base = g_dist2_static_ptr[dev];
+    }
+    StaticArena arena{base, sizeof(uint32_t) * kDist2StaticWords};
+    const int rc = gsr::launch_dist2(P, points, out, GsrAlloc{static_arena_alloc, &arena}, (cudaStream_t)stream);
+    if (rc == GSR_ENOMEM) return gsr::record_error_text(GSR_ETOOBIG, "gsr_dist2_static: scratch array too small for this P");
+    return rc;
+}
