@@ -64,9 +64,8 @@ def main():
 
     variants = {
         "default": dict(),
+        "bwd7_guarded": dict(bwd_variant=70),
         "fwd3_bwd6": dict(fwd_variant=3, bwd_variant=6),
-        "fwd4_bwd6": dict(fwd_variant=4, bwd_variant=6),
-        "fwd3_bwd7": dict(fwd_variant=3, bwd_variant=7),
         "default_again": dict(),
     }
     ref_g = None

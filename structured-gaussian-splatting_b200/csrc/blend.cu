@@ -148,7 +148,8 @@ blend_fwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
 
     float T = 1.0f;
     uint32_t last_contributor = 0;
-    float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+    float2 C01 = make_float2(0.f, 0.f);         // red and green accumulate as one register pair (FFMA2)
+    float C2 = 0.f;
 
     uint32_t id_next = 0;
     {
@@ -198,8 +199,13 @@ blend_fwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                 const float4 a = st.q0[j], c = st.q1[j];
                 const float b = st.b[j];
                 float* w = pw + (lane >> 1) * (int)(sizeof(PairRec) / 4) + (lane & 1);
-                w[0] = a.x; w[2] = a.y; w[4] = a.z; w[6] = a.w; w[8] = c.x; w[10] = c.y; w[12] = c.z; w[14] = c.w;
+                w[0] = a.x; w[2] = a.y; w[4] = a.z; w[6] = a.w; w[8] = c.x; w[10] = c.y;
+                w[12 + (lane & 1)] = c.z; w[13 + (lane & 1)] = c.w;          // colours: (r0 g0 r1 g1), see blend_step_rg
+               
                 w[16] = b; w[18] = __uint_as_float(pos_base + (uint32_t)j);
+            } else if (lane == n) {                     // an odd group's last pair: its second slot blends nothing (opacity 0)
+                float* w = pw + (lane >> 1) * (int)(sizeof(PairRec) / 4) + (lane & 1);
+                w[0] = 0.f; w[2] = 0.f; w[4] = 0.f; w[6] = 0.f; w[8] = 0.f; w[10] = 0.f;
             }
             __syncwarp();
 #pragma unroll 1
@@ -209,9 +215,9 @@ blend_fwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                 pair_head(r, pxf, pyf, dx, dy, power, araw);
                 const float al0 = fminf(0.99f, araw.x), al1 = fminf(0.99f, araw.y);
                 const bool ok0 = !(power.x > 0.0f) && !(al0 < 1.0f / 255.0f);
-                const bool ok1 = !(power.y > 0.0f) && !(al1 < 1.0f / 255.0f) && 2 * q + 1 < n;    // the odd tail: a stale slot
-                blend_step(al0, ok0, r.rg.x, r.rg.z, r.bp.x, __float_as_uint(r.bp.z), done, T, C0, C1, C2, last_contributor);
-                blend_step(al1, ok1, r.rg.y, r.rg.w, r.bp.y, __float_as_uint(r.bp.w), done, T, C0, C1, C2, last_contributor);
+                const bool ok1 = !(power.y > 0.0f) && !(al1 < 1.0f / 255.0f);
+                blend_step_rg(al0, ok0, make_float2(r.rg.x, r.rg.y), r.bp.x, __float_as_uint(r.bp.z), done, T, C01, C2, last_contributor);
+                blend_step_rg(al1, ok1, make_float2(r.rg.z, r.rg.w), r.bp.y, __float_as_uint(r.bp.w), done, T, C01, C2, last_contributor);
             }
             if (__all_sync(0xffffffffu, done)) break;    // (also orders this group's reads before the next group's writes)
         }
@@ -223,8 +229,8 @@ blend_fwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
         final_T[view * HW + pix] = T;
         n_contrib[view * HW + pix] = last_contributor;
         float* o = out + 3 * view * HW + pix;
-        o[0] = C0 + T * bg[0];
-        o[HW] = C1 + T * bg[1];
+        o[0] = C01.x + T * bg[0];
+        o[HW] = C01.y + T * bg[1];
         o[2 * HW] = C2 + T * bg[2];
     }
 }
@@ -914,7 +920,7 @@ __device__ __forceinline__ void v7_pair(const PairRec r, float pxf, float pyf, i
     w1 = araw_s.y * dL1;
 }
 
-template <int MINB>
+template <int MINB, bool FULL>
 __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_bwd_v7_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     const uint32_t* __restrict__ planes, uint32_t plane_words, int W, int H, const float* __restrict__ bg,
@@ -1068,14 +1074,27 @@ blend_bwd_v7_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
 #pragma unroll 1
         for (int jb = 0; jb < n; jb += SLOTS) {
             const int cnt = min(SLOTS, n - jb);             // entries of this flush group (warp-uniform)
+            if (FULL && cnt == SLOTS) {
+                // a full flush group (all but a warp's last one): straight-line code, the eight pairs' loads and heads can be
+                // scheduled across each other
 #pragma unroll
-            for (int c = 0; c < SLOTS; c += 2) {
-                if (c < cnt) {
+                for (int c = 0; c < SLOTS; c += 2) {
                     float w0, at0, w1, at1;
                     v7_pair(P[(jb + c) >> 1], pxf, pyf, last_contributor, dp0, dp1, dp2, T, Sd, w0, at0, w1, at1);
                     float* const sp = ((c >> 3) ? a_hi : a_lo) + (c & 7) * GS;
                     *reinterpret_cast<float2*>(sp) = make_float2(w0, at0);
                     *reinterpret_cast<float2*>(sp + GS) = make_float2(w1, at1);
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < SLOTS; c += 2) {
+                    if (c < cnt) {
+                        float w0, at0, w1, at1;
+                        v7_pair(P[(jb + c) >> 1], pxf, pyf, last_contributor, dp0, dp1, dp2, T, Sd, w0, at0, w1, at1);
+                        float* const sp = ((c >> 3) ? a_hi : a_lo) + (c & 7) * GS;
+                        *reinterpret_cast<float2*>(sp) = make_float2(w0, at0);
+                        *reinterpret_cast<float2*>(sp + GS) = make_float2(w1, at1);
+                    }
                 }
             }
             v6_flush<SLOTS>(S.a, S.b2, SM.b1, [&](int j, float2& xy, uint32_t& id) {
@@ -1153,7 +1172,8 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
     int rc;
     if ((rc = device_ctx(&ctx))) return rc;
     rc = ctx_once(ctx, 2u, [] {    // per device: opt in to the kernels' dynamic shared memory
-        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v7_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV7)));
+        GSR_CUDA(cudaFuncSetAttribute((blend_bwd_v7_kernel<3, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV7)));
+        GSR_CUDA(cudaFuncSetAttribute((blend_bwd_v7_kernel<3, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV7)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
@@ -1178,7 +1198,10 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
         // bwd_variant 6: 16 reduction rows, 3 CTAs per SM;  68 / 84 / 83: 8 rows (4 / 4 / 3 CTAs per SM), trips of 2 / 4 / 4 entries;
         // 64: 16 rows, trips of 4
         if (o.bwd_variant == 7) {
-            GSR_LAUNCH((blend_bwd_v7_kernel<3>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
+            GSR_LAUNCH((blend_bwd_v7_kernel<3, true>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
+                       im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
+        } else if (o.bwd_variant == 70) {
+            GSR_LAUNCH((blend_bwd_v7_kernel<3, false>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
                        im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
         } else if (o.bwd_variant == 68) GSR_V6(8, 2, 4);
         else if (o.bwd_variant == 84) GSR_V6(8, 4, 4);
