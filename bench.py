@@ -62,6 +62,12 @@ def parse_args():
                     help="how a step's views are summed: deferred = blending backward per view, ONE per-Gaussian backward per step "
                          "(set_grad_mode('deferred') + flush_deferred); kernels = every view's backward adds into the buffer "
                          "(set_grad_mode overwrite / accumulate); autograd = plain .grad += (same as --plain-autograd)")
+    ap.add_argument("--pipeline", type=int, default=1,
+                    help="deferred steps: 1 = the forward of view i+1 is issued before the backward of view i, its front (preprocess, "
+                         "depth order, tile split) on a high-priority stream of its own (set_front_stream / gsr_forward_front); 0 = one "
+                         "view at a time on one stream")
+    ap.add_argument("--front-priority", default="high", choices=["high", "default"],
+                    help="priority of the front stream of --pipeline 1 (A/B: `default` = same priority as the rendering stream)")
     ap.add_argument("--no-extras", action="store_true",
                     help="headline + stages only: skip batched / two-stream / forward-only / plain-api / dist2 / reference-cuda / c5 legs")
     ap.add_argument("--no-c5", action="store_true", help="skip the config C5 leg (6 M Gaussians)")
@@ -436,6 +442,8 @@ def main():
         flat.all_reduce()
 
     use_deferred = [True]            # (switched off for the `grad_sum_in_kernels` comparison leg)
+    front_st = lambda: dgr.front_stream(dev, args.front_priority == "high")
+    use_pipeline = [bool(args.pipeline) and deferred]      # (switched off for the per-stage timing pass and the `one_stream` leg)
 
     def run_views(prm, flt, views, loss_of, chunks, collect=False):
         """One rank's share of a step through the drop-in API: the views' gradients are summed in the backward kernels; with
@@ -444,16 +452,32 @@ def main():
         if deferred and use_deferred[0]:
             # per view: forward + blending backward; once per step: the per-Gaussian backward of all views (in `chunks` ranges
             # with each range's all-reduce issued behind it when N > 1)
+            views = list(views)
+            piped = use_pipeline[0] and len(views) > 1
             prev = dgr.set_grad_mode("deferred")
+            prev_front = dgr.set_front_stream(front_st()) if piped else None
+
+            def back(color, radii, k):
+                loss_of(color, k).backward() if loss_of is not None else color.backward(go)
+                if collect:
+                    stats["Pv"] += int((radii > 0).sum())
+                    stats["views"] += 1
             try:
-                for k in views:
-                    color, radii, _ = dp.render_view(dgr, prm, cams[k], bg, spec.D)
-                    loss_of(color, k).backward() if loss_of is not None else color.backward(go)
-                    if collect:
-                        stats["Pv"] += int((radii > 0).sum())
-                        stats["views"] += 1
+                if piped:
+                    # software pipeline: forward of view i+1 (its front on the high-priority stream), then backward of view i
+                    ahead = dp.render_view(dgr, prm, cams[views[0]], bg, spec.D)
+                    for i, k in enumerate(views):
+                        color, radii, _ = ahead
+                        ahead = dp.render_view(dgr, prm, cams[views[i + 1]], bg, spec.D) if i + 1 < len(views) else None
+                        back(color, radii, k)
+                else:
+                    for k in views:
+                        color, radii, _ = dp.render_view(dgr, prm, cams[k], bg, spec.D)
+                        back(color, radii, k)
             finally:
                 dgr.set_grad_mode(prev)
+                if piped:
+                    dgr.set_front_stream(prev_front)
             if chunks > 0:
                 dgr.flush_deferred(False, chunks, lambda g0, g1: works.append(flt.all_reduce_rows(g0, g1)))
                 for w in works:
@@ -511,7 +535,7 @@ def main():
     # landing buffers for the prefetched views: a ring of three, allocated once, so the timed region makes no allocator calls
     # (a cudaMalloc on the copy stream stalls the whole device); a slot is overwritten only after the compute stream is
     # done with the view that used it
-    RING = 3
+    RING = 4
     ring_tgt = [torch.empty(3, spec.H, spec.W, device=dev) for _ in range(RING)]
     ring_cam = [torch.empty(cam_host[0].numel(), device=dev) for _ in range(RING)]
     ring_free = [None] * RING
@@ -534,6 +558,8 @@ def main():
             prefetch(k)
         slot, ev = pending.pop(k)
         torch.cuda.current_stream().wait_event(ev)
+        if use_pipeline[0]:
+            front_st().wait_event(ev)        # the camera is an input of the front too
         return ring_tgt[slot], ring_cam[slot], slot
 
     def release(slot):
@@ -579,20 +605,35 @@ def main():
         total = None
         works = []
         if deferred:
+            piped = use_pipeline[0] and len(views) > 1
             prev = dgr.set_grad_mode("deferred")
+            prev_front = dgr.set_front_stream(front_st()) if piped else None
+
+            def fwd(i):
+                k = views[i]
+                tgt, cm, slot = take(k)
+                nxt = views[i + 1] if i + 1 < len(views) else my_views(step + 1)[0]
+                prefetch(nxt)                              # next view's inputs travel while this one renders
+                cam = synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cm[:16].view(4, 4), cm[16:32].view(4, 4), cm[32:35])
+                color, radii, _ = dp.render_view(dgr, params, cam, bg, spec.D)
+                return color, tgt, slot
+
             try:
+                ahead = fwd(0) if piped else None
                 for i, k in enumerate(views):
-                    tgt, cm, slot = take(k)
-                    nxt = views[i + 1] if i + 1 < len(views) else my_views(step + 1)[0]
-                    prefetch(nxt)                              # next view's inputs travel while this one renders
-                    cam = synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cm[:16].view(4, 4), cm[16:32].view(4, 4), cm[32:35])
-                    color, radii, _ = dp.render_view(dgr, params, cam, bg, spec.D)
+                    if piped:
+                        color, tgt, slot = ahead
+                        ahead = fwd(i + 1) if i + 1 < len(views) else None
+                    else:
+                        color, tgt, slot = fwd(i)
                     loss = losses.l1_loss(color, tgt)
                     loss.backward()
                     release(slot)
                     total = loss.detach() if total is None else total + loss.detach()
             finally:
                 dgr.set_grad_mode(prev)
+                if piped:
+                    dgr.set_front_stream(prev_front)
             if overlap > 0:
                 dgr.flush_deferred(False, overlap, lambda g0, g1: works.append(flat.all_reduce_rows(g0, g1)))
                 for w in works:
@@ -652,13 +693,26 @@ def main():
         step_device(i)
     torch.cuda.synchronize()
     step_device(args.warmup, collect=True)           # untimed: realised P_v for the byte counts
-    C.timing_reset(); C.timing_enable(True); C.reset_launch_count()
+    piped = use_pipeline[0] and not args.batched and vps > 1
+    C.timing_reset(); C.timing_enable(not piped); C.reset_launch_count()
     sampler = ClockSampler(local_rank)
     sampler.start()
     ms_total = timed(step_device, args.steps, args.warmup + 1)
     clocks = sampler.stop()
     C.timing_enable(False)
     launches = int(C.launch_count())
+    one_stream = None
+    if piped:
+        # The per-stage event intervals overlap when two views are in flight, so the stage table (and the dominant kernel's
+        # launch duration the roofline uses) comes from a pass of the same steps WITHOUT the pipelining, timed as a whole too.
+        use_pipeline[0] = False
+        step_device(args.warmup)
+        C.timing_reset(); C.timing_enable(True)
+        ms_one = timed(step_device, args.steps, args.warmup + 1)
+        C.timing_enable(False)
+        use_pipeline[0] = True
+        one_stream = {"api": "the same step, one view at a time on one stream (--pipeline 0); the `stages` table is from this pass",
+                      "ms_per_view": ms_one / args.steps / vps, "value": args.steps * vps * world / (ms_one * 1e-3), "unit": UNIT}
     stage_rows = C.timing_collect()
     views_total = args.steps * vps * world
     value = views_total / (ms_total * 1e-3)
@@ -672,7 +726,7 @@ def main():
         e2e = {"value": views_total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps,
                "note": "per view: 24.9 MB target image + camera from pinned host memory on a copy stream one view ahead (ring of "
-                       "three preallocated landing buffers); loss read once per step"}
+                       "four preallocated landing buffers); loss read once per step"}
 
     # ---- the collective by itself (N > 1): the flat buffer's all-reduce timed alone, and what the step pays for it
     allreduce = None
@@ -987,13 +1041,16 @@ def main():
                            "grad_sum": ("deferred: blending backward per view, one per-Gaussian backward over the step's views "
                                         "(set_grad_mode('deferred') + flush_deferred)" if deferred else
                                         "in the backward kernels (set_grad_mode)" if fused else "autograd .grad +="),
-                           "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else "GaussianRasterizer: one call per view",
+                           "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else
+                                  ("GaussianRasterizer: one call per view; the forward of view i+1 is issued before the backward of view i, its "
+                                   "front (preprocess, depth order, tile split) on a high-priority stream (set_front_stream)" if piped else
+                                   "GaussianRasterizer: one call per view"),
                            "c5": "config C5 (6M Gaussians, %d views per step) measured by the same step at this N: see the `c5` object" % (vps * world),
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat_nbytes + 48 * P + 20 * R) / 1e9)},
                 "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "allreduce": allreduce, "c5": c5,
                 "reference_cuda": ref_extra, "plain_api": plain_extra, "grad_sum_in_kernels": kernels_extra, "dist2": dist2_extra,
-                "batched": batched_extra, "two_streams": streams_extra, "forward_only": forward_extra, "train_step": train_extra,
+                "batched": batched_extra, "one_stream": one_stream, "two_streams": streams_extra, "forward_only": forward_extra, "train_step": train_extra,
                 "gpu_launches": launches,
                 "clocks": clocks}
         print(json.dumps(line), flush=True)

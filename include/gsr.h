@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 4
+#define GSR_ABI_VERSION 5
 
 /* error codes */
 #define GSR_OK          0
@@ -102,6 +102,23 @@ typedef struct GsrFwdArgs {
  */
 int gsr_forward(const GsrFwdArgs* args, GsrAlloc geom, GsrAlloc binning, GsrAlloc img,
                 gsr_stream_t stream, int* num_rendered);
+
+/*
+ * gsr_forward on two streams (ABI 5).  Everything up to and including the tile split (preprocess, depth order, instance
+ * emission, tile split: rasterizer_impl.cu:216-318) is issued on `front_stream`, the blending (FORWARD::render,
+ * rasterizer_impl.cu:320-333) on `stream`, which waits for the front through an event of the library's own.  Results are
+ * those of gsr_forward.  What it is for: the front of a view is bound by memory latency and bandwidth, the blending kernels by
+ * instruction issue; a trainer that renders several views per step calls the forward of view i+1 BEFORE the backward of
+ * view i and gives `front_stream` a higher priority than `stream`, so the front of the next view runs inside the blending
+ * kernels of the current one (gsr_b200/dp.py `deferred_views(pipeline=True)`; the reference runs one view at a time on the
+ * legacy stream).  The caller's side of the contract: (1) every input (parameters, camera) must be valid ON `front_stream` -
+ * the library does not make `front_stream` wait for `stream`; (2) radii and the three blobs are written on `front_stream`
+ * and read on `stream`: an allocator that recycles memory by stream must be told about both (the torch binding allocates
+ * them under the front stream and calls record_stream for `stream`).  The host is blocked once, for the front's
+ * num_rendered only.  front_stream == stream (or NULL) is gsr_forward.
+ */
+int gsr_forward_front(const GsrFwdArgs* args, GsrAlloc geom, GsrAlloc binning, GsrAlloc img,
+                      gsr_stream_t front_stream, gsr_stream_t stream, int* num_rendered);
 
 /*
  * Batched forward: n_views cameras over ONE Gaussian set in a single pass (the reference

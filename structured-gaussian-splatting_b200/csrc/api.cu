@@ -168,10 +168,12 @@ size_t gsr_bwd_accum_bytes(int P) { return (size_t)(P > 0 ? P : 1) * 12 * sizeof
 // run once over all of them.  V = 1 is the reference's single-view call.
 // S > 1: S scenes of P Gaussians each (parameter arrays [S][P][...]) with V / S cameras per scene: preprocess runs once per scene
 // on that scene's parameters and cameras, everything after it once over all S * (V / S) * P virtual Gaussians.
+// front_ (gsr_forward_front): the stream of everything before the blending; the blending stays on stream_.
 static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream_,
-                        int* num_rendered)
+                        int* num_rendered, gsr_stream_t front_ = nullptr)
 {
-    cudaStream_t s = (cudaStream_t)stream_;
+    cudaStream_t const blend_s = (cudaStream_t)stream_;
+    cudaStream_t s = front_ ? (cudaStream_t)front_ : blend_s;       // the front's stream until the blending starts
     if (!a || !num_rendered || !geom.fn || !binning.fn || !img.fn) return GSR_EINVAL;
     *num_rendered = 0;
     if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3 || V < 1 || S < 1 || V % S != 0) return GSR_EINVAL;
@@ -183,7 +185,7 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     const int gyT = gy * V, HT = gyT * GSR_TILE; // the tall image in whole tiles
     if (a->P == 0) {
         // reference binding returns the zero-filled image without calling the core (rasterize_points.cu:81)
-        GSR_CUDA(cudaMemsetAsync(a->out_color, 0, sizeof(float) * 3 * (size_t)a->W * a->H * V, s));
+        GSR_CUDA(cudaMemsetAsync(a->out_color, 0, sizeof(float) * 3 * (size_t)a->W * a->H * V, blend_s));
         return GSR_OK;
     }
     if (!a->means3D || !a->opacities || !a->radii) return GSR_EINVAL;
@@ -271,6 +273,12 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     stage_end(2, s);
     GSR_STAGE(a->debug, s, "tile_split");
 
+    if (s != blend_s) {
+        // two-stream form: the blending stream waits for the front (the call's own event is free again after the wait above)
+        GSR_CUDA(cudaEventRecord(slot->ev, s));
+        GSR_CUDA(cudaStreamWaitEvent(blend_s, slot->ev, 0));
+        s = blend_s;
+    }
     stage_begin(3, s);
     if ((rc = launch_blend_forward(R, a->W, a->H, V, a->background, g, b, im, a->out_color, s))) return rc;
     stage_end(3, s);
@@ -286,6 +294,11 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
 int gsr_forward(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream, int* num_rendered)
 {
     return forward_impl(a, 1, 1, geom, binning, img, stream, num_rendered);
+}
+int gsr_forward_front(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t front_stream, gsr_stream_t stream,
+                      int* num_rendered)
+{
+    return forward_impl(a, 1, 1, geom, binning, img, stream, num_rendered, front_stream == stream ? nullptr : front_stream);
 }
 int gsr_forward_batched(const GsrFwdArgs* a, int n_views, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream,
                         int* num_rendered)

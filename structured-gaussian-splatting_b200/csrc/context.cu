@@ -74,7 +74,10 @@ int ctx_side_stream(DeviceCtx* c, int which, cudaStream_t user, SideStream* out)
         *out = s;
         return GSR_OK;
     }
-    GSR_CUDA(cudaStreamCreateWithFlags(&s.side, cudaStreamNonBlocking));
+    // the helper stream runs pieces of the caller's own work: it inherits the caller stream's priority
+    int prio = 0;
+    if (cudaStreamGetPriority(user, &prio) != cudaSuccess) { cudaGetLastError(); prio = 0; }
+    GSR_CUDA(cudaStreamCreateWithPriority(&s.side, cudaStreamNonBlocking, prio));
     GSR_CUDA(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
     GSR_CUDA(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
     c->sides[which].push_back(s);

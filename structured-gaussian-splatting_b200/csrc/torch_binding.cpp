@@ -12,6 +12,8 @@
 #include <torch/extension.h>
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <memory>
 #include <functional>
 #include <tuple>
 #include <string>
@@ -51,15 +53,17 @@ gsr_stream_t current_stream() { return reinterpret_cast<gsr_stream_t>(at::cuda::
 
 }  // namespace
 
-// `sh_rest` non-empty: split SH storage - `sh` is the model's _features_dc [P,1,3] and `sh_rest` its _features_rest [P,M-1,3]
-// (scene/gaussian_model.py:151-152), read in place instead of through the torch.cat of get_features (:119-122)
-std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
-rasterize_gaussians_split(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+// `front_stream` != 0 (a cudaStream_t of means3D's device, as an integer): gsr_forward_front - preprocess and binning are issued
+// on that stream, the blending on torch's current stream.  radii and the state blobs, which the front writes and the current
+// stream reads, are allocated under the front stream and recorded for the current one (the caching allocator recycles memory
+// per stream).  The caller has made the inputs valid on the front stream (diff_gaussian_rasterization.set_front_stream).
+static std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+forward_core(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
                           const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
                           const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
                           const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
                           const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
-                          const bool prefiltered, const bool debug, const torch::Tensor& sh_rest)
+                          const bool prefiltered, const bool debug, const torch::Tensor& sh_rest, int64_t front_stream)
 {
     if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
@@ -70,7 +74,17 @@ rasterize_gaussians_split(const torch::Tensor& background, const torch::Tensor& 
     auto i32 = means3D.options().dtype(torch::kInt32);
     auto u8 = means3D.options().dtype(torch::kByte);
 
+    // inputs the front would read through a .contiguous() copy made on the current stream: plain single-stream call
+    for (const torch::Tensor* t : {&background, &means3D, &colors, &opacity, &scales, &rotations, &cov3D_precomp, &viewmatrix, &projmatrix,
+                                   &sh, &campos, &sh_rest})
+        if (t->numel() > 0 && !t->is_contiguous()) front_stream = 0;
+    const c10::cuda::CUDAStream main_stream = at::cuda::getCurrentCUDAStream();
+    if (P == 0 || (cudaStream_t)front_stream == main_stream.stream()) front_stream = 0;
     torch::Tensor out_color = P == 0 ? torch::zeros({3, H, W}, f32) : torch::empty({3, H, W}, f32);
+    std::unique_ptr<c10::cuda::CUDAStreamGuard> front_guard;
+    if (front_stream)
+        front_guard.reset(new c10::cuda::CUDAStreamGuard(
+            c10::cuda::getStreamFromExternal(reinterpret_cast<cudaStream_t>(front_stream), means3D.device().index())));
     torch::Tensor radii = P == 0 ? torch::zeros({P}, i32) : torch::empty({P}, i32);
     torch::Tensor geomBuffer = torch::empty({0}, u8), binningBuffer = torch::empty({0}, u8), imgBuffer = torch::empty({0}, u8);
     int rendered = 0;
@@ -91,11 +105,49 @@ rasterize_gaussians_split(const torch::Tensor& background, const torch::Tensor& 
         a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
         a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.prefiltered = prefiltered; a.debug = debug;
         a.out_color = out_color.data_ptr<float>(); a.radii = radii.data_ptr<int>();
-        check(gsr_forward(&a, GsrAlloc{resize_cb, &geomBuffer}, GsrAlloc{resize_cb, &binningBuffer}, GsrAlloc{resize_cb, &imgBuffer},
-                          current_stream(), &rendered),
-              "rasterize_gaussians");
+        if (front_stream) {
+            // (torch's current stream is the front stream here: the blobs the callbacks resize belong to it)
+            check(gsr_forward_front(&a, GsrAlloc{resize_cb, &geomBuffer}, GsrAlloc{resize_cb, &binningBuffer}, GsrAlloc{resize_cb, &imgBuffer},
+                                    current_stream(), reinterpret_cast<gsr_stream_t>(main_stream.stream()), &rendered),
+                  "rasterize_gaussians");
+            front_guard.reset();
+            for (torch::Tensor* t : {&radii, &geomBuffer, &binningBuffer, &imgBuffer})
+                if (t->numel() > 0) t->record_stream(main_stream);
+        } else {
+            check(gsr_forward(&a, GsrAlloc{resize_cb, &geomBuffer}, GsrAlloc{resize_cb, &binningBuffer}, GsrAlloc{resize_cb, &imgBuffer},
+                              current_stream(), &rendered),
+                  "rasterize_gaussians");
+        }
     }
     return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer);
+}
+
+// `sh_rest` non-empty: split SH storage - `sh` is the model's _features_dc [P,1,3] and `sh_rest` its _features_rest [P,M-1,3]
+// (scene/gaussian_model.py:151-152), read in place instead of through the torch.cat of get_features (:119-122)
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_split(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                          const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                          const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                          const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+                          const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                          const bool prefiltered, const bool debug, const torch::Tensor& sh_rest)
+{
+    return forward_core(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                        tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug, sh_rest, 0);
+}
+
+// rasterize_gaussians with the front of the view on a stream of its own (gsr_forward_front)
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_front(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                          const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                          const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                          const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+                          const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                          const bool prefiltered, const bool debug, int64_t front_stream)
+{
+    return forward_core(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                        tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug, torch::empty({0}),
+                        front_stream);
 }
 
 // the reference's entry point (rasterize_points.h:18-38)
@@ -761,6 +813,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
     m.def("rasterize_gaussians_batched_backward", &rasterize_gaussians_batched_backward, nogil());
     m.def("rasterize_gaussians", &rasterize_gaussians, nogil());
     m.def("rasterize_gaussians_split", &rasterize_gaussians_split, nogil());
+    m.def("rasterize_gaussians_front", &rasterize_gaussians_front, nogil());
     m.def("rasterize_gaussians_backward_split", &rasterize_gaussians_backward_split, nogil());
     m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward, nogil());
     m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into, nogil());

@@ -140,6 +140,46 @@ def set_chunk_hook(hook):
     return prev
 
 
+# ---- extension (off by default): the front of a view (preprocess, depth order, tile split) on a stream of its own
+# (gsr_forward_front).  Those stages are bound by memory latency and bandwidth, the blending kernels by instruction issue: a
+# step that renders several views issues the forward of view i+1 BEFORE the backward of view i, and with a high-priority front
+# stream the next view's front runs inside the current view's blending kernels (gsr_b200.dp.deferred_views(pipeline=True)).
+# Contract: the front stream does NOT wait for the stream the render is called on - that is the point - so every input of
+# the render (parameters, camera tensors) must be valid on it.  set_front_stream() makes it wait for the calling stream ONCE,
+# at the moment of the call (so: call it after the optimizer step, before the first render of the step); inputs produced
+# later on another stream (a camera copied in by a loader) are the caller's to order: front.wait_event(...).
+_FRONT = None                    # torch.cuda.Stream or None
+
+
+def set_front_stream(stream):
+    """stream: a torch.cuda.Stream (ideally created with a higher priority than the rendering stream) or None; returns the
+    previous one.  The stream waits for everything queued so far on the current stream."""
+    global _FRONT
+    prev, _FRONT = _FRONT, stream
+    if stream is not None:
+        stream.wait_stream(torch.cuda.current_stream(stream.device))
+    return prev
+
+
+def front_stream(device=None, high_priority=True):
+    """A stream for set_front_stream (one per device and priority class, created on first use); high priority by default, so
+    the front's small kernels get SM slots as the blending kernels' thread blocks retire."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    st = _FRONT_STREAMS.get((dev, bool(high_priority)))
+    if st is None:
+        prio = 0
+        if high_priority:
+            lo, hi = torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream, "priority_range") else (0, -1)
+            prio = min(lo, hi)
+        st = _FRONT_STREAMS[(dev, bool(high_priority))] = torch.cuda.Stream(device=dev, priority=prio)
+    return st
+
+
+_FRONT_STREAMS = {}
+
+
 class GaussianRasterizationSettings(NamedTuple):
     image_height: int
     image_width: int
@@ -163,8 +203,12 @@ class _RasterizeGaussians(torch.autograd.Function):
         args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree,
                 rs.campos, rs.prefiltered, rs.debug)
-        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = _call_with_snapshot(
-            _C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward")
+        front = _FRONT
+        if front is not None and means3D.is_cuda and front.device == means3D.device and not rs.debug:
+            num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = _C.rasterize_gaussians_front(*args, front.cuda_stream)
+        else:
+            num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = _call_with_snapshot(
+                _C.rasterize_gaussians, args, rs.debug, "snapshot_fw.dump", "forward")
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
         ctx.grad_mode = _GRAD_MODE

@@ -199,22 +199,41 @@ def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
 
 def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
                    loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None,
-                   overlap_chunks: int = 0, all_reduce: bool = True):
+                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False):
     """The step in DEFERRED form (diff_gaussian_rasterization.set_grad_mode("deferred")): every view runs its forward and its
     blending backward; the per-Gaussian backward of all the rank's views then runs once (parameters read once, every gradient
     row written once: 0.2 instead of 0.4 ms per view at C3), in `overlap_chunks` ranges of Gaussians when > 0, the all-reduce
     of a range being issued right behind it - the whole per-Gaussian stage of the step (not just the last view's) is the
-    window the collective hides in.  Returns the summed local loss."""
+    window the collective hides in.  Returns the summed local loss.
+    pipeline=True: the forward of view i+1 is issued BEFORE the backward of view i, and the front of every forward
+    (preprocess, depth order, tile split: latency- and bandwidth-bound) goes to a high-priority stream of its own
+    (set_front_stream / gsr_forward_front), so it runs inside the issue-bound blending kernels of the views around it.
+    Same results; two views' state is alive at a time."""
     total = None
+    views = list(view_ids)
     prev = rasterizer_mod.set_grad_mode("deferred")
+    piped = (pipeline and len(views) > 1 and hasattr(rasterizer_mod, "set_front_stream")
+             and params[flat.names[0]].is_cuda)
+    prev_front = rasterizer_mod.set_front_stream(rasterizer_mod.front_stream(params[flat.names[0]].device)) if piped else None
     try:
-        for k in view_ids:
-            color, _radii, _m2d = render_view(rasterizer_mod, params, cams[k], bg, sh_degree)
-            loss = loss_fn(color, k)
-            loss.backward()
-            total = loss.detach() if total is None else total + loss.detach()
+        if piped:
+            ahead = render_view(rasterizer_mod, params, cams[views[0]], bg, sh_degree)
+            for i, k in enumerate(views):
+                color = ahead[0]
+                ahead = render_view(rasterizer_mod, params, cams[views[i + 1]], bg, sh_degree) if i + 1 < len(views) else None
+                loss = loss_fn(color, k)
+                loss.backward()
+                total = loss.detach() if total is None else total + loss.detach()
+        else:
+            for k in views:
+                color, _radii, _m2d = render_view(rasterizer_mod, params, cams[k], bg, sh_degree)
+                loss = loss_fn(color, k)
+                loss.backward()
+                total = loss.detach() if total is None else total + loss.detach()
     finally:
         rasterizer_mod.set_grad_mode(prev)
+        if piped:
+            rasterizer_mod.set_front_stream(prev_front)
     multi = all_reduce and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
     works = []
     if multi and overlap_chunks > 0:

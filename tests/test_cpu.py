@@ -234,7 +234,7 @@ def test_cabi_exports_every_declared_symbol():
     for s in sorted(declared):
         assert hasattr(lib, s), "libgsr_b200.so does not export %s" % s
     lib.gsr_abi_version.restype = ctypes.c_int
-    assert lib.gsr_abi_version() == 4
+    assert lib.gsr_abi_version() == 5
     lib.gsr_strerror.restype = ctypes.c_char_p
     assert b"precomputed" in lib.gsr_strerror(-4)
     lib.gsr_geom_bytes.restype = ctypes.c_size_t
@@ -243,6 +243,7 @@ def test_cabi_exports_every_declared_symbol():
     # argument validation happens before any CUDA call
     assert lib.gsr_forward(None, None, None, None, None, None) == -1
     assert lib.gsr_backward(None, None) == -1
+    assert lib.gsr_forward_front(None, None, None, None, None, None, None) == -1
     assert lib.gsr_backward_staged(None, 3, 0, -1, None) == -1
     assert lib.gsr_backward_views(None, 1, None, 0, -1, None) == -1
     # the product library carries no comparison arms (they live in the test-only libgsr_b200_arms.so) ...
