@@ -714,6 +714,14 @@ def main():
         one_stream = {"api": "the same step, one view at a time on one stream (--pipeline 0); the `stages` table is from this pass",
                       "ms_per_view": ms_one / args.steps / vps, "value": args.steps * vps * world / (ms_one * 1e-3), "unit": UNIT}
     stage_rows = C.timing_collect()
+    stages_piped = None
+    if piped:
+        # the same stage intervals with two views in flight: how far each stage is stretched by what runs next to it
+        C.timing_reset(); C.timing_enable(True)
+        timed(step_device, args.steps, args.warmup + 1)
+        C.timing_enable(False)
+        stages_piped = {name: round(ms / (args.steps * vps if name == "preprocess_backward" else max(1, calls)), 4)
+                        for name, ms, calls in C.timing_collect() if calls}
     views_total = args.steps * vps * world
     value = views_total / (ms_total * 1e-3)
 
@@ -1048,7 +1056,7 @@ def main():
                            "c5": "config C5 (6M Gaussians, %d views per step) measured by the same step at this N: see the `c5` object" % (vps * world),
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %
                                  ((flat_nbytes + 48 * P + 20 * R) / 1e9)},
-                "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline, "e2e": e2e, "allreduce": allreduce, "c5": c5,
+                "roofline": roofline, "stages": stages, "stages_pipelined_ms": stages_piped, "cpu_baseline": cpu_baseline, "e2e": e2e, "allreduce": allreduce, "c5": c5,
                 "reference_cuda": ref_extra, "plain_api": plain_extra, "grad_sum_in_kernels": kernels_extra, "dist2": dist2_extra,
                 "batched": batched_extra, "one_stream": one_stream, "two_streams": streams_extra, "forward_only": forward_extra, "train_step": train_extra,
                 "gpu_launches": launches,
