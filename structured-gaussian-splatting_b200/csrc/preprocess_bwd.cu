@@ -42,6 +42,8 @@ struct PreBwdArgs {
     int sh_done;             // the SH part (dL_dsh, its share of dL_dmean3D) was done by sh_bwd_m16_kernel
 };
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // out = v, or out += v when accumulating
 __device__ __forceinline__ void put(float* p, float v, bool acc) { *p = acc ? *p + v : v; }
 // dL/dmean3D gets a share from the SH kernel and one from preprocess_bwd_kernel; when the two run concurrently
@@ -161,6 +163,12 @@ __global__ void __launch_bounds__(256, WITH_SH ? 1 : 4) preprocess_bwd_kernel(Pr
     bool sh_written = false;
     (void)sh_written;
     for (int v = 0; v < NV; v++) {
+    if (MULTI && v + 1 < NV) {
+        // the next view's rows on their way into L2 while this view is computed (the loop is a chain of dependent loads)
+        prefetch_l2(vt.radii[v + 1] + idx);
+        prefetch_l2(vt.accum[v + 1] + (size_t)12 * idx);
+        prefetch_l2(&vt.rec[v + 1][idx]);
+    }
     const Camera& cam = cams[v];
     const int* v_radii = MULTI ? vt.radii[v] : a.radii;
     float* v_m2d = MULTI ? vt.m2d[v] : a.dL_dmean2D;
@@ -692,6 +700,14 @@ __global__ void __launch_bounds__(32 * SHB_WARPS, 7) sh_bwd_m16_views_kernel(int
     if (lane < nrow)
         for (int v = 0; v < V; v++) visible = visible || vt.radii[v][gid] > 0;
     const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
+    if (visible) {
+        // every view's accumulator row and clamp byte on their way into L2 while the SH rows are staged: the chunk loops
+        // below read them view after view, each read a dependent miss otherwise
+        for (int v = 0; v < V; v++) {
+            prefetch_l2(vt.accum[v] + (size_t)12 * gid);
+            if (lane == __ffs(vis_mask) - 1) prefetch_l2(vt.clamped[v] + gid);
+        }
+    }
     float* const flat = reinterpret_cast<float*>(my);
     const RowFlat frow{flat + lane * 3, flat + SHB_FLAT_DC + lane * 45};
     if (SPLIT) {
