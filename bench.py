@@ -66,6 +66,9 @@ def parse_args():
                     help="deferred steps: 1 = the forward of view i+1 is issued before the backward of view i, its front (preprocess, "
                          "depth order, tile split) on a high-priority stream of its own (set_front_stream / gsr_forward_front); 0 = one "
                          "view at a time on one stream")
+    ap.add_argument("--prepare", type=int, default=1,
+                    help="deferred steps: 1 = the preprocess stage of the step's views runs in one pass over the parameters "
+                         "(prepare_views / gsr_preprocess_views) before the per-view calls; 0 = every call preprocesses its view")
     ap.add_argument("--front-priority", default="high", choices=["high", "default"],
                     help="priority of the front stream of --pipeline 1 (A/B: `default` = same priority as the rendering stream)")
     ap.add_argument("--no-extras", action="store_true",
@@ -443,6 +446,7 @@ def main():
 
     use_deferred = [True]            # (switched off for the `grad_sum_in_kernels` comparison leg)
     front_st = lambda: dgr.front_stream(dev, args.front_priority == "high")
+    use_prepare = [bool(args.prepare) and deferred]        # (switched off with the pipelining for the `one_stream` leg)
     use_pipeline = [bool(args.pipeline) and deferred]      # (switched off for the per-stage timing pass and the `one_stream` leg)
 
     def run_views(prm, flt, views, loss_of, chunks, collect=False):
@@ -463,6 +467,8 @@ def main():
                     stats["Pv"] += int((radii > 0).sum())
                     stats["views"] += 1
             try:
+                if use_prepare[0]:
+                    dp.prepare_step_views(dgr, prm, cams, bg, spec.D, views)
                 if piped:
                     # software pipeline: forward of view i+1 (its front on the high-priority stream), then backward of view i
                     ahead = dp.render_view(dgr, prm, cams[views[0]], bg, spec.D)
@@ -713,6 +719,13 @@ def main():
         use_pipeline[0] = True
         one_stream = {"api": "the same step, one view at a time on one stream (--pipeline 0); the `stages` table is from this pass",
                       "ms_per_view": ms_one / args.steps / vps, "value": args.steps * vps * world / (ms_one * 1e-3), "unit": UNIT}
+        if use_prepare[0]:
+            # ... and with every call preprocessing its own view as well (round 2 g's form of the step)
+            use_pipeline[0] = False; use_prepare[0] = False
+            step_device(args.warmup)
+            ms_pv = timed(step_device, args.steps, args.warmup + 1)
+            use_pipeline[0] = True; use_prepare[0] = True
+            one_stream["per_view_preprocess_ms_per_view"] = ms_pv / args.steps / vps
     stage_rows = C.timing_collect()
     stages_piped = None
     if piped:
@@ -720,7 +733,8 @@ def main():
         C.timing_reset(); C.timing_enable(True)
         timed(step_device, args.steps, args.warmup + 1)
         C.timing_enable(False)
-        stages_piped = {name: round(ms / (args.steps * vps if name == "preprocess_backward" else max(1, calls)), 4)
+        per_step = ("preprocess_backward", "preprocess") if use_prepare[0] else ("preprocess_backward",)
+        stages_piped = {name: round(ms / (args.steps * vps if name in per_step else max(1, calls)), 4)
                         for name, ms, calls in C.timing_collect() if calls}
     views_total = args.steps * vps * world
     value = views_total / (ms_total * 1e-3)
@@ -981,13 +995,17 @@ def main():
             # per view: record, accumulator row, radii, clamp byte in, dL/dmean2D out (113 B per Gaussian); per step: parameters
             # in and gradients out once (44 + 12 M and 4 (11 + 3 M) B per Gaussian)
             sb["preprocess_backward"] = 113 * P + (44 + 12 * M + 4 * (11 + 3 * M)) * P / vps
+            if use_prepare[0]:
+                # prepared steps: parameters (44 B + the SH row) in once per step, every view's record / clamp byte / radii /
+                # depth key / tile rect out
+                sb["preprocess"] = (44 + 12 * M) * P / vps + (48 + 1 + 4 + 4 + 8) * P
         stages = {}
         dom, dom_ms = None, -1.0
         for name, ms, calls in stage_rows:
             if calls == 0 or name not in sb:
                 continue
             # per view (a batched call covers vps views; so does the deferred per-Gaussian backward, once per step)
-            if deferred and name == "preprocess_backward":
+            if deferred and (name == "preprocess_backward" or (name == "preprocess" and use_prepare[0])):
                 avg = ms / args.steps / vps                   # (calls = steps x ranges when the flush runs in ranges)
             else:
                 avg = ms / calls / (vps if args.batched else 1)

@@ -121,6 +121,34 @@ int gsr_forward_front(const GsrFwdArgs* args, GsrAlloc geom, GsrAlloc binning, G
                       gsr_stream_t front_stream, gsr_stream_t stream, int* num_rendered);
 
 /*
+ * Preprocess of several views at once (ABI 5).  A step that renders n_views <= 16 views of ONE Gaussian set through
+ * single-view calls reads the Gaussian parameters once per view - at SH degree 3 that is 236 of the ~300 bytes per Gaussian
+ * a view's preprocess (preprocessCUDA, forward.cu:155-259) moves.  gsr_preprocess_views runs that stage for all the views in
+ * one pass over the parameters: `common` carries what the views share (P, D, M, W, H, tan_fov*, scale_modifier, prefiltered,
+ * means3D, shs / shs_rest, opacities, scales, rotations; colors_precomp / cov3D_precomp must be NULL, out_color / radii /
+ * camera fields are ignored), every view brings its camera, its radii output and a geometry blob of gsr_geom_bytes(P) bytes.
+ * Each blob is then handed to gsr_forward_prepared, which runs the rest of gsr_forward (depth order, tile split, blending) on
+ * it; results are those of gsr_forward with that camera.  A prepared blob is consumed by exactly one gsr_forward_prepared
+ * call.  (The reference preprocesses one view per call: rasterizer_impl.cu:232-260.)
+ */
+typedef struct GsrViewFront {
+    const float* viewmatrix;     /* [16] */
+    const float* projmatrix;     /* [16] */
+    const float* cam_pos;        /* [3]  */
+    int*         radii;          /* [P], written */
+    void*        geom_blob;      /* gsr_geom_bytes(P) bytes, written */
+} GsrViewFront;
+int gsr_preprocess_views(const GsrFwdArgs* common, int n_views, const GsrViewFront* views, gsr_stream_t stream);
+
+/*
+ * The rest of gsr_forward on a blob prepared by gsr_preprocess_views.  `args` as for gsr_forward with the view's camera
+ * (args->radii is not written: gsr_preprocess_views did); front_stream as in gsr_forward_front (NULL or == stream: one stream).
+ * The work of gsr_preprocess_views must be complete on (or ordered before) the stream the front runs on.
+ */
+int gsr_forward_prepared(const GsrFwdArgs* args, void* prepared_geom_blob, GsrAlloc binning, GsrAlloc img,
+                         gsr_stream_t front_stream, gsr_stream_t stream, int* num_rendered);
+
+/*
  * Batched forward: n_views cameras over ONE Gaussian set in a single pass (the reference
  * renders one view per call, train_lgm.py:111-120).  Same argument struct with these per-view extensions:
  *   viewmatrix [n_views,16], projmatrix [n_views,16], cam_pos [n_views,3]  (W, H, tan_fov*, background shared)

@@ -169,12 +169,14 @@ size_t gsr_bwd_accum_bytes(int P) { return (size_t)(P > 0 ? P : 1) * 12 * sizeof
 // S > 1: S scenes of P Gaussians each (parameter arrays [S][P][...]) with V / S cameras per scene: preprocess runs once per scene
 // on that scene's parameters and cameras, everything after it once over all S * (V / S) * P virtual Gaussians.
 // front_ (gsr_forward_front): the stream of everything before the blending; the blending stays on stream_.
+// prepared (gsr_forward_prepared): a geometry blob gsr_preprocess_views has already filled - stage 0 is skipped.
 static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream_,
-                        int* num_rendered, gsr_stream_t front_ = nullptr)
+                        int* num_rendered, gsr_stream_t front_ = nullptr, void* prepared = nullptr)
 {
     cudaStream_t const blend_s = (cudaStream_t)stream_;
     cudaStream_t s = front_ ? (cudaStream_t)front_ : blend_s;       // the front's stream until the blending starts
-    if (!a || !num_rendered || !geom.fn || !binning.fn || !img.fn) return GSR_EINVAL;
+    if (!a || !num_rendered || (!geom.fn && !prepared) || !binning.fn || !img.fn) return GSR_EINVAL;
+    if (prepared && (V != 1 || S != 1 || a->colors_precomp || a->cov3D_precomp)) return GSR_EINVAL;
     *num_rendered = 0;
     if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3 || V < 1 || S < 1 || V % S != 0) return GSR_EINVAL;
     if (!a->out_color || !a->background || !a->viewmatrix || !a->projmatrix) return GSR_EINVAL;
@@ -188,23 +190,26 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
         GSR_CUDA(cudaMemsetAsync(a->out_color, 0, sizeof(float) * 3 * (size_t)a->W * a->H * V, blend_s));
         return GSR_OK;
     }
-    if (!a->means3D || !a->opacities || !a->radii) return GSR_EINVAL;
+    if (!a->means3D || !a->opacities || (!a->radii && !prepared)) return GSR_EINVAL;
     if (!a->shs && !a->colors_precomp) return GSR_ECHANNELS;
     if (a->shs && !a->colors_precomp && (!a->cam_pos || a->M < (a->D + 1) * (a->D + 1))) return GSR_EINVAL;
     if (a->shs && a->shs_rest && a->M != 16 && a->M != 1) return GSR_EINVAL;       // split SH storage: M = 16 (or DC only)
     if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return GSR_ECOV;
 
-    void* gblob = geom.fn(geom.ctx, gsr_geom_bytes(Pv));
+    void* gblob = prepared ? prepared : geom.fn(geom.ctx, gsr_geom_bytes(Pv));
     void* iblob = img.fn(img.ctx, gsr_img_bytes_batched(a->W, a->H, V));
     if (!gblob || !iblob) return GSR_ENOMEM;
     GeomView g = geom_view(gblob, Pv);
     ImgView im = img_view(iblob, a->W, a->H, V);
-    GSR_CUDA(cudaMemsetAsync(g.hdr, 0, sizeof(BlobHeader), s));
     const GeomScratch sc = carve_geom_scratch(g.scratch, Pv);
-    GSR_CUDA(cudaMemsetAsync(sc.ctl, 0, sc.ctl_words * 4, s));       // counters, histograms, look-back words
+    if (!prepared) {
+        GSR_CUDA(cudaMemsetAsync(g.hdr, 0, sizeof(BlobHeader), s));
+        GSR_CUDA(cudaMemsetAsync(sc.ctl, 0, sc.ctl_words * 4, s));       // counters, histograms, look-back words
+    }
     GSR_CUDA(cudaMemsetAsync(im.tile_diff, 0, sizeof(int) * (size_t)(gx + 1) * (gy + 1) * V, s));
 
     int rc;
+    if (!prepared) {
     stage_begin(0, s);
     {
         const int Vs = V / S;
@@ -226,6 +231,7 @@ static int forward_impl(const GsrFwdArgs* a, int V, int S, GsrAlloc geom, GsrAll
     }
     stage_end(0, s);
     GSR_STAGE(a->debug, s, "preprocess");
+    }
 
     // R (sum of tiles touched) is accumulated by preprocess: start its read-back now and wait for it only after
     // the depth sort has been queued, so the host's launch work overlaps the device
@@ -299,6 +305,40 @@ int gsr_forward_front(const GsrFwdArgs* a, GsrAlloc geom, GsrAlloc binning, GsrA
                       int* num_rendered)
 {
     return forward_impl(a, 1, 1, geom, binning, img, stream, num_rendered, front_stream == stream ? nullptr : front_stream);
+}
+int gsr_preprocess_views(const GsrFwdArgs* a, int n_views, const GsrViewFront* views, gsr_stream_t stream_)
+{
+    cudaStream_t s = (cudaStream_t)stream_;
+    if (!a || !views || n_views < 1 || n_views > GSR_MAX_VIEWS) return GSR_EINVAL;
+    if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->D < 0 || a->D > 3) return GSR_EINVAL;
+    const int gx = (a->W + GSR_TILE - 1) / GSR_TILE, gy = (a->H + GSR_TILE - 1) / GSR_TILE;
+    if (gx > 65535 || gy > 65535 || (long long)a->P >= (1ll << 30)) return GSR_ETOOBIG;
+    if (a->P == 0) return GSR_OK;
+    if (!a->means3D || !a->opacities || !a->scales || !a->rotations || a->colors_precomp || a->cov3D_precomp) return GSR_EINVAL;
+    if (!a->shs) return GSR_ECHANNELS;
+    if (a->M < (a->D + 1) * (a->D + 1)) return GSR_EINVAL;
+    if (a->shs_rest && a->M != 16 && a->M != 1) return GSR_EINVAL;
+    GeomView g[GSR_MAX_VIEWS];
+    for (int v = 0; v < n_views; v++) {
+        if (!views[v].viewmatrix || !views[v].projmatrix || !views[v].cam_pos || !views[v].radii || !views[v].geom_blob) return GSR_EINVAL;
+        g[v] = geom_view(views[v].geom_blob, a->P);
+        const GeomScratch sc = carve_geom_scratch(g[v].scratch, a->P);
+        GSR_CUDA(cudaMemsetAsync(g[v].hdr, 0, sizeof(BlobHeader), s));
+        GSR_CUDA(cudaMemsetAsync(sc.ctl, 0, sc.ctl_words * 4, s));       // counters, histograms, look-back words
+    }
+    stage_begin(0, s);
+    int rc = launch_preprocess_views(*a, n_views, views, g, s);
+    if (rc) return rc;
+    stage_end(0, s);
+    GSR_STAGE(a->debug, s, "preprocess");
+    return GSR_OK;
+}
+int gsr_forward_prepared(const GsrFwdArgs* a, void* prepared_geom_blob, GsrAlloc binning, GsrAlloc img, gsr_stream_t front_stream,
+                         gsr_stream_t stream, int* num_rendered)
+{
+    if (!prepared_geom_blob) return GSR_EBLOB;
+    return forward_impl(a, 1, 1, GsrAlloc{nullptr, nullptr}, binning, img, stream, num_rendered,
+                        (front_stream == stream) ? nullptr : front_stream, prepared_geom_blob);
 }
 int gsr_forward_batched(const GsrFwdArgs* a, int n_views, GsrAlloc geom, GsrAlloc binning, GsrAlloc img, gsr_stream_t stream,
                         int* num_rendered)

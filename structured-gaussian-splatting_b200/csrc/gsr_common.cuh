@@ -156,6 +156,8 @@ __device__ __forceinline__ void load_camera(Camera& cam, const CameraArgs& ca)
 
 // preprocess.cu
 int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, const GeomView& g, cudaStream_t s);
+// n_views <= GSR_MAX_VIEWS single-view blobs filled in one pass over the parameters (gsr_preprocess_views)
+int launch_preprocess_views(const GsrFwdArgs& a, int n_views, const GsrViewFront* views, const GeomView* g, cudaStream_t s);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
 // per-view base pointers of a multi-view per-Gaussian backward (kernel parameter; <= GSR_MAX_VIEWS views)
 struct ViewTab {

@@ -178,49 +178,24 @@ struct PreArgs {
 constexpr int PRE_THREADS = 128;
 constexpr int PRE_ROW4 = 13;        // float4 per staged SH row: 12 + 1 padding (odd: conflict-free LDS.128 by row)
 
-// STAGE (SH degree 3 on [P,16,3] storage, 16-byte aligned): the 192-byte SH rows are 60 % of this kernel's traffic.  Read
-// per thread (12 x LDG.128 at a 192-byte lane stride) every load instruction touches 32 different lines and the kernel is
-// bound by the L1's line rate, not by HBM (measured 4.3 TB/s).  Instead the warp copies the 6 KB its 32 Gaussians occupy
-// with fully coalesced 16-byte cp.async into shared memory at the top of the kernel - the copy overlaps the cull /
-// covariance / rect arithmetic and costs no registers - and every visible lane then reads its own row from there.
-// Rows of Gaussians that turn out culled are fetched for nothing (15 % at C3).
-template <bool STAGE>
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreArgs a, CameraArgs ca)
-{
-    __shared__ Camera cam;
-    __shared__ float4 stage[STAGE ? (PRE_THREADS / 32) * 32 * PRE_ROW4 : 1];
-    // blockIdx.y = view of a batched call (gsr_forward_batched): its camera, its slice v * P + idx of the per-view
-    // outputs, its band of tile rows in the stacked image
-    // (the launch's camera arrays and Gaussian parameters start at its first view / its scene; outputs are indexed by the
-    // global view a.view_base + blockIdx.y)
-    const int lview = blockIdx.y;
-    const int view = a.view_base + lview;
-    const int lane = threadIdx.x & 31;
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    float4* const st = stage + (STAGE ? (threadIdx.x >> 5) * 32 * PRE_ROW4 : 0);
-    if (STAGE) {
-        const int wbase = idx - lane;                                   // first Gaussian of this warp
-        const int n4 = max(0, min(32, a.P - wbase)) * 12;               // float4s of the warp's rows
-        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)wbase * 12;
-#pragma unroll
-        for (int i = 0; i < 12; i++) {
-            const int e = i * 32 + lane;
-            if (e < n4) {
-                const int r = e / 12, c = e - r * 12;
-                const uint32_t dst = (uint32_t)__cvta_generic_to_shared(st + r * PRE_ROW4 + c);
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(src + e) : "memory");
-            }
-        }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
-    }
-    ca.view += 16 * lview;
-    if (ca.proj) ca.proj += 16 * lview;
-    if (ca.cam) ca.cam += 3 * lview;
-    load_camera(cam, ca);
-    const bool inb = idx < a.P;
-    if (!STAGE && !inb) return;
-    const size_t oidx = (size_t)view * a.P + idx;
+// where one view's results go (a slice of a batched call's arrays, or a view's own blob)
+struct PreOut {
+    int* radii;
+    SplatRec* rec;
+    uint8_t* clamped;
+    uint32_t* depthkey;
+    ushort4* rect;
+    uint32_t* total;    // sum of tiles touched (R)
+    int* err;           // device flag: prefiltered violated
+};
 
+// One Gaussian under one camera (forward.cu:155-259): cull, covariance, conic, tile rect, colour; writes row `oidx` of the
+// view's outputs.  `band`: the view's band of tile rows in a batched call's stacked image.  The whole warp calls (the
+// staged SH rows were copied by all of its lanes).
+template <bool STAGE>
+__device__ __forceinline__ void preprocess_gaussian(const PreArgs& a, const Camera& cam, const PreOut& o, size_t oidx, int band, int idx,
+                                                    int lane, const float4* st, bool inb)
+{
     SplatRec out;
     out.q0 = make_float4(0.f, 0.f, 0.f, 0.f);
     out.q1 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -268,12 +243,12 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreArgs a, 
                 out.q1 = make_float4(conic.z, a.opac[idx], 0.f, 0.f);
                 out.q2 = make_float4(0.f, p_view.z, __int_as_float((int)my_radius), __uint_as_float(area));
                 radius_out = (int)my_radius;
-                const int yoff = view * cam.gy;
+                const int yoff = band * cam.gy;
                 rect_out = make_ushort4((unsigned short)x0, (unsigned short)(y0 + yoff), (unsigned short)x1, (unsigned short)(y1 + yoff));
             }
         }
     } else if (a.prefiltered) {
-        *a.err = 1;   // reference: printf + __trap (auxiliary.h:156-160); we flag it and report GSR_EINVAL in debug mode
+        *o.err = 1;   // reference: printf + __trap (auxiliary.h:156-160); we flag it and report GSR_EINVAL in debug mode
     }
     }
 
@@ -325,16 +300,109 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreArgs a, 
         out.q1.z = rgb[0]; out.q1.w = rgb[1]; out.q2.x = rgb[2];
     }
     if (!inb) return;
-    a.radii[oidx] = radius_out;
-    a.rec[oidx] = out;
-    a.clamped[oidx] = (uint8_t)clamp_bits;
-    a.depthkey[oidx] = __float_as_uint(out.q2.y);
-    a.rect[oidx] = rect_out;
+    o.radii[oidx] = radius_out;
+    o.rec[oidx] = out;
+    o.clamped[oidx] = (uint8_t)clamp_bits;
+    o.depthkey[oidx] = __float_as_uint(out.q2.y);
+    o.rect[oidx] = rect_out;
     // R = sum of tiles touched: one atomic per warp that has any
     uint32_t tiles = __float_as_uint(out.q2.w);
     const unsigned am = __activemask();
     tiles = __reduce_add_sync(am, tiles);
-    if (tiles && (int)(threadIdx.x & 31) == __ffs(am) - 1) atomicAdd(a.total, tiles);
+    if (tiles && (int)(threadIdx.x & 31) == __ffs(am) - 1) atomicAdd(o.total, tiles);
+}
+
+// STAGE (SH degree 3 on [P,16,3] storage, 16-byte aligned): the 192-byte SH rows are 60 % of this kernel's traffic.  Read
+// per thread (12 x LDG.128 at a 192-byte lane stride) every load instruction touches 32 different lines and the kernel is
+// bound by the L1's line rate, not by HBM (measured 4.3 TB/s).  Instead the warp copies the 6 KB its 32 Gaussians occupy
+// with fully coalesced 16-byte cp.async into shared memory at the top of the kernel - the copy overlaps the cull /
+// covariance / rect arithmetic and costs no registers - and every visible lane then reads its own row from there.
+// Rows of Gaussians that turn out culled are fetched for nothing (15 % at C3).
+template <bool STAGE>
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreArgs a, CameraArgs ca)
+{
+    __shared__ Camera cam;
+    __shared__ float4 stage[STAGE ? (PRE_THREADS / 32) * 32 * PRE_ROW4 : 1];
+    // blockIdx.y = view of a batched call (gsr_forward_batched): its camera, its slice v * P + idx of the per-view
+    // outputs, its band of tile rows in the stacked image
+    // (the launch's camera arrays and Gaussian parameters start at its first view / its scene; outputs are indexed by the
+    // global view a.view_base + blockIdx.y)
+    const int lview = blockIdx.y;
+    const int view = a.view_base + lview;
+    const int lane = threadIdx.x & 31;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    float4* const st = stage + (STAGE ? (threadIdx.x >> 5) * 32 * PRE_ROW4 : 0);
+    if (STAGE) {
+        const int wbase = idx - lane;                                   // first Gaussian of this warp
+        const int n4 = max(0, min(32, a.P - wbase)) * 12;               // float4s of the warp's rows
+        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)wbase * 12;
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane;
+            if (e < n4) {
+                const int r = e / 12, c = e - r * 12;
+                const uint32_t dst = (uint32_t)__cvta_generic_to_shared(st + r * PRE_ROW4 + c);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(src + e) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
+    ca.view += 16 * lview;
+    if (ca.proj) ca.proj += 16 * lview;
+    if (ca.cam) ca.cam += 3 * lview;
+    load_camera(cam, ca);
+    const bool inb = idx < a.P;
+    if (!STAGE && !inb) return;
+    const size_t oidx = (size_t)view * a.P + idx;
+
+    PreOut o;
+    o.radii = a.radii; o.rec = a.rec; o.clamped = a.clamped; o.depthkey = a.depthkey; o.rect = a.rect; o.total = a.total; o.err = a.err;
+    preprocess_gaussian<STAGE>(a, cam, o, oidx, view, idx, lane, st, inb);
+}
+
+// ------------------------------------------------------------------ several views of ONE Gaussian set, parameters read once
+// gsr_preprocess_views: a step that renders V views through single-view calls reads the Gaussian parameters V times - at SH
+// degree 3 that is 236 of the ~300 bytes per Gaussian a view's preprocess moves.  Here a thread keeps its Gaussian (the SH
+// row stays staged in shared memory) and walks the views' cameras; every view's results go to that view's own blob, exactly
+// as preprocess_fwd_kernel writes them (same device function).
+struct PreViews {
+    PreOut out[GSR_MAX_VIEWS];
+    const float* view[GSR_MAX_VIEWS];
+    const float* proj[GSR_MAX_VIEWS];
+    const float* cam[GSR_MAX_VIEWS];
+};
+
+template <bool STAGE>
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_views_kernel(PreArgs a, CameraArgs ca, const __grid_constant__ PreViews pv, int V)
+{
+    __shared__ Camera cams[GSR_MAX_VIEWS];
+    __shared__ float4 stage[STAGE ? (PRE_THREADS / 32) * 32 * PRE_ROW4 : 1];
+    const int lane = threadIdx.x & 31;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    float4* const st = stage + (STAGE ? (threadIdx.x >> 5) * 32 * PRE_ROW4 : 0);
+    if (STAGE) {
+        const int wbase = idx - lane;                                   // first Gaussian of this warp
+        const int n4 = max(0, min(32, a.P - wbase)) * 12;               // float4s of the warp's rows
+        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)wbase * 12;
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            const int e = i * 32 + lane;
+            if (e < n4) {
+                const int r = e / 12, c = e - r * 12;
+                const uint32_t dst = (uint32_t)__cvta_generic_to_shared(st + r * PRE_ROW4 + c);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(src + e) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
+    for (int v = 0; v < V; v++) {
+        CameraArgs cv = ca;
+        cv.view = pv.view[v]; cv.proj = pv.proj[v]; cv.cam = pv.cam[v];
+        load_camera(cams[v], cv);
+    }
+    const bool inb = idx < a.P;
+    if (!STAGE && !inb) return;
+    for (int v = 0; v < V; v++) preprocess_gaussian<STAGE>(a, cams[v], pv.out[v], (size_t)idx, 0, idx, lane, st, inb);
 }
 
 int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, const GeomView& g, cudaStream_t s)
@@ -352,6 +420,28 @@ int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, co
     const bool stage = options().pre_stage && a.shs && !a.colors_precomp && !k.shs_rest && a.M == 16 && a.D == 3 && (((size_t)a.shs) & 15) == 0;
     if (stage) GSR_LAUNCH(preprocess_fwd_kernel<true>, dim3(cdiv(a.P, PRE_THREADS), V), PRE_THREADS, 0, s, k, cam);
     else GSR_LAUNCH(preprocess_fwd_kernel<false>, dim3(cdiv(a.P, PRE_THREADS), V), PRE_THREADS, 0, s, k, cam);
+    return GSR_OK;
+}
+
+int launch_preprocess_views(const GsrFwdArgs& a, int n_views, const GsrViewFront* views, const GeomView* g, cudaStream_t s)
+{
+    const CameraArgs cam = make_camera_args(views[0].viewmatrix, views[0].projmatrix, views[0].cam_pos, a.tan_fovx, a.tan_fovy, a.W, a.H);
+    PreArgs k = {};
+    k.P = a.P; k.D = a.D; k.M = a.M;
+    k.means = a.means3D; k.shs = a.shs; k.shs_rest = (a.shs && a.M > 1) ? a.shs_rest : nullptr; k.colors_pre = nullptr; k.opac = a.opacities;
+    k.scales = a.scales; k.rots = a.rotations; k.cov_pre = nullptr; k.mod = a.scale_modifier;
+    k.prefiltered = a.prefiltered;
+    PreViews pv = {};
+    for (int v = 0; v < n_views; v++) {
+        const GeomScratch sc = carve_geom_scratch(g[v].scratch, a.P);
+        PreOut& o = pv.out[v];
+        o.radii = views[v].radii; o.rec = g[v].rec; o.clamped = g[v].clamped; o.depthkey = sc.depthkey; o.rect = sc.rect;
+        o.total = sc.counters; o.err = reinterpret_cast<int*>(sc.counters + 8);
+        pv.view[v] = views[v].viewmatrix; pv.proj[v] = views[v].projmatrix; pv.cam[v] = views[v].cam_pos;
+    }
+    const bool stage = options().pre_stage && a.shs && !k.shs_rest && a.M == 16 && a.D == 3 && (((size_t)a.shs) & 15) == 0;
+    if (stage) GSR_LAUNCH(preprocess_fwd_views_kernel<true>, cdiv(a.P, PRE_THREADS), PRE_THREADS, 0, s, k, cam, pv, n_views);
+    else GSR_LAUNCH(preprocess_fwd_views_kernel<false>, cdiv(a.P, PRE_THREADS), PRE_THREADS, 0, s, k, cam, pv, n_views);
     return GSR_OK;
 }
 

@@ -63,7 +63,8 @@ forward_core(const torch::Tensor& background, const torch::Tensor& means3D, cons
                           const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
                           const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
                           const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
-                          const bool prefiltered, const bool debug, const torch::Tensor& sh_rest, int64_t front_stream)
+                          const bool prefiltered, const bool debug, const torch::Tensor& sh_rest, int64_t front_stream,
+                          const torch::Tensor* prepared_geom = nullptr, const torch::Tensor* prepared_radii = nullptr)
 {
     if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
@@ -85,8 +86,10 @@ forward_core(const torch::Tensor& background, const torch::Tensor& means3D, cons
     if (front_stream)
         front_guard.reset(new c10::cuda::CUDAStreamGuard(
             c10::cuda::getStreamFromExternal(reinterpret_cast<cudaStream_t>(front_stream), means3D.device().index())));
-    torch::Tensor radii = P == 0 ? torch::zeros({P}, i32) : torch::empty({P}, i32);
-    torch::Tensor geomBuffer = torch::empty({0}, u8), binningBuffer = torch::empty({0}, u8), imgBuffer = torch::empty({0}, u8);
+    const bool prepared = prepared_geom != nullptr && P != 0;
+    torch::Tensor radii = prepared ? *prepared_radii : (P == 0 ? torch::zeros({P}, i32) : torch::empty({P}, i32));
+    torch::Tensor geomBuffer = prepared ? *prepared_geom : torch::empty({0}, u8);
+    torch::Tensor binningBuffer = torch::empty({0}, u8), imgBuffer = torch::empty({0}, u8);
     int rendered = 0;
     if (P != 0) {
         int M = 0;
@@ -105,7 +108,18 @@ forward_core(const torch::Tensor& background, const torch::Tensor& means3D, cons
         a.viewmatrix = vm.ptr(); a.projmatrix = pm.ptr(); a.cam_pos = cam.ptr();
         a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.prefiltered = prefiltered; a.debug = debug;
         a.out_color = out_color.data_ptr<float>(); a.radii = radii.data_ptr<int>();
-        if (front_stream) {
+        if (prepared) {
+            TORCH_CHECK(prepared_geom->is_cuda() && prepared_geom->numel() >= (int64_t)gsr_geom_bytes(P) && prepared_radii->numel() == P,
+                        "prepared view: geometry blob / radii of another size");
+            check(gsr_forward_prepared(&a, geomBuffer.data_ptr(), GsrAlloc{resize_cb, &binningBuffer}, GsrAlloc{resize_cb, &imgBuffer},
+                                       front_stream ? current_stream() : nullptr, reinterpret_cast<gsr_stream_t>(main_stream.stream()),
+                                       &rendered),
+                  "rasterize_gaussians");
+            front_guard.reset();
+            // (the blob and radii may have been allocated under another stream than the one that reads them from here on)
+            for (torch::Tensor* t : {&radii, &geomBuffer, &binningBuffer, &imgBuffer})
+                if (t->numel() > 0) t->record_stream(main_stream);
+        } else if (front_stream) {
             // (torch's current stream is the front stream here: the blobs the callbacks resize belong to it)
             check(gsr_forward_front(&a, GsrAlloc{resize_cb, &geomBuffer}, GsrAlloc{resize_cb, &binningBuffer}, GsrAlloc{resize_cb, &imgBuffer},
                                     current_stream(), reinterpret_cast<gsr_stream_t>(main_stream.stream()), &rendered),
@@ -162,6 +176,64 @@ rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3
     return rasterize_gaussians_split(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                                      projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug,
                                      torch::empty({0}));
+}
+
+// gsr_preprocess_views: the preprocess stage of n views (lists of camera tensors) in one pass over the parameters; returns every
+// view's geometry blob and radii, to be handed to rasterize_gaussians_prepared.  Issued on torch's current stream.
+std::tuple<std::vector<torch::Tensor>, std::vector<torch::Tensor>>
+prepare_views(const torch::Tensor& means3D, const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+              const float scale_modifier, const torch::Tensor& sh, const int degree, const float tan_fovx, const float tan_fovy,
+              const int image_height, const int image_width, const std::vector<torch::Tensor>& viewmatrices,
+              const std::vector<torch::Tensor>& projmatrices, const std::vector<torch::Tensor>& camposs, const bool prefiltered)
+{
+    TORCH_CHECK(means3D.is_cuda() && means3D.ndimension() == 2 && means3D.size(1) == 3, "means3D must be a CUDA tensor (num_points, 3)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = (int)means3D.size(0);
+    const size_t V = viewmatrices.size();
+    TORCH_CHECK(V >= 1 && V <= 16 && projmatrices.size() == V && camposs.size() == V, "prepare_views: 1..16 cameras");
+    TORCH_CHECK(sh.dim() == 3 && sh.size(0) == P, "prepare_views: sh [P,M,3] expected");
+    for (const torch::Tensor* t : {&means3D, &opacity, &scales, &rotations, &sh})
+        TORCH_CHECK(t->is_cuda() && t->is_contiguous() && t->scalar_type() == torch::kFloat32, "prepare_views: contiguous fp32 CUDA parameters");
+    auto i32 = means3D.options().dtype(torch::kInt32);
+    auto u8 = means3D.options().dtype(torch::kByte);
+    std::vector<torch::Tensor> geoms, radii;
+    std::vector<GsrViewFront> vf(V);
+    std::vector<F32> keep;
+    keep.reserve(3 * V);
+    for (size_t v = 0; v < V; v++) {
+        geoms.push_back(torch::empty({(int64_t)gsr_geom_bytes(P)}, u8));
+        radii.push_back(P == 0 ? torch::zeros({P}, i32) : torch::empty({P}, i32));
+        for (const torch::Tensor* t : {&viewmatrices[v], &projmatrices[v], &camposs[v]})
+            TORCH_CHECK(t->is_cuda() && t->is_contiguous() && t->scalar_type() == torch::kFloat32, "prepare_views: contiguous fp32 CUDA cameras");
+        vf[v].viewmatrix = viewmatrices[v].data_ptr<float>(); vf[v].projmatrix = projmatrices[v].data_ptr<float>();
+        vf[v].cam_pos = camposs[v].data_ptr<float>();
+        vf[v].radii = radii[v].data_ptr<int>(); vf[v].geom_blob = geoms[v].data_ptr();
+    }
+    if (P != 0) {
+        GsrFwdArgs a = {};
+        a.P = P; a.D = degree; a.M = (int)sh.size(1); a.W = image_width; a.H = image_height;
+        a.means3D = means3D.data_ptr<float>(); a.shs = sh.data_ptr<float>(); a.opacities = opacity.data_ptr<float>();
+        a.scales = scales.data_ptr<float>(); a.scale_modifier = scale_modifier; a.rotations = rotations.data_ptr<float>();
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.prefiltered = prefiltered;
+        check(gsr_preprocess_views(&a, (int)V, vf.data(), current_stream()), "prepare_views");
+    }
+    return std::make_tuple(geoms, radii);
+}
+
+// rasterize_gaussians on a view prepare_views has preprocessed (gsr_forward_prepared); front_stream as in rasterize_gaussians_front
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_gaussians_prepared(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                             const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                             const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                             const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+                             const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                             const bool prefiltered, const bool debug, const torch::Tensor& geom, const torch::Tensor& radii,
+                             int64_t front_stream)
+{
+    TORCH_CHECK(colors.numel() == 0 && cov3D_precomp.numel() == 0, "prepared views take SH colours and scale / rotation covariances");
+    return forward_core(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                        tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug, torch::empty({0}),
+                        front_stream, &geom, &radii);
 }
 
 // returns the reference's eight gradients plus dL_dsh_rest (empty unless sh_rest is given)
@@ -814,6 +886,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
     m.def("rasterize_gaussians", &rasterize_gaussians, nogil());
     m.def("rasterize_gaussians_split", &rasterize_gaussians_split, nogil());
     m.def("rasterize_gaussians_front", &rasterize_gaussians_front, nogil());
+    m.def("prepare_views", &prepare_views, nogil());
+    m.def("rasterize_gaussians_prepared", &rasterize_gaussians_prepared, nogil());
     m.def("rasterize_gaussians_backward_split", &rasterize_gaussians_backward_split, nogil());
     m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward, nogil());
     m.def("rasterize_gaussians_backward_into", &rasterize_gaussians_backward_into, nogil());

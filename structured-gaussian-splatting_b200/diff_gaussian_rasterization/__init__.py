@@ -180,6 +180,61 @@ def front_stream(device=None, high_priority=True):
 _FRONT_STREAMS = {}
 
 
+# ---- extension (off by default): the preprocess stage of a step's views in ONE pass over the parameters
+# (gsr_preprocess_views).  A view's preprocess moves ~300 bytes per Gaussian, 236 of them the parameters (192 the SH row);
+# a step that renders V views of the same Gaussians reads them V times.  prepare_views() runs that stage for up to 16
+# cameras at once - each thread keeps its Gaussian and walks the cameras - and parks every view's state; the following
+# GaussianRasterizer calls with those cameras find it and run only depth order, tile split and blending.  Results are those
+# of the plain call (the same device function computes them).
+# A parked view is matched by the IDENTITY and VERSION of the tensors it was prepared from (parameters and camera): a
+# parameter updated in place, a camera buffer rewritten, another raster setting - and the render takes the plain path.
+_PREPARED = {}
+
+
+def _tensor_key(t):
+    return (t.data_ptr(), t._version, tuple(t.shape))
+
+
+def _prepared_key(means3D, opacities, sh, scales, rotations, rs):
+    return (_tensor_key(means3D), _tensor_key(opacities), _tensor_key(sh), _tensor_key(scales), _tensor_key(rotations),
+            _tensor_key(rs.viewmatrix), _tensor_key(rs.projmatrix), _tensor_key(rs.campos), int(rs.image_height), int(rs.image_width),
+            float(rs.tanfovx), float(rs.tanfovy), int(rs.sh_degree), float(rs.scale_modifier), bool(rs.prefiltered))
+
+
+def prepare_views(means3D, opacities, shs, scales, rotations, settings):
+    """Preprocesses the views of `settings` (a list of GaussianRasterizationSettings sharing image size, field of view, SH
+    degree and scale modifier) in one pass over the parameters; the renders that follow with exactly these tensors and
+    settings use the result.  Runs on the front stream when one is set (set_front_stream), else on the current stream.
+    Views prepared earlier and never rendered are dropped.  Returns the number of views prepared."""
+    _PREPARED.clear()
+    settings = list(settings)
+    if not settings or not means3D.is_cuda or means3D.numel() == 0 or shs is None or shs.dim() != 3:
+        return 0
+    first = settings[0]
+    same = lambda r: (r.image_height, r.image_width, r.tanfovx, r.tanfovy, r.sh_degree, r.scale_modifier, r.prefiltered)
+    if any(same(r) != same(first) for r in settings) or any(r.debug for r in settings):
+        return 0
+    tensors = [means3D, opacities, shs, scales, rotations] + [t for r in settings for t in (r.viewmatrix, r.projmatrix, r.campos)]
+    if not all(t.is_cuda and t.is_contiguous() and t.dtype == torch.float32 for t in tensors):
+        return 0
+    front = _FRONT if (_FRONT is not None and _FRONT.device == means3D.device) else None
+    stream = front if front is not None else torch.cuda.current_stream(means3D.device)
+    n = 0
+    with torch.no_grad(), torch.cuda.stream(stream):
+        for base in range(0, len(settings), 16):
+            part = settings[base:base + 16]
+            geoms, radii = _C.prepare_views(means3D, opacities, scales, rotations, first.scale_modifier, shs, first.sh_degree,
+                                            first.tanfovx, first.tanfovy, first.image_height, first.image_width,
+                                            [r.viewmatrix for r in part], [r.projmatrix for r in part], [r.campos for r in part],
+                                            bool(first.prefiltered))
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            for r, g, rad in zip(part, geoms, radii):
+                _PREPARED[_prepared_key(means3D, opacities, shs, scales, rotations, r)] = (g, rad, ev)
+                n += 1
+    return n
+
+
 class GaussianRasterizationSettings(NamedTuple):
     image_height: int
     image_width: int
@@ -204,7 +259,16 @@ class _RasterizeGaussians(torch.autograd.Function):
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree,
                 rs.campos, rs.prefiltered, rs.debug)
         front = _FRONT
-        if front is not None and means3D.is_cuda and front.device == means3D.device and not rs.debug:
+        use_front = front is not None and means3D.is_cuda and front.device == means3D.device and not rs.debug
+        parked = None
+        if _PREPARED and means3D.is_cuda and colors_precomp.numel() == 0 and cov3Ds_precomp.numel() == 0 and sh.dim() == 3:
+            parked = _PREPARED.pop(_prepared_key(means3D, opacities, sh, scales, rotations, rs), None)
+        if parked is not None:
+            geom, rad, ev = parked
+            (front if use_front else torch.cuda.current_stream(means3D.device)).wait_event(ev)
+            num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = _C.rasterize_gaussians_prepared(
+                *args, geom, rad, front.cuda_stream if use_front else 0)
+        elif use_front:
             num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = _C.rasterize_gaussians_front(*args, front.cuda_stream)
         else:
             num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = _call_with_snapshot(

@@ -125,18 +125,33 @@ def make_leaf_params(scene: Dict[str, torch.Tensor], device) -> Dict[str, torch.
     return {k: scene[k].to(device).clone().requires_grad_(True) for k in PARAM_ORDER if k in scene}
 
 
-def render_view(rasterizer_mod, params, cam, bg, sh_degree: int, scale_modifier: float = 1.0):
-    """One forward through the drop-in API, exactly as gaussian_renderer.render() calls it
-    (gaussian_renderer/__init__.py:36-93).  Returns (color[3,H,W], radii, means2D grad sink)."""
-    rs = rasterizer_mod.GaussianRasterizationSettings(
+def view_settings(rasterizer_mod, cam, bg, sh_degree: int, scale_modifier: float = 1.0):
+    """GaussianRasterizationSettings of one camera, as gaussian_renderer.render() builds them (gaussian_renderer/__init__.py:36-50)."""
+    return rasterizer_mod.GaussianRasterizationSettings(
         image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=bg,
         scale_modifier=scale_modifier, viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, sh_degree=sh_degree,
         campos=cam.campos, prefiltered=False, debug=False)
+
+
+def render_view(rasterizer_mod, params, cam, bg, sh_degree: int, scale_modifier: float = 1.0):
+    """One forward through the drop-in API, exactly as gaussian_renderer.render() calls it
+    (gaussian_renderer/__init__.py:36-93).  Returns (color[3,H,W], radii, means2D grad sink)."""
+    rs = view_settings(rasterizer_mod, cam, bg, sh_degree, scale_modifier)
     means2D = torch.zeros_like(params["means3D"], requires_grad=True)
     color, radii = rasterizer_mod.GaussianRasterizer(rs)(
         means3D=params["means3D"], means2D=means2D, opacities=params["opacities"], shs=params["shs"],
         scales=params["scales"], rotations=params["rotations"])
     return color, radii, means2D
+
+
+def prepare_step_views(rasterizer_mod, params, cams: Sequence, bg, sh_degree: int, view_ids: Iterable[int]) -> int:
+    """The preprocess stage of the step's views in one pass over the parameters (diff_gaussian_rasterization.prepare_views /
+    gsr_preprocess_views): the render_view calls that follow with these cameras skip it.  Returns the number of views prepared
+    (0 where the rasterizer module has no such entry point, e.g. the reference package)."""
+    if not hasattr(rasterizer_mod, "prepare_views"):
+        return 0
+    return rasterizer_mod.prepare_views(params["means3D"], params["opacities"], params["shs"], params["scales"], params["rotations"],
+                                        [view_settings(rasterizer_mod, cams[k], bg, sh_degree) for k in view_ids])
 
 
 _STREAMS: List["torch.cuda.Stream"] = []
@@ -199,7 +214,7 @@ def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
 
 def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
                    loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None,
-                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False):
+                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False, prepare: bool = False):
     """The step in DEFERRED form (diff_gaussian_rasterization.set_grad_mode("deferred")): every view runs its forward and its
     blending backward; the per-Gaussian backward of all the rank's views then runs once (parameters read once, every gradient
     row written once: 0.2 instead of 0.4 ms per view at C3), in `overlap_chunks` ranges of Gaussians when > 0, the all-reduce
@@ -208,7 +223,9 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
     pipeline=True: the forward of view i+1 is issued BEFORE the backward of view i, and the front of every forward
     (preprocess, depth order, tile split: latency- and bandwidth-bound) goes to a high-priority stream of its own
     (set_front_stream / gsr_forward_front), so it runs inside the issue-bound blending kernels of the views around it.
-    Same results; two views' state is alive at a time."""
+    Same results; two views' state is alive at a time.
+    prepare=True: the preprocess stage of all the step's views runs first, in one pass over the parameters
+    (prepare_step_views): 236 of the ~300 bytes per Gaussian a view's preprocess moves are read once per step."""
     total = None
     views = list(view_ids)
     prev = rasterizer_mod.set_grad_mode("deferred")
@@ -216,6 +233,8 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
              and params[flat.names[0]].is_cuda)
     prev_front = rasterizer_mod.set_front_stream(rasterizer_mod.front_stream(params[flat.names[0]].device)) if piped else None
     try:
+        if prepare and views:
+            prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views)
         if piped:
             ahead = render_view(rasterizer_mod, params, cams[views[0]], bg, sh_degree)
             for i, k in enumerate(views):

@@ -244,6 +244,8 @@ def test_cabi_exports_every_declared_symbol():
     assert lib.gsr_forward(None, None, None, None, None, None) == -1
     assert lib.gsr_backward(None, None) == -1
     assert lib.gsr_forward_front(None, None, None, None, None, None, None) == -1
+    assert lib.gsr_preprocess_views(None, 1, None, None) == -1
+    assert lib.gsr_forward_prepared(None, None, None, None, None, None, None) == -6       # GSR_EBLOB: no prepared blob
     assert lib.gsr_backward_staged(None, 3, 0, -1, None) == -1
     assert lib.gsr_backward_views(None, 1, None, 0, -1, None) == -1
     # the product library carries no comparison arms (they live in the test-only libgsr_b200_arms.so) ...
