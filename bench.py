@@ -559,6 +559,29 @@ def main():
             ev.record(copy_stream)
         pending[k] = (slot, ev)
 
+    # cameras of a whole step (prepared steps): [views, 35] floats, a ring of three buffers
+    cam_ring = [torch.empty(vps, cam_host[0].numel(), device=dev) for _ in range(3)]
+    cam_pending = {}
+
+    def prefetch_cams(step):
+        buf = cam_ring[step % 3]
+        with torch.cuda.stream(copy_stream):
+            # (the buffer's previous user is two steps back: its renders were queued before the loss read-back of that step)
+            for j, k in enumerate(my_views(step)):
+                buf[j].copy_(cam_host[k], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        cam_pending[step] = (buf, ev)
+
+    def take_cams(step):
+        if step not in cam_pending:
+            prefetch_cams(step)
+        buf, ev = cam_pending.pop(step)
+        torch.cuda.current_stream().wait_event(ev)
+        if use_pipeline[0]:
+            front_st().wait_event(ev)
+        return buf
+
     def take(k):
         if k not in pending:
             prefetch(k)
@@ -614,13 +637,23 @@ def main():
             piped = use_pipeline[0] and len(views) > 1
             prev = dgr.set_grad_mode("deferred")
             prev_front = dgr.set_front_stream(front_st()) if piped else None
+            step_cams = None
+            if use_prepare[0]:
+                # the step's cameras (a trainer samples them before the step): one small copy per view from pinned host
+                # memory on the copy stream, a step ahead; the views' preprocess then runs in one pass over the parameters
+                cmb = take_cams(step)
+                prefetch_cams(step + 1)
+                step_cams = [synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cmb[j, :16].view(4, 4),
+                                          cmb[j, 16:32].view(4, 4), cmb[j, 32:35]) for j, k in enumerate(views)]
+                dp.prepare_step_views(dgr, params, step_cams, bg, spec.D, range(len(views)))
 
             def fwd(i):
                 k = views[i]
                 tgt, cm, slot = take(k)
                 nxt = views[i + 1] if i + 1 < len(views) else my_views(step + 1)[0]
                 prefetch(nxt)                              # next view's inputs travel while this one renders
-                cam = synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cm[:16].view(4, 4), cm[16:32].view(4, 4), cm[32:35])
+                cam = step_cams[i] if step_cams is not None else synth.Camera(
+                    spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cm[:16].view(4, 4), cm[16:32].view(4, 4), cm[32:35])
                 color, radii, _ = dp.render_view(dgr, params, cam, bg, spec.D)
                 return color, tgt, slot
 
@@ -745,7 +778,8 @@ def main():
         for i in range(max(3, args.warmup)):      # untimed: allocator, pinned buffers and NCCL settle
             step_e2e(i)
         ms_e2e = timed(step_e2e, args.steps, args.warmup)
-        e2e = {"value": views_total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_view * vps,
+        e2e = {"value": views_total / (ms_e2e * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": h2d_view * vps + (cam_host[0].numel() * 4 * vps if (use_prepare[0] and not args.batched) else 0),
                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps,
                "note": "per view: 24.9 MB target image + camera from pinned host memory on a copy stream one view ahead (ring of "
                        "four preallocated landing buffers); loss read once per step"}
@@ -952,9 +986,9 @@ def main():
         def step_c5(step):
             run_views(params5, flat5, my_views(step), None, overlap)
 
-        for i in range(2):
+        for i in range(4):                           # (the allocator's pool of stream-shared blobs settles within three steps)
             step_c5(i)
-        ms5 = timed(step_c5, steps5, 2)
+        ms5 = timed(step_c5, steps5, 4)
         R5 = probe_R(C, params5, cams[my_views(0)[0]], bg, spec5.D)
         c5 = {"workload": "C5: 6M Gaussians, SH degree 3, 1920x1080, %d views per step (%d per GPU), view-sharded over %d GPU(s), fwd+bwd via "
                           "GaussianRasterizer API + gradient all-reduce" % (vps * world, vps, world),
