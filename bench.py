@@ -69,6 +69,8 @@ def parse_args():
     ap.add_argument("--prepare", type=int, default=1,
                     help="deferred steps: 1 = the preprocess stage of the step's views runs in one pass over the parameters "
                          "(prepare_views / gsr_preprocess_views) before the per-view calls; 0 = every call preprocesses its view")
+    ap.add_argument("--views-of-rank", default="", help="diagnostic (N = 1): r/w = render the cameras rank r of w ranks would get")
+    ap.add_argument("--nccl-priority", default="high", choices=["high", "default"], help="priority of NCCL's stream (N > 1)")
     ap.add_argument("--front-priority", default="high", choices=["high", "default"],
                     help="priority of the front stream of --pipeline 1 (A/B: `default` = same priority as the rendering stream)")
     ap.add_argument("--no-extras", action="store_true",
@@ -390,7 +392,12 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL's kernels on a high-priority stream: a range's all-reduce is issued while the next range of the per-Gaussian
+        # backward fills every SM, and an NCCL CTA needs most of an SM to itself - at default priority it waits for the tail
+        pg_options = None
+        if args.nccl_priority == "high":
+            pg_options = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+        dist.init_process_group("nccl", device_id=dev, pg_options=pg_options)
     import diff_gaussian_rasterization as dgr
     from gsr_b200 import dp, losses
     C = dgr._C
@@ -408,9 +415,14 @@ def main():
     N = spec.W * spec.H
     tiles = ((spec.W + 15) // 16) * ((spec.H + 15) // 16)
 
+    vr, vw = rank, world
+    if args.views_of_rank:
+        # (diagnostic, N = 1: render the camera set rank r of w would get - how uneven are the ranks' loads?)
+        vr, vw = (int(x) for x in args.views_of_rank.split("/"))
+
     def my_views(step):
         # view k of the step goes to rank k mod world; camera ids walk round the ring
-        return [(step * vps * world + j * world + rank) % V for j in range(vps)]
+        return [(step * vps * vw + j * vw + vr) % V for j in range(vps)]
 
     stats = {"R": 0, "Pv": 0, "views": 0}
     if args.plain_autograd:
