@@ -394,10 +394,8 @@ def main():
     if world > 1:
         # NCCL's kernels on a high-priority stream: a range's all-reduce is issued while the next range of the per-Gaussian
         # backward fills every SM, and an NCCL CTA needs most of an SM to itself - at default priority it waits for the tail
-        pg_options = None
-        if args.nccl_priority == "high":
-            pg_options = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
-        dist.init_process_group("nccl", device_id=dev, pg_options=pg_options)
+        from gsr_b200 import dp as _dp
+        _dp.init_nccl(dev, high_priority=args.nccl_priority == "high")
     import diff_gaussian_rasterization as dgr
     from gsr_b200 import dp, losses
     C = dgr._C

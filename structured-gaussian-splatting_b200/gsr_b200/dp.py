@@ -29,6 +29,15 @@ import torch.distributed as dist
 PARAM_ORDER = ("means3D", "scales", "rotations", "opacities", "shs")
 
 
+def init_nccl(device, high_priority: bool = True, **kw):
+    """dist.init_process_group("nccl") with NCCL's kernels on a HIGH-PRIORITY stream.  The overlapped steps below issue the
+    all-reduce of a range of Gaussians while the next range of the per-Gaussian backward fills every SM; an NCCL thread
+    block needs most of an SM to itself, so at default priority it only gets one in the compute kernels' tail (measured at
+    C3, N = 2: 17.85 -> 17.32 ms per step).  Extra keyword arguments go to init_process_group."""
+    opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True) if high_priority else None
+    return dist.init_process_group("nccl", device_id=device, pg_options=opts, **kw)
+
+
 def shard_views(n_views: int, rank: int, world: int) -> List[int]:
     """Views owned by `rank`: k with k mod world == rank."""
     return [k for k in range(n_views) if k % world == rank]

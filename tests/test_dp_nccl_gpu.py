@@ -23,7 +23,7 @@ def _worker(rank, world, port, q):
         from gsr_b200 import dp
         torch.cuda.set_device(rank)
         dev = torch.device("cuda", rank)
-        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world, device_id=dev)
+        dp.init_nccl(dev, init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)      # (NCCL on a high-priority stream)
         sc, _, bg = util.small_scene(P, D, W, H, 111)
         bg = bg.to(dev)
         cams = [synth.make_camera(k, 9, W, H, 3.0, 50.0).to(dev) for k in range(V)]
@@ -31,7 +31,8 @@ def _worker(rank, world, port, q):
         loss_fn = lambda color, k: (color * go[k]).sum()
         res = {}
         for name, kw in (("plain", dict()), ("overlap3", dict(overlap_chunks=3)), ("overlap5_registered", dict(overlap_chunks=5)),
-                         ("deferred", dict()), ("deferred_overlap4_registered", dict(overlap_chunks=4))):
+                         ("deferred", dict()), ("deferred_overlap4_registered", dict(overlap_chunks=4)),
+                         ("deferred_piped_prepared_overlap3", dict(overlap_chunks=3, pipeline=True, prepare=True))):
             params = dp.make_leaf_params(sc, dev)
             flat = dp.FlatGrads(params, nccl_registered=name.endswith("registered"))
             flat.flat.fill_(float("nan"))
@@ -70,9 +71,9 @@ def test_dp_step_nccl_world2_equals_single_gpu():
         assert err is None, "rank %d failed:\n%s" % (rank, err)
     ref_flat, ref_total = out[0][2]
     assert np.isfinite(ref_flat).all()
-    for name in ("plain", "overlap3", "overlap5_registered", "deferred", "deferred_overlap4_registered"):
+    for name in ("plain", "overlap3", "overlap5_registered", "deferred", "deferred_overlap4_registered", "deferred_piped_prepared_overlap3"):
         f0, t0, _ = out[0][1][name]
         f1, t1, _ = out[1][1][name]
         assert np.array_equal(f0, f1), name + ": replicas must hold identical sums"
-        assert util.rel_err(f0, ref_flat) <= 1e-5, name
+        assert util.rel_err(f0, ref_flat) <= (1e-4 if "piped" in name else 1e-5), name       # (atomics' order moves with concurrency)
         assert abs((t0 + t1) - ref_total) <= 1e-5 * max(1.0, abs(ref_total)), name
