@@ -202,6 +202,9 @@ typedef struct GsrBwdArgs {
     /* split SH storage as in GsrFwdArgs (ABI 2): dL_dsh is then [P,1,3] and dL_dsh_rest [P,M-1,3] */
     const float* shs_rest;
     float*       dL_dsh_rest;
+    /* ABI 5: non-zero = `accum` already holds zeros (the caller cleared it off the critical path, e.g. on the front stream
+       of gsr_forward_front while the forward's blending ran); 0 = the blending backward clears it itself (144 MB at C3). */
+    int          accum_zeroed;
 } GsrBwdArgs;
 
 #define GSR_ACC_MEAN3D   1u

@@ -397,7 +397,7 @@ static int backward_impl(const GsrBwdArgs* a, int V, int S, gsr_stream_t stream_
     int rc;
     if (stages & 1) {
         stage_begin(4, s);
-        GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(Pv), s));
+        if (!a->accum_zeroed) GSR_CUDA(cudaMemsetAsync(accum, 0, gsr_bwd_accum_bytes(Pv), s));
         if ((rc = launch_blend_backward(a->R, a->W, a->H, V, a->background, g, b, im, a->dL_dpix, accum, s))) return rc;
         stage_end(4, s);
         GSR_STAGE(a->debug, s, "blend_backward");

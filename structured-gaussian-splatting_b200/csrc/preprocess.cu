@@ -192,9 +192,16 @@ struct PreOut {
 // One Gaussian under one camera (forward.cu:155-259): cull, covariance, conic, tile rect, colour; writes row `oidx` of the
 // view's outputs.  `band`: the view's band of tile rows in a batched call's stacked image.  The whole warp calls (the
 // staged SH rows were copied by all of its lanes).
-template <bool STAGE>
+// what does not depend on the camera, loaded / computed once when a thread walks several views (PRE)
+struct GaussIn {
+    float3 p;
+    float c6[6];
+    float opac;
+};
+
+template <bool STAGE, bool PRE>
 __device__ __forceinline__ void preprocess_gaussian(const PreArgs& a, const Camera& cam, const PreOut& o, size_t oidx, int band, int idx,
-                                                    int lane, const float4* st, bool inb)
+                                                    int lane, const float4* st, bool inb, const GaussIn& gi)
 {
     SplatRec out;
     out.q0 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -207,7 +214,7 @@ __device__ __forceinline__ void preprocess_gaussian(const PreArgs& a, const Came
     float3 p = {0.f, 0.f, 0.f};
 
     if (inb) {
-    p = make_float3(a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]);
+    p = PRE ? gi.p : make_float3(a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]);
     const float3 p_view = xform4x3(p, cam.view);
     if (!(p_view.z <= 0.2f)) {   // near cull only (auxiliary.h:154); NaN passes like the reference
         const float4 p_hom = xform4x4(p, cam.proj);
@@ -215,7 +222,10 @@ __device__ __forceinline__ void preprocess_gaussian(const PreArgs& a, const Came
         const float projx = p_hom.x * p_w, projy = p_hom.y * p_w;
 
         float c6[6];
-        if (a.cov_pre != nullptr) {
+        if (PRE) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) c6[k] = gi.c6[k];
+        } else if (a.cov_pre != nullptr) {
 #pragma unroll
             for (int k = 0; k < 6; k++) c6[k] = a.cov_pre[6 * (size_t)idx + k];
         } else {
@@ -240,7 +250,7 @@ __device__ __forceinline__ void preprocess_gaussian(const PreArgs& a, const Came
                 vis = true;
                 // (the colour is filled in below)
                 out.q0 = make_float4(px, py, conic.x, conic.y);
-                out.q1 = make_float4(conic.z, a.opac[idx], 0.f, 0.f);
+                out.q1 = make_float4(conic.z, PRE ? gi.opac : a.opac[idx], 0.f, 0.f);
                 out.q2 = make_float4(0.f, p_view.z, __int_as_float((int)my_radius), __uint_as_float(area));
                 radius_out = (int)my_radius;
                 const int yoff = band * cam.gy;
@@ -357,7 +367,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreArgs a, 
 
     PreOut o;
     o.radii = a.radii; o.rec = a.rec; o.clamped = a.clamped; o.depthkey = a.depthkey; o.rect = a.rect; o.total = a.total; o.err = a.err;
-    preprocess_gaussian<STAGE>(a, cam, o, oidx, view, idx, lane, st, inb);
+    preprocess_gaussian<STAGE, false>(a, cam, o, oidx, view, idx, lane, st, inb, GaussIn{});
 }
 
 // ------------------------------------------------------------------ several views of ONE Gaussian set, parameters read once
@@ -402,7 +412,15 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_views_kernel(PreAr
     }
     const bool inb = idx < a.P;
     if (!STAGE && !inb) return;
-    for (int v = 0; v < V; v++) preprocess_gaussian<STAGE>(a, cams[v], pv.out[v], (size_t)idx, 0, idx, lane, st, inb);
+    GaussIn gi = {};
+    if (inb) {
+        gi.p = make_float3(a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]);
+        const float3 s = {a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]};
+        const float4 q = {a.rots[4 * idx], a.rots[4 * idx + 1], a.rots[4 * idx + 2], a.rots[4 * idx + 3]};
+        cov3d_from_scale_rot(s, a.mod, q, gi.c6);
+        gi.opac = a.opac[idx];
+    }
+    for (int v = 0; v < V; v++) preprocess_gaussian<STAGE, true>(a, cams[v], pv.out[v], (size_t)idx, 0, idx, lane, st, inb, gi);
 }
 
 int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, const GeomView& g, cudaStream_t s)

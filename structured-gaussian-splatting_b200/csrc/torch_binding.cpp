@@ -428,14 +428,19 @@ torch::Tensor rasterize_gaussians_backward_blend(const torch::Tensor& background
                                                  const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix, const float tan_fovx,
                                                  const float tan_fovy, const torch::Tensor& dL_dout_color, const int M, const int degree,
                                                  const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
-                                                 const torch::Tensor& imageBuffer, const bool debug)
+                                                 const torch::Tensor& imageBuffer, const bool debug, const torch::Tensor& zeroed_accum)
 {
+    // zeroed_accum non-empty: a [P,12] fp32 buffer of zeros the caller cleared off the critical path (GsrBwdArgs.accum_zeroed)
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor");
     const c10::cuda::CUDAGuard guard(means3D.device());
     const int P = (int)means3D.size(0);
     const int H = (int)dL_dout_color.size(1), W = (int)dL_dout_color.size(2);
     auto f32 = means3D.options().dtype(torch::kFloat32);
-    torch::Tensor accum = torch::empty({(long long)P, 12}, f32);
+    const bool given = zeroed_accum.numel() != 0;
+    if (given)
+        TORCH_CHECK(zeroed_accum.is_cuda() && zeroed_accum.is_contiguous() && zeroed_accum.scalar_type() == torch::kFloat32 &&
+                    zeroed_accum.numel() == (int64_t)P * 12, "zeroed_accum: contiguous fp32 CUDA [P,12] expected");
+    torch::Tensor accum = given ? zeroed_accum : torch::empty({(long long)P, 12}, f32);
     if (P != 0) {
         F32 bg(background), m3(means3D), vm(viewmatrix), pm(projmatrix), dpix(dL_dout_color);
         torch::Tensor radii_c = radii.contiguous();
@@ -447,6 +452,7 @@ torch::Tensor rasterize_gaussians_backward_blend(const torch::Tensor& background
         a.geom_blob = geomBuffer.data_ptr(); a.binning_blob = binningBuffer.data_ptr(); a.img_blob = imageBuffer.data_ptr();
         a.dL_dpix = dpix.ptr();
         a.accum = accum.data_ptr();
+        a.accum_zeroed = given ? 1 : 0;
         a.debug = debug;
         check(gsr_backward_staged(&a, 1, 0, 0, current_stream()), "rasterize_gaussians_backward_blend");
     }

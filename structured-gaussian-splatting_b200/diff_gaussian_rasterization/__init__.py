@@ -8,6 +8,7 @@ Public surface mirrors the reference package
   _RasterizeGaussians            (:44-155)   autograd.Function, same argument / gradient order
 so gaussian_renderer/__init__.py, train.py, train_lgm.py and render.py call it unchanged.
 """
+import os
 import threading
 import weakref
 from typing import NamedTuple
@@ -149,6 +150,7 @@ def set_chunk_hook(hook):
 # at the moment of the call (so: call it after the optimizer step, before the first render of the step); inputs produced
 # later on another stream (a camera copied in by a loader) are the caller's to order: front.wait_event(...).
 _FRONT = None                    # torch.cuda.Stream or None
+_FRONT_ZERO_ACCUM = os.environ.get("GSR_FRONT_ZERO_ACCUM", "1") != "0"
 
 
 def set_front_stream(stream):
@@ -260,6 +262,14 @@ class _RasterizeGaussians(torch.autograd.Function):
                 rs.campos, rs.prefiltered, rs.debug)
         front = _FRONT
         use_front = front is not None and means3D.is_cuda and front.device == means3D.device and not rs.debug
+        # deferred steps with a front stream: the accumulator rows the blending backward adds into are cleared on the front
+        # stream, ahead of the front's kernels, instead of in front of the blending backward (144 MB at C3)
+        ctx.zeroed_accum = None
+        if (_FRONT_ZERO_ACCUM and use_front and _GRAD_MODE == "deferred" and getattr(_TLS, "grad_enabled", False)
+                and means3D.shape[0] > 0):
+            with torch.cuda.stream(front):
+                ctx.zeroed_accum = torch.zeros((means3D.shape[0], 12), dtype=torch.float32, device=means3D.device)
+            ctx.zeroed_accum.record_stream(torch.cuda.current_stream(means3D.device))
         parked = None
         if _PREPARED and means3D.is_cuda and colors_precomp.numel() == 0 and cov3Ds_precomp.numel() == 0 and sh.dim() == 3:
             parked = _PREPARED.pop(_prepared_key(means3D, opacities, sh, scales, rotations, rs), None)
@@ -310,7 +320,9 @@ class _RasterizeGaussians(torch.autograd.Function):
             # the blending backward now, the per-Gaussian backward with the other pending views in flush_deferred()
             accum = _C.rasterize_gaussians_backward_blend(rs.bg, means3D, radii, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                                                           grad_out_color, int(sh.shape[1]), rs.sh_degree, geomBuffer, ctx.num_rendered,
-                                                          binningBuffer, imgBuffer, rs.debug)
+                                                          binningBuffer, imgBuffer, rs.debug,
+                                                          ctx.zeroed_accum if ctx.zeroed_accum is not None else torch.Tensor([]))
+            ctx.zeroed_accum = None
             _DEFERRED.append(dict(accum=accum, geom=geomBuffer, radii=radii, viewmatrix=rs.viewmatrix, projmatrix=rs.projmatrix,
                                   campos=rs.campos, means2D=ctx.means2D_ref, leaves=ctx.grad_leaves,
                                   key=(rs.image_height, rs.image_width, rs.tanfovx, rs.tanfovy, rs.sh_degree, rs.scale_modifier)))
