@@ -183,7 +183,8 @@ int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const
 // words of control state, zeroed by the call unless ctl_zeroed
 size_t radix_ctl_words(uint32_t n);
 int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n,
-                          uint32_t* ctl, bool ctl_zeroed, cudaStream_t s, uint32_t val_base = 0);   // values = val_base + index
+                          uint32_t* ctl, bool ctl_zeroed, cudaStream_t s, uint32_t val_base = 0,     // values = val_base + index
+                          int shape = 0);                                                           // block shape, see radix_pass
 
 // blend.cu
 size_t blend_plane_words(long long R, int W, int H);
@@ -209,7 +210,8 @@ struct Options {
     int sh_split = 1;           // dedicated M = 16 SH backward kernel
     int pre_stage = 1;          // preprocess moves the SH rows of a warp's 32 Gaussians through shared memory (coalesced cp.async)
     int radix_split = 1;        // block shape of the tile-split radix passes: 0 = 512 threads x 8 items, 1 = 256 x 16
-    int radix_depth = 0;        // same for the depth-sort passes
+    int radix_depth = 1;        // same for the depth-sort passes (alone 0.150 vs 0.155 ms for shape 0 / 1; next to the blending
+                                // kernels of a pipelined step the smaller blocks find room sooner: 2.042 -> 2.021 ms per view)
     int depth_seg_items = -1;   // >= 0: batched calls sort the depth keys in runs of whole views (comparison arm)
     // comparison arms: honoured only when the test-only library libgsr_b200_arms.so is loaded (else GSR_EINVAL)
     int blend_arm = 0;          // 1: plain blending kernels (no culling)   2: forward staging through cp.async.bulk + mbarrier

@@ -236,6 +236,19 @@ static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t
     // R-sized tile-split passes gain from four independent blocks per SM instead of two (0.299 -> 0.260 ms for the stage:
     // a block stalled in its look-back or at a barrier leaves three others issuing), the P-sized depth passes do not
     // (0.148 vs 0.151 ms: they are bound by the look-back chain itself).
+    if (shape == 2) {
+        // 256 threads x 8 items: 2048 items per block, twice as many (shorter-lived) blocks, eight resident per SM
+#define GSR_PASS_C(B)                                                                                                    \
+    case B:                                                                                                              \
+        GSR_LAUNCH((radix_onesweep_kernel<B, 256, 8>), cdiv(n, 2048), 256, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, ghist, \
+                   status, ticket, val_base);                                                                            \
+        return GSR_OK;
+        switch (bits) {
+            GSR_PASS_C(1) GSR_PASS_C(2) GSR_PASS_C(3) GSR_PASS_C(4) GSR_PASS_C(5) GSR_PASS_C(6) GSR_PASS_C(7) GSR_PASS_C(8)
+        default: return GSR_EINVAL;
+        }
+#undef GSR_PASS_C
+    }
     const int nblocks = cdiv(n, RS_TILE);
     if (shape == 1) {
 #define GSR_PASS_B(B)                                                                                                    \
@@ -266,14 +279,18 @@ static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t
 // K0, K1, V0: n-word ping-pong buffers; result values land in vals_out (keys are not kept).
 // ctl: radix_ctl_words(n) words (digit histograms, tickets, look-back status), zeroed here.
 size_t radix_ctl_words(uint32_t n) { return 4 * RS_NB + 64 + (size_t)4 * RS_NB * cdiv(n > 0 ? n : 1, RS_TILE); }
+// ... for any block shape (the smallest block takes 2048 items)
+static size_t radix_ctl_words_any(uint32_t n) { return 4 * RS_NB + 64 + (size_t)4 * RS_NB * cdiv(n > 0 ? n : 1, 2048); }
 int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n,
-                          uint32_t* ctl, bool ctl_zeroed, cudaStream_t s, uint32_t val_base)
+                          uint32_t* ctl, bool ctl_zeroed, cudaStream_t s, uint32_t val_base, int shape)
 {
-    const int nblocks = cdiv(n, RS_TILE);
+    // shape 2 needs radix_ctl_words_any(n) words of control block (the geometry scratch has them; radix_ctl_words(n) is what
+    // shapes 0 and 1 need)
+    const int nblocks = cdiv(n, shape == 2 ? 2048 : RS_TILE);
     uint32_t* ghist = ctl;
     uint32_t* tickets = ctl + 4 * RS_NB;
     uint32_t* status = tickets + 64;
-    if (!ctl_zeroed) GSR_CUDA(cudaMemsetAsync(ctl, 0, radix_ctl_words(n) * 4, s));
+    if (!ctl_zeroed) GSR_CUDA(cudaMemsetAsync(ctl, 0, (shape == 2 ? radix_ctl_words_any(n) : radix_ctl_words(n)) * 4, s));
     GSR_LAUNCH(radix_hist4_kernel, min(cdiv(n, 4 * RS_THREADS * 4), 148 * 4), RS_THREADS, 0, s, keys, n, ghist);
     uint32_t* Vb[2] = {V0, vals_out};       // 4 passes: the last one writes vals_out
     uint32_t* Kb[2] = {K0, K1};
@@ -282,7 +299,7 @@ int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint
     for (int p = 0; p < 4; p++) {
         const bool last = p == 3;
         int rc = radix_pass(kin, vin, last ? nullptr : Kb[p & 1], Vb[p & 1], n, 8 * p, 8, ghist + p * RS_NB,
-                            status + (size_t)p * RS_NB * nblocks, tickets + p, s, val_base, options().radix_depth);
+                            status + (size_t)p * RS_NB * nblocks, tickets + p, s, val_base, shape);
         if (rc) return rc;
         kin = Kb[p & 1]; vin = Vb[p & 1];
     }
@@ -307,7 +324,7 @@ GeomScratch carve_geom_scratch(uint32_t* p, int P)
     g.view_status = p + 64 + 4 * RS_NB + 2 * align_up((size_t)cdiv(Pp, 256), 32);          // ticket + one word per view
     g.radix_ctl = g.view_status + (DEPTH_MAX_VIEWS + 1);
     g.ctl_words = align_up(64 + 4 * RS_NB + 2 * align_up((size_t)cdiv(Pp, 256), 32) + (DEPTH_MAX_VIEWS + 1) +
-                               radix_ctl_words((uint32_t)Pp) + (size_t)DEPTH_MAX_SEGMENTS * (8 * RS_NB + 64),
+                               radix_ctl_words_any((uint32_t)Pp) + (size_t)DEPTH_MAX_SEGMENTS * (8 * RS_NB + 64),
                            64);                                                           // + slack for the segmented depth sort
     p += g.ctl_words;
     g.depthkey = p; p += Pa;
@@ -539,14 +556,14 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
     // depth keys were written by preprocess; the control block was zeroed before it
     int rc = GSR_OK;
     if (seg_items <= 0 || seg_items >= P || (seg_items & 3) != 0 || cdiv(P, seg_items) > DEPTH_MAX_SEGMENTS) {
-        rc = radix_sort_by_key_u32(sc.depthkey, sc.K0, sc.K1, sc.V0, g.order, (uint32_t)P, sc.radix_ctl, true, s, 0);
+        rc = radix_sort_by_key_u32(sc.depthkey, sc.K0, sc.K1, sc.V0, g.order, (uint32_t)P, sc.radix_ctl, true, s, 0, options().radix_depth);
     } else {
         uint32_t* ctl = sc.radix_ctl;
         for (int off = 0; off < P && rc == GSR_OK; off += seg_items) {
             const int n = min(seg_items, P - off);
             rc = radix_sort_by_key_u32(sc.depthkey + off, sc.K0 + off, sc.K1 + off, sc.V0 + off, g.order + off, (uint32_t)n, ctl, true, s,
-                                       (uint32_t)off);
-            ctl += radix_ctl_words((uint32_t)n);
+                                       (uint32_t)off, options().radix_depth);
+            ctl += radix_ctl_words_any((uint32_t)n);
         }
     }
     if (forked) GSR_CUDA(cudaStreamWaitEvent(main_s, ss.join, 0));      // join even when a launch failed
@@ -693,7 +710,7 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, int gx, cons
 // scratch layout (u32 words): T0[R] G0[R] T1[R] G1[R] status[sum over passes of nblk * 2^bits] tickets[64]
 static size_t bin_status_words(long long R)
 {
-    return (size_t)4 * RS_NB * cdiv(R > 0 ? R : 1, RS_TILE) + 64;       // worst case: 4 passes of 8 bits
+    return (size_t)4 * RS_NB * cdiv(R > 0 ? R : 1, 2048) + 64;          // worst case: 4 passes of 8 bits in 2048-item blocks
 }
 size_t bin_scratch_bytes(long long R)
 {
@@ -713,7 +730,7 @@ int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const
     uint32_t* G[2] = {b.scratch + Ra, b.scratch + 3 * Ra};
     uint32_t* status = b.scratch + 4 * Ra;
     const TileDigits td = tile_digits((uint32_t)(gx * gy));
-    const int nblk = cdiv(R, RS_TILE);
+    const int nblk = cdiv(R, options().radix_split == 2 ? 2048 : RS_TILE);
     size_t status_words = 64;
     for (int p = 0; p < td.npass; p++) status_words += (size_t)nblk << td.bits[p];
     GSR_CUDA(cudaMemsetAsync(status, 0, status_words * 4, s));
