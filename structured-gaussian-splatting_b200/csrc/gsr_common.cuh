@@ -102,7 +102,8 @@ struct GeomScratch {
     unsigned long long* emit_status;   // [ceil(P/256)] look-back words of the fused tile-count scan
     uint32_t* view_status;     // tile_prefix_kernel: ticket + one look-back word per view of a batched call
     uint32_t* radix_ctl;       // digit histograms, tickets and look-back words of the four depth passes
-    uint32_t* depthkey;        // [P] float bits of the view-space depth, 0xFFFFFFFF for culled Gaussians (written by preprocess)
+    uint32_t* depthkey;        // [P] sort key of the depth pass (written by preprocess): float bits of the view-space depth, 0xFFFFFFFF for
+                               // culled Gaussians; under radix_depth = 3 the bits minus those of the near plane, culled 0 (depth_key_bias)
     ushort4*  rect;            // [P] tile rect (x0, y0, x1, y1) of every Gaussian, all zero when culled (written by preprocess)
     uint32_t *K0, *K1, *V0;    // [P] ping-pong buffers of the depth sort
     size_t    total_words;
@@ -180,8 +181,14 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
 int launch_tile_split(int P, long long R, int W, int H, const GeomView& g, const BinView& b, const ImgView& im, cudaStream_t s);
 
 // generic stable radix sort of (u32 key, identity value) pairs on all 32 key bits (sort.cu); ctl = radix_ctl_words(n)
-// words of control state, zeroed by the call unless ctl_zeroed
+// words of control state, zeroed by the call unless ctl_zeroed.  shape 3 (three 9-bit passes + a conditional fourth) needs
+// radix_ctl_words_wide(n) words and DESTROYS the keys (the array serves as a value buffer).
 size_t radix_ctl_words(uint32_t n);
+size_t radix_ctl_words_wide(uint32_t n);
+// depth keys under radix_depth = 3: bits(depth) - bits(0.2f) for Gaussians that emit instances (their depth is > 0.2 or NaN,
+// so the difference never wraps and the unsigned order is unchanged), 0 for culled ones (they emit nothing: their place in
+// the order is immaterial)
+constexpr uint32_t GSR_DEPTH_KEY_BIAS = 0x3E4CCCCDu;
 int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n,
                           uint32_t* ctl, bool ctl_zeroed, cudaStream_t s, uint32_t val_base = 0,     // values = val_base + index
                           int shape = 0);                                                           // block shape, see radix_pass
@@ -210,8 +217,9 @@ struct Options {
     int sh_split = 1;           // dedicated M = 16 SH backward kernel
     int pre_stage = 1;          // preprocess moves the SH rows of a warp's 32 Gaussians through shared memory (coalesced cp.async)
     int radix_split = 1;        // block shape of the tile-split radix passes: 0 = 512 threads x 8 items, 1 = 256 x 16
-    int radix_depth = 1;        // same for the depth-sort passes (alone 0.150 vs 0.155 ms for shape 0 / 1; next to the blending
-                                // kernels of a pipelined step the smaller blocks find room sooner: 2.042 -> 2.021 ms per view)
+    int radix_depth = 3;        // depth-sort passes: 0 / 1 = four 8-bit passes in those block shapes (alone 0.150 vs 0.155 ms; next to the
+                                // blending kernels of a pipelined step the smaller blocks find room sooner: 2.042 -> 2.021 ms per view);
+                                // 3 = biased keys, three 9-bit passes in 256 x 16 blocks + a fourth only for depths >= 13107 (sort.cu)
     int depth_seg_items = -1;   // >= 0: batched calls sort the depth keys in runs of whole views (comparison arm)
     // comparison arms: honoured only when the test-only library libgsr_b200_arms.so is loaded (else GSR_EINVAL)
     int blend_arm = 0;          // 1: plain blending kernels (no culling)   2: forward staging through cp.async.bulk + mbarrier

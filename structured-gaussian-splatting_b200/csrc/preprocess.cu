@@ -173,6 +173,8 @@ struct PreArgs {
     uint32_t* total;    // sum of tiles touched (R)
     int* err;          // device flag: prefiltered violated
     int view_base;     // first view of this launch inside the batched call (scene s of a multi-scene call: s * views_per_scene)
+    uint32_t key_bias; // depth key of a Gaussian that emits instances = bits(depth) - key_bias (gsr_common.cuh: GSR_DEPTH_KEY_BIAS or 0)
+    uint32_t key_cull; // depth key of a culled Gaussian
 };
 
 constexpr int PRE_THREADS = 128;
@@ -313,7 +315,7 @@ __device__ __forceinline__ void preprocess_gaussian(const PreArgs& a, const Came
     o.radii[oidx] = radius_out;
     o.rec[oidx] = out;
     o.clamped[oidx] = (uint8_t)clamp_bits;
-    o.depthkey[oidx] = __float_as_uint(out.q2.y);
+    o.depthkey[oidx] = vis ? __float_as_uint(out.q2.y) - a.key_bias : a.key_cull;
     o.rect[oidx] = rect_out;
     // R = sum of tiles touched: one atomic per warp that has any
     uint32_t tiles = __float_as_uint(out.q2.w);
@@ -435,6 +437,8 @@ int launch_preprocess(const GsrFwdArgs& a, int V, int view_base, int V_total, co
     k.view_base = view_base;
     k.depthkey = sc.depthkey; k.rect = sc.rect; k.total = sc.counters;
     k.err = reinterpret_cast<int*>(sc.counters + 8);
+    const bool biased = options().radix_depth == 3;
+    k.key_bias = biased ? GSR_DEPTH_KEY_BIAS : 0u; k.key_cull = biased ? 0u : 0xFFFFFFFFu;
     const bool stage = options().pre_stage && a.shs && !a.colors_precomp && !k.shs_rest && a.M == 16 && a.D == 3 && (((size_t)a.shs) & 15) == 0;
     if (stage) GSR_LAUNCH(preprocess_fwd_kernel<true>, dim3(cdiv(a.P, PRE_THREADS), V), PRE_THREADS, 0, s, k, cam);
     else GSR_LAUNCH(preprocess_fwd_kernel<false>, dim3(cdiv(a.P, PRE_THREADS), V), PRE_THREADS, 0, s, k, cam);
@@ -449,6 +453,8 @@ int launch_preprocess_views(const GsrFwdArgs& a, int n_views, const GsrViewFront
     k.means = a.means3D; k.shs = a.shs; k.shs_rest = (a.shs && a.M > 1) ? a.shs_rest : nullptr; k.colors_pre = nullptr; k.opac = a.opacities;
     k.scales = a.scales; k.rots = a.rotations; k.cov_pre = nullptr; k.mod = a.scale_modifier;
     k.prefiltered = a.prefiltered;
+    const bool biased = options().radix_depth == 3;
+    k.key_bias = biased ? GSR_DEPTH_KEY_BIAS : 0u; k.key_cull = biased ? 0u : 0xFFFFFFFFu;
     PreViews pv = {};
     for (int v = 0; v < n_views; v++) {
         const GeomScratch sc = carve_geom_scratch(g[v].scratch, a.P);

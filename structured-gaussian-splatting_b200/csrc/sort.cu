@@ -112,11 +112,14 @@ __global__ void __launch_bounds__(THREADS) radix_onesweep_kernel(const uint32_t*
                                                                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                                     uint32_t n, int shift, const uint32_t* __restrict__ ghist,
                                                                     uint32_t* __restrict__ status, uint32_t* __restrict__ ticket,
-                                                                    uint32_t val_base)
+                                                                    uint32_t val_base, int skip_if_single)
 {
     constexpr uint32_t NB = 1u << BITS, MASK = NB - 1;
     constexpr int RS_THREADS = THREADS, RS_IPT = IPT, RS_WARPS = THREADS / 32, RS_TILE = THREADS * IPT;     // (shadow the defaults)
     static_assert(NB <= (uint32_t)THREADS, "one thread per digit in phase 2");
+    // skip_if_single: every item carries the same digit (one bin of ghist holds all n) - the pass is the identity and the
+    // pass before it has already written its values to vals_out (radix_onesweep_wide_kernel, vals_out_alt): nothing to do
+    if (skip_if_single && __syncthreads_or(threadIdx.x < NB && ghist[threadIdx.x] == n)) return;
     __shared__ uint32_t skey[RS_TILE];
     __shared__ uint32_t sval[RS_TILE];
     uint32_t (*wcount)[NB] = reinterpret_cast<uint32_t (*)[NB]>(sval);     // [RS_WARPS][NB], dead before sval is written
@@ -230,7 +233,7 @@ __global__ void __launch_bounds__(THREADS) radix_onesweep_kernel(const uint32_t*
 // one pass; bits in 1..8
 static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, uint32_t n,
                       int shift, int bits, const uint32_t* ghist, uint32_t* status, uint32_t* ticket, cudaStream_t s,
-                      uint32_t val_base = 0, int shape = 0)
+                      uint32_t val_base = 0, int shape = 0, int skip = 0)
 {
     // Block shape (both 4096 items per block): 0 = 512 threads x 8 items, 1 = 256 threads x 16 items.  Measured at C3: the
     // R-sized tile-split passes gain from four independent blocks per SM instead of two (0.299 -> 0.260 ms for the stage:
@@ -241,7 +244,7 @@ static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t
 #define GSR_PASS_C(B)                                                                                                    \
     case B:                                                                                                              \
         GSR_LAUNCH((radix_onesweep_kernel<B, 256, 8>), cdiv(n, 2048), 256, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, ghist, \
-                   status, ticket, val_base);                                                                            \
+                   status, ticket, val_base, skip);                                                                      \
         return GSR_OK;
         switch (bits) {
             GSR_PASS_C(1) GSR_PASS_C(2) GSR_PASS_C(3) GSR_PASS_C(4) GSR_PASS_C(5) GSR_PASS_C(6) GSR_PASS_C(7) GSR_PASS_C(8)
@@ -254,7 +257,7 @@ static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t
 #define GSR_PASS_B(B)                                                                                                    \
     case B:                                                                                                              \
         GSR_LAUNCH((radix_onesweep_kernel<B, 256, 16>), nblocks, 256, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, ghist, \
-                   status, ticket, val_base);                                                                            \
+                   status, ticket, val_base, skip);                                                                      \
         return GSR_OK;
         switch (bits) {
             GSR_PASS_B(1) GSR_PASS_B(2) GSR_PASS_B(3) GSR_PASS_B(4) GSR_PASS_B(5) GSR_PASS_B(6) GSR_PASS_B(7) GSR_PASS_B(8)
@@ -265,7 +268,7 @@ static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t
 #define GSR_PASS(B)                                                                                                      \
     case B:                                                                                                              \
         GSR_LAUNCH((radix_onesweep_kernel<B, RS_THREADS, RS_IPT>), nblocks, RS_THREADS, 0, s, keys_in, vals_in, keys_out, vals_out, n, shift, ghist, \
-                   status, ticket, val_base);                                                                            \
+                   status, ticket, val_base, skip);                                                                      \
         break;
     switch (bits) {
         GSR_PASS(1) GSR_PASS(2) GSR_PASS(3) GSR_PASS(4) GSR_PASS(5) GSR_PASS(6) GSR_PASS(7) GSR_PASS(8)
@@ -273,6 +276,231 @@ static int radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t
     }
 #undef GSR_PASS
     return GSR_OK;
+}
+
+// ------------------------------------------------------------------ depth sort in three 9-bit passes (+ a conditional fourth)
+// The depth keys preprocess writes under radix_depth = 3 are float bits minus the bits of the near plane (0.2f), culled
+// Gaussians 0: monotone in the depth, so the order of the visible Gaussians is the one the raw float bits give, and every
+// depth below 0.2 * 2^16 = 13107 leaves the five top bits zero.  The sort then runs digits of 9 + 9 + 9 + 5 bits: the
+// histogram kernel sees (on the device) whether the fourth digit is the same for all n items; if so the third pass
+// writes its values straight to the sort's output and the fourth pass returns at once - three P-sized passes instead of
+// four.  Deeper scenes take all four passes; the result is the same stable order either way.
+constexpr int RW_BITS = 9, RW_NB = 1 << RW_BITS, RW_TOP_BITS = 32 - 3 * RW_BITS, RW_TOP_NB = 1 << RW_TOP_BITS;
+constexpr int RW_HIST = 3 * RW_NB + RW_TOP_NB;        // 1568 counters
+constexpr int RW_CTL_HEAD = RW_HIST + 64;             // + tickets; even, so the 64-bit status words behind it stay aligned
+
+__global__ void __launch_bounds__(RS_THREADS) radix_hist_wide_kernel(const uint32_t* __restrict__ keys, uint32_t n,
+                                                                     uint32_t* __restrict__ ghist)
+{
+    __shared__ uint32_t sh[RW_HIST];
+    for (int i = threadIdx.x; i < RW_HIST; i += RS_THREADS) sh[i] = 0;
+    __syncthreads();
+    const uint32_t n4 = n >> 2;
+    const int lane = threadIdx.x & 31;
+    const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+    // (warp-uniform trip count: the two high digits are nearly constant, so a warp whose lanes agree adds once)
+    for (uint32_t base = blockIdx.x * RS_THREADS; base < n4; base += gridDim.x * RS_THREADS) {
+        const uint32_t i = base + threadIdx.x;
+        const bool valid = i < n4;
+        const uint4 k = valid ? k4[i] : make_uint4(0u, 0u, 0u, 0u);
+        const uint32_t kk[4] = {k.x, k.y, k.z, k.w};
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            if (valid) {
+                atomicAdd(&sh[kk[c] & (RW_NB - 1)], 1u);
+                atomicAdd(&sh[RW_NB + ((kk[c] >> RW_BITS) & (RW_NB - 1))], 1u);
+            }
+            const uint32_t hi = kk[c] >> (2 * RW_BITS);                    // third and top digit together (14 bits)
+            const uint32_t hi0 = __shfl_sync(0xffffffffu, hi, 0);
+            if (__all_sync(0xffffffffu, valid && hi == hi0)) {
+                if (lane == 0) {
+                    atomicAdd(&sh[2 * RW_NB + (hi0 & (RW_NB - 1))], 32u);
+                    atomicAdd(&sh[3 * RW_NB + (hi0 >> RW_BITS)], 32u);
+                }
+            } else if (valid) {
+                atomicAdd(&sh[2 * RW_NB + (hi & (RW_NB - 1))], 1u);
+                atomicAdd(&sh[3 * RW_NB + (hi >> RW_BITS)], 1u);
+            }
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3u)) {
+        const uint32_t k = keys[(n4 << 2) + threadIdx.x];
+        atomicAdd(&sh[k & (RW_NB - 1)], 1u);
+        atomicAdd(&sh[RW_NB + ((k >> RW_BITS) & (RW_NB - 1))], 1u);
+        atomicAdd(&sh[2 * RW_NB + ((k >> (2 * RW_BITS)) & (RW_NB - 1))], 1u);
+        atomicAdd(&sh[3 * RW_NB + (k >> (3 * RW_BITS))], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < RW_HIST; i += RS_THREADS)
+        if (sh[i]) atomicAdd(&ghist[i], sh[i]);
+}
+
+// radix_onesweep_kernel for digits of 2 x THREADS bins: thread t owns the digits 2t and 2t + 1, whose look-back status
+// words travel as ONE 64-bit word (low half: digit 2t), published and read with single 8-byte accesses, so the look-back
+// makes as many round trips as the narrow kernel's.  vals_out_alt / next_hist: when one bin of next_hist[0 .. next_nb)
+// holds all n items the NEXT pass is the identity; this pass then writes its values to vals_out_alt (the sort's output)
+// and no keys.
+template <int BITS, int THREADS, int IPT>
+__global__ void __launch_bounds__(THREADS) radix_onesweep_wide_kernel(const uint32_t* __restrict__ keys_in,
+                                                                         const uint32_t* __restrict__ vals_in,
+                                                                         uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                                         uint32_t* __restrict__ vals_out_alt,
+                                                                         uint32_t n, int shift, const uint32_t* __restrict__ ghist,
+                                                                         const uint32_t* __restrict__ next_hist, int next_nb,
+                                                                         unsigned long long* __restrict__ status,
+                                                                         uint32_t* __restrict__ ticket, uint32_t val_base)
+{
+    constexpr uint32_t NB = 1u << BITS, MASK = NB - 1;
+    constexpr int WARPS = THREADS / 32, TILE = THREADS * IPT;
+    static_assert(NB == 2u * THREADS, "two digits per thread in phase 2");
+    __shared__ uint32_t skey[TILE];
+    __shared__ __align__(8) uint32_t sval[TILE];
+    uint32_t (*wcount)[NB] = reinterpret_cast<uint32_t (*)[NB]>(sval);     // [WARPS][NB], dead before sval is written
+    static_assert(WARPS * NB <= TILE, "wcount must fit in sval");
+    __shared__ uint32_t lbase[NB];          // CTA-local exclusive offset of each digit
+    __shared__ uint32_t gdelta[NB];         // global position of local slot lp of digit d = gdelta[d] + lp
+    __shared__ uint32_t warp_sum[WARPS];
+    __shared__ uint32_t s_blk;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t t = threadIdx.x;
+
+    if (t == 0) s_blk = atomicAdd(ticket, 1u);
+    for (uint32_t i = t; i < WARPS * NB; i += THREADS) sval[i] = 0;
+    const bool next_single = next_hist != nullptr && (int)t < next_nb && next_hist[t] == n;
+    const bool alt = __syncthreads_or(next_single) != 0;
+    const uint32_t blk = s_blk;
+
+    // phase 1: stable rank of every item among the warp's items with the same digit (BITS ballots)
+    const uint32_t wbase_idx = blk * TILE + w * (32 * IPT);
+    const uint32_t lt_mask = (1u << lane) - 1;
+    uint32_t key[IPT];
+    uint32_t loff[IPT];
+#pragma unroll
+    for (int i = 0; i < IPT; i++) {
+        const uint32_t idx = wbase_idx + i * 32 + lane;
+        key[i] = idx < n ? keys_in[idx] : 0xFFFFFFFFu;
+    }
+#pragma unroll
+    for (int i = 0; i < IPT; i++) {
+        const uint32_t idx = wbase_idx + i * 32 + lane;
+        const bool valid = idx < n;
+        const uint32_t d = (key[i] >> shift) & MASK;
+        uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int b = 0; b < BITS; b++) {
+            const uint32_t bit = (d >> b) & 1u;
+            const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+            peers &= ~(bal ^ (0u - bit));
+        }
+        const uint32_t old = wcount[w][d];
+        __syncwarp();
+        const uint32_t cnt = __popc(peers), rank = __popc(peers & lt_mask);
+        if (valid && rank == cnt - 1) wcount[w][d] = old + cnt;
+        __syncwarp();
+        loff[i] = old + rank;
+    }
+    __syncthreads();
+
+    // phase 2: digits 2t, 2t + 1
+    uint32_t tot0 = 0, tot1 = 0, excl0 = 0, excl1 = 0;
+    {
+#pragma unroll
+        for (int i = 0; i < WARPS; i++) {
+            uint2* wc = reinterpret_cast<uint2*>(&wcount[i][2 * t]);
+            const uint2 c = *wc;
+            *wc = make_uint2(tot0, tot1);
+            tot0 += c.x; tot1 += c.y;
+        }
+        auto pack = [](uint32_t flag, uint32_t a, uint32_t b) -> unsigned long long {
+            return ((unsigned long long)(flag | b) << 32) | (unsigned long long)(flag | a);
+        };
+        unsigned long long* mine = status + (size_t)blk * THREADS + t;
+        if (blk == 0) st_volatile64(mine, pack(ST_INC, tot0, tot1));
+        else {
+            st_volatile64(mine, pack(ST_AGG, tot0, tot1));
+            bool found = false;
+            for (int k = (int)blk - 1; !found; k -= 4) {
+                unsigned long long sv[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) sv[j] = k - j >= 0 ? ld_volatile64(status + (size_t)(k - j) * THREADS + t) : pack(ST_INC, 0u, 0u);
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (found) break;
+                    unsigned long long v = sv[j];
+                    while (((uint32_t)v >> 30) == 0) v = ld_volatile64(status + (size_t)(k - j) * THREADS + t);
+                    excl0 += (uint32_t)v & ST_VAL;
+                    excl1 += (uint32_t)(v >> 32) & ST_VAL;
+                    found = ((uint32_t)v & ST_INC) != 0;
+                }
+            }
+            st_volatile64(mine, pack(ST_INC, excl0 + tot0, excl1 + tot1));
+        }
+    }
+    const uint2 gh = *reinterpret_cast<const uint2*>(ghist + 2 * t);
+    const uint32_t gbase = block_excl_scan<WARPS>(gh.x + gh.y, warp_sum);
+    const uint32_t lb = block_excl_scan<WARPS>(tot0 + tot1, warp_sum);
+    lbase[2 * t] = lb; lbase[2 * t + 1] = lb + tot0;
+    gdelta[2 * t] = gbase + excl0 - lb; gdelta[2 * t + 1] = gbase + gh.x + excl1 - (lb + tot0);
+    __syncthreads();
+
+    // phase 3: place items in digit order in shared memory
+    uint32_t val[IPT];
+#pragma unroll
+    for (int i = 0; i < IPT; i++) {
+        const uint32_t idx = wbase_idx + i * 32 + lane;
+        val[i] = (vals_in && idx < n) ? vals_in[idx] : idx + val_base;
+        const uint32_t d = (key[i] >> shift) & MASK;
+        loff[i] += lbase[d] + wcount[w][d];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < IPT; i++) {
+        const uint32_t idx = wbase_idx + i * 32 + lane;
+        if (idx < n) { skey[loff[i]] = key[i]; sval[loff[i]] = val[i]; }
+    }
+    __syncthreads();
+    // phase 4: coalesced write-out
+    const uint32_t n_blk = min((uint32_t)TILE, n - blk * TILE);
+    uint32_t* const vo = alt ? vals_out_alt : vals_out;
+    uint32_t* const ko = alt ? nullptr : keys_out;
+#pragma unroll
+    for (int i = 0; i < IPT; i++) {
+        const uint32_t lp = i * THREADS + t;
+        if (lp < n_blk) {
+            const uint32_t k = skey[lp];
+            const uint32_t gpos = gdelta[(k >> shift) & MASK] + lp;
+            if (ko) ko[gpos] = k;
+            vo[gpos] = sval[lp];
+        }
+    }
+}
+
+size_t radix_ctl_words_wide(uint32_t n) { return RW_CTL_HEAD + (size_t)RW_HIST * cdiv(n > 0 ? n : 1, RS_TILE); }
+
+// ctl: radix_ctl_words_wide(n) zeroed words.  The key array is used as a value buffer once the first pass has read it
+// (keys are DESTROYED): the third pass must be able to write the sort's output, so neither of the buffers it reads may be
+// vals_out, and K0 / K1 / V0 are taken.
+static int radix_sort_by_key_u32_wide(uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n,
+                                      uint32_t* ctl, cudaStream_t s, uint32_t val_base)
+{
+    const int nblocks = cdiv(n, RS_TILE);
+    uint32_t* ghist = ctl;
+    uint32_t* tickets = ctl + RW_HIST;
+    uint32_t* status = ctl + RW_CTL_HEAD;
+    GSR_LAUNCH(radix_hist_wide_kernel, min(cdiv(n, 4 * RS_THREADS * 4), 148 * 4), RS_THREADS, 0, s, keys, n, ghist);
+    uint32_t* Vb[3] = {V0, keys, V0};       // values: pass 0 -> V0, 1 -> keys, 2 -> V0 (vals_out when pass 3 is the identity), 3 -> vals_out
+    uint32_t* Kb[3] = {K0, K1, K0};
+    const uint32_t* kin = keys;
+    const uint32_t* vin = nullptr;
+    for (int p = 0; p < 3; p++) {
+        const bool third = p == 2;
+        GSR_LAUNCH((radix_onesweep_wide_kernel<RW_BITS, 256, 16>), nblocks, 256, 0, s, kin, vin, Kb[p], Vb[p],
+                   third ? vals_out : nullptr, n, RW_BITS * p, ghist + p * RW_NB, third ? ghist + 3 * RW_NB : nullptr, RW_TOP_NB,
+                   reinterpret_cast<unsigned long long*>(status + (size_t)p * RW_NB * nblocks), tickets + p, val_base);
+        kin = Kb[p]; vin = Vb[p];
+    }
+    return radix_pass(kin, vin, nullptr, vals_out, n, 3 * RW_BITS, RW_TOP_BITS, ghist + 3 * RW_NB, status + (size_t)3 * RW_NB * nblocks,
+                      tickets + 3, s, val_base, 1, 1);
 }
 
 // stable LSD sort of n (key, value) pairs on all 32 key bits; values start as identity.
@@ -284,6 +512,12 @@ static size_t radix_ctl_words_any(uint32_t n) { return 4 * RS_NB + 64 + (size_t)
 int radix_sort_by_key_u32(const uint32_t* keys, uint32_t* K0, uint32_t* K1, uint32_t* V0, uint32_t* vals_out, uint32_t n,
                           uint32_t* ctl, bool ctl_zeroed, cudaStream_t s, uint32_t val_base, int shape)
 {
+    // shape 3: three 9-bit passes + a conditional fourth (needs radix_ctl_words_wide(n) zeroed words; the depth sort of the
+    // geometry scratch has them)
+    if (shape == 3) {
+        if (!ctl_zeroed) GSR_CUDA(cudaMemsetAsync(ctl, 0, radix_ctl_words_wide(n) * 4, s));
+        return radix_sort_by_key_u32_wide(const_cast<uint32_t*>(keys), K0, K1, V0, vals_out, n, ctl, s, val_base);
+    }
     // shape 2 needs radix_ctl_words_any(n) words of control block (the geometry scratch has them; radix_ctl_words(n) is what
     // shapes 0 and 1 need)
     const int nblocks = cdiv(n, shape == 2 ? 2048 : RS_TILE);
@@ -324,7 +558,8 @@ GeomScratch carve_geom_scratch(uint32_t* p, int P)
     g.view_status = p + 64 + 4 * RS_NB + 2 * align_up((size_t)cdiv(Pp, 256), 32);          // ticket + one word per view
     g.radix_ctl = g.view_status + (DEPTH_MAX_VIEWS + 1);
     g.ctl_words = align_up(64 + 4 * RS_NB + 2 * align_up((size_t)cdiv(Pp, 256), 32) + (DEPTH_MAX_VIEWS + 1) +
-                               radix_ctl_words_any((uint32_t)Pp) + (size_t)DEPTH_MAX_SEGMENTS * (8 * RS_NB + 64),
+                               max(radix_ctl_words_any((uint32_t)Pp), radix_ctl_words_wide((uint32_t)Pp)) +
+                               (size_t)DEPTH_MAX_SEGMENTS * (8 * RS_NB + 64),
                            64);                                                           // + slack for the segmented depth sort
     p += g.ctl_words;
     g.depthkey = p; p += Pa;
@@ -562,7 +797,7 @@ int launch_depth_order(int P, int W, int H, const GeomView& g, const ImgView& im
         for (int off = 0; off < P && rc == GSR_OK; off += seg_items) {
             const int n = min(seg_items, P - off);
             rc = radix_sort_by_key_u32(sc.depthkey + off, sc.K0 + off, sc.K1 + off, sc.V0 + off, g.order + off, (uint32_t)n, ctl, true, s,
-                                       (uint32_t)off, options().radix_depth);
+                                       (uint32_t)off, options().radix_depth == 3 ? 1 : options().radix_depth);
             ctl += radix_ctl_words_any((uint32_t)n);
         }
     }

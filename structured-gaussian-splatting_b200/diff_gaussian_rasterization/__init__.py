@@ -303,11 +303,15 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
                               binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
+        # no zero-filled stand-in for the gradient of `radii` (an int32 [P] fill per backward call: 12 MB at C3)
+        ctx.set_materialize_grads(False)
         return color, radii
 
     @staticmethod
     def backward(ctx, grad_out_color, _grad_radii):
         rs = ctx.raster_settings
+        if grad_out_color is None:              # (only with set_materialize_grads(False): the image took no part in the loss)
+            grad_out_color = torch.zeros((3, rs.image_height, rs.image_width), dtype=torch.float32, device=ctx.saved_tensors[1].device)
         colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer, binningBuffer, imgBuffer = \
             ctx.saved_tensors
         # argument order of _C.rasterize_gaussians_backward (rasterize_points.h:40-62)

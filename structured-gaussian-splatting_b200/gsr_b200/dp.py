@@ -223,7 +223,8 @@ def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
 
 def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
                    loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None,
-                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False, prepare: bool = False):
+                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False, prepare: bool = False,
+                   prepare_first: int = 0):
     """The step in DEFERRED form (diff_gaussian_rasterization.set_grad_mode("deferred")): every view runs its forward and its
     blending backward; the per-Gaussian backward of all the rank's views then runs once (parameters read once, every gradient
     row written once: 0.2 instead of 0.4 ms per view at C3), in `overlap_chunks` ranges of Gaussians when > 0, the all-reduce
@@ -234,7 +235,10 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
     (set_front_stream / gsr_forward_front), so it runs inside the issue-bound blending kernels of the views around it.
     Same results; two views' state is alive at a time.
     prepare=True: the preprocess stage of all the step's views runs first, in one pass over the parameters
-    (prepare_step_views): 236 of the ~300 bytes per Gaussian a view's preprocess moves are read once per step."""
+    (prepare_step_views): 236 of the ~300 bytes per Gaussian a view's preprocess moves are read once per step.
+    prepare_first = K > 0 (with pipeline and prepare): only the first K views are prepared ahead of the step; the pass over
+    the remaining views is queued on the front stream once the K-th forward has been issued, so it runs inside the first
+    views' blending kernels instead of in front of them (nothing else can run next to the step's first preprocess)."""
     total = None
     views = list(view_ids)
     prev = rasterizer_mod.set_grad_mode("deferred")
@@ -242,13 +246,18 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
              and params[flat.names[0]].is_cuda)
     prev_front = rasterizer_mod.set_front_stream(rasterizer_mod.front_stream(params[flat.names[0]].device)) if piped else None
     try:
+        first = prepare_first if (piped and prepare and 0 < prepare_first < len(views)) else len(views)
         if prepare and views:
-            prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views)
+            prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[:first])
         if piped:
             ahead = render_view(rasterizer_mod, params, cams[views[0]], bg, sh_degree)
+            if first == 1 and prepare:
+                prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[1:])
             for i, k in enumerate(views):
                 color = ahead[0]
                 ahead = render_view(rasterizer_mod, params, cams[views[i + 1]], bg, sh_degree) if i + 1 < len(views) else None
+                if i + 2 == first and first < len(views):          # forwards 0 .. first-1 are issued: the rest of the step's views
+                    prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[first:])
                 loss = loss_fn(color, k)
                 loss.backward()
                 total = loss.detach() if total is None else total + loss.detach()
