@@ -70,8 +70,8 @@ def parse_args():
                     help="deferred steps: 1 = the preprocess stage of the step's views runs in one pass over the parameters "
                          "(prepare_views / gsr_preprocess_views) before the per-view calls; 0 = every call preprocesses its view")
     ap.add_argument("--prepare-first", type=int, default=0,
-                    help="with --prepare 1 --pipeline 1: K > 0 = only the first K views are preprocessed ahead of the step, the rest in a "
-                         "second pass queued behind the K-th forward (it runs inside the first views' blending kernels); 0 = all at once")
+                    help="with --prepare 1 --pipeline 1: K > 0 = the first K views are preprocessed in a pass of their own, the rest in a "
+                         "second pass on a second stream next to the first view's depth sort / tile split; 0 = all views in one pass")
     ap.add_argument("--views-of-rank", default="", help="diagnostic (N = 1): r/w = render the cameras rank r of w ranks would get")
     ap.add_argument("--nccl-priority", default="high", choices=["high", "default"], help="priority of NCCL's stream (N > 1)")
     ap.add_argument("--front-priority", default="high", choices=["high", "default"],
@@ -480,19 +480,14 @@ def main():
                     stats["Pv"] += int((radii > 0).sum())
                     stats["views"] += 1
             try:
-                first = args.prepare_first if (piped and use_prepare[0] and 0 < args.prepare_first < len(views)) else len(views)
                 if use_prepare[0]:
-                    dp.prepare_step_views(dgr, prm, cams, bg, spec.D, views[:first])
+                    dp.prepare_step_views_split(dgr, prm, cams, bg, spec.D, views, args.prepare_first if piped else 0)
                 if piped:
                     # software pipeline: forward of view i+1 (its front on the high-priority stream), then backward of view i
                     ahead = dp.render_view(dgr, prm, cams[views[0]], bg, spec.D)
-                    if first == 1 and use_prepare[0]:
-                        dp.prepare_step_views(dgr, prm, cams, bg, spec.D, views[1:])
                     for i, k in enumerate(views):
                         color, radii, _ = ahead
                         ahead = dp.render_view(dgr, prm, cams[views[i + 1]], bg, spec.D) if i + 1 < len(views) else None
-                        if i + 2 == first and first < len(views):      # (--prepare-first) the rest of the step's views
-                            dp.prepare_step_views(dgr, prm, cams, bg, spec.D, views[first:])
                         back(color, radii, k)
                 else:
                     for k in views:
@@ -663,8 +658,7 @@ def main():
                 prefetch_cams(step + 1)
                 step_cams = [synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cmb[j, :16].view(4, 4),
                                           cmb[j, 16:32].view(4, 4), cmb[j, 32:35]) for j, k in enumerate(views)]
-                first_e = args.prepare_first if (piped and 0 < args.prepare_first < len(views)) else len(views)
-                dp.prepare_step_views(dgr, params, step_cams, bg, spec.D, range(first_e))
+                dp.prepare_step_views_split(dgr, params, step_cams, bg, spec.D, range(len(views)), args.prepare_first if piped else 0)
 
             def fwd(i):
                 k = views[i]
@@ -678,14 +672,10 @@ def main():
 
             try:
                 ahead = fwd(0) if piped else None
-                if piped and step_cams is not None and first_e == 1:
-                    dp.prepare_step_views(dgr, params, step_cams, bg, spec.D, range(1, len(views)))
                 for i, k in enumerate(views):
                     if piped:
                         color, tgt, slot = ahead
                         ahead = fwd(i + 1) if i + 1 < len(views) else None
-                        if step_cams is not None and i + 2 == first_e and first_e < len(views):
-                            dp.prepare_step_views(dgr, params, step_cams, bg, spec.D, range(first_e, len(views)))
                     else:
                         color, tgt, slot = fwd(i)
                     loss = losses.l1_loss(color, tgt)

@@ -1,7 +1,8 @@
 """A/B of step-level variants inside ONE process (C3, 8 views per step, deferred + pipelined + prepared, the step of
 bench.py's headline through gsr_b200.dp.deferred_views): the arms are run interleaved, several rounds, device-timed.
-  arm = radix_depth : prepare_first      (gsr_debug_set_option RADIX_DEPTH, dp.deferred_views(prepare_first=))
-usage: python scripts/ab_step.py [--steps 10] [--rounds 3] [--arms 1:0,3:0,3:2] [--out gpurun_out/ab_step.json]
+  arm = OPTION=value[;OPTION=value...][:prepare_first]   ('-' = defaults; options through gsr_debug_set_option, restored after
+        the arm; prepare_first -> dp.deferred_views(prepare_first=))
+usage: python scripts/ab_step.py [--steps 10] [--rounds 3] [--arms -,RADIX_DEPTH=1,FWD_MINB=4:2] [--out gpurun_out/ab_step.json]
 Also checks that every arm produces the same gradients as the first one (bit-identical flat buffer expected: the depth
 order of the visible Gaussians and every per-view result are the same)."""
 import argparse
@@ -19,7 +20,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--rounds", type=int, default=3)
-    ap.add_argument("--arms", default="1:0,3:0,3:1,3:2,3:3,1:2")
+    ap.add_argument("--arms", default="-,RADIX_DEPTH=1")
     ap.add_argument("--config", default="C3")
     ap.add_argument("--views-per-step", type=int, default=8)
     ap.add_argument("--out", default="gpurun_out/ab_step.json")
@@ -47,33 +48,50 @@ def main():
         dp.deferred_views(dgr, params, flat, cams, bg, spec.D, loss_fn, views(i), all_reduce=False, pipeline=True, prepare=True,
                           prepare_first=first)
 
-    arms = [tuple(int(x) for x in a.split(":")) for a in args.arms.split(",")]
-    res = {"%d:%d" % a: [] for a in arms}
+    def parse(a):
+        spec_, _, first = a.partition(":")
+        opts = [(kv.split("=")[0], int(kv.split("=")[1])) for kv in spec_.split(";") if "=" in kv]       # (no '=': defaults)
+        return a, opts, int(first) if first else 0
+
+    arms = [parse(a) for a in args.arms.split(",")]
+
+    class applied:
+        def __init__(self, opts):
+            self.opts, self.prev = opts, []
+
+        def __enter__(self):
+            self.prev = [(k, dgr._C.set_option(k, v)) for k, v in self.opts]
+
+        def __exit__(self, *exc):
+            for k, v in reversed(self.prev):
+                dgr._C.set_option(k, v)
+
+    res = {a[0]: [] for a in arms}
     ref_grad = None
     same = {}
-    for a in arms:                                  # correctness: the same step under every arm
-        dgr._C.set_option("RADIX_DEPTH", a[0])
-        step(0, a[1])
-        torch.cuda.synchronize()
+    for name, opts, first in arms:                  # correctness: the same step under every arm
+        with applied(opts):
+            step(0, first)
+            torch.cuda.synchronize()
         g = flat.flat.clone()
         if ref_grad is None:
             ref_grad = g
-        same["%d:%d" % a] = {"bit_identical": bool(torch.equal(g, ref_grad)),
-                             "max_abs_diff": float((g - ref_grad).abs().max()), "ref_abs_max": float(ref_grad.abs().max())}
+        same[name] = {"bit_identical": bool(torch.equal(g, ref_grad)),
+                      "max_abs_diff": float((g - ref_grad).abs().max()), "ref_abs_max": float(ref_grad.abs().max())}
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for r in range(args.rounds):
-        for a in arms:
-            dgr._C.set_option("RADIX_DEPTH", a[0])
-            for i in range(3):
-                step(i, a[1])
-            torch.cuda.synchronize()
-            e0.record()
-            for i in range(args.steps):
-                step(3 + i, a[1])
-            e1.record()
-            torch.cuda.synchronize()
-            res["%d:%d" % a].append(e0.elapsed_time(e1) / (args.steps * vps))
-    out = {"what": "ms per view, C3 step (deferred, pipelined, prepared), arms = radix_depth:prepare_first, %d rounds x %d steps"
+        for name, opts, first in arms:
+            with applied(opts):
+                for i in range(3):
+                    step(i, first)
+                torch.cuda.synchronize()
+                e0.record()
+                for i in range(args.steps):
+                    step(3 + i, first)
+                e1.record()
+                torch.cuda.synchronize()
+            res[name].append(e0.elapsed_time(e1) / (args.steps * vps))
+    out = {"what": "ms per view, C3 step (deferred, pipelined, prepared), arms = options[:prepare_first], %d rounds x %d steps"
                    % (args.rounds, args.steps),
            "ms_per_view": {k: [round(x, 4) for x in v] for k, v in res.items()},
            "best": {k: round(min(v), 4) for k, v in res.items()}, "same_gradients": same}

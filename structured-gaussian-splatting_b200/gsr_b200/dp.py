@@ -153,14 +153,33 @@ def render_view(rasterizer_mod, params, cam, bg, sh_degree: int, scale_modifier:
     return color, radii, means2D
 
 
-def prepare_step_views(rasterizer_mod, params, cams: Sequence, bg, sh_degree: int, view_ids: Iterable[int]) -> int:
+def prepare_step_views(rasterizer_mod, params, cams: Sequence, bg, sh_degree: int, view_ids: Iterable[int], **kw) -> int:
     """The preprocess stage of the step's views in one pass over the parameters (diff_gaussian_rasterization.prepare_views /
     gsr_preprocess_views): the render_view calls that follow with these cameras skip it.  Returns the number of views prepared
     (0 where the rasterizer module has no such entry point, e.g. the reference package)."""
     if not hasattr(rasterizer_mod, "prepare_views"):
         return 0
     return rasterizer_mod.prepare_views(params["means3D"], params["opacities"], params["shs"], params["scales"], params["rotations"],
-                                        [view_settings(rasterizer_mod, cams[k], bg, sh_degree) for k in view_ids])
+                                        [view_settings(rasterizer_mod, cams[k], bg, sh_degree) for k in view_ids], **kw)
+
+
+def prepare_step_views_split(rasterizer_mod, params, cams: Sequence, bg, sh_degree: int, view_ids: Iterable[int], first: int = 0) -> int:
+    """prepare_step_views in two passes when 0 < first < number of views and a front stream is set: views[:first] on the
+    front stream, views[first:] on a second high-priority stream that waits for the first pass (and for the parameters,
+    i.e. for everything queued so far on the current stream) - see deferred_views(prepare_first=)."""
+    views = list(view_ids)
+    if not (0 < first < len(views)) or not hasattr(rasterizer_mod, "get_front_stream") or not hasattr(rasterizer_mod, "prepare_views"):
+        return prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views)
+    dev = params["means3D"].device
+    n = prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[:first])
+    if n == 0:
+        return prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views)
+    front = rasterizer_mod.get_front_stream()
+    second = rasterizer_mod.front_stream(dev, True, 1)
+    second.wait_stream(torch.cuda.current_stream(dev))
+    if front is not None:
+        second.wait_stream(front)          # (the first pass is queued on the front stream, or else on the current stream)
+    return n + prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[first:], stream=second, keep=True)
 
 
 _STREAMS: List["torch.cuda.Stream"] = []
@@ -236,9 +255,11 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
     Same results; two views' state is alive at a time.
     prepare=True: the preprocess stage of all the step's views runs first, in one pass over the parameters
     (prepare_step_views): 236 of the ~300 bytes per Gaussian a view's preprocess moves are read once per step.
-    prepare_first = K > 0 (with pipeline and prepare): only the first K views are prepared ahead of the step; the pass over
-    the remaining views is queued on the front stream once the K-th forward has been issued, so it runs inside the first
-    views' blending kernels instead of in front of them (nothing else can run next to the step's first preprocess)."""
+    prepare_first = K > 0 (with pipeline and prepare): the preprocess pass is split - the first K views on the front stream,
+    the remaining views in a second pass on a stream of its own that starts when the first pass has finished and so runs
+    (bandwidth-bound) next to the first view's depth sort and tile split (latency-bound) instead of in front of them: the
+    first forward starts after K views' preprocess, not after the whole step's.  (Queueing the second pass on the front
+    stream behind the K-th forward was measured slower than one pass: 2.053 vs 2.041 ms per view.)"""
     total = None
     views = list(view_ids)
     prev = rasterizer_mod.set_grad_mode("deferred")
@@ -246,18 +267,13 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
              and params[flat.names[0]].is_cuda)
     prev_front = rasterizer_mod.set_front_stream(rasterizer_mod.front_stream(params[flat.names[0]].device)) if piped else None
     try:
-        first = prepare_first if (piped and prepare and 0 < prepare_first < len(views)) else len(views)
         if prepare and views:
-            prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[:first])
+            prepare_step_views_split(rasterizer_mod, params, cams, bg, sh_degree, views, prepare_first if piped else 0)
         if piped:
             ahead = render_view(rasterizer_mod, params, cams[views[0]], bg, sh_degree)
-            if first == 1 and prepare:
-                prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[1:])
             for i, k in enumerate(views):
                 color = ahead[0]
                 ahead = render_view(rasterizer_mod, params, cams[views[i + 1]], bg, sh_degree) if i + 1 < len(views) else None
-                if i + 2 == first and first < len(views):          # forwards 0 .. first-1 are issued: the rest of the step's views
-                    prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[first:])
                 loss = loss_fn(color, k)
                 loss.backward()
                 total = loss.detach() if total is None else total + loss.detach()
