@@ -69,9 +69,6 @@ def parse_args():
     ap.add_argument("--prepare", type=int, default=1,
                     help="deferred steps: 1 = the preprocess stage of the step's views runs in one pass over the parameters "
                          "(prepare_views / gsr_preprocess_views) before the per-view calls; 0 = every call preprocesses its view")
-    ap.add_argument("--prepare-first", type=int, default=0,
-                    help="with --prepare 1 --pipeline 1: K > 0 = the first K views are preprocessed in a pass of their own, the rest in a "
-                         "second pass on a second stream next to the first view's depth sort / tile split; 0 = all views in one pass")
     ap.add_argument("--views-of-rank", default="", help="diagnostic (N = 1): r/w = render the cameras rank r of w ranks would get")
     ap.add_argument("--nccl-priority", default="high", choices=["high", "default"], help="priority of NCCL's stream (N > 1)")
     ap.add_argument("--front-priority", default="high", choices=["high", "default"],
@@ -481,7 +478,7 @@ def main():
                     stats["views"] += 1
             try:
                 if use_prepare[0]:
-                    dp.prepare_step_views_split(dgr, prm, cams, bg, spec.D, views, args.prepare_first if piped else 0)
+                    dp.prepare_step_views(dgr, prm, cams, bg, spec.D, views)
                 if piped:
                     # software pipeline: forward of view i+1 (its front on the high-priority stream), then backward of view i
                     ahead = dp.render_view(dgr, prm, cams[views[0]], bg, spec.D)
@@ -658,7 +655,7 @@ def main():
                 prefetch_cams(step + 1)
                 step_cams = [synth.Camera(spec.W, spec.H, cams[k].tanfovx, cams[k].tanfovy, cmb[j, :16].view(4, 4),
                                           cmb[j, 16:32].view(4, 4), cmb[j, 32:35]) for j, k in enumerate(views)]
-                dp.prepare_step_views_split(dgr, params, step_cams, bg, spec.D, range(len(views)), args.prepare_first if piped else 0)
+                dp.prepare_step_views(dgr, params, step_cams, bg, spec.D, range(len(views)))
 
             def fwd(i):
                 k = views[i]

@@ -1,10 +1,8 @@
 """A/B of step-level variants inside ONE process (C3, 8 views per step, deferred + pipelined + prepared, the step of
 bench.py's headline through gsr_b200.dp.deferred_views): the arms are run interleaved, several rounds, device-timed.
-  arm = OPTION=value[;OPTION=value...][:prepare_first]   ('-' = defaults; options through gsr_debug_set_option, restored after
-        the arm; prepare_first -> dp.deferred_views(prepare_first=))
-usage: python scripts/ab_step.py [--steps 10] [--rounds 3] [--arms -,RADIX_DEPTH=1,FWD_MINB=4:2] [--out gpurun_out/ab_step.json]
-Also checks that every arm produces the same gradients as the first one (bit-identical flat buffer expected: the depth
-order of the visible Gaussians and every per-view result are the same)."""
+  arm = OPTION=value[;OPTION=value...]   (a name without '=' = defaults; options through gsr_debug_set_option, restored after the arm)
+usage: python scripts/ab_step.py [--steps 10] [--rounds 3] [--arms=base,RADIX_DEPTH=1,FWD_MINB=4] [--out gpurun_out/ab_step.json]
+Also reports every arm's gradients against the first arm's (equal up to the order of the atomic adds)."""
 import argparse
 import json
 import os
@@ -20,7 +18,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--rounds", type=int, default=3)
-    ap.add_argument("--arms", default="-,RADIX_DEPTH=1")
+    ap.add_argument("--arms", default="base,RADIX_DEPTH=1")
     ap.add_argument("--config", default="C3")
     ap.add_argument("--views-per-step", type=int, default=8)
     ap.add_argument("--out", default="gpurun_out/ab_step.json")
@@ -44,14 +42,11 @@ def main():
     def views(step):
         return [(step * vps + j) % V for j in range(vps)]
 
-    def step(i, first):
-        dp.deferred_views(dgr, params, flat, cams, bg, spec.D, loss_fn, views(i), all_reduce=False, pipeline=True, prepare=True,
-                          prepare_first=first)
+    def step(i):
+        dp.deferred_views(dgr, params, flat, cams, bg, spec.D, loss_fn, views(i), all_reduce=False, pipeline=True, prepare=True)
 
     def parse(a):
-        spec_, _, first = a.partition(":")
-        opts = [(kv.split("=")[0], int(kv.split("=")[1])) for kv in spec_.split(";") if "=" in kv]       # (no '=': defaults)
-        return a, opts, int(first) if first else 0
+        return a, [(kv.split("=")[0], int(kv.split("=")[1])) for kv in a.split(";") if "=" in kv]       # (no '=': defaults)
 
     arms = [parse(a) for a in args.arms.split(",")]
 
@@ -69,9 +64,9 @@ def main():
     res = {a[0]: [] for a in arms}
     ref_grad = None
     same = {}
-    for name, opts, first in arms:                  # correctness: the same step under every arm
+    for name, opts in arms:                  # correctness: the same step under every arm
         with applied(opts):
-            step(0, first)
+            step(0)
             torch.cuda.synchronize()
         g = flat.flat.clone()
         if ref_grad is None:
@@ -80,18 +75,18 @@ def main():
                       "max_abs_diff": float((g - ref_grad).abs().max()), "ref_abs_max": float(ref_grad.abs().max())}
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for r in range(args.rounds):
-        for name, opts, first in arms:
+        for name, opts in arms:
             with applied(opts):
                 for i in range(3):
-                    step(i, first)
+                    step(i)
                 torch.cuda.synchronize()
                 e0.record()
                 for i in range(args.steps):
-                    step(3 + i, first)
+                    step(3 + i)
                 e1.record()
                 torch.cuda.synchronize()
             res[name].append(e0.elapsed_time(e1) / (args.steps * vps))
-    out = {"what": "ms per view, C3 step (deferred, pipelined, prepared), arms = options[:prepare_first], %d rounds x %d steps"
+    out = {"what": "ms per view, C3 step (deferred, pipelined, prepared), arms = option settings, %d rounds x %d steps"
                    % (args.rounds, args.steps),
            "ms_per_view": {k: [round(x, 4) for x in v] for k, v in res.items()},
            "best": {k: round(min(v), 4) for k, v in res.items()}, "same_gradients": same}

@@ -210,7 +210,8 @@ struct Options {
     int bwd_variant = 7;        // blending backward kernel: 7 = blend_bwd_v7_kernel (packed pairs), 6 = blend_bwd_v6_kernel, 5 = blend_bwd_v5_kernel (round 1)
     int fwd_variant = 4;        // blending forward kernel: 4 = blend_fwd_v4_kernel (packed pairs), 3 = blend_fwd_v3_kernel
     int lpt = 1;                // blending kernels take their tiles longest list first
-    int fwd_minb = 5;           // __launch_bounds__ min blocks of the forward blending kernel (3, 4 or 5; 52 = trips of 2 at 5)
+    int fwd_minb = 6;           // __launch_bounds__ min blocks of the forward blending kernel (v4: 4, 5 or 6; v3: 3, 4 or 5, 52 = trips of 2 at 5);
+                                // six CTAs per SM (40 registers): 2.040 vs 2.043 ms per view in the pipelined step, 0.646 vs 0.659 ms alone
     int bwd_minb = 3;           // same for the backward (v5: 3 or 4; v6: 3)
     int side_stream = 1;        // tile-count kernels on a side stream next to the depth sort
     int bwd_side = 1;           // SH backward on a side stream next to the cov/projection backward

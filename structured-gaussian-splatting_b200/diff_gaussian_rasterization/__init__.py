@@ -163,26 +163,19 @@ def set_front_stream(stream):
     return prev
 
 
-def get_front_stream():
-    """The stream set by set_front_stream (None when none is set)."""
-    return _FRONT
-
-
-def front_stream(device=None, high_priority=True, index=0):
-    """A stream for set_front_stream (one per device, priority class and `index`, created on first use); high priority by
-    default, so the front's small kernels get SM slots as the blending kernels' thread blocks retire.  index = 1: a second
-    such stream (gsr_b200.dp runs the preprocess of a step's later views there, next to the first view's depth sort)."""
+def front_stream(device=None, high_priority=True):
+    """A stream for set_front_stream (one per device and priority class, created on first use); high priority by default, so
+    the front's small kernels get SM slots as the blending kernels' thread blocks retire."""
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     if dev.index is None:
         dev = torch.device("cuda", torch.cuda.current_device())
-    key = (dev, bool(high_priority)) if index == 0 else (dev, bool(high_priority), int(index))
-    st = _FRONT_STREAMS.get(key)
+    st = _FRONT_STREAMS.get((dev, bool(high_priority)))
     if st is None:
         prio = 0
         if high_priority:
             lo, hi = torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream, "priority_range") else (0, -1)
             prio = min(lo, hi)
-        st = _FRONT_STREAMS[key] = torch.cuda.Stream(device=dev, priority=prio)
+        st = _FRONT_STREAMS[(dev, bool(high_priority))] = torch.cuda.Stream(device=dev, priority=prio)
     return st
 
 
@@ -210,15 +203,12 @@ def _prepared_key(means3D, opacities, sh, scales, rotations, rs):
             float(rs.tanfovx), float(rs.tanfovy), int(rs.sh_degree), float(rs.scale_modifier), bool(rs.prefiltered))
 
 
-def prepare_views(means3D, opacities, shs, scales, rotations, settings, stream=None, keep=False):
+def prepare_views(means3D, opacities, shs, scales, rotations, settings):
     """Preprocesses the views of `settings` (a list of GaussianRasterizationSettings sharing image size, field of view, SH
     degree and scale modifier) in one pass over the parameters; the renders that follow with exactly these tensors and
-    settings use the result.  Runs on `stream` when given (the caller orders it behind whatever produced the parameters),
-    else on the front stream when one is set (set_front_stream), else on the current stream; a render waits for the pass
-    that prepared its view wherever it ran.  Views prepared earlier and never rendered are dropped unless `keep`.
-    Returns the number of views prepared."""
-    if not keep:
-        _PREPARED.clear()
+    settings use the result.  Runs on the front stream when one is set (set_front_stream), else on the current stream.
+    Views prepared earlier and never rendered are dropped.  Returns the number of views prepared."""
+    _PREPARED.clear()
     settings = list(settings)
     if not settings or not means3D.is_cuda or means3D.numel() == 0 or shs is None or shs.dim() != 3:
         return 0
@@ -230,8 +220,7 @@ def prepare_views(means3D, opacities, shs, scales, rotations, settings, stream=N
     if not all(t.is_cuda and t.is_contiguous() and t.dtype == torch.float32 for t in tensors):
         return 0
     front = _FRONT if (_FRONT is not None and _FRONT.device == means3D.device) else None
-    if stream is None:
-        stream = front if front is not None else torch.cuda.current_stream(means3D.device)
+    stream = front if front is not None else torch.cuda.current_stream(means3D.device)
     n = 0
     with torch.no_grad(), torch.cuda.stream(stream):
         for base in range(0, len(settings), 16):

@@ -153,33 +153,14 @@ def render_view(rasterizer_mod, params, cam, bg, sh_degree: int, scale_modifier:
     return color, radii, means2D
 
 
-def prepare_step_views(rasterizer_mod, params, cams: Sequence, bg, sh_degree: int, view_ids: Iterable[int], **kw) -> int:
+def prepare_step_views(rasterizer_mod, params, cams: Sequence, bg, sh_degree: int, view_ids: Iterable[int]) -> int:
     """The preprocess stage of the step's views in one pass over the parameters (diff_gaussian_rasterization.prepare_views /
     gsr_preprocess_views): the render_view calls that follow with these cameras skip it.  Returns the number of views prepared
     (0 where the rasterizer module has no such entry point, e.g. the reference package)."""
     if not hasattr(rasterizer_mod, "prepare_views"):
         return 0
     return rasterizer_mod.prepare_views(params["means3D"], params["opacities"], params["shs"], params["scales"], params["rotations"],
-                                        [view_settings(rasterizer_mod, cams[k], bg, sh_degree) for k in view_ids], **kw)
-
-
-def prepare_step_views_split(rasterizer_mod, params, cams: Sequence, bg, sh_degree: int, view_ids: Iterable[int], first: int = 0) -> int:
-    """prepare_step_views in two passes when 0 < first < number of views and a front stream is set: views[:first] on the
-    front stream, views[first:] on a second high-priority stream that waits for the first pass (and for the parameters,
-    i.e. for everything queued so far on the current stream) - see deferred_views(prepare_first=)."""
-    views = list(view_ids)
-    if not (0 < first < len(views)) or not hasattr(rasterizer_mod, "get_front_stream") or not hasattr(rasterizer_mod, "prepare_views"):
-        return prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views)
-    dev = params["means3D"].device
-    n = prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[:first])
-    if n == 0:
-        return prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views)
-    front = rasterizer_mod.get_front_stream()
-    second = rasterizer_mod.front_stream(dev, True, 1)
-    second.wait_stream(torch.cuda.current_stream(dev))
-    if front is not None:
-        second.wait_stream(front)          # (the first pass is queued on the front stream, or else on the current stream)
-    return n + prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views[first:], stream=second, keep=True)
+                                        [view_settings(rasterizer_mod, cams[k], bg, sh_degree) for k in view_ids])
 
 
 _STREAMS: List["torch.cuda.Stream"] = []
@@ -242,8 +223,7 @@ def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
 
 def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
                    loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None,
-                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False, prepare: bool = False,
-                   prepare_first: int = 0):
+                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False, prepare: bool = False):
     """The step in DEFERRED form (diff_gaussian_rasterization.set_grad_mode("deferred")): every view runs its forward and its
     blending backward; the per-Gaussian backward of all the rank's views then runs once (parameters read once, every gradient
     row written once: 0.2 instead of 0.4 ms per view at C3), in `overlap_chunks` ranges of Gaussians when > 0, the all-reduce
@@ -254,12 +234,7 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
     (set_front_stream / gsr_forward_front), so it runs inside the issue-bound blending kernels of the views around it.
     Same results; two views' state is alive at a time.
     prepare=True: the preprocess stage of all the step's views runs first, in one pass over the parameters
-    (prepare_step_views): 236 of the ~300 bytes per Gaussian a view's preprocess moves are read once per step.
-    prepare_first = K > 0 (with pipeline and prepare): the preprocess pass is split - the first K views on the front stream,
-    the remaining views in a second pass on a stream of its own that starts when the first pass has finished and so runs
-    (bandwidth-bound) next to the first view's depth sort and tile split (latency-bound) instead of in front of them: the
-    first forward starts after K views' preprocess, not after the whole step's.  (Queueing the second pass on the front
-    stream behind the K-th forward was measured slower than one pass: 2.053 vs 2.041 ms per view.)"""
+    (prepare_step_views): 236 of the ~300 bytes per Gaussian a view's preprocess moves are read once per step."""
     total = None
     views = list(view_ids)
     prev = rasterizer_mod.set_grad_mode("deferred")
@@ -268,7 +243,7 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
     prev_front = rasterizer_mod.set_front_stream(rasterizer_mod.front_stream(params[flat.names[0]].device)) if piped else None
     try:
         if prepare and views:
-            prepare_step_views_split(rasterizer_mod, params, cams, bg, sh_degree, views, prepare_first if piped else 0)
+            prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views)
         if piped:
             ahead = render_view(rasterizer_mod, params, cams[views[0]], bg, sh_degree)
             for i, k in enumerate(views):
