@@ -621,10 +621,42 @@ __device__ __forceinline__ void v6_commit(const Fetch& fetch, int j, bool valid,
     }
 }
 
+// v6_commit with every lane computing and sending: the moments of an entry go out as ONE two-float reduction per lane of
+// its quad - lane 0: columns 8, 9 = (S0, 0), lane 1: 4, 5, lane 2: 6, 7, lane 3: columns 2, 3 = (0, sum w dx); column 9 is
+// padding and a zero added to the blue column changes nothing - and the colour sums as one scalar reduction from lanes 0-2:
+// two guarded instructions, the arithmetic outside any divergent region (the branchy form spends 15 % of
+// blend_bwd_v7_kernel's time, a third of it resolving its four nested branches).  A lane whose row is not valid reads a
+// stale ring entry; nothing of it is sent.
+template <class Fetch>
+__device__ __forceinline__ void v6_commit_quad(const Fetch& fetch, int j, bool valid, int lane, float m0, float m1, float col,
+                                               float X0s, float Y0s, float* __restrict__ accum)
+{
+    const int t = lane & 3, q0l = lane & ~3;
+    const float S0 = __shfl_sync(0xffffffffu, m0, q0l);
+    const float Sx = __shfl_sync(0xffffffffu, m1, q0l);
+    const float Sy = __shfl_sync(0xffffffffu, m0, q0l + 1);
+    float2 xy;
+    uint32_t id;
+    fetch(j, xy, id);
+    const float u = xy.x - X0s, v = xy.y - Y0s;
+    const float a1 = fmaf(u, S0, -Sx);                   // sum w dx
+    const float a2 = fmaf(v, S0, -Sy);                   // sum w dy
+    const float o3 = fmaf(u, a1 - Sx, m1);               // sum w dx^2      (lane 1)
+    const float o4 = fmaf(-v, Sx, fmaf(u, a2, m0));      // sum w dx dy     (lane 2)
+    const float o5 = fmaf(v, a2 - Sy, m1);               // sum w dy^2      (lane 2)
+    const float out0 = fsel(t == 0, m0, fsel(t == 1, a2, fsel(t == 2, o4, 0.f)));
+    const float out1 = fsel(t == 0, 0.f, fsel(t == 1, o3, fsel(t == 2, o5, a1)));
+    const int off = (0x2648 >> (4 * t)) & 15;            // t = 0, 1, 2, 3 -> columns 8, 4, 6, 2
+    float* rowp = accum + (size_t)id * 12;
+    // an entry without a live lane has exactly zero sums: adding them is a no-op, so they are not sent
+    if (valid && (out0 != 0.f || out1 != 0.f)) red_add_v2(rowp + off, out0, out1);
+    if (valid && t < 3 && col != 0.f) atomicAdd(rowp + t, col);
+}
+
 // Reduces rows [0, cnt) of the warp's A operand(s) (entries jbase .. jbase + cnt - 1 of ring buffer kq) over the 32 lanes
 // and commits them.  Fragments of m16n8k8 (g = lane >> 2, t = lane & 3): A rows g / g+8 at k = t / t+4, B column g at
 // k = t / t+4, D rows g / g+8, columns 2t, 2t+1.  Columns of D2: r_hi r_lo | g_hi g_lo | b_hi b_lo | - -.
-template <int SLOTS, class Fetch>
+template <int SLOTS, bool PRED = false, class Fetch>
 __device__ __forceinline__ void v6_flush(const float* __restrict__ Sa, const float2 (*Sb2)[32], const float2 (*b1)[32], const Fetch& fetch,
                                          int jbase, int cnt, int lane, float X0s, float Y0s, float* __restrict__ accum)
 {
@@ -657,9 +689,14 @@ __device__ __forceinline__ void v6_flush(const float* __restrict__ Sa, const flo
             mma_tf32(d2, alo, __float_as_uint(q.x), __float_as_uint(q.y));
         }
 #pragma unroll
-        for (int hi = 0; hi < 2; hi++)
-            v6_commit(fetch, jbase + g + 8 * hi, g + 8 * hi < cnt, lane, d1[2 * hi], d1[2 * hi + 1], d2[2 * hi] + d2[2 * hi + 1],
-                      X0s, Y0s, accum);
+        for (int hi = 0; hi < 2; hi++) {
+            if (PRED)
+                v6_commit_quad(fetch, jbase + g + 8 * hi, g + 8 * hi < cnt, lane, d1[2 * hi], d1[2 * hi + 1], d2[2 * hi] + d2[2 * hi + 1],
+                               X0s, Y0s, accum);
+            else
+                v6_commit(fetch, jbase + g + 8 * hi, g + 8 * hi < cnt, lane, d1[2 * hi], d1[2 * hi + 1], d2[2 * hi] + d2[2 * hi + 1],
+                          X0s, Y0s, accum);
+        }
     } else {
         const float* ab = Sa + g * GS + t * 4;
 #pragma unroll
@@ -920,7 +957,7 @@ __device__ __forceinline__ void v7_pair(const PairRec r, float pxf, float pyf, i
     w1 = araw_s.y * dL1;
 }
 
-template <int MINB, bool FULL>
+template <int MINB, bool FULL, bool PRED = false>
 __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_bwd_v7_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     const uint32_t* __restrict__ planes, uint32_t plane_words, int W, int H, const float* __restrict__ bg,
@@ -1097,7 +1134,7 @@ blend_bwd_v7_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                     }
                 }
             }
-            v6_flush<SLOTS>(S.a, S.b2, SM.b1, [&](int j, float2& xy, uint32_t& id) {
+            v6_flush<SLOTS, PRED>(S.a, S.b2, SM.b1, [&](int j, float2& xy, uint32_t& id) {
                 const float* q = Pw + (j >> 1) * (int)(sizeof(PairRec) / 4) + (j & 1);
                 xy = make_float2(q[0], q[2]);
                 id = __float_as_uint(Pw[320 + j]);
@@ -1174,6 +1211,7 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
     rc = ctx_once(ctx, 2u, [] {    // per device: opt in to the kernels' dynamic shared memory
         GSR_CUDA(cudaFuncSetAttribute((blend_bwd_v7_kernel<3, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV7)));
         GSR_CUDA(cudaFuncSetAttribute((blend_bwd_v7_kernel<3, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV7)));
+        GSR_CUDA(cudaFuncSetAttribute((blend_bwd_v7_kernel<3, true, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV7)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
@@ -1197,7 +1235,10 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
                b.scratch, pw, W, H, bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt)
         // bwd_variant 6: 16 reduction rows, 3 CTAs per SM;  68 / 84 / 83: 8 rows (4 / 4 / 3 CTAs per SM), trips of 2 / 4 / 4 entries;
         // 64: 16 rows, trips of 4
-        if (o.bwd_variant == 7) {
+        if (o.bwd_variant == 7) {                 // v7 with the quad commit (v6_commit_quad): the product kernel
+            GSR_LAUNCH((blend_bwd_v7_kernel<3, true, true>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
+                       im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
+        } else if (o.bwd_variant == 72) {         // v7 with the branchy commit of v6 (2.039 vs 2.009 ms per view in the step)
             GSR_LAUNCH((blend_bwd_v7_kernel<3, true>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
                        im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
         } else if (o.bwd_variant == 70) {
