@@ -235,197 +235,6 @@ blend_fwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
     }
 }
 
-// ------------------------------------------------------------------------------------------ forward, warps one batch apart
-// blend_fwd_v4_kernel spends 19 % of its warp-time at the block barrier of every batch: the eight sub-tiles of a tile do
-// not carry the same number of surviving entries in a batch (63 of 256 on average, +- 8), and every warp waits for the
-// slowest one batch after batch.  Here the barrier is split (mbarrier arrive / wait) and the staging ring has four
-// buffers instead of two: a warp classifies its 32 entries of batch j+1 and arrives BEFORE it blends batch j, so the wait
-// in front of batch j is for arrivals that were made one blend earlier - a warp may run one whole batch ahead of the
-// slowest, and the per-batch differences average out over the tile list.  Same classification, planes, queues, pair
-// records and per-pixel arithmetic as v4 (bit-identical outputs).  The block ends when all eight warps have flagged their
-// 32 pixels done (a counter polled at every wait: a warp that is not done is owed every arrival it waits for, so nobody
-// leaves while somebody still needs a batch).
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(unsigned long long* bar)
-{
-    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, uint32_t parity)
-{
-    uint32_t ok;
-    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(ok) : "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
-    return ok != 0;
-}
-
-constexpr int F5_STAGES = 4;
-struct __align__(16) FwdSmemV5 {
-    BlendStage stage[F5_STAGES];
-    FwdPairs pairs[8];
-    uint32_t bits[F5_STAGES][8][8];         // [buffer][consumer warp][chunk of 32 entries]
-    uint8_t queue[8][BL_THREADS];
-    unsigned long long cls[F5_STAGES];      // batch b classified by all 256 threads: barrier b % 4, phase b / 4
-    uint32_t done_warps;
-};
-
-template <int MINB>
-__global__ void __launch_bounds__(BL_THREADS, MINB)
-blend_fwd_v5_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
-                    int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                    float* __restrict__ out, uint32_t* __restrict__ planes, uint32_t plane_words, int gyv,
-                    const uint32_t* __restrict__ tile_order)
-{
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    FwdSmemV5& SM = *reinterpret_cast<FwdSmemV5*>(smem_raw);
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;                  // see blend_fwd_v3_kernel
-    const uint32_t tile = tile_order ? tile_order[lin] : lin;
-    const uint32_t trow = tile / gridDim.x, bx = tile - trow * gridDim.x;
-    const uint32_t view = trow / (uint32_t)gyv, by = trow - view * (uint32_t)gyv;
-    const float X0 = (float)(bx * GSR_TILE), Y0 = (float)(by * GSR_TILE);
-    const uint32_t px = bx * GSR_TILE + (wid & 1) * 8 + (lane & 7);
-    const uint32_t py = by * GSR_TILE + (wid >> 1) * 4 + (lane >> 3);
-    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    const float pxf = (float)px, pyf = (float)py;
-    bool done = !inside;
-
-    const uint2 range = ranges[tile];
-    const int total = (int)(range.y - range.x);
-    uint32_t* const plane = planes + (size_t)lane * plane_words + (range.x >> 5) + 16u * tile + wid;
-    const int rounds = (total + BL_THREADS - 1) / BL_THREADS;
-    const uint32_t below = (1u << lane) - 1u;
-    float* const pw = reinterpret_cast<float*>(SM.pairs[wid].p);              // this warp's pair records, as words
-    const PairRec* const pr = SM.pairs[wid].p;
-    uint8_t* const qu = SM.queue[wid];
-
-    float T = 1.0f;
-    uint32_t last_contributor = 0;
-    float2 C01 = make_float2(0.f, 0.f);
-    float C2 = 0.f;
-
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int b = 0; b < F5_STAGES; b++) mbar_init(&SM.cls[b], BL_THREADS);
-        SM.done_warps = 0;
-    }
-    __syncthreads();                        // the barriers are initialised; the only block-wide barrier
-
-    // classification of batch i by this thread (its entry has landed): sub-tile masks -> words for the eight consumer warps
-    auto classify = [&](int i) {
-        const int buf = i & (F5_STAGES - 1);
-        uint32_t m = 0;
-        if (i * BL_THREADS + (int)threadIdx.x < total) m = subtile_mask(SM.stage[buf].q0[threadIdx.x], SM.stage[buf].q1[threadIdx.x], X0, Y0);
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-            const uint32_t bk = __ballot_sync(0xffffffffu, (m >> k) & 1u);
-            if (lane == k) { SM.bits[buf][k][wid] = bk; plane[i * 8] = bk; }
-        }
-    };
-
-    uint32_t id_next = 0;
-    if (rounds > 0) {
-        const bool v0 = (int)threadIdx.x < total;
-        const uint32_t id0 = v0 ? vals[range.x + threadIdx.x] : 0;
-        stage_gather(SM.stage[0], rec, id0, v0);
-        const int p1 = BL_THREADS + threadIdx.x;
-        const uint32_t id1 = p1 < total ? vals[range.x + p1] : 0;
-        stage_gather(SM.stage[1], rec, id1, p1 < total);
-        const int p2 = p1 + BL_THREADS;
-        if (p2 < total) id_next = vals[range.x + p2];
-        cp_async_wait<1>();                 // my entry of batch 0 has landed
-        classify(0);
-        mbar_arrive(&SM.cls[0]);
-    }
-    bool warp_done = false;
-    for (int j = 0; j < rounds; j++) {
-        // my entry of batch j+1 has landed (its gather was issued one blend ago): classify it, then announce it - and with it
-        // that this warp has left batch j-1
-        if (j + 1 < rounds) {
-            cp_async_wait<0>();
-            classify(j + 1);
-        }
-        if (!warp_done && __all_sync(0xffffffffu, done)) {
-            warp_done = true;
-            if (lane == 0) atomicAdd(&SM.done_warps, 1u);
-        }
-        mbar_arrive(&SM.cls[(j + 1) & (F5_STAGES - 1)]);
-        // every warp has classified batch j (and so has left batch j-2: its staging buffer is free)
-        {
-            unsigned long long* bar = &SM.cls[j & (F5_STAGES - 1)];
-            const uint32_t parity = (uint32_t)(j / F5_STAGES) & 1u;
-            bool all_done = false;
-            while (!mbar_try_wait(bar, parity)) {
-                if (*reinterpret_cast<volatile uint32_t*>(&SM.done_warps) == 8u) { all_done = true; break; }
-            }
-            // (warp-uniform: either the phase is complete for every lane, or every warp is done and nobody arrives any more)
-            if (__any_sync(0xffffffffu, all_done)) break;
-            if (*reinterpret_cast<volatile uint32_t*>(&SM.done_warps) == 8u) break;
-        }
-        {
-            const int p2 = (j + 2) * BL_THREADS + threadIdx.x;
-            stage_gather(SM.stage[(j + 2) & (F5_STAGES - 1)], rec, id_next, j + 2 < rounds && p2 < total);
-            const int p3 = p2 + BL_THREADS;
-            if (p3 < total) id_next = vals[range.x + p3];
-        }
-        if (warp_done) continue;
-        const int buf = j & (F5_STAGES - 1);
-        const BlendStage& st = SM.stage[buf];
-        const uint32_t pos_base = (uint32_t)(j * BL_THREADS) + 1u;
-        // the warp's surviving entries of this batch, in list order: one byte per entry
-        int cnt = 0;
-#pragma unroll
-        for (int cch = 0; cch < 8; cch++) {
-            const uint32_t m = SM.bits[buf][wid][cch];
-            if ((m >> lane) & 1u) qu[cnt + __popc(m & below)] = (uint8_t)(cch * 32 + lane);
-            cnt += __popc(m);
-        }
-        __syncwarp();
-#pragma unroll 1
-        for (int g = 0; g < cnt; g += 32) {
-            const int n = min(32, cnt - g);
-            if (lane < n) {                             // entry g + lane becomes slot lane & 1 of pair lane >> 1
-                const int e = qu[g + lane];
-                const float4 a = st.q0[e], c = st.q1[e];
-                const float b = st.b[e];
-                float* w = pw + (lane >> 1) * (int)(sizeof(PairRec) / 4) + (lane & 1);
-                w[0] = a.x; w[2] = a.y; w[4] = a.z; w[6] = a.w; w[8] = c.x; w[10] = c.y;
-                w[12 + (lane & 1)] = c.z; w[13 + (lane & 1)] = c.w;          // colours: (r0 g0 r1 g1), see blend_step_rg
-                w[16] = b; w[18] = __uint_as_float(pos_base + (uint32_t)e);
-            } else if (lane == n) {                     // an odd group's last pair: its second slot blends nothing (opacity 0)
-                float* w = pw + (lane >> 1) * (int)(sizeof(PairRec) / 4) + (lane & 1);
-                w[0] = 0.f; w[2] = 0.f; w[4] = 0.f; w[6] = 0.f; w[8] = 0.f; w[10] = 0.f;
-            }
-            __syncwarp();
-#pragma unroll 1
-            for (int q = 0; 2 * q < n; q++) {
-                const PairRec r = pr[q];
-                float2 dx, dy, power, araw;
-                pair_head(r, pxf, pyf, dx, dy, power, araw);
-                const float al0 = fminf(0.99f, araw.x), al1 = fminf(0.99f, araw.y);
-                const bool ok0 = !(power.x > 0.0f) && !(al0 < 1.0f / 255.0f);
-                const bool ok1 = !(power.y > 0.0f) && !(al1 < 1.0f / 255.0f);
-                blend_step_rg(al0, ok0, make_float2(r.rg.x, r.rg.y), r.bp.x, __float_as_uint(r.bp.z), done, T, C01, C2, last_contributor);
-                blend_step_rg(al1, ok1, make_float2(r.rg.z, r.rg.w), r.bp.y, __float_as_uint(r.bp.w), done, T, C01, C2, last_contributor);
-            }
-            if (__all_sync(0xffffffffu, done)) break;    // (also orders this group's reads before the next group's writes)
-        }
-    }
-    cp_async_wait<0>();
-    if (inside) {
-        const size_t HW = (size_t)H * W;
-        const size_t pix = (size_t)W * py + px;
-        final_T[view * HW + pix] = T;
-        n_contrib[view * HW + pix] = last_contributor;
-        float* o = out + 3 * view * HW + pix;
-        o[0] = C01.x + T * bg[0];
-        o[HW] = C01.y + T * bg[1];
-        o[2 * HW] = C2 + T * bg[2];
-    }
-}
-
 // classification words kept for the backward (in the binning blob's sort scratch, dead once the tile split is done):
 // 8 planes (one per sub-tile of a tile) of (R >> 5) + 16 tiles + 16 words
 size_t blend_plane_words(long long R, int W, int H)
@@ -1125,12 +934,11 @@ __device__ __forceinline__ void v7_pair(const PairRec r, float pxf, float pyf, i
 {
     float2 dx, dy, power, araw;
     pair_head(r, pxf, pyf, dx, dy, power, araw);
-    // min(0.99, a) < 1/255 exactly when a < 1/255 (a NaN fails both tests), so the skip test reads a itself and alpha is
-    // the clamp of the SELECTED a (a dead lane: min(0.99, 0) = 0): the values of v6_entry with two selects fewer per pair
-    const bool live0 = __float_as_int(r.bp.z) < last_contributor && !(power.x > 0.0f) && !(araw.x < 1.0f / 255.0f);
-    const bool live1 = __float_as_int(r.bp.w) < last_contributor && !(power.y > 0.0f) && !(araw.y < 1.0f / 255.0f);
+    const float al0 = fminf(0.99f, araw.x), al1 = fminf(0.99f, araw.y);
+    const bool live0 = __float_as_int(r.bp.z) < last_contributor && !(power.x > 0.0f) && !(al0 < 1.0f / 255.0f);
+    const bool live1 = __float_as_int(r.bp.w) < last_contributor && !(power.y > 0.0f) && !(al1 < 1.0f / 255.0f);
     const float2 araw_s = make_float2(live0 ? araw.x : 0.f, live1 ? araw.y : 0.f);
-    const float2 alpha_s = make_float2(fminf(0.99f, araw_s.x), fminf(0.99f, araw_s.y));
+    const float2 alpha_s = make_float2(live0 ? al0 : 0.f, live1 ? al1 : 0.f);
     const float2 om = __fadd2_rn(bc2(1.f), neg2(alpha_s));
     float r0, r1;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(om.x));              // rcp(1) == 1 exactly
@@ -1391,19 +1199,6 @@ int launch_blend_forward(long long R, int W, int H, int V, const float* bg, cons
         if (!g_arms.blend_forward_bulk) return GSR_EINVAL;
         return g_arms.blend_forward_bulk(R, W, H, V, bg, g, b, im, out_color, s);
     }
-    if (o.fwd_variant == 5) {               // v4 with warps one batch apart (mbarrier pipeline, four staging buffers)
-        DeviceCtx* ctx = nullptr;
-        int rc;
-        if ((rc = device_ctx(&ctx))) return rc;
-        rc = ctx_once(ctx, 4u, [] {
-            GSR_CUDA(cudaFuncSetAttribute(blend_fwd_v5_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmemV5)));
-            return (int)GSR_OK;
-        });
-        if (rc) return rc;
-        GSR_LAUNCH((blend_fwd_v5_kernel<4>), grid, BL_THREADS, sizeof(FwdSmemV5), s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib,
-                   out_color, b.scratch, pw, gyv, lpt);
-        return GSR_OK;
-    }
     if (o.fwd_variant == 4) {
 #define GSR_F4(MINB)                                                                                                        \
     GSR_LAUNCH((blend_fwd_v4_kernel<MINB>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, \
@@ -1472,11 +1267,11 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
                b.scratch, pw, W, H, bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt)
         // bwd_variant 6: 16 reduction rows, 3 CTAs per SM;  68 / 84 / 83: 8 rows (4 / 4 / 3 CTAs per SM), trips of 2 / 4 / 4 entries;
         // 64: 16 rows, trips of 4
-        if (o.bwd_variant == 7) {                 // v7 with the quad commit (v6_commit_quad): the product kernel
-            GSR_LAUNCH((blend_bwd_v7_kernel<3, true, true>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
-                       im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
-        } else if (o.bwd_variant == 73) {         // + ids through cp.async (IDQ)
+        if (o.bwd_variant == 7) {                 // v7 with the quad commit and the ids through cp.async: the product kernel
             GSR_LAUNCH((blend_bwd_v7_kernel<3, true, true, true>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
+                       im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
+        } else if (o.bwd_variant == 73) {         // ids loaded into a register two groups ahead (2.0235 vs 2.011 ms per view in the step)
+            GSR_LAUNCH((blend_bwd_v7_kernel<3, true, true>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
                        im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
         } else if (o.bwd_variant == 72) {         // v7 with the branchy commit of v6 (2.039 vs 2.009 ms per view in the step)
             GSR_LAUNCH((blend_bwd_v7_kernel<3, true>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,

@@ -207,7 +207,8 @@ int launch_dist2(int P, const float* points, float* out, GsrAlloc scratch, cudaS
 // Read from the environment ONCE, at the first call into the library (GSR_<NAME>); tests and benchmarks change them through
 // gsr_debug_set_option().  The product defaults are the values below; nothing calls getenv on the hot path.
 struct Options {
-    int bwd_variant = 7;        // blending backward kernel: 7 = blend_bwd_v7_kernel (packed pairs, quad commit), 72 = with v6's branchy commit,
+    int bwd_variant = 7;        // blending backward kernel: 7 = blend_bwd_v7_kernel (packed pairs, quad commit, ids through cp.async),
+                                // 73 = ids through a register, 72 = with v6's branchy commit (and ids through a register),
                                 // 70 = without the straight-line path, 6 = blend_bwd_v6_kernel, 5 = blend_bwd_v5_kernel (round 1)
     int fwd_variant = 4;        // blending forward kernel: 4 = blend_fwd_v4_kernel (packed pairs), 3 = blend_fwd_v3_kernel
     int lpt = 1;                // blending kernels take their tiles longest list first
