@@ -114,7 +114,7 @@ blend_fwd_v3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
 // arithmetic runs as FADD2 / FMUL2 / FFMA2 (blend_common.cuh).  The sequential part (blend_step) is the scalar code of v3.
 struct __align__(16) FwdPairs { PairRec p[16]; };
 
-template <int MINB>
+template <int MINB, int UNR = 1>
 __global__ void __launch_bounds__(BL_THREADS, MINB)
 blend_fwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ vals, const SplatRec* __restrict__ rec,
                     int W, int H, const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
@@ -208,7 +208,7 @@ blend_fwd_v4_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict
                 w[0] = 0.f; w[2] = 0.f; w[4] = 0.f; w[6] = 0.f; w[8] = 0.f; w[10] = 0.f;
             }
             __syncwarp();
-#pragma unroll 1
+#pragma unroll UNR
             for (int q = 0; 2 * q < n; q++) {
                 const PairRec r = pr[q];
                 float2 dx, dy, power, araw;
@@ -1200,11 +1200,18 @@ int launch_blend_forward(long long R, int W, int H, int V, const float* bg, cons
         return g_arms.blend_forward_bulk(R, W, H, V, bg, g, b, im, out_color, s);
     }
     if (o.fwd_variant == 4) {
+#define COMMA ,
 #define GSR_F4(MINB)                                                                                                        \
     GSR_LAUNCH((blend_fwd_v4_kernel<MINB>), grid, BL_THREADS, 0, s, im.ranges, b.vals, g.rec, W, H, bg, im.final_T, im.n_contrib, \
                out_color, b.scratch, pw, gyv, lpt)
         if (o.fwd_minb == 6) GSR_F4(6);
         else if (o.fwd_minb == 4) GSR_F4(4);
+        else if (o.fwd_minb == 62) GSR_F4(6 COMMA 2);      // pair loop unrolled twice
+        else if (o.fwd_minb == 52) GSR_F4(5 COMMA 2);
+        else if (o.fwd_minb == 42) GSR_F4(4 COMMA 2);
+        else if (o.fwd_minb == 44) GSR_F4(4 COMMA 4);
+        else if (o.fwd_minb == 32) GSR_F4(3 COMMA 2);
+        else if (o.fwd_minb == 34) GSR_F4(3 COMMA 4);
         else GSR_F4(5);
 #undef GSR_F4
         return GSR_OK;
