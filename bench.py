@@ -69,6 +69,9 @@ def parse_args():
     ap.add_argument("--prepare", type=int, default=1,
                     help="deferred steps: 1 = the preprocess stage of the step's views runs in one pass over the parameters "
                          "(prepare_views / gsr_preprocess_views) before the per-view calls; 0 = every call preprocesses its view")
+    ap.add_argument("--front-streams", type=int, default=2,
+                    help="--pipeline 1: the views' fronts alternate over this many high-priority streams (2: the fronts of consecutive "
+                         "views may run next to each other - 1.962 against 1.975 ms per view with 1)")
     ap.add_argument("--views-of-rank", default="", help="diagnostic (N = 1): r/w = render the cameras rank r of w ranks would get")
     ap.add_argument("--nccl-priority", default="high", choices=["high", "default"], help="priority of NCCL's stream (N > 1)")
     ap.add_argument("--front-priority", default="high", choices=["high", "default"],
@@ -455,7 +458,20 @@ def main():
         flat.all_reduce()
 
     use_deferred = [True]            # (switched off for the `grad_sum_in_kernels` comparison leg)
-    front_st = lambda: dgr.front_stream(dev, args.front_priority == "high")
+    front_st = lambda j=0: dgr.front_stream(dev, args.front_priority == "high", j)
+    n_fronts = max(1, args.front_streams)
+
+    def fronts_begin():
+        # every front stream is ordered behind what is queued so far (the parameters); the first one stays set
+        prev_ = dgr.set_front_stream(front_st(n_fronts - 1))
+        for j in range(n_fronts - 2, -1, -1):
+            dgr.set_front_stream(front_st(j))
+        return prev_
+
+    def front_for(i):
+        # view i's front goes to stream i mod n (no further wait: the streams were ordered at the start of the step)
+        if n_fronts > 1:
+            dgr.set_front_stream(front_st(i % n_fronts), wait=False)
     use_prepare = [bool(args.prepare) and deferred]        # (switched off with the pipelining for the `one_stream` leg)
     use_pipeline = [bool(args.pipeline) and deferred]      # (switched off for the per-stage timing pass and the `one_stream` leg)
 
@@ -469,7 +485,7 @@ def main():
             views = list(views)
             piped = use_pipeline[0] and len(views) > 1
             prev = dgr.set_grad_mode("deferred")
-            prev_front = dgr.set_front_stream(front_st()) if piped else None
+            prev_front = fronts_begin() if piped else None
 
             def back(color, radii, k):
                 loss_of(color, k).backward() if loss_of is not None else color.backward(go)
@@ -481,9 +497,11 @@ def main():
                     dp.prepare_step_views(dgr, prm, cams, bg, spec.D, views)
                 if piped:
                     # software pipeline: forward of view i+1 (its front on the high-priority stream), then backward of view i
+                    front_for(0)
                     ahead = dp.render_view(dgr, prm, cams[views[0]], bg, spec.D)
                     for i, k in enumerate(views):
                         color, radii, _ = ahead
+                        front_for(i + 1)
                         ahead = dp.render_view(dgr, prm, cams[views[i + 1]], bg, spec.D) if i + 1 < len(views) else None
                         back(color, radii, k)
                 else:
@@ -589,7 +607,8 @@ def main():
         buf, ev = cam_pending.pop(step)
         torch.cuda.current_stream().wait_event(ev)
         if use_pipeline[0]:
-            front_st().wait_event(ev)
+            for j in range(n_fronts):
+                front_st(j).wait_event(ev)
         return buf
 
     def take(k):
@@ -598,7 +617,8 @@ def main():
         slot, ev = pending.pop(k)
         torch.cuda.current_stream().wait_event(ev)
         if use_pipeline[0]:
-            front_st().wait_event(ev)        # the camera is an input of the front too
+            for j in range(n_fronts):
+                front_st(j).wait_event(ev)   # the camera is an input of the front too
         return ring_tgt[slot], ring_cam[slot], slot
 
     def release(slot):
@@ -646,7 +666,7 @@ def main():
         if deferred:
             piped = use_pipeline[0] and len(views) > 1
             prev = dgr.set_grad_mode("deferred")
-            prev_front = dgr.set_front_stream(front_st()) if piped else None
+            prev_front = fronts_begin() if piped else None
             step_cams = None
             if use_prepare[0]:
                 # the step's cameras (a trainer samples them before the step): one small copy per view from pinned host
@@ -659,6 +679,8 @@ def main():
 
             def fwd(i):
                 k = views[i]
+                if piped:
+                    front_for(i)
                 tgt, cm, slot = take(k)
                 nxt = views[i + 1] if i + 1 < len(views) else my_views(step + 1)[0]
                 prefetch(nxt)                              # next view's inputs travel while this one renders
@@ -1115,7 +1137,8 @@ def main():
                                         "in the backward kernels (set_grad_mode)" if fused else "autograd .grad +="),
                            "api": "GaussianRasterizerBatched: one call per rank and step" if args.batched else
                                   ("GaussianRasterizer: one call per view; the forward of view i+1 is issued before the backward of view i, its "
-                                   "front (preprocess, depth order, tile split) on a high-priority stream (set_front_stream)" if piped else
+                                   "front (preprocess, depth order, tile split) on a high-priority stream (set_front_stream), the views alternating over "
+                                   + str(n_fronts) + " such stream(s)" if piped else
                                    "GaussianRasterizer: one call per view"),
                            "c5": "config C5 (6M Gaussians, %d views per step) measured by the same step at this N: see the `c5` object" % (vps * world),
                            "l2": "inputs (%.1f GB of parameters + state per view) exceed the 126 MB L2; no flush needed" %

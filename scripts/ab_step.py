@@ -42,8 +42,11 @@ def main():
     def views(step):
         return [(step * vps + j) % V for j in range(vps)]
 
+    fronts = [1]
+
     def step(i):
-        dp.deferred_views(dgr, params, flat, cams, bg, spec.D, loss_fn, views(i), all_reduce=False, pipeline=True, prepare=True)
+        dp.deferred_views(dgr, params, flat, cams, bg, spec.D, loss_fn, views(i), all_reduce=False, pipeline=True, prepare=True,
+                          front_streams=fronts[0])
 
     def parse(a):
         return a, [(kv.split("=")[0], int(kv.split("=")[1])) for kv in a.split(";") if "=" in kv]       # (no '=': defaults)
@@ -54,10 +57,12 @@ def main():
         def __init__(self, opts):
             self.opts, self.prev = opts, []
 
-        def __enter__(self):
-            self.prev = [(k, dgr._C.set_option(k, v)) for k, v in self.opts]
+        def __enter__(self):            # (FRONTS = n is not a library option: dp.deferred_views(front_streams=n))
+            fronts[0] = dict(self.opts).get("FRONTS", 1)
+            self.prev = [(k, dgr._C.set_option(k, v)) for k, v in self.opts if k != "FRONTS"]
 
         def __exit__(self, *exc):
+            fronts[0] = 1
             for k, v in reversed(self.prev):
                 dgr._C.set_option(k, v)
 

@@ -153,29 +153,31 @@ _FRONT = None                    # torch.cuda.Stream or None
 _FRONT_ZERO_ACCUM = os.environ.get("GSR_FRONT_ZERO_ACCUM", "1") != "0"
 
 
-def set_front_stream(stream):
+def set_front_stream(stream, wait=True):
     """stream: a torch.cuda.Stream (ideally created with a higher priority than the rendering stream) or None; returns the
-    previous one.  The stream waits for everything queued so far on the current stream."""
+    previous one.  The stream waits for everything queued so far on the current stream unless wait=False (a caller that
+    alternates between front streams inside a step orders each of them once, at the start of the step)."""
     global _FRONT
     prev, _FRONT = _FRONT, stream
-    if stream is not None:
+    if stream is not None and wait:
         stream.wait_stream(torch.cuda.current_stream(stream.device))
     return prev
 
 
-def front_stream(device=None, high_priority=True):
-    """A stream for set_front_stream (one per device and priority class, created on first use); high priority by default, so
-    the front's small kernels get SM slots as the blending kernels' thread blocks retire."""
+def front_stream(device=None, high_priority=True, index=0):
+    """A stream for set_front_stream (one per device, priority class and index, created on first use); high priority by
+    default, so the front's small kernels get SM slots as the blending kernels' thread blocks retire."""
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     if dev.index is None:
         dev = torch.device("cuda", torch.cuda.current_device())
-    st = _FRONT_STREAMS.get((dev, bool(high_priority)))
+    key = (dev, bool(high_priority), int(index))
+    st = _FRONT_STREAMS.get(key)
     if st is None:
         prio = 0
         if high_priority:
             lo, hi = torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream, "priority_range") else (0, -1)
             prio = min(lo, hi)
-        st = _FRONT_STREAMS[(dev, bool(high_priority))] = torch.cuda.Stream(device=dev, priority=prio)
+        st = _FRONT_STREAMS[key] = torch.cuda.Stream(device=dev, priority=prio)
     return st
 
 

@@ -223,7 +223,8 @@ def backward_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
 
 def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, sh_degree: int,
                    loss_fn: Callable[[torch.Tensor, int], torch.Tensor], view_ids: Iterable[int], group=None,
-                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False, prepare: bool = False):
+                   overlap_chunks: int = 0, all_reduce: bool = True, pipeline: bool = False, prepare: bool = False,
+                   front_streams: int = 2):
     """The step in DEFERRED form (diff_gaussian_rasterization.set_grad_mode("deferred")): every view runs its forward and its
     blending backward; the per-Gaussian backward of all the rank's views then runs once (parameters read once, every gradient
     row written once: 0.2 instead of 0.4 ms per view at C3), in `overlap_chunks` ranges of Gaussians when > 0, the all-reduce
@@ -233,6 +234,8 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
     (preprocess, depth order, tile split: latency- and bandwidth-bound) goes to a high-priority stream of its own
     (set_front_stream / gsr_forward_front), so it runs inside the issue-bound blending kernels of the views around it.
     Same results; two views' state is alive at a time.
+    front_streams = n > 1 (with pipeline): the views' fronts alternate over n high-priority streams, so the (latency-bound)
+    fronts of consecutive views may run next to each other: 1.962 against 1.975 ms per view at C3 for n = 2.
     prepare=True: the preprocess stage of all the step's views runs first, in one pass over the parameters
     (prepare_step_views): 236 of the ~300 bytes per Gaussian a view's preprocess moves are read once per step."""
     total = None
@@ -240,14 +243,29 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
     prev = rasterizer_mod.set_grad_mode("deferred")
     piped = (pipeline and len(views) > 1 and hasattr(rasterizer_mod, "set_front_stream")
              and params[flat.names[0]].is_cuda)
-    prev_front = rasterizer_mod.set_front_stream(rasterizer_mod.front_stream(params[flat.names[0]].device)) if piped else None
+    fronts = []
+    prev_front = None
+    if piped:
+        dev = params[flat.names[0]].device
+        fronts = [rasterizer_mod.front_stream(dev, True, j) for j in range(max(1, front_streams))]
+        # every front stream is ordered behind what is queued so far (the parameters); inside the step the views alternate
+        # between them without further waits, so the fronts of consecutive views may run next to each other
+        prev_front = rasterizer_mod.set_front_stream(fronts[-1])
+        for f in reversed(fronts[:-1]):
+            rasterizer_mod.set_front_stream(f)
+    use_front = (lambda i: rasterizer_mod.set_front_stream(fronts[i % len(fronts)], wait=False)) if len(fronts) > 1 else (lambda i: None)
     try:
         if prepare and views:
             prepare_step_views(rasterizer_mod, params, cams, bg, sh_degree, views)
+            if len(fronts) > 1:
+                for f in fronts[1:]:
+                    f.wait_stream(fronts[0])       # (the pass ran on the first front stream)
         if piped:
+            use_front(0)
             ahead = render_view(rasterizer_mod, params, cams[views[0]], bg, sh_degree)
             for i, k in enumerate(views):
                 color = ahead[0]
+                use_front(i + 1)
                 ahead = render_view(rasterizer_mod, params, cams[views[i + 1]], bg, sh_degree) if i + 1 < len(views) else None
                 loss = loss_fn(color, k)
                 loss.backward()
