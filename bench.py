@@ -768,7 +768,9 @@ def main():
     C.timing_reset(); C.timing_enable(not piped); C.reset_launch_count()
     sampler = ClockSampler(local_rank)
     sampler.start()
+    dev_allocs0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
     ms_total = timed(step_device, args.steps, args.warmup + 1)
+    dev_allocs = torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - dev_allocs0     # cudaMallocs inside the timed region
     clocks = sampler.stop()
     C.timing_enable(False)
     launches = int(C.launch_count())
@@ -1146,7 +1148,7 @@ def main():
                 "roofline": roofline, "stages": stages, "stages_pipelined_ms": stages_piped, "cpu_baseline": cpu_baseline, "e2e": e2e, "allreduce": allreduce, "c5": c5,
                 "reference_cuda": ref_extra, "plain_api": plain_extra, "grad_sum_in_kernels": kernels_extra, "dist2": dist2_extra,
                 "batched": batched_extra, "one_stream": one_stream, "two_streams": streams_extra, "forward_only": forward_extra, "train_step": train_extra,
-                "gpu_launches": launches,
+                "gpu_launches": launches, "device_allocs_in_timed_region": int(dev_allocs),
                 "clocks": clocks}
         print(json.dumps(line), flush=True)
     if world > 1:

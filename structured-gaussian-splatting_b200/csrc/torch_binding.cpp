@@ -27,10 +27,21 @@ extern "C" int gsr_debug_arms_loaded(void);
 
 namespace {
 
+// The binning blob's size follows the view's instance count, which differs from camera to camera: handed to torch's caching
+// allocator byte-exact, a step keeps meeting sizes no cached block fits and falls through to cudaMalloc in the middle of the
+// pipelined step (3-4 times in 20 steps at C3, the odd run 5 % slower).  Large blobs are rounded up to eight size classes
+// per power of two (at most 12.5 % more), so that after the first steps every request finds a cached block.
 void* resize_cb(void* ctx, size_t bytes)
 {
     auto* t = static_cast<torch::Tensor*>(ctx);
-    t->resize_({(long long)bytes});
+    size_t cap = bytes;
+    if (bytes > (size_t(1) << 20)) {
+        int top = 0;
+        while ((bytes >> (top + 1)) != 0) top++;
+        const size_t g = size_t(1) << (top - 3);
+        cap = (bytes + g - 1) / g * g;
+    }
+    t->resize_({(long long)cap});
     return t->data_ptr();
 }
 
