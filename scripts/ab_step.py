@@ -42,7 +42,7 @@ def main():
     def views(step):
         return [(step * vps + j) % V for j in range(vps)]
 
-    fronts = [1]
+    fronts = [2]
 
     def step(i):
         dp.deferred_views(dgr, params, flat, cams, bg, spec.D, loss_fn, views(i), all_reduce=False, pipeline=True, prepare=True,
@@ -58,11 +58,13 @@ def main():
             self.opts, self.prev = opts, []
 
         def __enter__(self):            # (FRONTS = n is not a library option: dp.deferred_views(front_streams=n))
-            fronts[0] = dict(self.opts).get("FRONTS", 1)
-            self.prev = [(k, dgr._C.set_option(k, v)) for k, v in self.opts if k != "FRONTS"]
+            fronts[0] = dict(self.opts).get("FRONTS", 2)
+            os.environ["GSR_DP_FRONT_GATE"] = str(dict(self.opts).get("GATE", 0))
+            self.prev = [(k, dgr._C.set_option(k, v)) for k, v in self.opts if k not in ("FRONTS", "GATE")]
 
         def __exit__(self, *exc):
-            fronts[0] = 1
+            fronts[0] = 2
+            os.environ["GSR_DP_FRONT_GATE"] = "0"
             for k, v in reversed(self.prev):
                 dgr._C.set_option(k, v)
 
