@@ -59,12 +59,10 @@ def main():
 
         def __enter__(self):            # (FRONTS = n is not a library option: dp.deferred_views(front_streams=n))
             fronts[0] = dict(self.opts).get("FRONTS", 2)
-            os.environ["GSR_DP_FRONT_GATE"] = str(dict(self.opts).get("GATE", 0))
-            self.prev = [(k, dgr._C.set_option(k, v)) for k, v in self.opts if k not in ("FRONTS", "GATE")]
+            self.prev = [(k, dgr._C.set_option(k, v)) for k, v in self.opts if k != "FRONTS"]
 
         def __exit__(self, *exc):
             fronts[0] = 2
-            os.environ["GSR_DP_FRONT_GATE"] = "0"
             for k, v in reversed(self.prev):
                 dgr._C.set_option(k, v)
 

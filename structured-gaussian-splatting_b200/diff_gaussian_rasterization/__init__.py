@@ -164,6 +164,11 @@ def set_front_stream(stream, wait=True):
     return prev
 
 
+def get_front_stream():
+    """The stream set by set_front_stream (None when none is set)."""
+    return _FRONT
+
+
 def front_stream(device=None, high_priority=True, index=0):
     """A stream for set_front_stream (one per device, priority class and index, created on first use); high priority by
     default, so the front's small kernels get SM slots as the blending kernels' thread blocks retire."""

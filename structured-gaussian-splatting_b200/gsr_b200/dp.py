@@ -23,8 +23,6 @@ from __future__ import annotations
 
 from typing import Callable, Dict, Iterable, List, Optional, Sequence
 
-import os
-
 import torch
 import torch.distributed as dist
 
@@ -263,22 +261,12 @@ def deferred_views(rasterizer_mod, params, flat: FlatGrads, cams: Sequence, bg, 
                 for f in fronts[1:]:
                     f.wait_stream(fronts[0])       # (the pass ran on the first front stream)
         if piped:
-            gate = int(os.environ.get("GSR_DP_FRONT_GATE", "0"))      # (experiment) 1: front j >= 2 starts when forward j-1 has finished
-            main = torch.cuda.current_stream(params[flat.names[0]].device)
             use_front(0)
             ahead = render_view(rasterizer_mod, params, cams[views[0]], bg, sh_degree)
-            ev_prev = torch.cuda.Event() if gate else None
-            if gate:
-                ev_prev.record(main)
             for i, k in enumerate(views):
                 color = ahead[0]
                 use_front(i + 1)
-                if gate and i + 1 >= 2 and i + 1 < len(views):
-                    fronts[(i + 1) % len(fronts)].wait_event(ev_prev)
                 ahead = render_view(rasterizer_mod, params, cams[views[i + 1]], bg, sh_degree) if i + 1 < len(views) else None
-                if gate and ahead is not None:
-                    ev_prev = torch.cuda.Event()
-                    ev_prev.record(main)
                 loss = loss_fn(color, k)
                 loss.backward()
                 total = loss.detach() if total is None else total + loss.detach()
