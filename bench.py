@@ -96,7 +96,9 @@ def host_threads() -> int:
 
 # ------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
-    """Samples SM clock and throttle reasons with NVML every 10 ms while the timed region runs."""
+    """Samples SM clock and throttle reasons with NVML every 50 ms while the timed region runs.  (Every 10 ms was too often:
+    the headline pass - the only one the sampler runs next to - came out at 1.99-2.45 ms per view in some processes while every
+    other pass of the same process measured the same step at 1.91; NVML queries take a driver lock kernel launches also need.)"""
 
     def __init__(self, index: int):
         self.index, self.samples, self.reasons, self._stop, self.max_mhz = index, [], set(), threading.Event(), None
@@ -125,7 +127,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.01)
+            self._stop.wait(0.05)
 
     def start(self):
         if self.nv is not None:
