@@ -1206,13 +1206,8 @@ int launch_blend_forward(long long R, int W, int H, int V, const float* bg, cons
                out_color, b.scratch, pw, gyv, lpt)
         if (o.fwd_minb == 6) GSR_F4(6);
         else if (o.fwd_minb == 4) GSR_F4(4);
-        else if (o.fwd_minb == 62) GSR_F4(6 COMMA 2);      // pair loop unrolled twice
-        else if (o.fwd_minb == 52) GSR_F4(5 COMMA 2);
-        else if (o.fwd_minb == 42) GSR_F4(4 COMMA 2);
-        else if (o.fwd_minb == 44) GSR_F4(4 COMMA 4);
-        else if (o.fwd_minb == 32) GSR_F4(3 COMMA 2);
-        else if (o.fwd_minb == 34) GSR_F4(3 COMMA 4);
-        else GSR_F4(5);
+        else if (o.fwd_minb == 5) GSR_F4(5);
+        else GSR_F4(4 COMMA 2);                            // 42, the default: four CTAs per SM, pair loop unrolled twice
 #undef GSR_F4
         return GSR_OK;
     }
@@ -1254,8 +1249,6 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<16, 4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<16>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
-        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
-        GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v6_kernel<8, 4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV6<8>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
         GSR_CUDA(cudaFuncSetAttribute(blend_bwd_v5_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmemV5<2>)));
         return (int)GSR_OK;
@@ -1272,7 +1265,7 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
 #define GSR_V6(SLOTS, TRIP, MINB)                                                                                                  \
     GSR_LAUNCH((blend_bwd_v6_kernel<SLOTS, TRIP, MINB>), grid, BL_THREADS, sizeof(BwdSmemV6<SLOTS>), s, im.ranges, b.vals, g.rec,   \
                b.scratch, pw, W, H, bg, im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt)
-        // bwd_variant 6: 16 reduction rows, 3 CTAs per SM;  68 / 84 / 83: 8 rows (4 / 4 / 3 CTAs per SM), trips of 2 / 4 / 4 entries;
+        // bwd_variant 6: 16 reduction rows, 3 CTAs per SM;  68: 8 rows, 4 CTAs per SM, trips of 2 entries;
         // 64: 16 rows, trips of 4
         if (o.bwd_variant == 7) {                 // v7 with the quad commit and the ids through cp.async: the product kernel
             GSR_LAUNCH((blend_bwd_v7_kernel<3, true, true, true>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
@@ -1287,8 +1280,6 @@ int launch_blend_backward(long long R, int W, int H, int V, const float* bg, con
             GSR_LAUNCH((blend_bwd_v7_kernel<3, false>), grid, BL_THREADS, sizeof(BwdSmemV7), s, im.ranges, b.vals, g.rec, b.scratch, pw, W, H, bg,
                        im.final_T, im.n_contrib, dL_dpix, accum, gyv, lpt);
         } else if (o.bwd_variant == 68) GSR_V6(8, 2, 4);
-        else if (o.bwd_variant == 84) GSR_V6(8, 4, 4);
-        else if (o.bwd_variant == 83) GSR_V6(8, 4, 3);
         else if (o.bwd_variant == 64) GSR_V6(16, 4, 3);
         else GSR_V6(16, 2, 3);
 #undef GSR_V6

@@ -212,10 +212,10 @@ struct Options {
                                 // 70 = without the straight-line path, 6 = blend_bwd_v6_kernel, 5 = blend_bwd_v5_kernel (round 1)
     int fwd_variant = 4;        // blending forward kernel: 4 = blend_fwd_v4_kernel (packed pairs), 3 = blend_fwd_v3_kernel
     int lpt = 1;                // blending kernels take their tiles longest list first
-    int fwd_minb = 42;          // forward blending kernel: __launch_bounds__ min blocks (v4: 4, 5 or 6; v3: 3, 4 or 5, 52 = trips of 2 at 5), a second
-                                // digit = unroll factor of v4's pair loop (62, 52, 42, 44, 32, 34).  Measured in the pipelined step, ms per view:
-                                // 5: 1.995, 6: 1.992, 62: 1.984, 52: 1.980, 42 (four CTAs per SM, 64 registers, two pairs per trip): 1.974-1.979,
-                                // 44: 1.975-2.01, 32: 2.014, 34: 2.003 (profiles/round2_zl_ab_fwd_unroll.json)
+    int fwd_minb = 42;          // forward blending kernel: v4: 42 = four CTAs per SM (64 registers), pair loop unrolled twice; 4, 5, 6 = that many
+                                // CTAs per SM, no unrolling; v3: 3, 4 or 5, 52 = trips of 2 at 5.  In the pipelined step, ms per view: 5: 1.995,
+                                // 6: 1.992, 42: 1.974-1.979; measured and dropped: 62: 1.984, 52: 1.980, 44: 1.975-2.01, 32: 2.014, 34: 2.003
+                                // (profiles/round2_zl_ab_fwd_unroll.json)
     int bwd_minb = 3;           // same for the backward (v5: 3 or 4; v6: 3)
     int side_stream = 1;        // tile-count kernels on a side stream next to the depth sort
     int bwd_side = 1;           // SH backward on a side stream next to the cov/projection backward
