@@ -224,6 +224,27 @@ def test_training_step_modules_import_without_gpu_and_refuse_cpu_tensors():
 
 
 # ------------------------------------------------------------------------------ the C-ABI library
+def test_biased_depth_keys_keep_the_order_and_leave_five_zero_bits():
+    """The depth keys of radix_depth = 3 (csrc/preprocess.cu, GSR_DEPTH_KEY_BIAS in csrc/gsr_common.cuh): bits(depth) minus the
+    bits of the near plane 0.2f.  Monotone over every depth the near cull lets through (z > 0.2 or NaN), never wrapping, and
+    below 2^27 - five zero top bits, so the fourth radix pass is the identity - for every depth under 0.2 * 2^16."""
+    bias = np.float32(0.2).view(np.uint32)
+    assert int(bias) == 0x3E4CCCCD
+    rng = np.random.default_rng(0)
+    z = np.concatenate([np.nextafter(np.float32(0.2), np.float32(1.0), dtype=np.float32).reshape(1),
+                        rng.uniform(0.2, 100.0, 200000).astype(np.float32), rng.uniform(100.0, 13107.0, 50000).astype(np.float32),
+                        np.float32([13107.0, 13107.19, 13107.2, 13108.0, 1e6, 3e38, np.inf, np.nan])])
+    z = z[~(z <= np.float32(0.2))]                        # the cull of preprocess: !(z <= 0.2) passes NaN like the reference
+    bits = z.view(np.uint32)
+    key = (bits - bias).astype(np.uint32)
+    assert (bits >= bias).all()                           # no wrap-around
+    o1 = np.argsort(bits, kind="stable"); o2 = np.argsort(key, kind="stable")
+    assert np.array_equal(o1, o2)                         # the same stable order
+    shallow = z < np.float32(0.2 * 65536.0)
+    assert (key[shallow] < (1 << 27)).all() and (key[shallow] >= 1).all()
+    assert (key[~shallow & ~np.isnan(z)] >= (1 << 27)).all()
+
+
 def test_cabi_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "gsr.h")).read()
     hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
